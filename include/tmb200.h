@@ -1,0 +1,152 @@
+/*
+ * tmb200.h — C ABI of libtmb200.so, the sm_100a kernels behind the classification-metric
+ * update path (torchmetrics 1.3.0dev; citations are relative to /root/reference/src/torchmetrics/).
+ *
+ * Conventions shared by every entry point
+ *   - plain pointers and sizes only; no torch types, nothing here allocates or frees device memory
+ *     (scratch is caller-owned and passed in; the *_scratch_bytes functions are pure host code);
+ *   - all data pointers are device pointers on the current device unless a comment says "host";
+ *   - kernels are enqueued on `stream` (a cudaStream_t passed as void*) and the call returns without
+ *     synchronising;
+ *   - return value: 0 = enqueued, negative = TMB_E_* argument error (nothing enqueued),
+ *     positive = cudaError_t of a failed launch;
+ *   - integer metric states are int64 and are ACCUMULATED IN PLACE (`state += batch`), which is what
+ *     lets MetricCollection compute groups keep sharing one tensor (collections.py:289-307);
+ *   - data errors (a label outside [0, num_classes)) do not abort the kernel: the offending sample is
+ *     skipped and a bit is OR-ed into the caller's device error word `err` (int32[1]); the host layer
+ *     turns a non-zero word into RuntimeError like the reference's failing reshape/bincount would
+ *     (functional/classification/confusion_matrix.py:335-337, utilities/data.py:199).
+ */
+#ifndef TMB200_H_
+#define TMB200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- enums ------------------------------------------------------------------------------------ */
+
+/* floating dtypes of `preds` */
+#define TMB_F32 0
+#define TMB_F16 1
+#define TMB_BF16 2
+
+/* integer dtypes of `target` (and of label-valued `preds`) */
+#define TMB_I64 0
+#define TMB_I32 1
+#define TMB_I16 2
+#define TMB_U8 3 /* also torch.bool */
+#define TMB_I8 4
+
+/* argument errors */
+#define TMB_E_DTYPE (-1)
+#define TMB_E_SHAPE (-2)
+#define TMB_E_NULL (-3)
+#define TMB_E_MODE (-4)
+#define TMB_E_SCRATCH (-5)
+#define TMB_E_LIMIT (-6)
+
+/* bits of the device error word */
+#define TMB_ERR_TARGET_RANGE 1 /* a non-ignored target outside [0, num_classes)            */
+#define TMB_ERR_PREDS_RANGE 2  /* a label-valued pred outside [0, num_classes)              */
+#define TMB_ERR_TARGET_BINARY 4 /* a non-ignored binary/multilabel target that is not 0 or 1 */
+
+/* what the multiclass kernels accumulate */
+#define TMB_MC_CONFMAT 0 /* out = int64 state [C, C], row = target, col = pred                    */
+#define TMB_MC_STATS 1   /* out = int64 scratch [3C]: hist_target[C] hist_pred[C] match[C]        */
+#define TMB_MC_MICRO 2   /* out = int64 scratch [2]: number of matches, number of counted samples */
+
+/* Library / build identification: returns the compiled-for SM (100) and writes nothing. */
+int tmb_build_arch(void);
+
+/* ---- K1: multiclass argmax + histogram ---------------------------------------------------------
+ *
+ * tmb_mc_argmax_hist replaces, in one pass over `preds`:
+ *   _multiclass_confusion_matrix_format  functional/classification/confusion_matrix.py:306-330
+ *   _multiclass_confusion_matrix_update  functional/classification/confusion_matrix.py:333-337
+ *   _multiclass_stat_scores_format       functional/classification/stat_scores.py:325-341
+ *   _multiclass_stat_scores_update       functional/classification/stat_scores.py:394-418 (global, top_k=1)
+ *   _bincount                            utilities/data.py:169-199
+ *
+ * preds  : float tensor [n_outer, num_classes, n_inner] contiguous (n_inner = 1 for [N, C]).
+ * target : integer tensor [n_outer, n_inner] contiguous.
+ * Per sample (n, s): skip if has_ignore && target == ignore_index; p = argmax_c preds[n, c, s] with
+ * torch.argmax's rule (first maximal index, NaN is maximal); then accumulate according to `mode`.
+ */
+int tmb_mc_argmax_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                       int64_t n_outer, int64_t num_classes, int64_t n_inner, int has_ignore,
+                       int64_t ignore_index, int mode, int64_t* out, int32_t* err, void* stream);
+
+/* Same accumulation for label-valued preds (preds.ndim == target.ndim): the int branch of
+ * _multiclass_confusion_matrix_format / _multiclass_stat_scores_format (no argmax). */
+int tmb_mc_label_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                      int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index, int mode,
+                      int64_t* out, int32_t* err, void* stream);
+
+/* Turns the TMB_MC_STATS / TMB_MC_MICRO scratch into `tp/fp/tn/fn += ...`
+ * (functional/classification/stat_scores.py:401-404 and :414-418) and re-zeroes the scratch so the
+ * next update needs no memset.  tp/fp/tn/fn are int64 [C] (STATS) or [1] (MICRO). */
+int tmb_mc_stats_finalize(int64_t* scratch, int64_t num_classes, int mode, int64_t* tp, int64_t* fp,
+                          int64_t* tn, int64_t* fn, void* stream);
+
+/* Scratch size in bytes for a mode (0 for TMB_MC_CONFMAT). Host only. */
+int64_t tmb_mc_scratch_bytes(int64_t num_classes, int mode);
+
+/* ---- K2 / K1b: one-pass threshold binning ----------------------------------------------------------
+ *
+ * tmb_thresh_bin_update + tmb_thresh_bin_finalize replace
+ *   _binary_precision_recall_curve_format/_update (+_vectorized, _loop)
+ *                                       functional/classification/precision_recall_curve.py:162-250
+ *   _multilabel_precision_recall_curve_format/_update              same file :739-793
+ *   _binary/_multilabel_stat_scores_format/_update     functional/classification/stat_scores.py:90-131, 647-681
+ *   _binary/_multilabel_confusion_matrix_format/_update
+ *                                       functional/classification/confusion_matrix.py:118-153, 486-526
+ *
+ * preds  : float (or 0/1 integer labels) [n_outer, num_labels, n_inner] contiguous; binary = num_labels 1.
+ * target : integers of the same shape.
+ * thr    : T float32 thresholds in ASCENDING order, device memory.
+ * Per non-ignored element: q = preds, or sigmoid(preds) when the batch has any value outside [0,1]
+ * (decided on the device; `flag_counts_ignored` says whether ignored positions take part in that test:
+ * 0 for binary curves / binary confusion matrix, 1 for stat scores and every multilabel metric);
+ * k = #{j : thr[j] <= q} (`cmp_gt` = 0, curves) or #{j : thr[j] < q} (`cmp_gt` = 1, the strict `preds >
+ * threshold` of stat scores / confusion matrices); hist[label][target][k] += 1.  NaN gives k = 0.
+ * The histogram lives in the caller's int64 scratch, which must be zero before the first call and is
+ * re-zeroed by tmb_thresh_bin_finalize.  (Where the reference compares in a narrow dtype, the host
+ * rounds thr to that dtype before the call.)
+ */
+#define TMB_TB_CURVE 0   /* out0 = int64 state [T, L, 2, 2] (binary: [T, 2, 2])                         */
+#define TMB_TB_CONFMAT 1 /* T == 1: out0 = int64 state [L, 2, 2] (binary: [2, 2]), [l][target][pred]     */
+#define TMB_TB_STATS 2   /* T == 1: out0..out3 = tp, fp, tn, fn, int64 [L] each                          */
+
+/* int64 elements of scratch for (num_labels, T). Host only. */
+int64_t tmb_thresh_bin_scratch_elems(int64_t num_labels, int64_t num_thresholds);
+
+int tmb_thresh_bin_update(const void* preds, int preds_dtype, int preds_is_label, const void* target,
+                          int target_dtype, int64_t n_outer, int64_t num_labels, int64_t n_inner,
+                          const float* thr, int64_t num_thresholds, int cmp_gt, int has_ignore,
+                          int64_t ignore_index, int flag_counts_ignored, int64_t* scratch,
+                          int64_t scratch_elems, int32_t* err, void* stream);
+
+/* Picks the raw or the sigmoid histogram, forms the per-threshold counts
+ * (TP_j = sum_{k>j} hist[l][1][k], FP_j likewise from hist[l][0], FN_j = n1 - TP_j, TN_j = n0 - FP_j;
+ * precision_recall_curve.py:246-249) and ADDS them into the state in the requested layout.
+ * `perm` (int32[T], device, may be NULL) maps the sorted threshold position to the row of the state,
+ * for thresholds the user did not give in ascending order.  Re-zeroes the scratch. */
+int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, int64_t num_labels,
+                            int64_t num_thresholds, const int32_t* perm, int layout, int64_t* out0,
+                            int64_t* out1, int64_t* out2, int64_t* out3, void* stream);
+
+/* ---- utilities ------------------------------------------------------------------------------------
+ * tmb_bincount: out[v] += 1 for every v = x[i] (integer dtype), 0 <= v < length; other values set
+ * TMB_ERR_PREDS_RANGE.  Replaces torch.bincount inside _bincount (utilities/data.py:169-199). */
+int tmb_bincount(const void* x, int x_dtype, int64_t n, int64_t length, int64_t* out, int32_t* err,
+                 void* stream);
+/* Largest value of x (int64 result, INT64_MIN for n == 0) -> *out_max, used to size a bincount. */
+int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out_max, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TMB200_H_ */

@@ -1,0 +1,60 @@
+"""Metric classes of the classification hot path (same names and constructor signatures as the reference)."""
+from torchmetrics_forked_b200.classification.accuracy import (
+    Accuracy,
+    BinaryAccuracy,
+    MulticlassAccuracy,
+    MultilabelAccuracy,
+)
+from torchmetrics_forked_b200.classification.auroc import AUROC, BinaryAUROC, MultilabelAUROC
+from torchmetrics_forked_b200.classification.average_precision import (
+    AveragePrecision,
+    BinaryAveragePrecision,
+    MultilabelAveragePrecision,
+)
+from torchmetrics_forked_b200.classification.confusion_matrix import (
+    BinaryConfusionMatrix,
+    ConfusionMatrix,
+    MulticlassConfusionMatrix,
+    MultilabelConfusionMatrix,
+)
+from torchmetrics_forked_b200.classification.f_beta import (
+    BinaryF1Score,
+    BinaryFBetaScore,
+    F1Score,
+    FBetaScore,
+    MulticlassF1Score,
+    MulticlassFBetaScore,
+    MultilabelF1Score,
+    MultilabelFBetaScore,
+)
+from torchmetrics_forked_b200.classification.jaccard import (
+    BinaryJaccardIndex,
+    JaccardIndex,
+    MulticlassJaccardIndex,
+    MultilabelJaccardIndex,
+)
+from torchmetrics_forked_b200.classification.precision_recall_curve import (
+    BinaryPrecisionRecallCurve,
+    MultilabelPrecisionRecallCurve,
+    PrecisionRecallCurve,
+)
+from torchmetrics_forked_b200.classification.roc import ROC, BinaryROC, MultilabelROC
+from torchmetrics_forked_b200.classification.stat_scores import (
+    BinaryStatScores,
+    MulticlassStatScores,
+    MultilabelStatScores,
+    StatScores,
+)
+
+__all__ = [
+    "Accuracy", "BinaryAccuracy", "MulticlassAccuracy", "MultilabelAccuracy",
+    "AUROC", "BinaryAUROC", "MultilabelAUROC",
+    "AveragePrecision", "BinaryAveragePrecision", "MultilabelAveragePrecision",
+    "BinaryConfusionMatrix", "ConfusionMatrix", "MulticlassConfusionMatrix", "MultilabelConfusionMatrix",
+    "BinaryF1Score", "BinaryFBetaScore", "F1Score", "FBetaScore", "MulticlassF1Score", "MulticlassFBetaScore",
+    "MultilabelF1Score", "MultilabelFBetaScore",
+    "BinaryJaccardIndex", "JaccardIndex", "MulticlassJaccardIndex", "MultilabelJaccardIndex",
+    "BinaryPrecisionRecallCurve", "MultilabelPrecisionRecallCurve", "PrecisionRecallCurve",
+    "ROC", "BinaryROC", "MultilabelROC",
+    "BinaryStatScores", "MulticlassStatScores", "MultilabelStatScores", "StatScores",
+]  # fmt: skip

@@ -1,0 +1,190 @@
+"""PrecisionRecallCurve metric classes.
+
+Reference: classification/precision_recall_curve.py (binary :45-243, multilabel :430-640, wrapper :643-675).
+Binned mode keeps an int64 ``confmat`` sum-state of shape ``[T, 2, 2]`` / ``[T, L, 2, 2]``; exact mode keeps
+``preds`` / ``target`` list states ("cat").  ``thresholds`` is a non-persistent buffer created on the CPU at
+construction exactly like the reference's (:150-156, H4) — the kernels read that buffer, never a recomputed
+linspace.
+"""
+from typing import Any, List, Optional, Tuple, Union
+
+import torch
+from torch import Tensor
+from typing_extensions import Literal
+
+from torchmetrics_forked_b200 import kernels
+from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
+from torchmetrics_forked_b200.functional.classification.precision_recall_curve import (
+    _adjust_threshold_arg,
+    _binary_precision_recall_curve_arg_validation,
+    _binary_precision_recall_curve_compute,
+    _binary_precision_recall_curve_format_exact,
+    _binary_precision_recall_curve_tensor_validation,
+    _binary_precision_recall_curve_update_,
+    _multilabel_precision_recall_curve_arg_validation,
+    _multilabel_precision_recall_curve_compute,
+    _multilabel_precision_recall_curve_format_exact,
+    _multilabel_precision_recall_curve_tensor_validation,
+    _multilabel_precision_recall_curve_update_,
+    _threshold_plan,
+)
+from torchmetrics_forked_b200.metric import Metric
+from torchmetrics_forked_b200.utilities.data import dim_zero_cat
+from torchmetrics_forked_b200.utilities.enums import ClassificationTask
+
+
+class _CurveStateMixin:
+    """Shared state set-up: binned (``confmat``) vs exact (``preds`` / ``target`` lists)."""
+
+    def _init_curve_state(self, thresholds: Optional[Union[int, List[float], Tensor]], confmat_shape) -> None:
+        thresholds = _adjust_threshold_arg(thresholds)
+        if thresholds is None:
+            self.thresholds = thresholds
+            self.add_state("preds", default=[], dist_reduce_fx="cat")
+            self.add_state("target", default=[], dist_reduce_fx="cat")
+            return
+        self.register_buffer("thresholds", thresholds, persistent=False)
+        ordered, perm = _threshold_plan(thresholds, torch.device("cpu"))
+        # the usual case (ascending float32) bins against the `thresholds` buffer itself
+        self._thr_direct = perm is None and thresholds.dtype == torch.float32 and thresholds.is_contiguous()
+        self.register_buffer("_thr_sorted", None if self._thr_direct else ordered, persistent=False)
+        self.register_buffer("_thr_perm", perm, persistent=False)
+        self.add_state(
+            "confmat", default=torch.zeros(len(thresholds), *confmat_shape, dtype=torch.long), dist_reduce_fx="sum"
+        )
+
+    def _bin_plan(self, device: torch.device) -> Tuple[Tensor, Optional[Tensor]]:
+        thr = self.thresholds if self._thr_direct else self._thr_sorted
+        if thr.device != device:
+            raise RuntimeError(
+                f"Expected all tensors to be on the same device, but the metric is on {thr.device} and the inputs"
+                f" on {device}"
+            )
+        return thr, self._thr_perm
+
+    def _curve_state(self) -> Union[Tensor, Tuple[Tensor, Tensor]]:
+        if self.thresholds is None:
+            return dim_zero_cat(self.preds), dim_zero_cat(self.target)
+        return self.confmat
+
+
+class BinaryPrecisionRecallCurve(_CurveStateMixin, Metric):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+
+    preds: List[Tensor]
+    target: List[Tensor]
+    confmat: Tensor
+
+    def __init__(
+        self,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(**kwargs)
+        if validate_args:
+            _binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._init_curve_state(thresholds, (2, 2))
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            _binary_precision_recall_curve_tensor_validation(preds, target, self.ignore_index)
+        dev = preds.device
+        err = self._error_word(dev)
+        if self.thresholds is None:
+            p, t = _binary_precision_recall_curve_format_exact(preds, target, self.ignore_index, err)
+            self.preds.append(p)
+            self.target.append(t)
+        else:
+            thr, perm = self._bin_plan(dev)
+            scratch = self._scratch_buffer("tb", kernels.thresh_bin_scratch_numel(1, thr.numel()), dev)
+            _binary_precision_recall_curve_update_(
+                preds, target, thr, perm, self.ignore_index, self.confmat, scratch, err
+            )
+        if self.validate_args:
+            self._raise_on_data_errors()
+
+    def compute(self) -> Tuple[Tensor, Tensor, Tensor]:
+        return _binary_precision_recall_curve_compute(self._curve_state(), self.thresholds)
+
+
+class MultilabelPrecisionRecallCurve(_CurveStateMixin, Metric):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+
+    preds: List[Tensor]
+    target: List[Tensor]
+    confmat: Tensor
+
+    def __init__(
+        self,
+        num_labels: int,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(**kwargs)
+        if validate_args:
+            _multilabel_precision_recall_curve_arg_validation(num_labels, thresholds, ignore_index)
+        self.num_labels = num_labels
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._init_curve_state(thresholds, (num_labels, 2, 2))
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            _multilabel_precision_recall_curve_tensor_validation(preds, target, self.num_labels, self.ignore_index)
+        dev = preds.device
+        err = self._error_word(dev)
+        if self.thresholds is None:
+            p, t = _multilabel_precision_recall_curve_format_exact(preds, target, self.num_labels, err)
+            self.preds.append(p)
+            self.target.append(t)
+        else:
+            thr, perm = self._bin_plan(dev)
+            scratch = self._scratch_buffer(
+                "tb", kernels.thresh_bin_scratch_numel(self.num_labels, thr.numel()), dev
+            )
+            _multilabel_precision_recall_curve_update_(
+                preds, target, self.num_labels, thr, perm, self.ignore_index, self.confmat, scratch, err
+            )
+        if self.validate_args:
+            self._raise_on_data_errors()
+
+    def compute(self) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+        return _multilabel_precision_recall_curve_compute(
+            self._curve_state(), self.num_labels, self.thresholds, self.ignore_index
+        )
+
+
+class PrecisionRecallCurve(_ClassificationTaskWrapper):
+    """``PrecisionRecallCurve(task=...)`` (reference :643-675); multiclass curves are a later row of SURVEY §8."""
+
+    def __new__(  # type: ignore[misc]
+        cls,
+        task: Literal["binary", "multiclass", "multilabel"],
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        num_classes: Optional[int] = None,
+        num_labels: Optional[int] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> Metric:
+        task = ClassificationTask.from_str(task)
+        kwargs.update({"thresholds": thresholds, "ignore_index": ignore_index, "validate_args": validate_args})
+        if task == ClassificationTask.BINARY:
+            return BinaryPrecisionRecallCurve(**kwargs)
+        if task == ClassificationTask.MULTICLASS:
+            raise NotImplementedError("multiclass precision-recall curves are not part of the sm_100a update path yet")
+        if task == ClassificationTask.MULTILABEL:
+            if not isinstance(num_labels, int):
+                raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
+            return MultilabelPrecisionRecallCurve(num_labels, **kwargs)
+        raise ValueError(f"Task {task} not supported!")

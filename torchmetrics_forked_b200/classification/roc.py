@@ -1,0 +1,51 @@
+"""ROC metric classes: same state and update as the precision-recall curve, different ``compute``.
+
+Reference: classification/roc.py (binary :42-156, multilabel :339-466).
+"""
+from typing import Any, List, Optional, Tuple, Union
+
+from torch import Tensor
+from typing_extensions import Literal
+
+from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
+from torchmetrics_forked_b200.classification.precision_recall_curve import (
+    BinaryPrecisionRecallCurve,
+    MultilabelPrecisionRecallCurve,
+)
+from torchmetrics_forked_b200.functional.classification.roc import _binary_roc_compute, _multilabel_roc_compute
+from torchmetrics_forked_b200.metric import Metric
+from torchmetrics_forked_b200.utilities.enums import ClassificationTask
+
+
+class BinaryROC(BinaryPrecisionRecallCurve):
+    def compute(self) -> Tuple[Tensor, Tensor, Tensor]:  # type: ignore[override]
+        return _binary_roc_compute(self._curve_state(), self.thresholds)
+
+
+class MultilabelROC(MultilabelPrecisionRecallCurve):
+    def compute(self) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+        return _multilabel_roc_compute(self._curve_state(), self.num_labels, self.thresholds, self.ignore_index)
+
+
+class ROC(_ClassificationTaskWrapper):
+    def __new__(  # type: ignore[misc]
+        cls,
+        task: Literal["binary", "multiclass", "multilabel"],
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        num_classes: Optional[int] = None,
+        num_labels: Optional[int] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> Metric:
+        task = ClassificationTask.from_str(task)
+        kwargs.update({"thresholds": thresholds, "ignore_index": ignore_index, "validate_args": validate_args})
+        if task == ClassificationTask.BINARY:
+            return BinaryROC(**kwargs)
+        if task == ClassificationTask.MULTICLASS:
+            raise NotImplementedError("multiclass ROC is not part of the sm_100a update path yet")
+        if task == ClassificationTask.MULTILABEL:
+            if not isinstance(num_labels, int):
+                raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
+            return MultilabelROC(num_labels, **kwargs)
+        raise ValueError(f"Task {task} not supported!")

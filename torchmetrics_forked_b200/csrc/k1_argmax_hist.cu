@@ -1,0 +1,513 @@
+// K1 — multiclass argmax + histogram, one pass over the logits.
+//
+// Replaces the reference's argmax -> flatten -> (boolean-mask) -> target*C+pred -> bincount chain
+// (functional/classification/confusion_matrix.py:306-337, stat_scores.py:325-341 and :394-418,
+// utilities/data.py:169-199) with kernels that read every logit exactly once and accumulate straight
+// into the int64 metric state (confusion matrix) or into a small int64 scratch (stat scores).
+//
+// Three input layouts, three kernels:
+//   rows_warp   [N, C] row-major, long rows   : one warp per row, vector loads, shuffle merge
+//   rows_thread [N, C] row-major, short rows  : one thread per row, rows staged through shared memory
+//   strided     [N, C, S] class stride S > 1  : one thread per group of adjacent pixels, loop over C
+// plus a label kernel for integer preds.  All are HBM-streaming: algorithmic bytes per sample are
+// C*sizeof(elem) + sizeof(target), there is no reuse, so the only shared-memory use is the coalescing
+// stage of rows_thread and the privatised histogram for small C.
+#include "common.cuh"
+
+namespace tmb {
+
+// ---- accumulation target -------------------------------------------------------------------------
+struct HistArgs {
+  int mode;        // TMB_MC_*
+  int C;           // num_classes
+  int sh_bins;     // > 0: privatise this many int32 bins in shared memory, flush at CTA exit
+  int has_ignore;
+  int64_t ignore;
+  unsigned long long* out;
+  int* err;
+};
+
+// per-thread micro counters (mode MICRO) live in registers and are flushed once per CTA
+struct Micro {
+  unsigned int match, n;
+};
+
+__device__ __forceinline__ void hist_add(const HistArgs& h, int* sh, int64_t bin) {
+  if (h.sh_bins > 0)
+    atomicAdd(&sh[bin], 1);
+  else
+    atomicAdd(&h.out[bin], 1ULL);
+}
+
+// one classified sample: t = target, p = predicted class
+__device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& mi, int64_t t, int64_t p,
+                                             bool p_is_label) {
+  if (h.has_ignore && t == h.ignore) return;
+  if (t < 0 || t >= h.C) {
+    atomicOr(h.err, TMB_ERR_TARGET_RANGE);
+    return;
+  }
+  if (p_is_label && (p < 0 || p >= h.C)) {
+    atomicOr(h.err, TMB_ERR_PREDS_RANGE);
+    return;
+  }
+  if (h.mode == TMB_MC_CONFMAT) {
+    hist_add(h, sh, t * h.C + p);
+  } else if (h.mode == TMB_MC_STATS) {
+    hist_add(h, sh, t);
+    hist_add(h, sh, h.C + p);
+    if (p == t) hist_add(h, sh, 2 * (int64_t)h.C + t);
+  } else {
+    mi.n += 1;
+    mi.match += (p == t);
+  }
+}
+
+__device__ __forceinline__ void hist_prologue(const HistArgs& h, int* sh) {
+  if (h.sh_bins > 0) {
+    for (int i = threadIdx.x; i < h.sh_bins; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+  }
+}
+
+__device__ __forceinline__ void hist_epilogue(const HistArgs& h, int* sh, Micro mi) {
+  if (h.sh_bins > 0) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < h.sh_bins; i += blockDim.x) {
+      int v = sh[i];
+      if (v) atomicAdd(&h.out[i], (unsigned long long)v);
+    }
+  }
+  if (h.mode == TMB_MC_MICRO) {
+    unsigned m = __reduce_add_sync(kFull, mi.match);
+    unsigned n = __reduce_add_sync(kFull, mi.n);
+    if ((threadIdx.x & 31) == 0 && n) {
+      atomicAdd(&h.out[0], (unsigned long long)m);
+      atomicAdd(&h.out[1], (unsigned long long)n);
+    }
+  }
+}
+
+// ---- vector helpers ------------------------------------------------------------------------------
+template <int VB>
+struct Vec;
+template <>
+struct Vec<16> {
+  uint32_t w[4];
+  __device__ __forceinline__ void load(const void* p) {
+    uint4 r = ldg_stream16(p);
+    w[0] = r.x; w[1] = r.y; w[2] = r.z; w[3] = r.w;
+  }
+};
+template <>
+struct Vec<8> {
+  uint32_t w[2];
+  __device__ __forceinline__ void load(const void* p) {
+    uint2 r = ldg_stream8(p);
+    w[0] = r.x; w[1] = r.y;
+  }
+};
+template <>
+struct Vec<4> {
+  uint32_t w[1];
+  __device__ __forceinline__ void load(const void* p) { w[0] = ldg_stream4(p); }
+};
+template <>
+struct Vec<2> {
+  uint32_t w[1];
+  __device__ __forceinline__ void load(const void* p) { w[0] = ldg_stream2(p); }
+};
+
+// element e of a vector of VB bytes holding elements of dtype DT
+template <int DT, int VB>
+__device__ __forceinline__ float vec_elem(const Vec<VB>& v, int e) {
+  if constexpr (Elem<DT>::kBytes == 4)
+    return Elem<DT>::get(v.w[e], 0);
+  else
+    return Elem<DT>::get(v.w[e >> 1], e & 1);
+}
+
+// ---- rows_warp: one warp per row -----------------------------------------------------------------
+// Lane L reads vectors L, L+32, ... of the row (U of them in flight), scans its elements in increasing
+// index order, then the 32 partial results are merged with the (value, index) rule of torch.argmax.
+template <int DT, int VB>
+__global__ void __launch_bounds__(256) k1_rows_warp(const char* __restrict__ preds, const void* __restrict__ target,
+                                                    int target_dtype, int64_t n_rows, HistArgs h) {
+  extern __shared__ int sh[];
+  constexpr int ES = Elem<DT>::kBytes;
+  constexpr int EPV = VB / ES;
+  constexpr int U = 4;
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t row_bytes = (int64_t)h.C * ES;
+  const int nvec = (int)(row_bytes / VB);
+
+  for (int64_t row = warp; row < n_rows; row += nwarps) {
+    const char* rp = preds + row * row_bytes;
+    Best b = best_init();
+    for (int v0 = 0; v0 < nvec; v0 += 32 * U) {
+      Vec<VB> r[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int vi = v0 + u * 32 + lane;
+        if (vi < nvec) r[u].load(rp + (int64_t)vi * VB);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int vi = v0 + u * 32 + lane;
+        if (vi < nvec) {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) best_step(b, vec_elem<DT, VB>(r[u], e), vi * EPV + e);
+        }
+      }
+    }
+    b = best_warp(b);
+    if (lane == 0) {
+      int64_t t = load_label(target, target_dtype, row);
+      count_sample(h, sh, mi, t, best_index(b), false);
+    }
+  }
+  hist_epilogue(h, sh, mi);
+}
+
+// ---- rows_thread: one thread per row, rows staged through shared memory ---------------------------
+// Rows shorter than a few vectors cannot keep a warp busy, so a CTA copies TILE consecutive rows
+// (a contiguous byte range) into shared memory with full-width coalesced loads and each thread then
+// scans its own row from there.
+constexpr int kTileRows = 128;
+
+template <int DT, int VB>
+__global__ void __launch_bounds__(kTileRows) k1_rows_thread(const char* __restrict__ preds,
+                                                            const void* __restrict__ target, int target_dtype,
+                                                            int64_t n_rows, HistArgs h) {
+  extern __shared__ int sh_all[];
+  constexpr int ES = Elem<DT>::kBytes;
+  const int64_t row_bytes = (int64_t)h.C * ES;
+  // layout: [tile bytes, rounded up to 16][histogram bins]
+  const int tile_cap = (int)((kTileRows * row_bytes + 15) / 16 * 16);
+  char* tile = (char*)sh_all;
+  int* sh = (int*)(tile + tile_cap);
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  const int64_t n_tiles = (n_rows + kTileRows - 1) / kTileRows;
+
+  for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
+    const int64_t row0 = tIdx * kTileRows;
+    const int rows = (int)min((int64_t)kTileRows, n_rows - row0);
+    const int64_t bytes = rows * row_bytes;
+    const char* src = preds + row0 * row_bytes;
+    const int nv = (int)(bytes / VB);
+    for (int i = threadIdx.x; i < nv; i += kTileRows) {
+      Vec<VB> v;
+      v.load(src + (int64_t)i * VB);
+      if constexpr (VB == 16) {
+        *(uint4*)(tile + i * 16) = make_uint4(v.w[0], v.w[1], v.w[2], v.w[3]);
+      } else if constexpr (VB == 8) {
+        *(uint2*)(tile + i * 8) = make_uint2(v.w[0], v.w[1]);
+      } else if constexpr (VB == 4) {
+        *(uint32_t*)(tile + i * 4) = v.w[0];
+      } else {
+        *(uint16_t*)(tile + i * 2) = (uint16_t)v.w[0];
+      }
+    }
+    // remainder (< VB bytes), element granular
+    for (int64_t off = (int64_t)nv * VB + threadIdx.x * ES; off < bytes; off += kTileRows * ES) {
+      if constexpr (ES == 4)
+        *(uint32_t*)(tile + off) = ldg_stream4(src + off);
+      else
+        *(uint16_t*)(tile + off) = ldg_stream2(src + off);
+    }
+    __syncthreads();
+    if ((int)threadIdx.x < rows) {
+      Best b = best_init();
+      const char* rp = tile + threadIdx.x * row_bytes;
+      for (int c = 0; c < h.C; ++c) {
+        float v;
+        if constexpr (ES == 4)
+          v = *(const float*)(rp + c * 4);
+        else
+          v = Elem<DT>::get(*(const uint16_t*)(rp + c * 2), 0);
+        best_step(b, v, c);
+      }
+      int64_t t = load_label(target, target_dtype, row0 + threadIdx.x);
+      count_sample(h, sh, mi, t, best_index(b), false);
+    }
+    __syncthreads();
+  }
+  hist_epilogue(h, sh, mi);
+}
+
+// ---- strided: [N, C, S], class stride S ------------------------------------------------------------
+// One thread owns PPT = VB/ES adjacent pixels of one outer index and walks the C class planes with U
+// loads in flight; a warp therefore reads 32*VB contiguous bytes of every plane.
+template <int DT, int VB>
+__global__ void __launch_bounds__(256) k1_strided(const char* __restrict__ preds, const void* __restrict__ target,
+                                                  int target_dtype, int64_t n_outer, int64_t S, HistArgs h) {
+  extern __shared__ int sh[];
+  constexpr int ES = Elem<DT>::kBytes;
+  constexpr int PPT = VB / ES;
+  constexpr int U = 8;
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  const int64_t groups_per_outer = S / PPT;
+  const int64_t n_groups = n_outer * groups_per_outer;
+  const int64_t plane_bytes = S * ES;
+
+  for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n_groups;
+       g += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t n = g / groups_per_outer;
+    const int64_t s0 = (g - n * groups_per_outer) * PPT;
+    const char* p0 = preds + (n * h.C * S + s0) * ES;
+    Best b[PPT];
+#pragma unroll
+    for (int q = 0; q < PPT; ++q) b[q] = best_init();
+    for (int c0 = 0; c0 < h.C; c0 += U) {
+      Vec<VB> r[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (c0 + u < h.C) r[u].load(p0 + (int64_t)(c0 + u) * plane_bytes);
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+        if (c0 + u < h.C) {
+#pragma unroll
+          for (int q = 0; q < PPT; ++q) best_step(b[q], vec_elem<DT, VB>(r[u], q), c0 + u);
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < PPT; ++q) {
+      int64_t t = load_label(target, target_dtype, n * S + s0 + q);
+      count_sample(h, sh, mi, t, best_index(b[q]), false);
+    }
+  }
+  hist_epilogue(h, sh, mi);
+}
+
+// ---- labels: integer preds -------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k1_labels(const void* __restrict__ preds, int preds_dtype,
+                                                 const void* __restrict__ target, int target_dtype, int64_t n,
+                                                 HistArgs h) {
+  extern __shared__ int sh[];
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t t = load_label(target, target_dtype, i);
+    int64_t p = load_label(preds, preds_dtype, i);
+    count_sample(h, sh, mi, t, p, true);
+  }
+  hist_epilogue(h, sh, mi);
+}
+
+// ---- stat-score finalize ---------------------------------------------------------------------------
+// tp/fp/tn/fn += f(hist_target, hist_pred, match), scratch re-zeroed for the next update.
+__global__ void __launch_bounds__(1024) k1_stats_finalize(unsigned long long* scratch, int C, int mode,
+                                                          long long* tp, long long* fp, long long* tn,
+                                                          long long* fn) {
+  if (mode == TMB_MC_MICRO) {
+    if (threadIdx.x == 0) {
+      long long m = (long long)scratch[0], n = (long long)scratch[1];
+      tp[0] += m;
+      fp[0] += n - m;
+      fn[0] += n - m;
+      tn[0] += (long long)C * n - 2 * n + m;  // C*n - (tp + fp + fn)
+      scratch[0] = 0;
+      scratch[1] = 0;
+    }
+    return;
+  }
+  __shared__ long long red[32];
+  __shared__ long long total;
+  long long part = 0;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) part += (long long)scratch[c];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long s = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) s += red[w];
+    total = s;
+  }
+  __syncthreads();
+  const long long n = total;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    long long ht = (long long)scratch[c], hp = (long long)scratch[C + c], m = (long long)scratch[2 * C + c];
+    tp[c] += m;
+    fp[c] += hp - m;
+    fn[c] += ht - m;
+    tn[c] += n - ht - hp + m;
+    scratch[c] = 0;
+    scratch[C + c] = 0;
+    scratch[2 * C + c] = 0;
+  }
+}
+
+// ---- host side --------------------------------------------------------------------------------------
+constexpr int kShBinsMax = 4096;  // privatise in shared memory up to this many bins (16 KB)
+
+static int hist_bins(int mode, int64_t C) {
+  if (mode == TMB_MC_CONFMAT) return (int)(C * C);
+  if (mode == TMB_MC_STATS) return (int)(3 * C);
+  return 0;
+}
+
+static int make_hist(HistArgs& h, int mode, int64_t C, int has_ignore, int64_t ignore, int64_t* out,
+                     int32_t* err) {
+  if (mode != TMB_MC_CONFMAT && mode != TMB_MC_STATS && mode != TMB_MC_MICRO) return TMB_E_MODE;
+  if (C < 1 || C > (1 << 24)) return TMB_E_SHAPE;
+  if (!out || !err) return TMB_E_NULL;
+  h.mode = mode;
+  h.C = (int)C;
+  int64_t bins = mode == TMB_MC_CONFMAT ? C * C : (mode == TMB_MC_STATS ? 3 * C : 0);
+  h.sh_bins = (bins > 0 && bins <= kShBinsMax) ? (int)bins : 0;
+  h.has_ignore = has_ignore;
+  h.ignore = ignore;
+  h.out = (unsigned long long*)out;
+  h.err = err;
+  (void)hist_bins;
+  return 0;
+}
+
+// widest power-of-two vector (<= 16 B) that divides both an address and a byte pitch
+static int vec_bytes(const void* p, int64_t pitch_bytes, int elem_bytes) {
+  uint64_t a = (uint64_t)(uintptr_t)p | (uint64_t)pitch_bytes;
+  int v = 16;
+  while (v > elem_bytes && (a & (uint64_t)(v - 1))) v >>= 1;
+  return v;
+}
+
+template <int DT>
+static int launch_rows(const void* preds, const void* target, int tdt, int64_t n_rows, const HistArgs& h,
+                       cudaStream_t st) {
+  constexpr int ES = Elem<DT>::kBytes;
+  const int64_t row_bytes = (int64_t)h.C * ES;
+  const int hist_smem = h.sh_bins * (int)sizeof(int);
+  if (row_bytes <= 256) {
+    // short rows: thread per row through shared memory
+    const int vb = vec_bytes(preds, kTileRows * row_bytes, ES);
+    const int tile_cap = (int)((kTileRows * row_bytes + 15) / 16 * 16);
+    const int smem = tile_cap + hist_smem;
+    const int grid = wave_grid((n_rows + kTileRows - 1) / kTileRows, 8);
+    const char* p = (const char*)preds;
+    switch (vb) {
+      case 16: k1_rows_thread<DT, 16><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
+      case 8: k1_rows_thread<DT, 8><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
+      case 4: k1_rows_thread<DT, 4><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
+      default:
+        if constexpr (ES == 2) {
+          k1_rows_thread<DT, 2><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h);
+          break;
+        } else {
+          return TMB_E_SHAPE;
+        }
+    }
+    return launch_status();
+  }
+  const int vb = vec_bytes(preds, row_bytes, ES);
+  const int block = 256;
+  const int grid = wave_grid((n_rows + 7) / 8, 8);
+  const char* p = (const char*)preds;
+  switch (vb) {
+    case 16: k1_rows_warp<DT, 16><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
+    case 8: k1_rows_warp<DT, 8><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
+    case 4: k1_rows_warp<DT, 4><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
+    default:
+      if constexpr (ES == 2) {
+        k1_rows_warp<DT, 2><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h);
+        break;
+      } else {
+        return TMB_E_SHAPE;
+      }
+  }
+  return launch_status();
+}
+
+template <int DT>
+static int launch_strided(const void* preds, const void* target, int tdt, int64_t n_outer, int64_t S,
+                          const HistArgs& h, cudaStream_t st) {
+  constexpr int ES = Elem<DT>::kBytes;
+  const int hist_smem = h.sh_bins * (int)sizeof(int);
+  const int vb = vec_bytes(preds, S * ES, ES);
+  const int64_t groups = n_outer * (S / (vb / ES));
+  const int block = 256;
+  const int grid = wave_grid((groups + block - 1) / block, 8);
+  const char* p = (const char*)preds;
+  switch (vb) {
+    case 16: k1_strided<DT, 16><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
+    case 8: k1_strided<DT, 8><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
+    case 4: k1_strided<DT, 4><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
+    default:
+      if constexpr (ES == 2) {
+        k1_strided<DT, 2><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h);
+        break;
+      } else {
+        return TMB_E_SHAPE;
+      }
+  }
+  return launch_status();
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" int tmb_build_arch(void) { return 100; }
+
+extern "C" int64_t tmb_mc_scratch_bytes(int64_t num_classes, int mode) {
+  if (mode == TMB_MC_STATS) return 3 * num_classes * (int64_t)sizeof(int64_t);
+  if (mode == TMB_MC_MICRO) return 2 * (int64_t)sizeof(int64_t);
+  return 0;
+}
+
+extern "C" int tmb_mc_argmax_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                  int64_t n_outer, int64_t num_classes, int64_t n_inner, int has_ignore,
+                                  int64_t ignore_index, int mode, int64_t* out, int32_t* err, void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_outer < 0 || n_inner < 1) return TMB_E_SHAPE;
+  HistArgs h;
+  if (int rc = make_hist(h, mode, num_classes, has_ignore, ignore_index, out, err)) return rc;
+  if (n_outer == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (n_inner == 1) {
+    switch (preds_dtype) {
+      case TMB_F32: return launch_rows<TMB_F32>(preds, target, target_dtype, n_outer, h, st);
+      case TMB_F16: return launch_rows<TMB_F16>(preds, target, target_dtype, n_outer, h, st);
+      default: return launch_rows<TMB_BF16>(preds, target, target_dtype, n_outer, h, st);
+    }
+  }
+  switch (preds_dtype) {
+    case TMB_F32: return launch_strided<TMB_F32>(preds, target, target_dtype, n_outer, n_inner, h, st);
+    case TMB_F16: return launch_strided<TMB_F16>(preds, target, target_dtype, n_outer, n_inner, h, st);
+    default: return launch_strided<TMB_BF16>(preds, target, target_dtype, n_outer, n_inner, h, st);
+  }
+}
+
+extern "C" int tmb_mc_label_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                 int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index, int mode,
+                                 int64_t* out, int32_t* err, void* stream) {
+  if (label_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n < 0) return TMB_E_SHAPE;
+  HistArgs h;
+  if (int rc = make_hist(h, mode, num_classes, has_ignore, ignore_index, out, err)) return rc;
+  if (n == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  const int block = 256;
+  const int grid = wave_grid((n + block * 4 - 1) / (block * 4), 8);
+  k1_labels<<<grid, block, h.sh_bins * sizeof(int), (cudaStream_t)stream>>>(preds, preds_dtype, target,
+                                                                            target_dtype, n, h);
+  return launch_status();
+}
+
+extern "C" int tmb_mc_stats_finalize(int64_t* scratch, int64_t num_classes, int mode, int64_t* tp, int64_t* fp,
+                                     int64_t* tn, int64_t* fn, void* stream) {
+  if (mode != TMB_MC_STATS && mode != TMB_MC_MICRO) return TMB_E_MODE;
+  if (!scratch || !tp || !fp || !tn || !fn) return TMB_E_NULL;
+  if (num_classes < 1 || num_classes > (1 << 24)) return TMB_E_SHAPE;
+  k1_stats_finalize<<<1, 1024, 0, (cudaStream_t)stream>>>((unsigned long long*)scratch, (int)num_classes, mode,
+                                                          (long long*)tp, (long long*)fp, (long long*)tn,
+                                                          (long long*)fn);
+  return launch_status();
+}

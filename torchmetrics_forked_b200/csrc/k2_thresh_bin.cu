@@ -1,0 +1,619 @@
+// K2 / K1b — one-pass threshold binning.
+//
+// The reference evaluates `preds >= thresholds[i]` once per threshold (200 full passes and ~1800
+// launches at T = 200, functional/classification/precision_recall_curve.py:228-250) or materialises an
+// N x T comparison (:210-225, :785-793).  Here every sample is read once: its bin index
+// k = #{j : thr[j] <= q} is found with a uniform-grid guess corrected by exact compares against the
+// metric's own threshold buffer (never a recomputed linspace, H4), and hist[label][target][k] is bumped.
+// The per-threshold counts are suffix sums of that histogram, formed by a tiny finalize kernel.
+//
+// Conditional sigmoid (H1): the reference applies sigmoid iff ANY value of the batch lies outside [0,1].
+// Two launches share one read of the data: pass A bins the raw values and raises a device flag at the
+// first outside value (every CTA polls the flag and quits, so for logits this pass ends after the first
+// wave); pass B bins sigmoid(x) and returns immediately when the flag is down.  Finalize picks.
+//
+// Hot case (binary, config 3): a shared-memory atomic per sample would cap the SM at <1 sample/clk
+// (B300_MICROARCH: ATOMS ~2 clk/lane), an order of magnitude under the HBM rate.  Instead every LANE owns
+// a private histogram column (word k*32+lane -> its own bank, plain LDS/IADD/STS, no conflicts, no
+// atomics) with the positive and negative counts packed as 16+16 bits; columns are summed by warp
+// reduction when a lane has seen 65535 samples and at exit.
+#include "common.cuh"
+
+namespace tmb {
+
+constexpr int kHdr = 8;  // scratch[0] = "saw a value outside [0,1]" flag, [1..7] reserved
+
+struct TbArgs {
+  const void* preds;
+  const void* target;
+  const float* thr;
+  unsigned long long* scratch;
+  int* err;
+  int64_t n_total;  // n_outer * L * S
+  int64_t S;
+  int64_t ignore;
+  int L;
+  int T;
+  int pdt;  // float code, or label code when preds_is_label
+  int tdt;
+  int preds_is_label;
+  int cmp_gt;
+  int has_ignore;
+  int flag_counts_ignored;
+};
+
+__device__ __forceinline__ unsigned long long* hist_base(const TbArgs& a, int variant) {
+  return a.scratch + kHdr + (int64_t)variant * a.L * 2 * (a.T + 1);
+}
+
+// torch's CUDA sigmoid for fp32 opmath: 1 / (1 + exp(-x)), IEEE division, full-precision expf
+// (aten/src/ATen/native/cuda/UnarySpecialOpsKernel.cu; the reference calls it at
+// precision_recall_curve.py:184).  Narrow dtypes round the result back, like the reference tensor would.
+template <int DT>
+__device__ __forceinline__ float sigmoid_as(float x) {
+  float y = 1.0f / (1.0f + expf(-x));
+  if constexpr (DT == TMB_BF16) y = __bfloat162float(__float2bfloat16_rn(y));
+  if constexpr (DT == TMB_F16) y = __half2float(__float2half_rn(y));
+  return y;
+}
+
+// Number of thresholds j with thr[j] <= q (GE mode) or thr[j] < q (GT mode); thr ascending; NaN -> 0.
+struct Binner {
+  const float* thr;  // shared or global
+  int T;
+  float lo, scale;  // guess = (q - lo) * scale
+  bool gt;
+  __device__ __forceinline__ bool below(int j, float q) const { return gt ? (thr[j] < q) : (thr[j] <= q); }
+  __device__ __forceinline__ int bin(float q) const {
+    float gf = (q - lo) * scale;
+    gf = fminf(fmaxf(gf, -1.0f), (float)T);  // NaN -> -1
+    int g = (int)gf + 1;
+    g = g > T ? T : g;
+    bool ok_lo = (g == 0) || below(g - 1, q);
+    bool ok_hi = (g == T) || !below(g, q);
+    if (ok_lo && ok_hi) return g;
+    // one step of local repair catches the rounding cases of an evenly spaced grid
+    if (ok_lo) {
+      ++g;
+      if (g == T || !below(g, q)) return g;
+    } else {
+      --g;
+      if (g == 0 || below(g - 1, q)) return g;
+    }
+    int lo_i = 0, hi_i = T;  // upper/lower bound by bisection
+    while (lo_i < hi_i) {
+      int mid = (lo_i + hi_i) >> 1;
+      if (below(mid, q)) lo_i = mid + 1; else hi_i = mid;
+    }
+    return lo_i;
+  }
+};
+
+__device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_thr, int sh_cap) {
+  Binner b;
+  b.T = a.T;
+  b.gt = a.cmp_gt != 0;
+  if (a.T <= sh_cap) {
+    for (int i = threadIdx.x; i < a.T; i += blockDim.x) sh_thr[i] = a.thr[i];
+    __syncthreads();
+    b.thr = sh_thr;
+  } else {
+    b.thr = a.thr;
+  }
+  float lo = a.thr[0], hi = a.thr[a.T - 1];
+  float span = hi - lo;
+  b.lo = lo;
+  b.scale = (span > 0.0f && a.T > 1) ? (float)(a.T - 1) / span : 0.0f;
+  return b;
+}
+
+__device__ __forceinline__ bool flag_up(const TbArgs& a) {
+  return *((volatile unsigned long long*)a.scratch) != 0ULL;
+}
+__device__ __forceinline__ void raise_flag(const TbArgs& a) { *((volatile unsigned long long*)a.scratch) = 1ULL; }
+
+// CTA-uniform decision whether this pass has anything to do (the flag may flip while pass A runs, so
+// one thread samples it for everybody).
+__device__ __forceinline__ bool pass_enabled(const TbArgs& a, bool sig_pass) {
+  __shared__ int go;
+  if (threadIdx.x == 0) go = sig_pass ? flag_up(a) : !flag_up(a);
+  __syncthreads();
+  return go != 0;
+}
+
+// ---- binary fast path: lane-private packed histograms ------------------------------------------------
+template <int TDT>
+struct Tgt;
+template <>
+struct Tgt<TMB_I64> {
+  static constexpr int kBytes = 8;
+};
+template <>
+struct Tgt<TMB_I32> {
+  static constexpr int kBytes = 4;
+};
+template <>
+struct Tgt<TMB_U8> {
+  static constexpr int kBytes = 1;
+};
+template <>
+struct Tgt<TMB_I8> {
+  static constexpr int kBytes = 1;
+};
+
+// four consecutive targets starting at element i (i % 4 == 0, base pointer 16-byte aligned)
+template <int TDT>
+__device__ __forceinline__ void load_targets4(const void* base, int64_t i, int64_t t[4]) {
+  if constexpr (TDT == TMB_I64) {
+    uint4 a = ldg_stream16((const char*)base + i * 8);
+    uint4 b = ldg_stream16((const char*)base + i * 8 + 16);
+    t[0] = (int64_t)(((uint64_t)a.y << 32) | a.x);
+    t[1] = (int64_t)(((uint64_t)a.w << 32) | a.z);
+    t[2] = (int64_t)(((uint64_t)b.y << 32) | b.x);
+    t[3] = (int64_t)(((uint64_t)b.w << 32) | b.z);
+  } else if constexpr (TDT == TMB_I32) {
+    uint4 a = ldg_stream16((const char*)base + i * 4);
+    t[0] = (int)a.x; t[1] = (int)a.y; t[2] = (int)a.z; t[3] = (int)a.w;
+  } else {
+    uint32_t w = ldg_stream4((const char*)base + i);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      uint32_t b = (w >> (8 * e)) & 0xffu;
+      t[e] = (TDT == TMB_I8) ? (int64_t)(signed char)b : (int64_t)b;
+    }
+  }
+}
+
+template <int PDT>
+__device__ __forceinline__ void load_preds4(const void* base, int64_t i, float x[4]) {
+  if constexpr (PDT == TMB_F32) {
+    uint4 a = ldg_stream16((const char*)base + i * 4);
+    x[0] = __uint_as_float(a.x); x[1] = __uint_as_float(a.y);
+    x[2] = __uint_as_float(a.z); x[3] = __uint_as_float(a.w);
+  } else {
+    uint2 a = ldg_stream8((const char*)base + i * 2);
+    x[0] = Elem<PDT>::get(a.x, 0); x[1] = Elem<PDT>::get(a.x, 1);
+    x[2] = Elem<PDT>::get(a.y, 0); x[3] = Elem<PDT>::get(a.y, 1);
+  }
+}
+
+struct LaneHist {
+  uint32_t* col;  // this warp's [T+1][32] words
+  int lane;
+  unsigned seen;  // samples since the last flush (per lane)
+};
+
+__device__ __forceinline__ void lane_flush(const TbArgs& a, LaneHist& h, unsigned long long* gh) {
+  __syncwarp();
+  for (int k = 0; k <= a.T; ++k) {
+    uint32_t w = h.col[k * 32 + h.lane];
+    h.col[k * 32 + h.lane] = 0;
+    unsigned neg = __reduce_add_sync(kFull, w & 0xffffu);
+    unsigned pos = __reduce_add_sync(kFull, w >> 16);
+    if (h.lane == 0) {
+      if (neg) atomicAdd(&gh[k], (unsigned long long)neg);
+      if (pos) atomicAdd(&gh[(a.T + 1) + k], (unsigned long long)pos);
+    }
+  }
+  h.seen = 0;
+  __syncwarp();
+}
+
+// One sample into the lane-private histogram. Returns false when pass A must stop (outside value seen).
+template <int PDT, bool SIG>
+__device__ __forceinline__ bool lane_sample(const TbArgs& a, const Binner& bn, LaneHist& h, float x, int64_t t) {
+  bool ignored = a.has_ignore && t == a.ignore;
+  if (!SIG) {
+    bool outside = !(x >= 0.0f && x <= 1.0f);
+    if (outside && (!ignored || a.flag_counts_ignored)) return false;
+  }
+  if (ignored) return true;
+  if (t != 0 && t != 1) {
+    atomicOr(a.err, TMB_ERR_TARGET_BINARY);
+    return true;
+  }
+  float q = SIG ? sigmoid_as<PDT>(x) : x;
+  int k = bn.bin(q);
+  h.col[k * 32 + h.lane] += t ? 0x10000u : 1u;
+  h.seen += 1;
+  return true;
+}
+
+template <int PDT, int TDT, bool SIG>
+__global__ void __launch_bounds__(256) k2_binary_lanes(TbArgs a, int warps_per_cta) {
+  extern __shared__ uint32_t sh_u32[];
+  if (!pass_enabled(a, SIG)) return;
+
+  float* sh_thr = (float*)sh_u32;  // [T] thresholds, then the lane histograms
+  const int thr_words = (a.T + 31) / 32 * 32;
+  Binner bn = make_binner(a, sh_thr, 1 << 30);
+  const int warp_in_cta = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint32_t* cols = sh_u32 + thr_words;
+  LaneHist h{cols + (int64_t)warp_in_cta * (a.T + 1) * 32, lane, 0};
+  for (int k = 0; k <= a.T; ++k) h.col[k * 32 + lane] = 0;
+  __syncwarp();
+
+  unsigned long long* gh = hist_base(a, SIG ? 1 : 0);
+  const int64_t n = a.n_total;
+  const int64_t n_vec = n / 4;  // groups of 4 consecutive samples
+  const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  constexpr int U = 4;
+  bool stop = false;
+
+  // `b` is warp-uniform so that every lane reaches the warp-collective calls below
+  for (int64_t b = gtid - lane; b < n_vec && !stop; b += gthreads * U) {
+    const int64_t v0 = b + lane;
+    float x[U][4];
+    int64_t t[U][4];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t v = v0 + (int64_t)u * gthreads;
+      if (v < n_vec) {
+        load_preds4<PDT>(a.preds, v * 4, x[u]);
+        load_targets4<TDT>(a.target, v * 4, t[u]);
+      }
+    }
+    bool mine = false;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int64_t v = v0 + (int64_t)u * gthreads;
+      if (v < n_vec) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (!lane_sample<PDT, SIG>(a, bn, h, x[u][e], t[u][e])) mine = true;
+      }
+    }
+    if (!SIG) {
+      if (mine) raise_flag(a);
+      // poll the flag: once anybody saw a logit the raw histogram is moot
+      stop = __any_sync(kFull, mine || flag_up(a));
+    }
+    if (__any_sync(kFull, h.seen > 65535u - 4u * U)) lane_flush(a, h, gh);
+  }
+  // tail samples (n % 4) — handled by the first threads of CTA 0
+  bool tail_stop = false;
+  if (!stop && blockIdx.x == 0) {
+    int64_t i = n_vec * 4 + threadIdx.x;
+    if (i < n) {
+      float x = load_elem<PDT>(a.preds, i);
+      int64_t t = load_label(a.target, a.tdt, i);
+      if (!lane_sample<PDT, SIG>(a, bn, h, x, t)) {
+        tail_stop = true;
+        raise_flag(a);
+      }
+    }
+  }
+  if (!SIG && (stop || __any_sync(kFull, tail_stop))) return;  // finalize discards the raw histogram anyway
+  lane_flush(a, h, gh);
+}
+
+// ---- generic path: any L / S / T, atomics into shared (small) or global (large) histograms ------------
+template <int PDT, bool SIG, bool LABELS>
+__global__ void __launch_bounds__(256) k2_generic(TbArgs a, int sh_bins, int sh_thr_cap) {
+  extern __shared__ uint32_t sh_u32[];
+  if (!LABELS) {
+    if (!pass_enabled(a, SIG)) return;
+  }
+  float* sh_thr = (float*)sh_u32;
+  int* sh_hist = (int*)(sh_u32 + sh_thr_cap);
+  Binner bn{};
+  if (!LABELS) bn = make_binner(a, sh_thr, sh_thr_cap);
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) sh_hist[i] = 0;
+  __syncthreads();
+
+  unsigned long long* gh = hist_base(a, SIG ? 1 : 0);
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // label / inner position of element i0, then advanced incrementally (no per-element division)
+  int64_t s = i0 % a.S;
+  int l = (int)((i0 / a.S) % a.L);
+  const int64_t ds = stride % a.S;
+  const int dl = (int)((stride / a.S) % a.L);
+  const int kbins = a.T + 1;
+  bool stop = false;
+
+  for (int64_t i = i0; i < a.n_total; i += stride) {
+    int64_t t = load_label(a.target, a.tdt, i);
+    bool ignored = a.has_ignore && t == a.ignore;
+    int k = -1;
+    if (LABELS) {
+      int64_t p = load_label(a.preds, a.pdt, i);
+      if (!ignored) {
+        if (p != 0 && p != 1) atomicOr(a.err, TMB_ERR_PREDS_RANGE);
+        k = (p == 1) ? 1 : 0;
+        // reference semantics for stray labels (stat_scores.py:127-130): only p == target counts as a match
+        if (p != 0 && p != 1) k = (t == 1) ? 0 : 1;
+      }
+    } else {
+      float x = load_elem<PDT>(a.preds, i);
+      if (!SIG) {
+        bool outside = !(x >= 0.0f && x <= 1.0f);
+        if (outside && (!ignored || a.flag_counts_ignored)) {
+          raise_flag(a);
+          stop = true;
+        }
+      }
+      if (!ignored && !stop) k = bn.bin(SIG ? sigmoid_as<PDT>(x) : x);
+    }
+    if (!SIG && !LABELS) {
+      if (__any_sync(__activemask(), stop)) break;
+    }
+    if (k >= 0) {
+      if (t != 0 && t != 1) {
+        atomicOr(a.err, TMB_ERR_TARGET_BINARY);
+      } else {
+        int64_t bin = ((int64_t)l * 2 + t) * kbins + k;
+        if (sh_bins > 0)
+          atomicAdd(&sh_hist[bin], 1);
+        else
+          atomicAdd(&gh[bin], 1ULL);
+      }
+    }
+    // advance (l, s) by `stride` elements
+    s += ds;
+    int carry = s >= a.S;
+    s -= carry ? a.S : 0;
+    l += dl + carry;
+    if (l >= a.L) l -= a.L;
+    if (l >= a.L) l -= a.L;
+  }
+  if (!SIG && !LABELS) {
+    if (__syncthreads_or(stop) || flag_up(a)) return;
+  } else {
+    __syncthreads();
+  }
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
+    int v = sh_hist[i];
+    if (v) atomicAdd(&gh[i], (unsigned long long)v);
+  }
+}
+
+// ---- finalize -------------------------------------------------------------------------------------------
+// One warp per (label, target class).  The per-threshold counts are suffix sums of the bin histogram:
+// above(j) = #{samples with q >= thr[j]} = sum_{k > j} hist[k].  Lanes take 32 bins at a time from the
+// top, a shuffle scan forms the running suffix sum, and the counts are ADDED into the state.
+__global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, int64_t scratch_elems, int L, int T,
+                                                   const int* __restrict__ perm, int layout, long long* out0,
+                                                   long long* out1, long long* out2, long long* out3) {
+  const int variant = scratch[0] != 0ULL ? 1 : 0;
+  const int kbins = T + 1;
+  const unsigned long long* h = scratch + kHdr + (int64_t)variant * L * 2 * kbins;
+  const int lane = threadIdx.x & 31;
+  const int job = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (job >= L * 2) return;
+  const int l = job >> 1, t = job & 1;
+  const unsigned long long* hc = h + ((int64_t)l * 2 + t) * kbins;
+  if (layout == TMB_TB_CURVE) {
+    long long total = 0;
+    for (int k = lane; k <= T; k += 32) total += (long long)hc[k];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) total += __shfl_xor_sync(kFull, total, d);
+    long long carry = 0;  // sum of the bins above the current chunk
+    for (int top = T; top >= 1; top -= 32) {
+      const int k = top - lane;  // lane 0 owns the highest bin of the chunk
+      long long v = (k >= 1) ? (long long)hc[k] : 0;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        long long o = __shfl_up_sync(kFull, v, d);
+        if (lane >= d) v += o;
+      }
+      const long long above = carry + v;  // sum_{k' >= k} hist[k']  ==  count for threshold j = k - 1
+      if (k >= 1) {
+        const int j = k - 1;
+        const int row = perm ? perm[j] : j;
+        long long* cell = out0 + ((int64_t)row * L + l) * 4 + t * 2;  // [row][l][t][pred]
+        cell[1] += above;
+        cell[0] += total - above;
+      }
+      carry += __shfl_sync(kFull, v, 31);
+    }
+  } else if (lane == 0) {
+    if (layout == TMB_TB_CONFMAT) {
+      long long* cell = out0 + (int64_t)l * 4 + t * 2;
+      cell[0] += (long long)hc[0];
+      cell[1] += (long long)hc[1];
+    } else if (t == 1) {
+      out0[l] += (long long)hc[1];  // tp
+      out3[l] += (long long)hc[0];  // fn
+    } else {
+      out1[l] += (long long)hc[1];  // fp
+      out2[l] += (long long)hc[0];  // tn
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) k2_clear(unsigned long long* scratch, int64_t scratch_elems) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < scratch_elems;
+       i += (int64_t)gridDim.x * blockDim.x)
+    scratch[i] = 0ULL;
+}
+
+// ---- utilities ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_bincount(const void* __restrict__ x, int dt, int64_t n, int64_t length,
+                                                  unsigned long long* out, int* err) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t v = load_label(x, dt, i);
+    if (v < 0 || v >= length)
+      atomicOr(err, TMB_ERR_PREDS_RANGE);
+    else
+      atomicAdd(&out[v], 1ULL);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_label_max(const void* __restrict__ x, int dt, int64_t n, long long* out) {
+  long long m = LLONG_MIN;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    long long v = load_label(x, dt, i);
+    m = v > m ? v : m;
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    long long o = __shfl_xor_sync(kFull, m, d);
+    m = o > m ? o : m;
+  }
+  if ((threadIdx.x & 31) == 0) atomicMax(out, m);
+}
+
+__global__ void k_set_i64(long long* p, long long v) { *p = v; }
+
+// ---- host ------------------------------------------------------------------------------------------------
+static int64_t scratch_elems_for(int64_t L, int64_t T) { return kHdr + 2 * L * 2 * (T + 1); }
+
+template <int PDT, int TDT>
+static int launch_binary_lanes(const TbArgs& a, int warps, int smem, cudaStream_t st) {
+  int per_sm = (int)((int64_t)dev_info().max_smem_optin / (smem + 1024));
+  per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+  const int grid = dev_info().sm_count * per_sm;
+  auto ka = k2_binary_lanes<PDT, TDT, false>;
+  auto kb = k2_binary_lanes<PDT, TDT, true>;
+  cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  ka<<<grid, warps * 32, smem, st>>>(a, warps);
+  if (int rc = launch_status()) return rc;
+  kb<<<grid, warps * 32, smem, st>>>(a, warps);
+  return launch_status();
+}
+
+template <int PDT>
+static int launch_binary_lanes_t(const TbArgs& a, int warps, int smem, cudaStream_t st) {
+  switch (a.tdt) {
+    case TMB_I64: return launch_binary_lanes<PDT, TMB_I64>(a, warps, smem, st);
+    case TMB_I32: return launch_binary_lanes<PDT, TMB_I32>(a, warps, smem, st);
+    case TMB_U8: return launch_binary_lanes<PDT, TMB_U8>(a, warps, smem, st);
+    default: return launch_binary_lanes<PDT, TMB_I8>(a, warps, smem, st);
+  }
+}
+
+template <int PDT>
+static int launch_generic(const TbArgs& a, cudaStream_t st) {
+  const int64_t bins = (int64_t)a.L * 2 * (a.T + 1);
+  const int sh_bins = bins <= 8192 ? (int)bins : 0;
+  const int sh_thr_cap = a.T <= 4096 ? (a.T + 31) / 32 * 32 : 0;
+  const int smem = (sh_thr_cap + sh_bins) * 4;
+  const int block = 256;
+  const int grid = wave_grid((a.n_total + block - 1) / block, 8);
+  if (a.preds_is_label) {
+    // labels are never sigmoided: they go to histogram variant 0, the one finalize reads while the flag is down
+    k2_generic<TMB_F32, false, true><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+    return launch_status();
+  }
+  k2_generic<PDT, false, false><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+  if (int rc = launch_status()) return rc;
+  k2_generic<PDT, true, false><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+  return launch_status();
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" int64_t tmb_thresh_bin_scratch_elems(int64_t num_labels, int64_t num_thresholds) {
+  if (num_labels < 1 || num_thresholds < 1) return 0;
+  return scratch_elems_for(num_labels, num_thresholds);
+}
+
+extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int preds_is_label, const void* target,
+                                     int target_dtype, int64_t n_outer, int64_t num_labels, int64_t n_inner,
+                                     const float* thr, int64_t num_thresholds, int cmp_gt, int has_ignore,
+                                     int64_t ignore_index, int flag_counts_ignored, int64_t* scratch,
+                                     int64_t scratch_elems, int32_t* err, void* stream) {
+  if (label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (preds_is_label ? label_bytes(preds_dtype) == 0 : float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (n_outer < 0 || num_labels < 1 || n_inner < 1 || num_labels > (1 << 24)) return TMB_E_SHAPE;
+  if (num_thresholds < 1 || num_thresholds > (1 << 26)) return TMB_E_SHAPE;
+  if (!scratch || !err || !thr) return TMB_E_NULL;
+  if (scratch_elems < scratch_elems_for(num_labels, num_thresholds)) return TMB_E_SCRATCH;
+  const int64_t n_total = n_outer * num_labels * n_inner;
+  if (n_total == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+
+  TbArgs a;
+  a.preds = preds;
+  a.target = target;
+  a.thr = thr;
+  a.scratch = (unsigned long long*)scratch;
+  a.err = err;
+  a.n_total = n_total;
+  a.S = n_inner;
+  a.ignore = ignore_index;
+  a.L = (int)num_labels;
+  a.T = (int)num_thresholds;
+  a.pdt = preds_dtype;
+  a.tdt = target_dtype;
+  a.preds_is_label = preds_is_label;
+  a.cmp_gt = cmp_gt;
+  a.has_ignore = has_ignore;
+  a.flag_counts_ignored = flag_counts_ignored;
+
+  // binary fast path: lane-private histograms need (T+1)*128 B per warp plus the thresholds
+  const bool aligned = (((uintptr_t)preds | (uintptr_t)target) & 15) == 0;
+  const bool tdt_ok = target_dtype != TMB_I16;
+  if (num_labels == 1 && !preds_is_label && aligned && tdt_ok) {
+    const int thr_bytes = (a.T + 31) / 32 * 32 * 4;
+    const int64_t per_warp = (int64_t)(a.T + 1) * 128;
+    const int64_t avail = (int64_t)dev_info().max_smem_optin - thr_bytes - 1024;
+    int warps = (int)(avail / per_warp);
+    if (warps >= 1) {
+      if (warps > 8) warps = 8;
+      const int smem = thr_bytes + (int)(warps * per_warp);
+      switch (preds_dtype) {
+        case TMB_F32: return launch_binary_lanes_t<TMB_F32>(a, warps, smem, st);
+        case TMB_F16: return launch_binary_lanes_t<TMB_F16>(a, warps, smem, st);
+        default: return launch_binary_lanes_t<TMB_BF16>(a, warps, smem, st);
+      }
+    }
+  }
+  if (preds_is_label) return launch_generic<TMB_F32>(a, st);
+  switch (preds_dtype) {
+    case TMB_F32: return launch_generic<TMB_F32>(a, st);
+    case TMB_F16: return launch_generic<TMB_F16>(a, st);
+    default: return launch_generic<TMB_BF16>(a, st);
+  }
+}
+
+extern "C" int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, int64_t num_labels,
+                                       int64_t num_thresholds, const int32_t* perm, int layout, int64_t* out0,
+                                       int64_t* out1, int64_t* out2, int64_t* out3, void* stream) {
+  if (!scratch || !out0) return TMB_E_NULL;
+  if (layout != TMB_TB_CURVE && layout != TMB_TB_CONFMAT && layout != TMB_TB_STATS) return TMB_E_MODE;
+  if (layout != TMB_TB_CURVE && num_thresholds != 1) return TMB_E_SHAPE;
+  if (layout == TMB_TB_STATS && (!out1 || !out2 || !out3)) return TMB_E_NULL;
+  if (num_labels < 1 || num_thresholds < 1) return TMB_E_SHAPE;
+  if (scratch_elems < scratch_elems_for(num_labels, num_thresholds)) return TMB_E_SCRATCH;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t threads = num_labels * 2 * 32;
+  k2_finalize<<<(int)((threads + 255) / 256), 256, 0, st>>>((unsigned long long*)scratch, scratch_elems, (int)num_labels,
+                                                     (int)num_thresholds, perm, layout, (long long*)out0,
+                                                     (long long*)out1, (long long*)out2, (long long*)out3);
+  if (int rc = launch_status()) return rc;
+  const int64_t used = scratch_elems_for(num_labels, num_thresholds);
+  k2_clear<<<wave_grid((used + 255) / 256, 4), 256, 0, st>>>((unsigned long long*)scratch, used);
+  return launch_status();
+}
+
+extern "C" int tmb_bincount(const void* x, int x_dtype, int64_t n, int64_t length, int64_t* out, int32_t* err,
+                            void* stream) {
+  if (label_bytes(x_dtype) == 0) return TMB_E_DTYPE;
+  if (n < 0 || length < 0) return TMB_E_SHAPE;
+  if (n == 0) return 0;
+  if (!x || !out || !err) return TMB_E_NULL;
+  const int grid = wave_grid((n + 255) / 256, 8);
+  k_bincount<<<grid, 256, 0, (cudaStream_t)stream>>>(x, x_dtype, n, length, (unsigned long long*)out, err);
+  return launch_status();
+}
+
+extern "C" int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out_max, void* stream) {
+  if (label_bytes(x_dtype) == 0) return TMB_E_DTYPE;
+  if (n < 0) return TMB_E_SHAPE;
+  if (!out_max) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  k_set_i64<<<1, 1, 0, st>>>((long long*)out_max, LLONG_MIN);
+  if (int rc = launch_status()) return rc;
+  if (n == 0) return 0;
+  if (!x) return TMB_E_NULL;
+  k_label_max<<<wave_grid((n + 255) / 256, 8), 256, 0, st>>>(x, x_dtype, n, (long long*)out_max);
+  return launch_status();
+}

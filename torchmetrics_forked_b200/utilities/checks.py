@@ -1,0 +1,10 @@
+"""Input checks that do not touch tensor contents (reference: utilities/checks.py:39-44)."""
+from torch import Tensor
+
+
+def _check_same_shape(preds: Tensor, target: Tensor) -> None:
+    """Raise ``RuntimeError`` unless both tensors have the same shape."""
+    if preds.shape != target.shape:
+        raise RuntimeError(
+            f"Predictions and targets are expected to have the same shape, but got {preds.shape} and {target.shape}."
+        )

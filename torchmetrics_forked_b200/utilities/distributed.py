@@ -1,0 +1,129 @@
+"""State synchronisation across ranks.
+
+`gather_all_tensors` keeps the reference's contract (utilities/distributed.py:97-147: a list with one
+tensor per rank, uneven shapes allowed) and is what user supplied ``dist_sync_fn`` replacements look
+like.  The default path of ``Metric._sync_dist`` does not use it: sum states are packed into one flat
+buffer per dtype and reduced with ONE all-reduce, list ("cat") states are exchanged with ONE size
+all-gather plus ONE data all-gather per state — no barrier, no gather-then-sum.
+Works with the NCCL backend (CUDA tensors, NVLink/NVSwitch) and with gloo (CPU tests).
+"""
+from typing import Any, Dict, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F  # noqa: N812
+from torch import Tensor
+
+
+def _world(group: Optional[Any]) -> Any:
+    return dist.group.WORLD if group is None else group
+
+
+def gather_all_tensors(result: Tensor, group: Optional[Any] = None) -> List[Tensor]:
+    """All-gather one tensor from every rank; shapes may differ in any dimension (same ndim)."""
+    group = _world(group)
+    result = result.contiguous()
+    world = dist.get_world_size(group)
+    if result.ndim == 0:
+        out = [torch.zeros_like(result) for _ in range(world)]
+        dist.all_gather(out, result, group=group)
+        return out
+    shape = torch.tensor(result.shape, device=result.device, dtype=torch.int64)
+    shapes = [torch.zeros_like(shape) for _ in range(world)]
+    dist.all_gather(shapes, shape, group=group)
+    shapes_cpu = torch.stack(shapes).cpu()
+    biggest = shapes_cpu.max(dim=0).values
+    if bool((shapes_cpu == biggest).all()):
+        out = [torch.zeros_like(result) for _ in range(world)]
+        dist.all_gather(out, result, group=group)
+        return out
+    pad: List[int] = []
+    for have, want in zip(reversed(result.shape), reversed(biggest.tolist())):
+        pad.extend([0, int(want) - int(have)])
+    padded = F.pad(result, pad)
+    out = [torch.zeros_like(padded) for _ in range(world)]
+    dist.all_gather(out, padded, group=group)
+    return [o[tuple(slice(int(d)) for d in shp)] for o, shp in zip(out, shapes_cpu.tolist())]
+
+
+def packed_all_reduce_sum(tensors: Sequence[Tensor], group: Optional[Any] = None) -> List[Tensor]:
+    """Sum every tensor over all ranks with one all-reduce per dtype present.
+
+    The inputs are left untouched (``unsync`` must be able to restore them, metric.py:523-550); the
+    outputs are views into the reduced flat buffer.
+    """
+    group = _world(group)
+    out: List[Optional[Tensor]] = [None] * len(tensors)
+    by_dtype: Dict[Any, List[int]] = {}
+    for i, t in enumerate(tensors):
+        by_dtype.setdefault((t.dtype, t.device), []).append(i)
+    for idxs in by_dtype.values():
+        flat = torch.cat([tensors[i].reshape(-1) for i in idxs])
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        offset = 0
+        for i in idxs:
+            n = tensors[i].numel()
+            out[i] = flat[offset : offset + n].view(tensors[i].shape)
+            offset += n
+    return out  # type: ignore[return-value]
+
+
+_DTYPES = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int64, torch.int32, torch.int16,
+           torch.int8, torch.uint8, torch.bool]
+_MAX_TRAIL = 6
+
+
+def all_gather_cat(local: Optional[Tensor], device: torch.device, group: Optional[Any] = None) -> Optional[Tensor]:
+    """Rank-ordered concatenation along dim 0 of every rank's ``local`` (``None`` = this rank has no rows).
+
+    One small all-gather exchanges (rows, trailing shape, dtype); one all-gather moves the data. Returns
+    ``None`` when no rank has rows.  Trailing shapes must agree between the ranks that have data.
+    """
+    group = _world(group)
+    world = dist.get_world_size(group)
+    meta = torch.zeros(3 + _MAX_TRAIL, dtype=torch.int64)
+    if local is not None:
+        if local.ndim == 0:
+            local = local.unsqueeze(0)
+        local = local.contiguous()
+        trail = list(local.shape[1:])
+        if len(trail) > _MAX_TRAIL:
+            raise ValueError(f"list states with more than {_MAX_TRAIL + 1} dimensions are not supported")
+        meta[0] = local.shape[0]
+        meta[1] = _DTYPES.index(local.dtype)
+        meta[2] = len(trail)
+        for k, d in enumerate(trail):
+            meta[3 + k] = d
+    else:
+        meta[1] = -1
+    meta = meta.to(device)
+    metas = torch.empty(world * meta.numel(), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(metas, meta, group=group)
+    metas_cpu = metas.view(world, -1).cpu()
+    owners = [r for r in range(world) if int(metas_cpu[r, 1]) >= 0]
+    if not owners:
+        return None
+    ref = metas_cpu[owners[0]]
+    for r in owners[1:]:
+        if not torch.equal(metas_cpu[r, 1:], ref[1:]):
+            raise RuntimeError("list states must have the same dtype and trailing shape on every rank to be synced")
+    dtype = _DTYPES[int(ref[1])]
+    trail = [int(d) for d in ref[3 : 3 + int(ref[2])]]
+    rows = [int(metas_cpu[r, 0]) if r in owners else 0 for r in range(world)]
+    most = max(rows)
+    if local is None:
+        local = torch.empty((0, *trail), dtype=dtype, device=device)
+    if local.shape[0] < most:
+        send = torch.empty((most, *trail), dtype=dtype, device=device)
+        send[: local.shape[0]] = local
+    else:
+        send = local
+    wire = send.view(torch.uint8) if dtype == torch.bool else send
+    recv = torch.empty((world * most, *trail), dtype=wire.dtype, device=device)
+    dist.all_gather_into_tensor(recv, wire, group=group)
+    if dtype == torch.bool:
+        recv = recv.view(torch.bool)
+    if all(r == most for r in rows):
+        return recv
+    recv = recv.view(world, most, *trail)
+    return torch.cat([recv[r, : rows[r]] for r in range(world)], dim=0)
