@@ -1,0 +1,382 @@
+#!/usr/bin/env python
+"""bench.py — throughput of the classification-metric update path on B200 (driver contract).
+
+    python bench.py --gpus N --steps K --warmup W            # our CUDA path (one JSON line on stdout)
+    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (op-for-op port)
+    torchrun ... bench.py --gpus N ...                        # N > 1: one rank per GPU, NCCL
+
+Headline workload (BASELINE.json configs[1]): `MulticlassConfusionMatrix(1000)`, one `update` = bf16 logits
+[2^22, 1000] + int64 targets per GPU (8.42 GB, far larger than the 126 MB L2, so no flush is needed),
+samples independent -> sharded by sample, weak scaling, one `compute()` (packed all-reduce sync) closes the
+timed region.  `value` = samples/s over all GPUs with inputs resident in HBM; `e2e` = the same through the
+public Metric API from pinned host buffers (H2D inside the timed region, accuracy read back every step).
+`extras` carries the other BASELINE configs (3, 5, 1) measured the same way on rank 0 at N = 1.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+import torch
+
+ROOT = Path(__file__).resolve().parent
+for _p in (str(ROOT), str(ROOT / "oracle")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+C2_ROWS, C2_CLASSES = 1 << 22, 1000
+METRIC = "samples/s per update, MulticlassConfusionMatrix(C=1000), bf16 logits [2^22,1000] per GPU"
+
+
+# ------------------------------------------------------------------------------------------ helpers
+def measured_peak_gbs():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        try:
+            return float(json.loads(p.read_text())["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        except Exception:  # noqa: BLE001
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(kernel: str):
+    """DRAM bytes per launch from the committed `ncu --set full` summary, if one exists for this kernel."""
+    p = ROOT / "profiles" / "traffic.json"
+    if p.exists():
+        try:
+            return json.loads(p.read_text()).get(kernel)
+        except Exception:  # noqa: BLE001
+            return None
+    return None
+
+
+class ClockSampler:
+    """`nvidia-smi` clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:  # noqa: BLE001
+            self.proc = None
+        return self
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *exc):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:  # noqa: BLE001
+                self.proc.kill()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "", 1).isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "", 1).isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+def dist_setup(n_gpus: int):
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def max_over_ranks(x: float, world: int, device) -> float:
+    if world == 1:
+        return x
+    import torch.distributed as dist
+
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def barrier(world: int):
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def make_cfg2(rows: int, device, seed: int):
+    """Config 2 inputs: bf16 logits with +4 on the target column for 70 % of the rows (diagonal heavy)."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    target = torch.randint(C2_CLASSES, (rows,), generator=g, device=device)
+    preds = torch.empty(rows, C2_CLASSES, dtype=torch.bfloat16, device=device)
+    chunk = 1 << 18
+    for s in range(0, rows, chunk):
+        e = min(rows, s + chunk)
+        x = torch.randn(e - s, C2_CLASSES, generator=g, device=device)
+        hot = torch.rand(e - s, generator=g, device=device) < 0.7
+        x[hot, target[s:e][hot]] += 4
+        preds[s:e] = x.bfloat16()
+    return preds, target
+
+
+def timed_loop(fn, steps: int, warmup: int, world: int, device, tail=None):
+    """W untimed calls, then K timed calls between barrier+sync fences. Returns (total ms max-over-ranks,
+    mean per-call ms on this rank from per-step events)."""
+    for _ in range(warmup):
+        fn()
+    barrier(world)
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+    end = torch.cuda.Event(enable_timing=True)
+    ev[0].record()
+    for i in range(steps):
+        fn()
+        ev[i + 1].record()
+    if tail is not None:
+        tail()
+    end.record()
+    barrier(world)
+    total = ev[0].elapsed_time(end)
+    per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(steps)]
+    return max_over_ranks(total, world, device), sum(per_step) / len(per_step)
+
+
+# ------------------------------------------------------------------------------------------ CPU arms
+def cpu_confmat_rate(rows: int, steps: int, warmup: int, budget_s: float = 25.0):
+    """The reference's CPU update path (op-for-op ATen port) on a bounded sample of config 2."""
+    import torch_cpu as ref_port
+
+    g = torch.Generator().manual_seed(1234)
+    target = torch.randint(C2_CLASSES, (rows,), generator=g)
+    preds = torch.randn(rows, C2_CLASSES, generator=g)
+    hot = torch.rand(rows, generator=g) < 0.7
+    preds[hot, target[hot]] += 4
+    preds = preds.bfloat16()
+    state = torch.zeros(C2_CLASSES, C2_CLASSES, dtype=torch.long)
+    for _ in range(warmup):
+        state += ref_port.multiclass_confusion_matrix_update(preds, target, C2_CLASSES, validate_args=False)
+    t0 = time.perf_counter()
+    done = 0
+    for _ in range(steps):
+        state += ref_port.multiclass_confusion_matrix_update(preds, target, C2_CLASSES, validate_args=False)
+        done += 1
+        if time.perf_counter() - t0 > budget_s:
+            break
+    dt = time.perf_counter() - t0
+    return rows * done / dt, dt / done * 1e3, done
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    rows = args.cpu_rows
+    rate, ms, done = cpu_confmat_rate(rows, args.steps, max(args.warmup, 1), budget_s=120.0)
+    cores = torch.get_num_threads()
+    sample = f"{done} updates of bf16 logits [{rows},1000] + int64 targets (config 2 rows, bounded sample)"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": "samples/s", "n_gpus": args.gpus,
+        "steps": done, "warmup": max(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "cfg2: MulticlassConfusionMatrix(1000).update, validate_args=False", "rows_per_step": rows,
+                   "classes": C2_CLASSES, "note": "reference algorithm on host cores: op-for-op torch-CPU port "
+                   "(oracle/torch_cpu.py); the pure-Python reference itself cannot travel to the GPU box"},
+        "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------ extras (other configs)
+def extras_block(device, steps: int, warmup: int, peak: float):
+    """BASELINE configs 3, 5 and 1 on one GPU: same timing rules, reported beside the headline."""
+    import torchmetrics_forked_b200 as tm
+    from torchmetrics_forked_b200.classification import (
+        BinaryPrecisionRecallCurve,
+        MulticlassAccuracy,
+        MulticlassConfusionMatrix,
+        MulticlassJaccardIndex,
+    )
+
+    out = {}
+    g = torch.Generator(device=device).manual_seed(4321)
+
+    def record(name, fn, samples, algo_bytes, preds_bytes, launches):
+        _, ms = timed_loop(fn, steps, warmup, 1, device)
+        out[name] = {
+            "ms_per_update": ms, "samples_per_s": samples / ms * 1e3, "preds_gbs": preds_bytes / ms / 1e6,
+            "algo_gbs": algo_bytes / ms / 1e6, "roofline_frac": algo_bytes / ms / 1e6 / peak,
+            "launches_per_update": launches,
+        }
+
+    # config 3: BinaryPrecisionRecallCurve(thresholds=200), 2^28 fp32 logits
+    n3 = 1 << 28
+    logits = torch.randn(n3, generator=g, device=device) * 3
+    for tdt, tag, tb in ((torch.int64, "cfg3_int64_targets", 8), (torch.uint8, "cfg3_uint8_targets", 1)):
+        tgt = torch.randint(2, (n3,), generator=g, device=device).to(tdt)
+        m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(device)
+        record(tag, lambda m=m, tgt=tgt: m.update(logits, tgt), n3, n3 * (4 + tb), n3 * 4, 4)
+        del tgt, m
+    probs = torch.rand(n3, generator=g, device=device)
+    tgt = torch.randint(2, (n3,), generator=g, device=device)
+    m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(device)
+    record("cfg3_probs_int64_targets", lambda: m.update(probs, tgt), n3, n3 * 12, n3 * 4, 4)
+    del logits, probs, tgt, m
+    torch.cuda.empty_cache()
+
+    # config 5: MulticlassJaccardIndex(150), logits [16,150,512,512]
+    for dt, tag, eb in ((torch.float32, "cfg5_fp32", 4), (torch.bfloat16, "cfg5_bf16", 2)):
+        preds = torch.randn(16, 150, 512, 512, generator=g, device=device).to(dt)
+        tgt = torch.randint(150, (16, 512, 512), generator=g, device=device)
+        m = MulticlassJaccardIndex(150, validate_args=False).to(device)
+        px = 16 * 512 * 512
+        record(tag, lambda m=m, preds=preds, tgt=tgt: m.update(preds, tgt), px, px * (150 * eb + 8), px * 150 * eb, 1)
+        del preds, tgt, m
+    torch.cuda.empty_cache()
+
+    # config 1: MetricCollection([MulticlassAccuracy, MulticlassConfusionMatrix]), 100 000 fp32 probs (latency bound)
+    for C in (5, 10):
+        preds = torch.randn(100_000, C, generator=g, device=device).softmax(-1)
+        tgt = torch.randint(C, (100_000,), generator=g, device=device)
+        coll = tm.MetricCollection(
+            [MulticlassAccuracy(C, average="micro", validate_args=False), MulticlassConfusionMatrix(C, validate_args=False)]
+        ).to(device)
+        record(f"cfg1_C{C}_collection", lambda coll=coll, preds=preds, tgt=tgt: coll.update(preds, tgt), 100_000,
+               2 * 100_000 * (4 * C + 8), 2 * 100_000 * 4 * C, 3)
+    return out
+
+
+# ------------------------------------------------------------------------------------------ our arm
+def run_ours(args):
+    rank, world, local = dist_setup(args.gpus)
+    device = torch.device("cuda", local)
+    from torchmetrics_forked_b200.classification import MulticlassConfusionMatrix
+
+    rows = args.rows
+    preds, target = make_cfg2(rows, device, 1234 + rank)
+    metric = MulticlassConfusionMatrix(C2_CLASSES, validate_args=False).to(device)
+    peak, peak_src = measured_peak_gbs()
+
+    def step():
+        metric.update(preds, target)
+
+    result = {}
+
+    def tail():  # one compute() per epoch of updates: packed all-reduce of the 8 MB state when world > 1
+        result["confmat"] = metric.compute()
+
+    with ClockSampler(local) as clocks:
+        total_ms, kernel_ms = timed_loop(step, args.steps, args.warmup, world, device, tail=tail)
+    clk = clocks.summary()
+    samples = rows * world * args.steps
+    value = samples / total_ms * 1e3
+    algo_bytes = rows * (2 * C2_CLASSES + 8)
+    achieved = algo_bytes / kernel_ms / 1e6
+
+    # sanity: every sample of every update landed in the state exactly once
+    seen = int(result["confmat"].sum().item())
+    expect = rows * world * (args.steps + args.warmup)
+    assert seen == expect, f"confusion matrix holds {seen} samples, expected {expect}"
+
+    # end to end through the public API from pinned host memory
+    metric.reset()
+    e2e_steps = min(args.steps, 10)
+    h_preds = torch.empty(rows, C2_CLASSES, dtype=torch.bfloat16, pin_memory=True)
+    h_target = torch.empty(rows, dtype=torch.int64, pin_memory=True)
+    h_preds.copy_(preds)
+    h_target.copy_(target)
+    del preds, target
+    torch.cuda.empty_cache()
+
+    def e2e_step():
+        p = h_preds.to(device, non_blocking=True)
+        t = h_target.to(device, non_blocking=True)
+        metric.update(p, t)
+        cm = metric.confmat
+        return float((cm.diagonal().sum() / cm.sum()).item())  # running accuracy read back every step
+
+    e2e_ms, _ = timed_loop(e2e_step, e2e_steps, 1, world, device)
+    e2e_value = rows * world * e2e_steps / e2e_ms * 1e3
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": "cfg2: MulticlassConfusionMatrix(1000).update(bf16 logits, int64 targets), validate_args=False;"
+                   " one compute() (state sync) per timed region", "rows_per_gpu_per_step": rows, "classes": C2_CLASSES,
+                   "l2": "inputs (8.4 GB/update) larger than L2, no flush", "parallelism": f"samples sharded over {world} GPU(s)"},
+        "preds_gbs": rows * world * args.steps * 2 * C2_CLASSES / total_ms / 1e6,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": recorded_traffic("k1_rows_bf16"), "peak_source": peak_src,
+                     "kernel": "k1 rows (bf16, C=1000)", "kernel_ms": kernel_ms, "algorithmic_bytes": algo_bytes,
+                     "frac_of_nominal_8000": achieved / 8000.0},
+        "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": rows * (2 * C2_CLASSES + 8),
+                "d2h_bytes_per_step": 4, "steps": e2e_steps, "ms_per_step": e2e_ms / e2e_steps},
+        "gpu_launches": args.steps,
+        "clocks": clk,
+    }
+    del h_preds, h_target
+    if rank == 0 and world == 1:
+        rate, ms, done = cpu_confmat_rate(args.cpu_rows, 1000, 1, budget_s=args.cpu_budget)
+        line["cpu_baseline"] = {
+            "value": rate, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
+            "sample": f"{done} updates of bf16 logits [{args.cpu_rows},1000] (op-for-op torch-CPU port of the reference, "
+                      f"{ms:.1f} ms each)",
+        }
+        if not args.no_extras:
+            try:
+                line["extras"] = extras_block(device, max(3, min(args.steps, 10)), max(args.warmup, 3), peak)
+            except Exception as e:  # noqa: BLE001
+                line["extras"] = {"error": repr(e)}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--rows", type=int, default=C2_ROWS, help="rows per GPU per update (default: config 2)")
+    ap.add_argument("--cpu-rows", type=int, default=1 << 16, help="rows of the bounded CPU sample")
+    ap.add_argument("--cpu-budget", type=float, default=15.0)
+    ap.add_argument("--no-extras", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

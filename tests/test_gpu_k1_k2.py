@@ -1,0 +1,507 @@
+"""GPU parity: K1 (argmax + histogram) and K2 / K1b (threshold binning) against the oracle.
+
+Every test calls the CUDA path — either the raw C ABI through ctypes or the public functional / Metric API,
+which are thin wrappers over the same entry points — and compares with `oracle/hotpath.py` on the same
+inputs.  Integer states must match bit for bit; derived floats within 1e-6 relative.
+"""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+from conftest import golden_names, ignore_of, load_golden
+
+import hotpath as O
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-6, 1e-7  # tolerance for derived float metrics (north_star: 1e-6 relative)
+
+
+def _cuda(x, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(x))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def cuda_sigmoid(x: np.ndarray) -> np.ndarray:
+    """What the reference would execute on this device: torch's CUDA sigmoid kernel."""
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).cuda().sigmoid().cpu().numpy()
+
+
+@pytest.fixture(scope="module")
+def F():
+    import torchmetrics_forked_b200.functional as fn
+
+    return fn
+
+
+# ------------------------------------------------------------------------------------------ raw C ABI
+def test_cabi_mc_argmax_hist_raw_pointers():
+    from torchmetrics_forked_b200 import _native as nat
+
+    lib = nat.lib()
+    g = torch.Generator().manual_seed(1)
+    preds = torch.randn(1000, 12, generator=g)
+    target = torch.randint(12, (1000,), generator=g)
+    dp, dt = preds.cuda(), target.cuda()
+    out = torch.zeros(12, 12, dtype=torch.int64, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    rc = lib.tmb_mc_argmax_hist(
+        ctypes.c_void_p(dp.data_ptr()), 0, ctypes.c_void_p(dt.data_ptr()), 0, 1000, 12, 1, 0, 0, 0,
+        ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(err.data_ptr()),
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream),
+    )
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert int(err.item()) == 0
+    assert np.array_equal(out.cpu().numpy(), O.multiclass_confusion_matrix(preds.numpy(), target.numpy(), 12))
+    # accumulation is in place: a second call doubles the state
+    lib.tmb_mc_argmax_hist(
+        ctypes.c_void_p(dp.data_ptr()), 0, ctypes.c_void_p(dt.data_ptr()), 0, 1000, 12, 1, 0, 0, 0,
+        ctypes.c_void_p(out.data_ptr()), ctypes.c_void_p(err.data_ptr()),
+        ctypes.c_void_p(torch.cuda.current_stream().cuda_stream),
+    )
+    assert np.array_equal(out.cpu().numpy(), 2 * O.multiclass_confusion_matrix(preds.numpy(), target.numpy(), 12))
+    # argument errors come back as negative codes, nothing is launched
+    assert lib.tmb_mc_argmax_hist(None, 7, None, 0, 10, 12, 1, 0, 0, 0, None, None, None) == -1
+    assert lib.tmb_mc_argmax_hist(None, 0, None, 0, 10, 12, 1, 0, 0, 9, ctypes.c_void_p(out.data_ptr()),
+                                  ctypes.c_void_p(err.data_ptr()), None) == -4
+
+
+def test_cabi_thresh_bin_raw_pointers():
+    from torchmetrics_forked_b200 import _native as nat
+
+    lib = nat.lib()
+    g = torch.Generator().manual_seed(2)
+    n, T = 100_003, 200
+    preds = torch.rand(n, generator=g)
+    target = torch.randint(2, (n,), generator=g)
+    thr = torch.linspace(0, 1, T)
+    dp, dt, dthr = preds.cuda(), target.cuda(), thr.cuda()
+    elems = lib.tmb_thresh_bin_scratch_elems(1, T)
+    scratch = torch.zeros(elems, dtype=torch.int64, device="cuda")
+    state = torch.zeros(T, 2, 2, dtype=torch.int64, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = lib.tmb_thresh_bin_update(
+        ctypes.c_void_p(dp.data_ptr()), 0, 0, ctypes.c_void_p(dt.data_ptr()), 0, n, 1, 1,
+        ctypes.c_void_p(dthr.data_ptr()), T, 0, 0, 0, 0, ctypes.c_void_p(scratch.data_ptr()), elems,
+        ctypes.c_void_p(err.data_ptr()), st,
+    )
+    assert rc == 0
+    rc = lib.tmb_thresh_bin_finalize(
+        ctypes.c_void_p(scratch.data_ptr()), elems, 1, T, None, 0, ctypes.c_void_p(state.data_ptr()), None, None,
+        None, st,
+    )
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert np.array_equal(state.cpu().numpy(), O.binary_curve_binned(preds.numpy(), target.numpy(), thr.numpy()))
+    assert int(scratch.abs().sum().item()) == 0, "finalize must leave the scratch zeroed"
+    assert lib.tmb_thresh_bin_update(None, 0, 0, None, 0, 5, 1, 1, ctypes.c_void_p(dthr.data_ptr()), T, 0, 0, 0, 0,
+                                     ctypes.c_void_p(scratch.data_ptr()), 3, ctypes.c_void_p(err.data_ptr()),
+                                     st) == -5
+
+
+# ------------------------------------------------------------------------------------------ K1 on the golden fixtures
+@pytest.mark.parametrize("name", golden_names("mc_"))
+def test_multiclass_golden(name, F):
+    c = load_golden(name)
+    C, ign = int(c["num_classes"]), ignore_of(c)
+    is_bf16 = "bf16" in name
+    preds = _cuda(c["preds"], torch.bfloat16 if is_bf16 else None)
+    target = _cuda(c["target"])
+    got = F.multiclass_confusion_matrix(preds, target, C, ignore_index=ign)
+    assert np.array_equal(got.cpu().numpy(), c["confmat"])
+    for avg in ("micro", "macro", "none"):
+        assert np.array_equal(
+            F.multiclass_stat_scores(preds, target, C, average=avg, ignore_index=ign).cpu().numpy(), c[f"stat_{avg}"]
+        ) or avg == "macro"
+        np.testing.assert_allclose(
+            F.multiclass_stat_scores(preds, target, C, average=avg, ignore_index=ign).cpu().numpy(),
+            c[f"stat_{avg}"], rtol=RTOL, atol=ATOL,
+        )
+        np.testing.assert_allclose(
+            F.multiclass_accuracy(preds, target, C, average=avg, ignore_index=ign).cpu().numpy(), c[f"acc_{avg}"],
+            rtol=RTOL, atol=ATOL,
+        )
+        np.testing.assert_allclose(
+            F.multiclass_f1_score(preds, target, C, average=avg, ignore_index=ign).cpu().numpy(), c[f"f1_{avg}"],
+            rtol=RTOL, atol=ATOL,
+        )
+    for avg in ("micro", "macro", "weighted", "none"):
+        np.testing.assert_allclose(
+            F.multiclass_jaccard_index(preds, target, C, average=avg, ignore_index=ign).cpu().numpy(),
+            c[f"jaccard_{avg}"], rtol=RTOL, atol=ATOL,
+        )
+
+
+# ------------------------------------------------------------------------------------------ K1 layouts, dtypes, alignment
+@pytest.mark.parametrize(
+    ("n", "C", "dtype"),
+    [
+        (100_000, 5, torch.float32),  # config 1 shape: thread-per-row kernel
+        (100_000, 10, torch.float32),
+        (20_000, 63, torch.float16),
+        (8192, 1000, torch.bfloat16),  # config 2 row shape: warp-per-row, 16-byte vectors
+        (4096, 1000, torch.float32),
+        (3000, 150, torch.float32),  # 600-byte rows: 8-byte vectors
+        (3000, 37, torch.bfloat16),  # 74-byte rows: 2-byte granularity
+        (1500, 333, torch.float16),
+        (257, 4099, torch.bfloat16),  # rows longer than one register tile
+    ],
+)
+@pytest.mark.parametrize("tdtype", [torch.int64, torch.uint8, torch.int32])
+def test_multiclass_rows_random(n, C, dtype, tdtype, F):
+    if tdtype == torch.uint8 and C > 255:
+        pytest.skip("labels do not fit uint8")
+    g = torch.Generator().manual_seed(n + C)
+    preds = torch.randn(n, C, generator=g).to(dtype)
+    target = torch.randint(C, (n,), generator=g)
+    # diagonal-heavy like real classifiers, and a few ties / NaNs
+    hot = torch.rand(n, generator=g) < 0.7
+    preds[hot, target[hot]] += 4
+    preds[5, :] = 1.0
+    preds[6, C // 2] = float("nan")
+    want = O.multiclass_confusion_matrix(preds.float().numpy(), target.numpy(), C)
+    got = F.multiclass_confusion_matrix(preds.cuda(), target.to(tdtype).cuda(), C, validate_args=False)
+    assert np.array_equal(got.cpu().numpy(), want)
+    tp, fp, tn, fn = O.multiclass_stat_scores(preds.float().numpy(), target.numpy(), C, None)
+    got = F.multiclass_stat_scores(preds.cuda(), target.to(tdtype).cuda(), C, average=None, validate_args=False)
+    assert np.array_equal(got.cpu().numpy(), np.stack([tp, fp, tn, fn, tp + fn], -1))
+    tp, fp, tn, fn = O.multiclass_stat_scores(preds.float().numpy(), target.numpy(), C, "micro")
+    got = F.multiclass_stat_scores(preds.cuda(), target.to(tdtype).cuda(), C, average="micro", validate_args=False)
+    assert got.cpu().tolist() == [tp, fp, tn, fn, tp + fn]
+
+
+@pytest.mark.parametrize("offset", [1, 2, 3])
+def test_multiclass_rows_misaligned_base(offset, F):
+    """A sliced view shifts the base pointer off 16 bytes: the launcher must pick a narrower vector."""
+    g = torch.Generator().manual_seed(offset)
+    C = 100
+    big = torch.randn(2000 * C + 8, generator=g).cuda()
+    preds = big[offset : offset + 2000 * C].view(2000, C)
+    assert preds.data_ptr() % 16 != 0 and preds.is_contiguous()
+    target = torch.randint(C, (2000,), generator=g)
+    want = O.multiclass_confusion_matrix(preds.cpu().numpy(), target.numpy(), C)
+    assert np.array_equal(F.multiclass_confusion_matrix(preds, target.cuda(), C).cpu().numpy(), want)
+
+
+@pytest.mark.parametrize(
+    ("shape", "dtype"),
+    [
+        ((4, 150, 64, 64), torch.float32),  # config 5 layout, scaled
+        ((3, 150, 33, 31), torch.float32),  # odd plane size -> 4-byte vectors
+        ((2, 19, 128, 128), torch.bfloat16),
+        ((8, 5, 3), torch.float32),  # the reference tests' EXTRA_DIM shape
+        ((2, 21, 7, 5, 3), torch.float16),
+    ],
+)
+def test_multiclass_strided_random(shape, dtype, F):
+    g = torch.Generator().manual_seed(sum(shape))
+    C = shape[1]
+    preds = torch.randn(*shape, generator=g).to(dtype)
+    target = torch.randint(C, (shape[0], *shape[2:]), generator=g)
+    target.view(-1)[::17] = C - 1
+    want = O.multiclass_confusion_matrix(preds.float().numpy(), target.numpy(), C, ignore_index=C - 1)
+    got = F.multiclass_confusion_matrix(preds.cuda(), target.cuda(), C, ignore_index=C - 1)
+    assert np.array_equal(got.cpu().numpy(), want)
+    # non-contiguous input (channels-last style) is accepted and gives the same answer
+    perm = preds.cuda().movedim(1, -1).contiguous().movedim(-1, 1)
+    assert not perm.is_contiguous()
+    assert np.array_equal(F.multiclass_confusion_matrix(perm, target.cuda(), C, ignore_index=C - 1).cpu().numpy(), want)
+
+
+def test_multiclass_empty_and_errors(F):
+    empty = F.multiclass_confusion_matrix(torch.zeros(0, 4).cuda(), torch.zeros(0, dtype=torch.long).cuda(), 4)
+    assert empty.shape == (4, 4) and int(empty.sum()) == 0
+    preds = torch.randn(10, 4).cuda()
+    bad = torch.tensor([0, 1, 2, 3, 4, 0, 1, 2, 3, 7]).cuda()
+    with pytest.raises(RuntimeError):
+        F.multiclass_confusion_matrix(preds, bad, 4)
+    with pytest.raises(RuntimeError):
+        F.multiclass_confusion_matrix(torch.tensor([0, 9]).cuda(), torch.tensor([0, 1]).cuda(), 4)
+    with pytest.raises(RuntimeError, match="no CPU"):
+        F.multiclass_confusion_matrix(torch.randn(10, 4), torch.zeros(10, dtype=torch.long), 4)
+    with pytest.raises(ValueError):
+        F.multiclass_confusion_matrix(preds, torch.zeros(10, 2, dtype=torch.long).cuda(), 4)
+
+
+# ------------------------------------------------------------------------------------------ K1b
+@pytest.mark.parametrize("name", golden_names("bin_"))
+def test_binary_counts_golden(name, F):
+    c = load_golden(name)
+    ign, thr = ignore_of(c), float(c["threshold"])
+    preds, target = _cuda(c["preds"]), _cuda(c["target"])
+    want_stat = O.binary_stat_scores(c["preds"], c["target"], thr, ign, sigmoid_fn=cuda_sigmoid)
+    got = F.binary_stat_scores(preds, target, thr, ignore_index=ign).cpu().tolist()
+    assert got[:4] == list(want_stat)
+    want_cm = O.binary_confusion_matrix(c["preds"], c["target"], thr, ign, sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(F.binary_confusion_matrix(preds, target, thr, ignore_index=ign).cpu().numpy(), want_cm)
+    if "logits" not in name and "multidim" not in name:
+        # no sigmoid involved: the CPU reference's golden output is bit exact too
+        assert got == c["stat"].tolist()
+        assert np.array_equal(want_cm, c["confmat"])
+
+
+@pytest.mark.parametrize("name", golden_names("ml_"))
+def test_multilabel_counts_golden(name, F):
+    c = load_golden(name)
+    L, ign, thr = int(c["num_labels"]), ignore_of(c), float(c["threshold"])
+    preds, target = _cuda(c["preds"]), _cuda(c["target"])
+    tp, fp, tn, fn = O.multilabel_stat_scores(c["preds"], c["target"], L, thr, ign, sigmoid_fn=cuda_sigmoid)
+    got = F.multilabel_stat_scores(preds, target, L, thr, average=None, ignore_index=ign).cpu().numpy()
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn, tp + fn], -1))
+    want_cm = O.multilabel_confusion_matrix(c["preds"], c["target"], L, thr, ign, sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(F.multilabel_confusion_matrix(preds, target, L, thr, ignore_index=ign).cpu().numpy(), want_cm)
+    if "logits" not in name:
+        assert np.array_equal(got, c["stat_none"]) and np.array_equal(want_cm, c["confmat"])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("logits", [False, True])
+def test_binary_counts_random(dtype, logits, F):
+    g = torch.Generator().manual_seed(11)
+    n = 300_007
+    preds = (torch.randn(n, generator=g) * 3 if logits else torch.rand(n, generator=g)).to(dtype)
+    target = torch.randint(2, (n,), generator=g)
+    sig = lambda x: torch.from_numpy(x).to(dtype).cuda().sigmoid().float().cpu().numpy()  # noqa: E731
+    thr = 0.3
+    thr_eff = float(torch.tensor(thr, dtype=dtype))  # the reference compares in the dtype of preds
+    want = O.binary_stat_scores(preds.float().numpy(), target.numpy(), thr_eff, None, sigmoid_fn=sig)
+    got = F.binary_stat_scores(preds.cuda(), target.cuda(), thr).cpu().tolist()
+    assert got[:4] == list(want)
+
+
+def test_multilabel_counts_random_layouts(F):
+    g = torch.Generator().manual_seed(12)
+    for shape in [(5000, 100), (64, 7, 33), (12, 3, 16, 16)]:
+        L = shape[1]
+        preds = torch.randn(*shape, generator=g)
+        target = torch.randint(2, shape, generator=g)
+        target.view(-1)[::13] = -1
+        tp, fp, tn, fn = O.multilabel_stat_scores(preds.numpy(), target.numpy(), L, 0.5, -1, sigmoid_fn=cuda_sigmoid)
+        got = F.multilabel_stat_scores(preds.cuda(), target.cuda(), L, average=None, ignore_index=-1).cpu().numpy()
+        assert np.array_equal(got, np.stack([tp, fp, tn, fn, tp + fn], -1)), shape
+
+
+def test_binary_target_validation(F):
+    with pytest.raises(RuntimeError):
+        F.binary_stat_scores(torch.rand(100).cuda(), torch.full((100,), 3).cuda())
+
+
+# ------------------------------------------------------------------------------------------ K2 curves
+@pytest.mark.parametrize("name", golden_names("bcurve_"))
+def test_binary_curve_golden(name, F):
+    from torchmetrics_forked_b200.classification import BinaryAUROC, BinaryAveragePrecision, BinaryPrecisionRecallCurve
+
+    c = load_golden(name)
+    ign = ignore_of(c)
+    thresholds = torch.from_numpy(c["thresholds"])
+    want = O.binary_curve_binned(c["preds"], c["target"], c["thresholds"], ign, sigmoid_fn=cuda_sigmoid)
+    m = BinaryPrecisionRecallCurve(thresholds=thresholds, ignore_index=ign).cuda()
+    m.update(_cuda(c["preds"]), _cuda(c["target"]))
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+    if "logits" not in name and "nan" not in name:
+        assert np.array_equal(want, c["state"])  # no sigmoid: identical to the CPU reference run
+    else:
+        assert np.abs(want - c["state"]).sum() <= 8  # CPU-vs-CUDA sigmoid may move a boundary sample (H5)
+    for cls, key in ((BinaryAUROC, "auroc"), (BinaryAveragePrecision, "ap")):
+        mm = cls(thresholds=thresholds, ignore_index=ign).cuda()
+        mm.update(_cuda(c["preds"]), _cuda(c["target"]))
+        np.testing.assert_allclose(mm.compute().cpu().numpy(), c[key], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", golden_names("mlcurve_"))
+def test_multilabel_curve_golden(name, F):
+    from torchmetrics_forked_b200.classification import MultilabelAUROC, MultilabelPrecisionRecallCurve
+
+    c = load_golden(name)
+    L, ign = int(c["num_labels"]), ignore_of(c)
+    thresholds = torch.from_numpy(c["thresholds"])
+    want = O.multilabel_curve_binned(c["preds"], c["target"], L, c["thresholds"], ign, sigmoid_fn=cuda_sigmoid)
+    m = MultilabelPrecisionRecallCurve(L, thresholds=thresholds, ignore_index=ign).cuda()
+    m.update(_cuda(c["preds"]), _cuda(c["target"]))
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+    if "logits" not in name:
+        assert np.array_equal(want, c["state"])
+    for avg in ("micro", "macro", "none"):
+        mm = MultilabelAUROC(L, average=avg, thresholds=thresholds, ignore_index=ign).cuda()
+        mm.update(_cuda(c["preds"]), _cuda(c["target"]))
+        np.testing.assert_allclose(mm.compute().cpu().numpy(), c[f"auroc_{avg}"], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("tdtype", [torch.int64, torch.uint8, torch.int32, torch.int8, torch.bool, torch.int16])
+@pytest.mark.parametrize("pdtype", [torch.float32, torch.bfloat16])
+def test_binary_curve_random_dtypes(tdtype, pdtype, F):
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(21)
+    n, T = 1_000_003, 200
+    preds = (torch.randn(n, generator=g) * 3).to(pdtype)
+    target = torch.randint(2, (n,), generator=g)
+    m = BinaryPrecisionRecallCurve(thresholds=T, validate_args=False).cuda()
+    m.update(preds.cuda(), target.to(tdtype).cuda())
+    sig = lambda x: torch.from_numpy(x).to(pdtype).cuda().sigmoid().float().cpu().numpy()  # noqa: E731
+    thr = torch.linspace(0, 1, T)
+    if pdtype != torch.float32:
+        thr = thr.to(pdtype).float()  # above 50 000 samples the reference compares in the dtype of preds
+    want = O.binary_curve_binned(preds.float().numpy(), target.numpy(), thr.numpy(), None, sigmoid_fn=sig)
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+
+
+def test_binary_curve_probs_and_accumulation(F):
+    """Inputs already in [0,1] take the raw pass only; two updates accumulate; forward() returns batch values."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(22)
+    m = BinaryPrecisionRecallCurve(thresholds=64).cuda()
+    total = np.zeros((64, 2, 2), np.int64)
+    thr = np.linspace(0, 1, 64, dtype=np.float32)
+    assert np.array_equal(thr, torch.linspace(0, 1, 64).numpy())
+    for i in range(3):
+        preds = torch.rand(70_001 + i, generator=g)
+        target = torch.randint(2, (70_001 + i,), generator=g)
+        m.update(preds.cuda(), target.cuda())
+        total += O.binary_curve_binned(preds.numpy(), target.numpy(), thr)
+    assert np.array_equal(m.confmat.cpu().numpy(), total)
+
+
+def test_binary_curve_h1_single_outlier(F):
+    """One logit hidden in a batch of probabilities flips the whole batch to sigmoid (H1)."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(23)
+    n = 400_000
+    preds = torch.rand(n, generator=g)
+    preds[n - 7] = 1.5
+    target = torch.randint(2, (n,), generator=g)
+    m = BinaryPrecisionRecallCurve(thresholds=50).cuda()
+    m.update(preds.cuda(), target.cuda())
+    want = O.binary_curve_binned(preds.numpy(), target.numpy(), torch.linspace(0, 1, 50).numpy(), sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+    # ... unless that logit sits at an ignored position (H2, binary curves filter first)
+    target[n - 7] = -1
+    m = BinaryPrecisionRecallCurve(thresholds=50, ignore_index=-1).cuda()
+    m.update(preds.cuda(), target.cuda())
+    want = O.binary_curve_binned(preds.numpy(), target.numpy(), torch.linspace(0, 1, 50).numpy(), -1, sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("T", [2, 3, 1000, 5000])
+def test_binary_curve_threshold_counts(T, F):
+    """Few thresholds, and more thresholds than the lane-private histograms can hold (generic path)."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(T)
+    preds = torch.rand(200_000, generator=g)
+    target = torch.randint(2, (200_000,), generator=g)
+    thr = torch.sort(torch.rand(T, generator=g)).values
+    m = BinaryPrecisionRecallCurve(thresholds=thr).cuda()
+    m.update(preds.cuda(), target.cuda())
+    assert np.array_equal(m.confmat.cpu().numpy(), O.binary_curve_binned(preds.numpy(), target.numpy(), thr.numpy()))
+
+
+def test_multilabel_curve_random(F):
+    from torchmetrics_forked_b200.classification import MultilabelPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(31)
+    for shape, T in [((20_000, 100), 200), ((300, 5, 40), 33)]:
+        L = shape[1]
+        preds = torch.randn(*shape, generator=g)
+        target = torch.randint(2, shape, generator=g)
+        m = MultilabelPrecisionRecallCurve(L, thresholds=T).cuda()
+        m.update(preds.cuda(), target.cuda())
+        want = O.multilabel_curve_binned(preds.numpy(), target.numpy(), L, torch.linspace(0, 1, T).numpy(),
+                                         sigmoid_fn=cuda_sigmoid)
+        assert np.array_equal(m.confmat.cpu().numpy(), want), shape
+
+
+def test_sigmoid_bits_match_torch_cuda():
+    """SURVEY Appendix B probe 1: the kernels' sigmoid must be torch's CUDA sigmoid bit for bit — checked
+    through the binned state with one threshold per distinct sigmoid value of a dense logit sweep."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    x = torch.linspace(-12, 12, 2_000_001)
+    s = x.cuda().sigmoid()
+    thr = torch.unique(s)[::997].cpu()  # thresholds that ARE sigmoid outputs: any 1-ulp drift moves a count
+    target = torch.ones_like(x, dtype=torch.long)
+    m = BinaryPrecisionRecallCurve(thresholds=thr).cuda()
+    m.update(x.cuda(), target.cuda())
+    want = (s.unsqueeze(1) >= thr.cuda().unsqueeze(0)).sum(0).cpu().numpy()
+    assert np.array_equal(m.confmat[:, 1, 1].cpu().numpy(), want)
+
+
+# ------------------------------------------------------------------------------------------ Metric classes end to end
+def test_collection_config1_matches_oracle():
+    """BASELINE config 1: MetricCollection([MulticlassAccuracy, MulticlassConfusionMatrix]), 10 updates."""
+    import torchmetrics_forked_b200 as tm
+    from torchmetrics_forked_b200.classification import MulticlassAccuracy, MulticlassConfusionMatrix
+
+    for C in (5, 10):
+        g = torch.Generator().manual_seed(C)
+        coll = tm.MetricCollection([MulticlassAccuracy(C, average="micro"), MulticlassConfusionMatrix(C)]).cuda()
+        allp, allt = [], []
+        for _ in range(10):
+            preds = torch.randn(10_000, C, generator=g).softmax(-1)
+            target = torch.randint(C, (10_000,), generator=g)
+            coll.update(preds.cuda(), target.cuda())
+            allp.append(preds)
+            allt.append(target)
+        out = coll.compute()
+        P, T = torch.cat(allp).numpy(), torch.cat(allt).numpy()
+        assert np.array_equal(out["MulticlassConfusionMatrix"].cpu().numpy(), O.multiclass_confusion_matrix(P, T, C))
+        tp, fp, tn, fn = O.multiclass_stat_scores(P, T, C, "micro")
+        np.testing.assert_allclose(out["MulticlassAccuracy"].cpu().numpy(), O.accuracy_reduce(tp, fp, tn, fn, "micro"),
+                                   rtol=RTOL)
+        # forward returns the batch value and keeps accumulating
+        coll.reset()
+        batch = coll(allp[0].cuda(), allt[0].cuda())
+        assert np.array_equal(batch["MulticlassConfusionMatrix"].cpu().numpy(),
+                              O.multiclass_confusion_matrix(allp[0].numpy(), allt[0].numpy(), C))
+        coll(allp[1].cuda(), allt[1].cuda())
+        both = O.multiclass_confusion_matrix(torch.cat(allp[:2]).numpy(), torch.cat(allt[:2]).numpy(), C)
+        assert np.array_equal(coll.compute()["MulticlassConfusionMatrix"].cpu().numpy(), both)
+
+
+def test_compute_groups_share_state_in_place():
+    """H11: members of a compute group alias one state tensor, so the kernels must add in place."""
+    import torchmetrics_forked_b200 as tm
+    from torchmetrics_forked_b200.classification import MulticlassAccuracy, MulticlassF1Score
+
+    g = torch.Generator().manual_seed(3)
+    coll = tm.MetricCollection([MulticlassAccuracy(7), MulticlassF1Score(7)]).cuda()
+    P, T = [], []
+    for _ in range(3):
+        preds, target = torch.randn(5000, 7, generator=g), torch.randint(7, (5000,), generator=g)
+        coll.update(preds.cuda(), target.cuda())
+        P.append(preds)
+        T.append(target)
+    assert coll.compute_groups == {0: ["MulticlassAccuracy", "MulticlassF1Score"]}
+    out = coll.compute()
+    tp, fp, tn, fn = O.multiclass_stat_scores(torch.cat(P).numpy(), torch.cat(T).numpy(), 7, "macro")
+    np.testing.assert_allclose(out["MulticlassAccuracy"].cpu().numpy(), O.accuracy_reduce(tp, fp, tn, fn, "macro"), rtol=RTOL)
+    np.testing.assert_allclose(out["MulticlassF1Score"].cpu().numpy(), O.fbeta_reduce(tp, fp, tn, fn, 1.0, "macro"), rtol=RTOL)
+
+
+def test_deferred_data_error_surfaces_at_compute():
+    from torchmetrics_forked_b200.classification import MulticlassConfusionMatrix
+
+    m = MulticlassConfusionMatrix(4, validate_args=False).cuda()
+    m.update(torch.randn(10, 4).cuda(), torch.tensor([0, 1, 2, 3, 9, 0, 1, 2, 3, 0]).cuda())
+    with pytest.raises(RuntimeError, match="outside"):
+        m.compute()
+
+
+def test_jaccard_config5_scaled():
+    from torchmetrics_forked_b200.classification import MulticlassJaccardIndex
+
+    g = torch.Generator().manual_seed(5)
+    preds = torch.randn(2, 150, 96, 96, generator=g)
+    target = torch.randint(150, (2, 96, 96), generator=g)
+    m = MulticlassJaccardIndex(150).cuda()
+    m.update(preds.cuda(), target.cuda())
+    confmat = O.multiclass_confusion_matrix(preds.numpy(), target.numpy(), 150)
+    assert np.array_equal(m.confmat.cpu().numpy(), confmat)
+    np.testing.assert_allclose(m.compute().cpu().numpy(), O.jaccard_reduce(confmat, "macro"), rtol=RTOL)

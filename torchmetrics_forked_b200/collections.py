@@ -73,6 +73,10 @@ class MetricCollection(ModuleDict):
             for members in self._groups.values():
                 head = getattr(self, members[0])
                 head.update(*args, **head._filter_kwargs(**kwargs))
+                # the followers see the new state through the shared tensors, so their cached results are
+                # stale too (the 1.3.0dev reference keeps serving the old value here; deliberate deviation)
+                for name in members[1:]:
+                    getattr(self, name)._computed = None
             if self._state_is_copy:
                 # states were handed out as copies in between: link them again
                 self._compute_groups_create_state_ref()
