@@ -48,8 +48,9 @@ def test_host_only_queries(lib):
     assert lib.tmb_mc_scratch_bytes(1000, 0) == 0
     assert lib.tmb_mc_scratch_bytes(1000, 1) == 3 * 1000 * 8
     assert lib.tmb_mc_scratch_bytes(1000, 2) == 16
-    assert lib.tmb_thresh_bin_scratch_elems(1, 200) == 8 + 2 * 2 * 201
-    assert lib.tmb_thresh_bin_scratch_elems(100, 200) == 8 + 2 * 100 * 2 * 201
+    # header + two histogram variants + a padded float copy of the thresholds
+    assert lib.tmb_thresh_bin_scratch_elems(1, 200) == 8 + 2 * 2 * 201 + 101
+    assert lib.tmb_thresh_bin_scratch_elems(100, 200) == 8 + 2 * 100 * 2 * 201 + 101
     assert lib.tmb_thresh_bin_scratch_elems(0, 5) == 0
 
 

@@ -47,6 +47,18 @@ inline int wave_grid(int64_t work_ctas, int per_sm) {
   return (int)(work_ctas < cap ? work_ctas : cap);
 }
 
+// grid for a grid-stride kernel whose CTAs must all be co-resident to share the work evenly: whole
+// waves of exactly as many CTAs as the occupancy calculator says fit (registers / smem of THIS kernel)
+template <typename Kernel>
+inline int resident_grid(Kernel kernel, int block, size_t dyn_smem, int64_t work_ctas) {
+  int per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, dyn_smem) != cudaSuccess || per_sm < 1) {
+    cudaGetLastError();
+    per_sm = 1;
+  }
+  return wave_grid(work_ctas, per_sm);
+}
+
 inline int launch_status() {
   cudaError_t e = cudaGetLastError();
   return e == cudaSuccess ? 0 : (int)e;

@@ -173,6 +173,143 @@ __global__ void __launch_bounds__(256) k1_rows_warp(const char* __restrict__ pre
   hist_epilogue(h, sh, mi);
 }
 
+// ---- rows_pipe: warp per row, the whole row in registers, next row in flight -----------------------
+// The config-2 shape (2000-byte bf16 rows) fits one register tile: U vectors of 16 B per lane.  While a
+// row is reduced, the NEXT row's vectors and target are already in flight (software pipelining), so each
+// warp keeps 2 x 2 KB outstanding and the target load is off the critical path.
+//
+// 16-bit dtypes use a two-phase packed argmax that costs ~2 instructions per element instead of ~4:
+//   phase 1  row maximum with NaN-propagating packed max (HMNMX2.NAN) + warp shuffle reduce;
+//   phase 2  first position that equals the maximum (or the first NaN when the row has one), found with
+//            packed equality masks; lanes report their lowest matching index, the warp takes the minimum.
+// "first index equal to the maximum, a NaN counts as the maximum" is exactly torch.argmax's rule.
+template <int DT>
+struct Packed;
+template <>
+struct Packed<TMB_BF16> {
+  using V2 = __nv_bfloat162;
+  static constexpr uint32_t kNegInf2 = 0xff80ff80u;
+  __device__ static __forceinline__ V2 as_v2(uint32_t w) { return *reinterpret_cast<V2*>(&w); }
+  __device__ static __forceinline__ uint32_t as_u32(V2 v) { return *reinterpret_cast<uint32_t*>(&v); }
+  __device__ static __forceinline__ uint32_t max_nan(uint32_t a, uint32_t b) {
+    return as_u32(__hmax2_nan(as_v2(a), as_v2(b)));
+  }
+  __device__ static __forceinline__ uint32_t eq_mask(uint32_t a, uint32_t b) { return __heq2_mask(as_v2(a), as_v2(b)); }
+  __device__ static __forceinline__ uint32_t nan_mask(uint32_t a) { return __hneu2_mask(as_v2(a), as_v2(a)); }
+  __device__ static __forceinline__ uint32_t splat(float m) {
+    return as_u32(__float2bfloat162_rn(m));  // m is one of the row's values: the conversion is exact
+  }
+};
+template <>
+struct Packed<TMB_F16> {
+  using V2 = __half2;
+  static constexpr uint32_t kNegInf2 = 0xfc00fc00u;
+  __device__ static __forceinline__ V2 as_v2(uint32_t w) { return *reinterpret_cast<V2*>(&w); }
+  __device__ static __forceinline__ uint32_t as_u32(V2 v) { return *reinterpret_cast<uint32_t*>(&v); }
+  __device__ static __forceinline__ uint32_t max_nan(uint32_t a, uint32_t b) {
+    return as_u32(__hmax2_nan(as_v2(a), as_v2(b)));
+  }
+  __device__ static __forceinline__ uint32_t eq_mask(uint32_t a, uint32_t b) { return __heq2_mask(as_v2(a), as_v2(b)); }
+  __device__ static __forceinline__ uint32_t nan_mask(uint32_t a) { return __hneu2_mask(as_v2(a), as_v2(a)); }
+  __device__ static __forceinline__ uint32_t splat(float m) { return as_u32(__float2half2_rn(m)); }
+};
+
+// argmax of one row held as U 16-byte vectors per lane (vector u of lane L is vector u*32+L of the row)
+template <int DT, int U>
+__device__ __forceinline__ int row_argmax_packed16(const Vec<16> (&r)[U], int nvec, int lane) {
+  using P = Packed<DT>;
+  // phase 1: maximum
+  uint32_t m2 = P::kNegInf2;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (u * 32 + lane < nvec) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) m2 = P::max_nan(m2, r[u].w[j]);
+    }
+  }
+  float lo = Elem<DT>::get(m2, 0), hi = Elem<DT>::get(m2, 1);
+  const bool lane_nan = (lo != lo) || (hi != hi);
+  float m = fmaxf(lo, hi);  // NaN-free when it matters: rows with a NaN take the other branch below
+  const bool row_nan = __any_sync(kFull, lane_nan);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+  // phase 2: first matching position
+  const uint32_t M2 = P::splat(m);
+  int mine = 0x7fffffff;
+#pragma unroll
+  for (int u = U - 1; u >= 0; --u) {
+    const int vi = u * 32 + lane;
+    if (vi < nvec) {
+      uint32_t k[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) k[j] = row_nan ? P::nan_mask(r[u].w[j]) : P::eq_mask(r[u].w[j], M2);
+      if (k[0] | k[1] | k[2] | k[3]) {
+        int pos = 0;
+#pragma unroll
+        for (int j = 3; j >= 0; --j)
+          if (k[j]) pos = 2 * j + ((k[j] & 0xffffu) ? 0 : 1);
+        mine = vi * 8 + pos;  // u descends, so the lowest vector index wins
+      }
+    }
+  }
+  return __reduce_min_sync(kFull, mine);
+}
+
+template <int DT, int VB>
+__global__ void __launch_bounds__(256) k1_rows_pipe(const char* __restrict__ preds, const void* __restrict__ target,
+                                                    int target_dtype, int64_t n_rows, HistArgs h) {
+  extern __shared__ int sh[];
+  constexpr int ES = Elem<DT>::kBytes;
+  constexpr int EPV = VB / ES;
+  constexpr int U = 4;
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t row_bytes = (int64_t)h.C * ES;
+  const int nvec = (int)(row_bytes / VB);  // <= 32 * U, checked by the launcher
+
+  Vec<VB> cur[U], nxt[U];
+  int64_t t_cur = 0, t_nxt = 0;
+  auto issue = [&](int64_t row, Vec<VB>(&r)[U], int64_t& t) {
+    const char* rp = preds + row * row_bytes;
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      int vi = u * 32 + lane;
+      if (vi < nvec) r[u].load(rp + (int64_t)vi * VB);
+    }
+    t = load_label(target, target_dtype, row);  // same address in every lane: one broadcast transaction
+  };
+
+  int64_t row = warp;
+  if (row < n_rows) issue(row, cur, t_cur);
+  for (; row < n_rows; row += nwarps) {
+    const int64_t next = row + nwarps;
+    if (next < n_rows) issue(next, nxt, t_nxt);
+    int p;
+    if constexpr (ES == 2 && VB == 16) {
+      p = row_argmax_packed16<DT, U>(cur, nvec, lane);
+    } else {
+      Best b = best_init();
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int vi = u * 32 + lane;
+        if (vi < nvec) {
+#pragma unroll
+          for (int e = 0; e < EPV; ++e) best_step(b, vec_elem<DT, VB>(cur[u], e), vi * EPV + e);
+        }
+      }
+      p = best_index(best_warp(b));
+    }
+    if (lane == 0) count_sample(h, sh, mi, t_cur, p, false);
+#pragma unroll
+    for (int u = 0; u < U; ++u) cur[u] = nxt[u];
+    t_cur = t_nxt;
+  }
+  hist_epilogue(h, sh, mi);
+}
+
 // ---- rows_thread: one thread per row, rows staged through shared memory ---------------------------
 // Rows shorter than a few vectors cannot keep a warp busy, so a CTA copies TILE consecutive rows
 // (a contiguous byte range) into shared memory with full-width coalesced loads and each thread then
@@ -389,38 +526,54 @@ static int launch_rows(const void* preds, const void* target, int tdt, int64_t n
     const int vb = vec_bytes(preds, kTileRows * row_bytes, ES);
     const int tile_cap = (int)((kTileRows * row_bytes + 15) / 16 * 16);
     const int smem = tile_cap + hist_smem;
-    const int grid = wave_grid((n_rows + kTileRows - 1) / kTileRows, 8);
+    const int64_t tiles = (n_rows + kTileRows - 1) / kTileRows;
     const char* p = (const char*)preds;
+#define TMB_LAUNCH_THREAD(VB_)                                                                          \
+  {                                                                                                     \
+    auto k = k1_rows_thread<DT, VB_>;                                                                   \
+    k<<<resident_grid(k, kTileRows, smem, tiles), kTileRows, smem, st>>>(p, target, tdt, n_rows, h);    \
+  }
     switch (vb) {
-      case 16: k1_rows_thread<DT, 16><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
-      case 8: k1_rows_thread<DT, 8><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
-      case 4: k1_rows_thread<DT, 4><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h); break;
+      case 16: TMB_LAUNCH_THREAD(16) break;
+      case 8: TMB_LAUNCH_THREAD(8) break;
+      case 4: TMB_LAUNCH_THREAD(4) break;
       default:
         if constexpr (ES == 2) {
-          k1_rows_thread<DT, 2><<<grid, kTileRows, smem, st>>>(p, target, tdt, n_rows, h);
+          TMB_LAUNCH_THREAD(2)
           break;
         } else {
           return TMB_E_SHAPE;
         }
     }
+#undef TMB_LAUNCH_THREAD
     return launch_status();
   }
   const int vb = vec_bytes(preds, row_bytes, ES);
   const int block = 256;
-  const int grid = wave_grid((n_rows + 7) / 8, 8);
+  const int64_t ctas = (n_rows + 7) / 8;
   const char* p = (const char*)preds;
+  const bool one_tile = row_bytes / vb <= 128;  // the row fits U = 4 vectors per lane: pipelined kernel
+#define TMB_LAUNCH_ROWS(VB_)                                                                              \
+  if (one_tile) {                                                                                         \
+    auto k = k1_rows_pipe<DT, VB_>;                                                                       \
+    k<<<resident_grid(k, block, hist_smem, ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h);     \
+  } else {                                                                                                \
+    auto k = k1_rows_warp<DT, VB_>;                                                                       \
+    k<<<resident_grid(k, block, hist_smem, ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h);     \
+  }
   switch (vb) {
-    case 16: k1_rows_warp<DT, 16><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
-    case 8: k1_rows_warp<DT, 8><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
-    case 4: k1_rows_warp<DT, 4><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h); break;
+    case 16: TMB_LAUNCH_ROWS(16) break;
+    case 8: TMB_LAUNCH_ROWS(8) break;
+    case 4: TMB_LAUNCH_ROWS(4) break;
     default:
       if constexpr (ES == 2) {
-        k1_rows_warp<DT, 2><<<grid, block, hist_smem, st>>>(p, target, tdt, n_rows, h);
+        TMB_LAUNCH_ROWS(2)
         break;
       } else {
         return TMB_E_SHAPE;
       }
   }
+#undef TMB_LAUNCH_ROWS
   return launch_status();
 }
 
@@ -432,20 +585,26 @@ static int launch_strided(const void* preds, const void* target, int tdt, int64_
   const int vb = vec_bytes(preds, S * ES, ES);
   const int64_t groups = n_outer * (S / (vb / ES));
   const int block = 256;
-  const int grid = wave_grid((groups + block - 1) / block, 8);
+  const int64_t ctas = (groups + block - 1) / block;
   const char* p = (const char*)preds;
+#define TMB_LAUNCH_STRIDED(VB_)                                                                            \
+  {                                                                                                        \
+    auto k = k1_strided<DT, VB_>;                                                                          \
+    k<<<resident_grid(k, block, hist_smem, ctas), block, hist_smem, st>>>(p, target, tdt, n_outer, S, h);  \
+  }
   switch (vb) {
-    case 16: k1_strided<DT, 16><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
-    case 8: k1_strided<DT, 8><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
-    case 4: k1_strided<DT, 4><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h); break;
+    case 16: TMB_LAUNCH_STRIDED(16) break;
+    case 8: TMB_LAUNCH_STRIDED(8) break;
+    case 4: TMB_LAUNCH_STRIDED(4) break;
     default:
       if constexpr (ES == 2) {
-        k1_strided<DT, 2><<<grid, block, hist_smem, st>>>(p, target, tdt, n_outer, S, h);
+        TMB_LAUNCH_STRIDED(2)
         break;
       } else {
         return TMB_E_SHAPE;
       }
   }
+#undef TMB_LAUNCH_STRIDED
   return launch_status();
 }
 

@@ -3,7 +3,7 @@
 // The reference evaluates `preds >= thresholds[i]` once per threshold (200 full passes and ~1800
 // launches at T = 200, functional/classification/precision_recall_curve.py:228-250) or materialises an
 // N x T comparison (:210-225, :785-793).  Here every sample is read once: its bin index
-// k = #{j : thr[j] <= q} is found with a uniform-grid guess corrected by exact compares against the
+// k = #{j : thr[j] <= q} is found with a uniform-grid guess verified by exact compares against the
 // metric's own threshold buffer (never a recomputed linspace, H4), and hist[label][target][k] is bumped.
 // The per-threshold counts are suffix sums of that histogram, formed by a tiny finalize kernel.
 //
@@ -16,7 +16,10 @@
 // (B300_MICROARCH: ATOMS ~2 clk/lane), an order of magnitude under the HBM rate.  Instead every LANE owns
 // a private histogram column (word k*32+lane -> its own bank, plain LDS/IADD/STS, no conflicts, no
 // atomics) with the positive and negative counts packed as 16+16 bits; columns are summed by warp
-// reduction when a lane has seen 65535 samples and at exit.
+// reduction when a lane has seen 65535 samples and at exit.  With 8 warps per SM the kernel lives on
+// instruction-level parallelism: each thread keeps 16 samples in registers, computes their 16 bin indices
+// in straight-line code (no data-dependent branch on the common path), and only then does the 16
+// read-modify-writes; the next 16 samples are already in flight while it does so.
 #include "common.cuh"
 
 namespace tmb {
@@ -58,47 +61,50 @@ __device__ __forceinline__ float sigmoid_as(float x) {
 }
 
 // Number of thresholds j with thr[j] <= q (GE mode) or thr[j] < q (GT mode); thr ascending; NaN -> 0.
+// `pad` is the threshold array with sentinels: pad[0] = -inf, pad[1 + j] = thr[j], pad[T + 1] = +inf, so
+// "k is the right bin" reads  pad[k] <= q  and not  pad[k + 1] <= q  without any index special-casing.
 struct Binner {
-  const float* thr;  // shared or global
+  const float* pad;  // shared or global, T + 2 entries
   int T;
   float lo, scale;  // guess = (q - lo) * scale
   bool gt;
-  __device__ __forceinline__ bool below(int j, float q) const { return gt ? (thr[j] < q) : (thr[j] <= q); }
-  __device__ __forceinline__ int bin(float q) const {
+  __device__ __forceinline__ bool below(float t, float q) const { return gt ? (t < q) : (t <= q); }
+  __device__ __forceinline__ int guess(float q) const {
     float gf = (q - lo) * scale;
     gf = fminf(fmaxf(gf, -1.0f), (float)T);  // NaN -> -1
     int g = (int)gf + 1;
-    g = g > T ? T : g;
-    bool ok_lo = (g == 0) || below(g - 1, q);
-    bool ok_hi = (g == T) || !below(g, q);
-    if (ok_lo && ok_hi) return g;
-    // one step of local repair catches the rounding cases of an evenly spaced grid
-    if (ok_lo) {
-      ++g;
-      if (g == T || !below(g, q)) return g;
-    } else {
-      --g;
-      if (g == 0 || below(g - 1, q)) return g;
-    }
-    int lo_i = 0, hi_i = T;  // upper/lower bound by bisection
+    return g > T ? T : g;
+  }
+  __device__ __forceinline__ bool verified(int g, float q) const {
+    return (below(pad[g], q) && !below(pad[g + 1], q)) || (q != q && g == 0);
+  }
+  __device__ __noinline__ int bisect(float q) const {  // cold path: guess was off
+    int lo_i = 0, hi_i = T;
     while (lo_i < hi_i) {
       int mid = (lo_i + hi_i) >> 1;
-      if (below(mid, q)) lo_i = mid + 1; else hi_i = mid;
+      if (below(pad[mid + 1], q)) lo_i = mid + 1; else hi_i = mid;
     }
     return lo_i;
   }
+  __device__ __forceinline__ int bin(float q) const {
+    int g = guess(q);
+    return verified(g, q) ? g : bisect(q);
+  }
 };
 
-__device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_thr, int sh_cap) {
+// `sh_pad` must hold T + 2 floats when T + 2 <= sh_cap; otherwise the padded copy in the scratch tail is
+// not available and the caller passes a global padded array instead.
+__device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_pad, int sh_cap, const float* global_pad) {
   Binner b;
   b.T = a.T;
   b.gt = a.cmp_gt != 0;
-  if (a.T <= sh_cap) {
-    for (int i = threadIdx.x; i < a.T; i += blockDim.x) sh_thr[i] = a.thr[i];
+  if (a.T + 2 <= sh_cap) {
+    for (int i = threadIdx.x; i < a.T + 2; i += blockDim.x)
+      sh_pad[i] = (i == 0) ? -INFINITY : (i == a.T + 1 ? INFINITY : a.thr[i - 1]);
     __syncthreads();
-    b.thr = sh_thr;
+    b.pad = sh_pad;
   } else {
-    b.thr = a.thr;
+    b.pad = global_pad;
   }
   float lo = a.thr[0], hi = a.thr[a.T - 1];
   float span = hi - lo;
@@ -122,25 +128,6 @@ __device__ __forceinline__ bool pass_enabled(const TbArgs& a, bool sig_pass) {
 }
 
 // ---- binary fast path: lane-private packed histograms ------------------------------------------------
-template <int TDT>
-struct Tgt;
-template <>
-struct Tgt<TMB_I64> {
-  static constexpr int kBytes = 8;
-};
-template <>
-struct Tgt<TMB_I32> {
-  static constexpr int kBytes = 4;
-};
-template <>
-struct Tgt<TMB_U8> {
-  static constexpr int kBytes = 1;
-};
-template <>
-struct Tgt<TMB_I8> {
-  static constexpr int kBytes = 1;
-};
-
 // four consecutive targets starting at element i (i % 4 == 0, base pointer 16-byte aligned)
 template <int TDT>
 __device__ __forceinline__ void load_targets4(const void* base, int64_t i, int64_t t[4]) {
@@ -199,37 +186,59 @@ __device__ __forceinline__ void lane_flush(const TbArgs& a, LaneHist& h, unsigne
   __syncwarp();
 }
 
-// One sample into the lane-private histogram. Returns false when pass A must stop (outside value seen).
+constexpr int kBatch = 4;             // vectors of 4 samples per thread per iteration
+constexpr int kPer = kBatch * 4;      // samples per thread per iteration
+
+// Classify and bin kPer samples held in registers.  Returns true if pass A saw a value outside [0,1].
 template <int PDT, bool SIG>
-__device__ __forceinline__ bool lane_sample(const TbArgs& a, const Binner& bn, LaneHist& h, float x, int64_t t) {
-  bool ignored = a.has_ignore && t == a.ignore;
-  if (!SIG) {
-    bool outside = !(x >= 0.0f && x <= 1.0f);
-    if (outside && (!ignored || a.flag_counts_ignored)) return false;
+__device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, LaneHist& h, const float (&x)[kPer],
+                                           const int64_t (&t)[kPer], unsigned live, bool& bad_target) {
+  int k[kPer];
+  uint32_t inc[kPer];
+  unsigned recheck = 0;
+  bool outside_any = false;
+  // phase 1: straight-line, 16 independent dependency chains for the scheduler to interleave
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
+    const bool is_live = (live >> i) & 1u;
+    const bool ignored = a.has_ignore && t[i] == a.ignore;
+    const bool is_one = t[i] == 1, is_zero = t[i] == 0;
+    const bool counted = is_live && !ignored && (is_one || is_zero);
+    bad_target |= is_live && !ignored && !(is_one || is_zero);
+    if (!SIG) {
+      const bool outside = !(x[i] >= 0.0f && x[i] <= 1.0f);
+      outside_any |= is_live && outside && (!ignored || a.flag_counts_ignored);
+    }
+    const float q = SIG ? sigmoid_as<PDT>(x[i]) : x[i];
+    const int g = bn.guess(q);
+    k[i] = g;
+    if (!bn.verified(g, q)) recheck |= counted ? (1u << i) : 0u;
+    inc[i] = counted ? (is_one ? 0x10000u : 1u) : 0u;
+    h.seen += counted ? 1u : 0u;
   }
-  if (ignored) return true;
-  if (t != 0 && t != 1) {
-    atomicOr(a.err, TMB_ERR_TARGET_BINARY);
-    return true;
+  // cold path: a guess that failed verification (non-uniform thresholds, rounding at a grid point)
+  if (recheck) {
+#pragma unroll
+    for (int i = 0; i < kPer; ++i)
+      if ((recheck >> i) & 1u) k[i] = bn.bisect(SIG ? sigmoid_as<PDT>(x[i]) : x[i]);
   }
-  float q = SIG ? sigmoid_as<PDT>(x) : x;
-  int k = bn.bin(q);
-  h.col[k * 32 + h.lane] += t ? 0x10000u : 1u;
-  h.seen += 1;
-  return true;
+  // phase 2: the read-modify-writes (a lane only ever touches its own bank, so no atomics)
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) h.col[k[i] * 32 + h.lane] += inc[i];
+  return outside_any;
 }
 
 template <int PDT, int TDT, bool SIG>
-__global__ void __launch_bounds__(256) k2_binary_lanes(TbArgs a, int warps_per_cta) {
+__global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_per_cta) {
   extern __shared__ uint32_t sh_u32[];
   if (!pass_enabled(a, SIG)) return;
 
-  float* sh_thr = (float*)sh_u32;  // [T] thresholds, then the lane histograms
-  const int thr_words = (a.T + 31) / 32 * 32;
-  Binner bn = make_binner(a, sh_thr, 1 << 30);
+  float* sh_pad = (float*)sh_u32;  // [T + 2] padded thresholds, then the lane histograms
+  const int pad_words = (a.T + 2 + 31) / 32 * 32;
+  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);
   const int warp_in_cta = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  uint32_t* cols = sh_u32 + thr_words;
+  uint32_t* cols = sh_u32 + pad_words;
   LaneHist h{cols + (int64_t)warp_in_cta * (a.T + 1) * 32, lane, 0};
   for (int k = 0; k <= a.T; ++k) h.col[k * 32 + lane] = 0;
   __syncwarp();
@@ -239,38 +248,51 @@ __global__ void __launch_bounds__(256) k2_binary_lanes(TbArgs a, int warps_per_c
   const int64_t n_vec = n / 4;  // groups of 4 consecutive samples
   const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
   const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  constexpr int U = 4;
-  bool stop = false;
+  const int64_t step = gthreads * kBatch;
+  bool stop = false, bad_target = false;
 
-  // `b` is warp-uniform so that every lane reaches the warp-collective calls below
-  for (int64_t b = gtid - lane; b < n_vec && !stop; b += gthreads * U) {
-    const int64_t v0 = b + lane;
-    float x[U][4];
-    int64_t t[U][4];
+  float xa[kPer], xb[kPer];
+  int64_t ta[kPer], tb[kPer];
+  auto fetch = [&](int64_t b, float (&x)[kPer], int64_t (&t)[kPer]) -> unsigned {
+    unsigned live = 0;
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      int64_t v = v0 + (int64_t)u * gthreads;
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = b + lane + (int64_t)u * gthreads;
       if (v < n_vec) {
-        load_preds4<PDT>(a.preds, v * 4, x[u]);
-        load_targets4<TDT>(a.target, v * 4, t[u]);
+        load_preds4<PDT>(a.preds, v * 4, *reinterpret_cast<float(*)[4]>(&x[u * 4]));
+        load_targets4<TDT>(a.target, v * 4, *reinterpret_cast<int64_t(*)[4]>(&t[u * 4]));
+        live |= 0xfu << (u * 4);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          x[u * 4 + e] = 0.0f;
+          t[u * 4 + e] = 0;
+        }
       }
     }
-    bool mine = false;
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      int64_t v = v0 + (int64_t)u * gthreads;
-      if (v < n_vec) {
-#pragma unroll
-        for (int e = 0; e < 4; ++e)
-          if (!lane_sample<PDT, SIG>(a, bn, h, x[u][e], t[u][e])) mine = true;
-      }
-    }
+    return live;
+  };
+
+  // `b` is warp-uniform so that every lane reaches the warp-collective calls below; the batch after the
+  // current one is fetched before the current one is processed (software pipelining)
+  int64_t b = gtid - lane;
+  unsigned live_a = (b < n_vec) ? fetch(b, xa, ta) : 0u;
+  while (b < n_vec && !stop) {
+    const int64_t b_next = b + step;
+    unsigned live_b = (b_next < n_vec) ? fetch(b_next, xb, tb) : 0u;
+    bool mine = lane_batch<PDT, SIG>(a, bn, h, xa, ta, live_a, bad_target);
     if (!SIG) {
       if (mine) raise_flag(a);
-      // poll the flag: once anybody saw a logit the raw histogram is moot
-      stop = __any_sync(kFull, mine || flag_up(a));
+      stop = __any_sync(kFull, mine || flag_up(a));  // once anybody saw a logit the raw histogram is moot
     }
-    if (__any_sync(kFull, h.seen > 65535u - 4u * U)) lane_flush(a, h, gh);
+    if (__any_sync(kFull, h.seen > 65535u - (unsigned)kPer)) lane_flush(a, h, gh);
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+      xa[i] = xb[i];
+      ta[i] = tb[i];
+    }
+    live_a = live_b;
+    b = b_next;
   }
   // tail samples (n % 4) — handled by the first threads of CTA 0
   bool tail_stop = false;
@@ -279,27 +301,37 @@ __global__ void __launch_bounds__(256) k2_binary_lanes(TbArgs a, int warps_per_c
     if (i < n) {
       float x = load_elem<PDT>(a.preds, i);
       int64_t t = load_label(a.target, a.tdt, i);
-      if (!lane_sample<PDT, SIG>(a, bn, h, x, t)) {
+      const bool ignored = a.has_ignore && t == a.ignore;
+      if (!SIG && !(x >= 0.0f && x <= 1.0f) && (!ignored || a.flag_counts_ignored)) {
         tail_stop = true;
         raise_flag(a);
       }
+      if (!ignored) {
+        if (t != 0 && t != 1) {
+          bad_target = true;
+        } else {
+          int k = bn.bin(SIG ? sigmoid_as<PDT>(x) : x);
+          h.col[k * 32 + lane] += t ? 0x10000u : 1u;
+        }
+      }
     }
   }
+  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_BINARY);
   if (!SIG && (stop || __any_sync(kFull, tail_stop))) return;  // finalize discards the raw histogram anyway
   lane_flush(a, h, gh);
 }
 
 // ---- generic path: any L / S / T, atomics into shared (small) or global (large) histograms ------------
 template <int PDT, bool SIG, bool LABELS>
-__global__ void __launch_bounds__(256) k2_generic(TbArgs a, int sh_bins, int sh_thr_cap) {
+__global__ void __launch_bounds__(256) k2_generic(TbArgs a, int sh_bins, int sh_pad_cap, const float* global_pad) {
   extern __shared__ uint32_t sh_u32[];
   if (!LABELS) {
     if (!pass_enabled(a, SIG)) return;
   }
-  float* sh_thr = (float*)sh_u32;
-  int* sh_hist = (int*)(sh_u32 + sh_thr_cap);
+  float* sh_pad = (float*)sh_u32;
+  int* sh_hist = (int*)(sh_u32 + sh_pad_cap);
   Binner bn{};
-  if (!LABELS) bn = make_binner(a, sh_thr, sh_thr_cap);
+  if (!LABELS) bn = make_binner(a, sh_pad, sh_pad_cap, global_pad);
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) sh_hist[i] = 0;
   __syncthreads();
 
@@ -370,11 +402,17 @@ __global__ void __launch_bounds__(256) k2_generic(TbArgs a, int sh_bins, int sh_
   }
 }
 
+// padded threshold copy in global memory for threshold counts that do not fit shared memory
+__global__ void k2_pad_thresholds(const float* __restrict__ thr, int T, float* __restrict__ pad) {
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T + 2; i += gridDim.x * blockDim.x)
+    pad[i] = (i == 0) ? -INFINITY : (i == T + 1 ? INFINITY : thr[i - 1]);
+}
+
 // ---- finalize -------------------------------------------------------------------------------------------
 // One warp per (label, target class).  The per-threshold counts are suffix sums of the bin histogram:
 // above(j) = #{samples with q >= thr[j]} = sum_{k > j} hist[k].  Lanes take 32 bins at a time from the
 // top, a shuffle scan forms the running suffix sum, and the counts are ADDED into the state.
-__global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, int64_t scratch_elems, int L, int T,
+__global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, int L, int T,
                                                    const int* __restrict__ perm, int layout, long long* out0,
                                                    long long* out1, long long* out2, long long* out3) {
   const int variant = scratch[0] != 0ULL ? 1 : 0;
@@ -459,20 +497,24 @@ __global__ void __launch_bounds__(256) k_label_max(const void* __restrict__ x, i
 __global__ void k_set_i64(long long* p, long long v) { *p = v; }
 
 // ---- host ------------------------------------------------------------------------------------------------
-static int64_t scratch_elems_for(int64_t L, int64_t T) { return kHdr + 2 * L * 2 * (T + 1); }
+// scratch layout (int64 elements): [0, kHdr) header | 2 histogram variants | padded thresholds (as floats)
+static int64_t hist_elems(int64_t L, int64_t T) { return 2 * L * 2 * (T + 1); }
+static int64_t pad_elems(int64_t T) { return (T + 2 + 1) / 2; }
+static int64_t scratch_elems_for(int64_t L, int64_t T) { return kHdr + hist_elems(L, T) + pad_elems(T); }
 
 template <int PDT, int TDT>
 static int launch_binary_lanes(const TbArgs& a, int warps, int smem, cudaStream_t st) {
-  int per_sm = (int)((int64_t)dev_info().max_smem_optin / (smem + 1024));
-  per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
-  const int grid = dev_info().sm_count * per_sm;
   auto ka = k2_binary_lanes<PDT, TDT, false>;
   auto kb = k2_binary_lanes<PDT, TDT, true>;
   cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  ka<<<grid, warps * 32, smem, st>>>(a, warps);
+  const int block = warps * 32;
+  // persistent grid: as many CTAs as stay resident (1 per SM at T = 200, more when the histograms are small)
+  const int64_t work = (a.n_total / 4 + (int64_t)block * kBatch - 1) / ((int64_t)block * kBatch);
+  const int grid = resident_grid(kb, block, smem, work);
+  ka<<<grid, block, smem, st>>>(a, warps);
   if (int rc = launch_status()) return rc;
-  kb<<<grid, warps * 32, smem, st>>>(a, warps);
+  kb<<<grid, block, smem, st>>>(a, warps);
   return launch_status();
 }
 
@@ -490,18 +532,26 @@ template <int PDT>
 static int launch_generic(const TbArgs& a, cudaStream_t st) {
   const int64_t bins = (int64_t)a.L * 2 * (a.T + 1);
   const int sh_bins = bins <= 8192 ? (int)bins : 0;
-  const int sh_thr_cap = a.T <= 4096 ? (a.T + 31) / 32 * 32 : 0;
-  const int smem = (sh_thr_cap + sh_bins) * 4;
+  const int sh_pad_cap = a.T + 2 <= 4096 ? (a.T + 2 + 31) / 32 * 32 : 0;
+  const int smem = (sh_pad_cap + sh_bins) * 4;
   const int block = 256;
-  const int grid = wave_grid((a.n_total + block - 1) / block, 8);
+  const int64_t work = (a.n_total + block - 1) / block;
+  float* global_pad = (float*)(a.scratch + kHdr + hist_elems(a.L, a.T));
   if (a.preds_is_label) {
     // labels are never sigmoided: they go to histogram variant 0, the one finalize reads while the flag is down
-    k2_generic<TMB_F32, false, true><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+    auto k = k2_generic<TMB_F32, false, true>;
+    k<<<resident_grid(k, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
     return launch_status();
   }
-  k2_generic<PDT, false, false><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+  if (sh_pad_cap == 0) {
+    k2_pad_thresholds<<<wave_grid((a.T + 2 + 255) / 256, 2), 256, 0, st>>>(a.thr, a.T, global_pad);
+    if (int rc = launch_status()) return rc;
+  }
+  auto ka = k2_generic<PDT, false, false>;
+  auto kb = k2_generic<PDT, true, false>;
+  ka<<<resident_grid(ka, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
   if (int rc = launch_status()) return rc;
-  k2_generic<PDT, true, false><<<grid, block, smem, st>>>(a, sh_bins, sh_thr_cap);
+  kb<<<resident_grid(kb, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
   return launch_status();
 }
 
@@ -548,17 +598,17 @@ extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int pre
   a.has_ignore = has_ignore;
   a.flag_counts_ignored = flag_counts_ignored;
 
-  // binary fast path: lane-private histograms need (T+1)*128 B per warp plus the thresholds
+  // binary fast path: lane-private histograms need (T+1)*128 B per warp plus the padded thresholds
   const bool aligned = (((uintptr_t)preds | (uintptr_t)target) & 15) == 0;
   const bool tdt_ok = target_dtype != TMB_I16;
   if (num_labels == 1 && !preds_is_label && aligned && tdt_ok) {
-    const int thr_bytes = (a.T + 31) / 32 * 32 * 4;
+    const int pad_bytes = (a.T + 2 + 31) / 32 * 32 * 4;
     const int64_t per_warp = (int64_t)(a.T + 1) * 128;
-    const int64_t avail = (int64_t)dev_info().max_smem_optin - thr_bytes - 1024;
+    const int64_t avail = (int64_t)dev_info().max_smem_optin - pad_bytes - 1024;
     int warps = (int)(avail / per_warp);
     if (warps >= 1) {
       if (warps > 8) warps = 8;
-      const int smem = thr_bytes + (int)(warps * per_warp);
+      const int smem = pad_bytes + (int)(warps * per_warp);
       switch (preds_dtype) {
         case TMB_F32: return launch_binary_lanes_t<TMB_F32>(a, warps, smem, st);
         case TMB_F16: return launch_binary_lanes_t<TMB_F16>(a, warps, smem, st);
@@ -585,9 +635,9 @@ extern "C" int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, 
   if (scratch_elems < scratch_elems_for(num_labels, num_thresholds)) return TMB_E_SCRATCH;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t threads = num_labels * 2 * 32;
-  k2_finalize<<<(int)((threads + 255) / 256), 256, 0, st>>>((unsigned long long*)scratch, scratch_elems, (int)num_labels,
-                                                     (int)num_thresholds, perm, layout, (long long*)out0,
-                                                     (long long*)out1, (long long*)out2, (long long*)out3);
+  k2_finalize<<<(int)((threads + 255) / 256), 256, 0, st>>>((unsigned long long*)scratch, (int)num_labels,
+                                                            (int)num_thresholds, perm, layout, (long long*)out0,
+                                                            (long long*)out1, (long long*)out2, (long long*)out3);
   if (int rc = launch_status()) return rc;
   const int64_t used = scratch_elems_for(num_labels, num_thresholds);
   k2_clear<<<wave_grid((used + 255) / 256, 4), 256, 0, st>>>((unsigned long long*)scratch, used);
