@@ -258,6 +258,42 @@ def extras_block(device, steps: int, warmup: int, peak: float):
         del preds, tgt, m
     torch.cuda.empty_cache()
 
+    # config 4: MultilabelAUROC(100, thresholds=None), 2^24 samples over 8 updates of 2^21; exact compute()
+    try:
+        from torchmetrics_forked_b200.classification import MultilabelAUROC
+
+        n4, L4, upd = 1 << 21, 100, 8
+        m = MultilabelAUROC(L4, thresholds=None, validate_args=False).to(device)
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(upd + 3)]
+        batches = []
+        for _ in range(upd):
+            batches.append((torch.randn(n4, L4, generator=g, device=device),
+                            torch.randint(2, (n4, L4), generator=g, device=device)))
+        torch.cuda.synchronize()
+        for i, (p, t) in enumerate(batches):
+            ev[i].record()
+            m.update(p, t)
+        ev[upd].record()
+        del batches
+        value = m.compute()
+        ev[upd + 1].record()
+        torch.cuda.synchronize()
+        upd_ms = ev[0].elapsed_time(ev[upd]) / upd
+        cmp_ms = ev[upd].elapsed_time(ev[upd + 1])
+        ls = n4 * upd * L4
+        out["cfg4_multilabel_auroc_exact"] = {
+            "update_ms": upd_ms, "update_algo_gbs": n4 * L4 * 8 / upd_ms / 1e6,
+            "update_roofline_frac": n4 * L4 * 8 / upd_ms / 1e6 / peak,
+            "compute_ms": cmp_ms, "compute_label_samples_per_s": ls / cmp_ms * 1e3,
+            "compute_gbs_lower_bound_24B": ls * 24 / cmp_ms / 1e6, "compute_gbs_radix_model_74B": ls * 74 / cmp_ms / 1e6,
+            "auroc": float(value), "samples": n4 * upd, "labels": L4,
+        }
+        del m, value
+        torch.cuda.empty_cache()
+    except Exception as e:  # noqa: BLE001
+        out["cfg4_multilabel_auroc_exact"] = {"error": repr(e)}
+        torch.cuda.empty_cache()
+
     # config 1: MetricCollection([MulticlassAccuracy, MulticlassConfusionMatrix]), 100 000 fp32 probs (latency bound)
     for C in (5, 10):
         preds = torch.randn(100_000, C, generator=g, device=device).softmax(-1)

@@ -52,6 +52,7 @@ extern "C" {
 #define TMB_ERR_TARGET_RANGE 1 /* a non-ignored target outside [0, num_classes)            */
 #define TMB_ERR_PREDS_RANGE 2  /* a label-valued pred outside [0, num_classes)              */
 #define TMB_ERR_TARGET_BINARY 4 /* a non-ignored binary/multilabel target that is not 0 or 1 */
+#define TMB_ERR_SCORE_RANGE 8   /* a negative score reached the exact-curve sort                */
 
 /* what the multiclass kernels accumulate */
 #define TMB_MC_CONFMAT 0 /* out = int64 state [C, C], row = target, col = pred                    */
@@ -137,6 +138,44 @@ int tmb_thresh_bin_update(const void* preds, int preds_dtype, int preds_is_label
 int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, int64_t num_labels,
                             int64_t num_thresholds, const int32_t* perm, int layout, int64_t* out0,
                             int64_t* out1, int64_t* out2, int64_t* out3, void* stream);
+
+/* ---- K3: exact curves (thresholds=None) ---------------------------------------------------------------
+ *
+ * tmb_sigmoid_normalize is the exact-mode half of
+ *   _binary_precision_recall_curve_format      functional/classification/precision_recall_curve.py:176-186
+ *   _multilabel_precision_recall_curve_format  same file :752-757
+ * out[i] = sigmoid(preds[i]) if ANY element taking part in the test lies outside [0,1] (NaN included),
+ * else out[i] = preds[i]; same dtype as preds.  With `target` non-NULL and has_ignore, elements whose target
+ * equals ignore_index take no part in the test.  `flag` is one caller-owned int64 that must start at 0 and
+ * `generation` a strictly increasing positive call counter for that flag (it replaces clearing the flag).
+ */
+int tmb_sigmoid_normalize(const void* preds, int preds_dtype, int64_t n, const void* target,
+                          int target_dtype, int has_ignore, int64_t ignore_index, void* out, int64_t* flag,
+                          int64_t generation, void* stream);
+
+/* tmb_clf_curves replaces, for all labels at once,
+ *   _binary_clf_curve                          functional/classification/precision_recall_curve.py:28-80
+ *   the per-label loops that call it           same file :819-829, functional/classification/roc.py:345-355
+ * preds [n, num_labels] row-major scores (non-negative or NaN — what the update stores; a negative score sets
+ * TMB_ERR_SCORE_RANGE), target [n, num_labels] integers; entries with target == ignore_index are dropped
+ * per label.  For label l with D_l distinct scores the first D_l entries of fps/tps/thresholds[l * n ...]
+ * receive, in order of DESCENDING score: false positives, true positives (both exact counts as float32,
+ * positives = target == pos_label) and the score; counts[l] = D_l (int64, device).  n < 2^31.
+ * scratch: tmb_clf_curve_scratch_bytes(n, num_labels) bytes of device memory, contents irrelevant. */
+int64_t tmb_clf_curve_scratch_bytes(int64_t n, int64_t num_labels);
+int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n,
+                   int64_t num_labels, int has_ignore, int64_t ignore_index, int64_t pos_label, void* scratch,
+                   int64_t scratch_bytes, float* fps, float* tps, float* thresholds, int64_t* counts,
+                   int32_t* err, void* stream);
+
+/* Order-preserving removal of the samples whose target equals ignore_index — the boolean-mask indexing of
+ * precision_recall_curve.py:178-181 (binary) and auroc.py:317-322 (micro average).  out_* must hold n
+ * elements; *count (int64, device) receives how many were kept.  preds is copied bytewise
+ * (preds_elem_bytes in {1,2,4,8}).  n < 2^32. */
+int64_t tmb_compact_scratch_bytes(int64_t n);
+int tmb_compact_not_ignored(const void* preds, int preds_elem_bytes, const void* target, int target_dtype,
+                            int64_t n, int64_t ignore_index, void* out_preds, void* out_target,
+                            int64_t* count, void* scratch, int64_t scratch_bytes, void* stream);
 
 /* ---- utilities ------------------------------------------------------------------------------------
  * tmb_bincount: out[v] += 1 for every v = x[i] (integer dtype), 0 <= v < length; other values set

@@ -1,0 +1,57 @@
+"""Tiny drivers for ncu: run one kernel family a few times on the BASELINE shape.
+
+    python profiles/drive.py k1   # config 2: MulticlassConfusionMatrix(1000), bf16 [2^22, 1000]
+    python profiles/drive.py k2   # config 3: BinaryPrecisionRecallCurve(thresholds=200), 2^28 fp32 logits
+    python profiles/drive.py k5   # config 5: MulticlassJaccardIndex(150), [16,150,512,512]
+    python profiles/drive.py k3   # config 4 (scaled): MultilabelAUROC exact, compute()
+"""
+import sys
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+
+which = sys.argv[1] if len(sys.argv) > 1 else "k1"
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+dev = torch.device("cuda")
+g = torch.Generator(device=dev).manual_seed(0)
+
+if which == "k1":
+    from torchmetrics_forked_b200.classification import MulticlassConfusionMatrix
+
+    rows = 1 << 22
+    t = torch.randint(1000, (rows,), generator=g, device=dev)
+    p = torch.empty(rows, 1000, dtype=torch.bfloat16, device=dev)
+    for s in range(0, rows, 1 << 18):
+        p[s : s + (1 << 18)] = torch.randn(1 << 18, 1000, generator=g, device=dev).bfloat16()
+    m = MulticlassConfusionMatrix(1000, validate_args=False).to(dev)
+    for _ in range(reps):
+        m.update(p, t)
+elif which == "k2":
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    n = 1 << 28
+    p = torch.randn(n, generator=g, device=dev) * 3
+    t = torch.randint(2, (n,), generator=g, device=dev)
+    m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(dev)
+    for _ in range(reps):
+        m.update(p, t)
+elif which == "k5":
+    from torchmetrics_forked_b200.classification import MulticlassJaccardIndex
+
+    p = torch.randn(16, 150, 512, 512, generator=g, device=dev)
+    t = torch.randint(150, (16, 512, 512), generator=g, device=dev)
+    m = MulticlassJaccardIndex(150, validate_args=False).to(dev)
+    for _ in range(reps):
+        m.update(p, t)
+elif which == "k3":
+    from torchmetrics_forked_b200.classification import MultilabelAUROC
+
+    n, L = 1 << 20, 100
+    m = MultilabelAUROC(L, thresholds=None, validate_args=False).to(dev)
+    for _ in range(2):
+        m.update(torch.randn(n, L, generator=g, device=dev), torch.randint(2, (n, L), generator=g, device=dev))
+    print(float(m.compute()))
+torch.cuda.synchronize()
+print("done", which)

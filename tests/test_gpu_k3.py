@@ -1,0 +1,313 @@
+"""GPU parity: K3 (exact curves) — conditional sigmoid, ordered ignore-filter, batched radix sort + scan —
+against the oracle and the reference's golden vectors.  Counts (fps / tps) and thresholds must match bit for
+bit; AUROC / AP within 1e-6 relative (float32 reductions on the device vs float64 in the oracle: 1e-5)."""
+import ctypes
+
+import numpy as np
+import pytest
+import torch
+from conftest import golden_names, ignore_of, load_golden
+
+import hotpath as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _cuda(x, dtype=None):
+    t = torch.from_numpy(np.ascontiguousarray(x))
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.cuda()
+
+
+def cuda_sigmoid(x: np.ndarray) -> np.ndarray:
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).cuda().sigmoid().cpu().numpy()
+
+
+def _check_curves(got, want):
+    fps, tps, thr = got
+    for i, (wf, wt, wh) in enumerate(want):
+        assert np.array_equal(fps[i].cpu().numpy(), wf), f"fps of label {i}"
+        assert np.array_equal(tps[i].cpu().numpy(), wt), f"tps of label {i}"
+        assert np.array_equal(thr[i].float().cpu().numpy(), wh, equal_nan=True), f"thresholds of label {i}"
+
+
+# ------------------------------------------------------------------------------------------ raw C ABI
+def test_cabi_clf_curves_raw_pointers():
+    from torchmetrics_forked_b200 import _native as nat
+
+    lib = nat.lib()
+    g = torch.Generator().manual_seed(5)
+    n, L = 30_011, 3
+    preds = (torch.rand(n, L, generator=g) * 64).round() / 64  # many ties
+    target = torch.randint(2, (n, L), generator=g)
+    dp, dt = preds.cuda(), target.cuda()
+    nbytes = lib.tmb_clf_curve_scratch_bytes(n, L)
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device="cuda")
+    fps, tps, thr = (torch.full((L, n), -7.0, device="cuda") for _ in range(3))
+    counts = torch.zeros(L, dtype=torch.int64, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    p = lambda t: ctypes.c_void_p(t.data_ptr())  # noqa: E731
+    rc = lib.tmb_clf_curves(p(dp), 0, p(dt), 0, n, L, 0, 0, 1, p(scratch), nbytes, p(fps), p(tps), p(thr), p(counts),
+                            p(err), ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    torch.cuda.synchronize()
+    assert int(err.item()) == 0
+    want = O.multilabel_clf_curves(preds.numpy(), target.numpy())
+    for l in range(L):
+        d = int(counts[l])
+        assert d == len(want[l][0]) == 65
+        assert np.array_equal(fps[l, :d].cpu().numpy(), want[l][0])
+        assert np.array_equal(tps[l, :d].cpu().numpy(), want[l][1])
+        assert np.array_equal(thr[l, :d].cpu().numpy(), want[l][2])
+        assert float(fps[l, d]) == -7.0  # nothing is written past the curve
+    assert lib.tmb_clf_curves(p(dp), 0, p(dt), 0, n, L, 0, 0, 1, p(scratch), 16, p(fps), p(tps), p(thr), p(counts),
+                              p(err), None) == -5
+    assert lib.tmb_clf_curves(p(dp), 0, p(dt), 0, 1 << 31, L, 0, 0, 1, p(scratch), nbytes, p(fps), p(tps), p(thr),
+                              p(counts), p(err), None) == -6
+
+
+# ------------------------------------------------------------------------------------------ golden vectors
+@pytest.mark.parametrize("name", golden_names("clf_"))
+def test_binary_exact_golden(name):
+    from torchmetrics_forked_b200.classification import BinaryAUROC, BinaryAveragePrecision
+    from torchmetrics_forked_b200.functional.classification.precision_recall_curve import _binary_clf_curve
+
+    c = load_golden(name)
+    preds, target = _cuda(c["preds"]), _cuda(c["target"])
+    fps, tps, thr = _binary_clf_curve(preds, target)
+    assert np.array_equal(fps.cpu().numpy(), c["fps"])
+    assert np.array_equal(tps.cpu().numpy(), c["tps"])
+    assert np.array_equal(thr.cpu().numpy(), c["thr"])
+    if c["preds"].size > 1:
+        for cls, key in ((BinaryAUROC, "auroc"), (BinaryAveragePrecision, "ap")):
+            m = cls(thresholds=None).cuda()
+            m.update(preds, target)
+            np.testing.assert_allclose(m.compute().cpu().numpy(), c[key], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("name", golden_names("mlexact_"))
+def test_multilabel_exact_golden(name):
+    from torchmetrics_forked_b200.classification import (
+        MultilabelAUROC,
+        MultilabelAveragePrecision,
+        MultilabelPrecisionRecallCurve,
+    )
+
+    c = load_golden(name)
+    L, ign = int(c["num_labels"]), ignore_of(c)
+    preds, target = _cuda(c["preds"]), _cuda(c["target"])
+    m = MultilabelPrecisionRecallCurve(L, thresholds=None, ignore_index=ign).cuda()
+    m.update(preds, target)
+    state = m.preds[0].cpu().numpy()
+    want_state = O.exact_state(c["preds"], sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(state, want_state)
+    if "logits" not in name:
+        assert np.array_equal(state, c["state_preds"])
+    from torchmetrics_forked_b200 import kernels
+
+    got = kernels.clf_curves(m.preds[0], m.target[0], ign, 1)
+    _check_curves(got, O.multilabel_clf_curves(want_state, c["target"], ign))
+    if "logits" not in name:
+        for i in range(L):
+            assert np.array_equal(got[0][i].cpu().numpy(), c[f"fps_{i}"])
+            assert np.array_equal(got[1][i].cpu().numpy(), c[f"tps_{i}"])
+            assert np.array_equal(got[2][i].cpu().numpy(), c[f"thr_{i}"])
+    for avg in ("micro", "macro", "none"):
+        for cls, key in ((MultilabelAUROC, "auroc"), (MultilabelAveragePrecision, "ap")):
+            mm = cls(L, average=avg, thresholds=None, ignore_index=ign).cuda()
+            mm.update(preds, target)
+            np.testing.assert_allclose(mm.compute().cpu().numpy(), c[f"{key}_{avg}"], rtol=2e-6, atol=1e-6)
+
+
+# ------------------------------------------------------------------------------------------ random cases vs the oracle
+@pytest.mark.parametrize(
+    ("n", "L", "levels"),
+    [
+        (1, 1, 0), (2, 1, 0), (33, 2, 4), (8191, 1, 0), (8192, 3, 16), (8193, 1, 1000),
+        (100_003, 7, 0), (300_000, 2, 257), (1_000_001, 1, 0),
+    ],
+)  # fmt: skip
+def test_clf_curves_random(n, L, levels):
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(n + L)
+    preds = torch.rand(n, L, generator=g)
+    if levels:
+        preds = (preds * levels).round() / levels  # heavy ties
+    target = torch.randint(2, (n, L), generator=g)
+    got = kernels.clf_curves(preds.cuda(), target.cuda(), None, 1)
+    _check_curves(got, O.multilabel_clf_curves(preds.numpy(), target.numpy()))
+
+
+def test_clf_curves_special_values_and_ignore():
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(77)
+    n, L = 50_000, 4
+    preds = (torch.rand(n, L, generator=g) * 100).round() / 100
+    preds[::97, 0] = float("nan")
+    preds[::89, 1] = 0.0
+    preds[5::89, 1] = -0.0
+    preds[::83, 2] = 1.0
+    preds[7::83, 2] = float("inf")
+    preds[::101, 3] = 1e-42  # denormal: distinct from 0 only without flush-to-zero
+    target = torch.randint(2, (n, L), generator=g)
+    target[torch.rand(n, L, generator=g) < 0.3] = -1
+    target[:, 3][target[:, 3] == -1] = 0
+    target[: n // 2, 3] = -1  # a long ignored prefix
+    # NaN (and inf) scores each form their own threshold, so the counts depend on the order argsort leaves
+    # them in — which the reference does not define (unstable sort).  Give them one target value so that
+    # every tie order yields the same curve.
+    target[::97, 0] = 1
+    target[7::83, 2] = 1
+    got = kernels.clf_curves(preds.cuda(), target.cuda(), -1, 1)
+    _check_curves(got, O.multilabel_clf_curves(preds.numpy(), target.numpy(), -1))
+    # every entry of one label ignored -> empty curve
+    target[:, 0] = -1
+    got = kernels.clf_curves(preds.cuda(), target.cuda(), -1, 1)
+    assert got[0][0].numel() == 0 and got[2][0].numel() == 0
+    with pytest.raises(RuntimeError, match="non-negative"):
+        kernels.clf_curves(-preds.abs().cuda() - 1, target.cuda(), None, 1)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_clf_curves_narrow_dtypes(dtype):
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(3)
+    preds = torch.rand(20_000, 2, generator=g).to(dtype)
+    target = torch.randint(2, (20_000, 2), generator=g)
+    got = kernels.clf_curves(preds.cuda(), target.cuda(), None, 1)
+    assert got[2][0].dtype == dtype
+    _check_curves(got, O.multilabel_clf_curves(preds.float().numpy(), target.numpy()))
+
+
+def test_sort_properties_at_scale():
+    """Size-independent properties on a case too big for the Python oracle loop: thresholds strictly
+    descending, counts monotone, totals add up, number of thresholds = number of distinct scores."""
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator(device="cuda").manual_seed(9)
+    n, L = 1 << 22, 3
+    preds = torch.rand(n, L, generator=g, device="cuda")
+    preds[:, 1] = (preds[:, 1] * 5000).round() / 5000
+    target = torch.randint(2, (n, L), generator=g, device="cuda")
+    fps, tps, thr = kernels.clf_curves(preds, target, None, 1)
+    for l in range(L):
+        assert bool((thr[l][1:] < thr[l][:-1]).all())
+        assert bool((tps[l][1:] >= tps[l][:-1]).all()) and bool((fps[l][1:] >= fps[l][:-1]).all())
+        assert float(tps[l][-1]) == float((target[:, l] == 1).sum())
+        assert float(tps[l][-1] + fps[l][-1]) == n
+        assert thr[l].numel() == torch.unique(preds[:, l]).numel()
+        assert torch.equal(thr[l], torch.unique(preds[:, l]).flip(0))
+    # AUROC of label 1 against a torch (not oracle) rank computation: U statistic with ties
+    p, t = preds[:, 1].double(), target[:, 1]
+    order = torch.argsort(p)
+    uniq, inv, cnt = torch.unique(p, return_inverse=True, return_counts=True)
+    start = torch.cumsum(cnt, 0) - cnt
+    avg_rank = (start + (cnt + 1) / 2.0)[inv]
+    n_pos = int((t == 1).sum())
+    u = avg_rank[t == 1].sum() - n_pos * (n_pos + 1) / 2
+    auc = float(u / (n_pos * (n - n_pos)))
+    from torchmetrics_forked_b200.functional.classification.auroc import _auc_compute_without_check
+    from torchmetrics_forked_b200.functional.classification.roc import _roc_from_curve
+
+    fpr, tpr, _ = _roc_from_curve(fps[1], tps[1], thr[1])
+    assert abs(float(_auc_compute_without_check(fpr.double(), tpr.double(), 1.0)) - auc) < 1e-9
+    del order
+
+
+# ------------------------------------------------------------------------------------------ update-time helpers
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+def test_sigmoid_normalize_matches_torch(dtype):
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(4)
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    logits = (torch.randn(1_000_003, generator=g) * 4).to(dtype).cuda()
+    assert torch.equal(kernels.sigmoid_normalize(logits, None, None, err), logits.sigmoid())
+    probs = torch.rand(1_000_003, generator=g).to(dtype).cuda()
+    out = kernels.sigmoid_normalize(probs, None, None, err)
+    assert torch.equal(out, probs) and out.data_ptr() != probs.data_ptr()
+    # one NaN, or one value a hair above 1, flips the whole batch
+    spiked = probs.clone()
+    spiked[12345] = float("nan")
+    out = kernels.sigmoid_normalize(spiked, None, None, err)
+    assert torch.equal(out[:100], spiked[:100].sigmoid()) and bool(out[12345].isnan())
+    spiked = probs.clone()
+    spiked[-1] = 1.5
+    assert torch.equal(kernels.sigmoid_normalize(spiked, None, None, err), spiked.sigmoid())
+    # ... unless it sits at an ignored position and the caller asks for that exclusion (H2)
+    target = torch.zeros(spiked.numel(), dtype=torch.long, device="cuda")
+    target[-1] = -1
+    assert torch.equal(kernels.sigmoid_normalize(spiked, target, -1, err), spiked)
+    assert torch.equal(kernels.sigmoid_normalize(spiked, target, -2, err), spiked.sigmoid())
+    assert kernels.sigmoid_normalize(probs[:0], None, None, err).numel() == 0
+
+
+@pytest.mark.parametrize("tdtype", [torch.int64, torch.int32, torch.uint8])
+@pytest.mark.parametrize("pdtype", [torch.float32, torch.bfloat16])
+def test_compact_not_ignored(tdtype, pdtype):
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(6)
+    for n in (1, 4095, 4096, 4097, 1_000_003):
+        preds = torch.rand(n, generator=g).to(pdtype).cuda()
+        target = torch.randint(3, (n,), generator=g).to(tdtype).cuda()
+        p, t = kernels.compact_not_ignored(preds, target, 2)
+        keep = target != 2
+        assert torch.equal(p, preds[keep]) and torch.equal(t, target[keep])
+    p, t = kernels.compact_not_ignored(preds, torch.full_like(target, 2), 2)
+    assert p.numel() == 0 and t.numel() == 0
+
+
+def test_binary_exact_with_ignore_index_and_logits():
+    from torchmetrics_forked_b200.classification import BinaryAUROC, BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(8)
+    n = 40_000
+    preds = torch.randn(n, generator=g)
+    target = torch.randint(2, (n,), generator=g)
+    target[torch.rand(n, generator=g) < 0.25] = -1
+    m = BinaryPrecisionRecallCurve(thresholds=None, ignore_index=-1).cuda()
+    m.update(preds[: n // 2].cuda(), target[: n // 2].cuda())
+    m.update(preds[n // 2 :].cuda(), target[n // 2 :].cuda())
+    keep = (target != -1).numpy()
+    stored = np.concatenate([
+        O.exact_state(preds[: n // 2].numpy()[keep[: n // 2]], sigmoid_fn=cuda_sigmoid),
+        O.exact_state(preds[n // 2 :].numpy()[keep[n // 2 :]], sigmoid_fn=cuda_sigmoid),
+    ])
+    assert np.array_equal(torch.cat(m.preds).cpu().numpy(), stored)
+    assert np.array_equal(torch.cat(m.target).cpu().numpy(), target.numpy()[keep])
+    precision, recall, thr = m.compute()
+    fps, tps, wthr = O.binary_clf_curve(stored, target.numpy()[keep])
+    assert np.array_equal(thr.cpu().numpy(), wthr[::-1])
+    np.testing.assert_allclose(precision.cpu().numpy()[:-1], (tps / (tps + fps))[::-1], rtol=1e-6)
+    a = BinaryAUROC(thresholds=None, ignore_index=-1).cuda()
+    a.update(preds.cuda(), target.cuda())
+    whole = O.exact_state(preds.numpy()[keep], sigmoid_fn=cuda_sigmoid)
+    f2, t2, _ = O.binary_clf_curve(whole, target.numpy()[keep])
+    np.testing.assert_allclose(float(a.compute()), O.binary_auroc_exact(f2, t2), rtol=1e-5)
+
+
+def test_multilabel_auroc_config4_scaled():
+    """BASELINE config 4 shape (L = 100, fp32 logits, exact mode) at a size the oracle finishes quickly."""
+    from torchmetrics_forked_b200.classification import MultilabelAUROC, MultilabelAveragePrecision
+
+    g = torch.Generator().manual_seed(10)
+    n, L = 6000, 100
+    auroc = MultilabelAUROC(L, thresholds=None, average="none").cuda()
+    ap = MultilabelAveragePrecision(L, thresholds=None, average="macro").cuda()
+    P, T = [], []
+    for _ in range(3):
+        preds, target = torch.randn(n, L, generator=g), torch.randint(2, (n, L), generator=g)
+        auroc.update(preds.cuda(), target.cuda())
+        ap.update(preds.cuda(), target.cuda())
+        P.append(O.exact_state(preds.numpy(), sigmoid_fn=cuda_sigmoid))
+        T.append(target.numpy())
+    curves = O.multilabel_clf_curves(np.concatenate(P), np.concatenate(T))
+    np.testing.assert_allclose(auroc.compute().cpu().numpy(), [O.binary_auroc_exact(f, t) for f, t, _ in curves],
+                               rtol=1e-5)
+    np.testing.assert_allclose(float(ap.compute()),
+                               np.mean([O.binary_average_precision_exact(f, t) for f, t, _ in curves]), rtol=1e-5)

@@ -19,7 +19,7 @@ FLOAT_CODES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 LABEL_CODES = {torch.int64: 0, torch.int32: 1, torch.int16: 2, torch.uint8: 3, torch.bool: 3, torch.int8: 4}
 
 MC_CONFMAT, MC_STATS, MC_MICRO = 0, 1, 2
-ERR_TARGET_RANGE, ERR_PREDS_RANGE, ERR_TARGET_BINARY = 1, 2, 4
+ERR_TARGET_RANGE, ERR_PREDS_RANGE, ERR_TARGET_BINARY, ERR_SCORE_RANGE = 1, 2, 4, 8
 
 _ARG_ERRORS = {
     -1: "unsupported dtype",
@@ -53,6 +53,21 @@ SIGNATURES = {
     "tmb_thresh_bin_finalize": (
         c_int,
         [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "tmb_sigmoid_normalize": (
+        c_int, [c_void_p, c_int, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int64, c_void_p]
+    ),
+    "tmb_clf_curve_scratch_bytes": (c_int64, [c_int64, c_int64]),
+    "tmb_clf_curves": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
+    "tmb_compact_scratch_bytes": (c_int64, [c_int64]),
+    "tmb_compact_not_ignored": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+         c_void_p],
     ),
     "tmb_bincount": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_label_max": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p]),

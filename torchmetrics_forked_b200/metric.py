@@ -60,6 +60,7 @@ _DATA_ERROR_TEXT = {
     1: "`target` contains values outside [0, num_classes) that are not `ignore_index`",
     2: "label-valued `preds` contains values outside [0, num_classes)",
     4: "`target` contains values other than 0, 1 (and `ignore_index`)",
+    8: "negative scores reached the exact-curve sort (stored scores must be probabilities / sigmoid outputs)",
 }
 
 
