@@ -139,6 +139,29 @@ int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, int64_t num
                             int64_t num_thresholds, const int32_t* perm, int layout, int64_t* out0,
                             int64_t* out1, int64_t* out2, int64_t* out3, void* stream);
 
+/* tmb_binary_curve_update_noalloc — no counterpart in the reference (which allocates temporaries freely
+ * through torch); it exists for callers of this C ABI that have no way to provide scratch memory:
+ *   - a host binding the library over a bare FFI (ctypes without torch, cgo, JNI) that owns no device
+ *     allocator and only holds the input / state pointers it was handed;
+ *   - a service that gives all device memory to one pool at start-up, where a later cudaMalloc fails or
+ *     fragments that pool;
+ *   - a latency-bound evaluation loop: cudaMalloc and cudaFree synchronise the device.
+ * It performs one whole binned binary-curve update — tmb_thresh_bin_update (num_labels 1, `>=` compare,
+ * ignored samples excluded from the sigmoid test) followed by tmb_thresh_bin_finalize (TMB_TB_CURVE) — and
+ * ADDS the result into `confmat` (int64 [num_thresholds, 2, 2]).  The caller still passes inputs, thresholds,
+ * state and error word; the histogram scratch is a static __device__ array inside the library (about 36 KB on
+ * every GPU that loads it, kept until the process exits).  The call itself allocates and frees nothing.
+ *   Limit: num_thresholds <= 1024; more returns TMB_E_LIMIT and launches nothing.
+ *   Set-up: the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that
+ *     device current.  Make that first call outside any stream capture.
+ *   Sharing: every call on a device uses the same array, and the array keeps the previous call's contents.
+ *     The call clears what has to start at zero before using it, but two calls whose kernels overlap on the GPU
+ *     (different streams, or different host threads) race on it — serialise them on one stream.
+ */
+int tmb_binary_curve_update_noalloc(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                    int64_t n, const float* thr, int64_t num_thresholds, int has_ignore,
+                                    int64_t ignore_index, int64_t* confmat, int32_t* err, void* stream);
+
 /* ---- K3: exact curves (thresholds=None) ---------------------------------------------------------------
  *
  * tmb_sigmoid_normalize is the exact-mode half of

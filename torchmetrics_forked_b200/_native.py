@@ -54,6 +54,9 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
+    "tmb_binary_curve_update_noalloc": (
+        c_int, [c_void_p, c_int, c_void_p, c_int, c_int64, c_void_p, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p]
+    ),
     "tmb_sigmoid_normalize": (
         c_int, [c_void_p, c_int, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int64, c_void_p]
     ),

@@ -667,3 +667,63 @@ extern "C" int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out
   k_label_max<<<wave_grid((n + 255) / 256, 8), 256, 0, st>>>(x, x_dtype, n, (long long*)out_max);
   return launch_status();
 }
+
+// ---- binned binary curve update for callers that cannot allocate device memory -------------------------------
+//
+// Everything above takes its histogram scratch from the caller.  Some callers have nowhere to get it from:
+//   * a host that binds this library over a bare FFI (ctypes without torch, cgo, JNI) and owns no device
+//     allocator — it holds the input and state pointers somebody else gave it and nothing more;
+//   * a service that hands every byte of device memory to one pool at start-up, so that a later cudaMalloc
+//     either fails or fragments what the pool thinks it owns;
+//   * an evaluation loop with a latency budget: cudaMalloc / cudaFree synchronise the whole device.
+// For them the scratch lives in the library image itself: one statically sized __device__ array per GPU that
+// loads the library (about 36 KB, held until the process exits).  The price is a hard cap on the number of
+// thresholds and the loss of re-entrancy — see the notes on the entry point.
+constexpr int kNoAllocMaxThresholds = 1024;
+constexpr int64_t kNoAllocScratchElems = kHdr + 2 * 2 * ((int64_t)kNoAllocMaxThresholds + 1) +
+                                         ((int64_t)kNoAllocMaxThresholds + 3) / 2;  // scratch_elems_for(1, 1024)
+static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocScratchElems];
+
+// `g_noalloc_scratch` in HOST code is only a handle for the runtime, not a device address; the address a
+// kernel can use has to be asked for, once per device, while that device is current.
+static int noalloc_scratch_address(unsigned long long** out) {
+  static unsigned long long* address[64] = {};
+  static bool known[64] = {};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= 64) return TMB_E_LIMIT;
+  if (!known[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return (int)cudaErrorInvalidSymbol;
+    address[dev] = (unsigned long long*)p;
+    known[dev] = true;
+  }
+  *out = address[dev];
+  return 0;
+}
+
+extern "C" int tmb_binary_curve_update_noalloc(const void* preds, int preds_dtype, const void* target,
+                                               int target_dtype, int64_t n, const float* thr,
+                                               int64_t num_thresholds, int has_ignore, int64_t ignore_index,
+                                               int64_t* confmat, int32_t* err, void* stream) {
+  if (num_thresholds < 1) return TMB_E_SHAPE;
+  if (num_thresholds > kNoAllocMaxThresholds) return TMB_E_LIMIT;  // the static array is sized for 1024
+  if (!confmat || !err || !thr) return TMB_E_NULL;
+  if (scratch_elems_for(1, num_thresholds) > kNoAllocScratchElems) return TMB_E_LIMIT;
+  unsigned long long* scratch = nullptr;
+  if (int rc = noalloc_scratch_address(&scratch)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // The array still holds whatever the previous call (or a failed one) left behind: the outside-[0,1] flag and
+  // both histograms must start at zero, so clear before use rather than trusting the last finalize.
+  k2_clear<<<wave_grid((kNoAllocScratchElems + 255) / 256, 1), 256, 0, st>>>(scratch, kNoAllocScratchElems);
+  if (int rc = launch_status()) return rc;
+  if (int rc = tmb_thresh_bin_update(preds, preds_dtype, 0, target, target_dtype, n, 1, 1, thr, num_thresholds,
+                                     /*cmp_gt=*/0, has_ignore, ignore_index, /*flag_counts_ignored=*/0,
+                                     (int64_t*)scratch, kNoAllocScratchElems, err, stream))
+    return rc;
+  return tmb_thresh_bin_finalize((int64_t*)scratch, kNoAllocScratchElems, 1, num_thresholds, nullptr, TMB_TB_CURVE,
+                                 confmat, nullptr, nullptr, nullptr, stream);
+}
