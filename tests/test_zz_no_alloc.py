@@ -60,13 +60,16 @@ def test_noalloc_matches_ordinary_entry_point_twice(T):
     got = torch.zeros(T, 2, 2, dtype=torch.int64, device="cuda")
     err = torch.zeros(1, dtype=torch.int32, device="cuda")
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
-    before = torch.cuda.memory_allocated()
+    def allocations():  # number of allocation events torch's caching allocator has served so far
+        return torch.cuda.memory_stats().get("allocation.all.allocated", 0)
 
     for batch in (logits, probs):  # two calls in a row on the same shared array
+        before = allocations()
         rc = lib.tmb_binary_curve_update_noalloc(_p(batch), 0, _p(target), 0, n, _p(thr), T, 1, -1, _p(got), _p(err), st)
+        after = allocations()
         assert rc == 0
+        assert after == before, "the entry point must not allocate through torch either"
         torch.cuda.synchronize()
-        assert torch.cuda.memory_allocated() == before, "the entry point must not allocate through torch either"
         _reference_state(lib, batch, target, thr, -1, want)
         assert int(err.item()) == 0
         assert torch.equal(got, want)  # exact: integer counts, same kernels, same sigmoid

@@ -128,25 +128,32 @@ __device__ __forceinline__ bool pass_enabled(const TbArgs& a, bool sig_pass) {
 }
 
 // ---- binary fast path: lane-private packed histograms ------------------------------------------------
-// four consecutive targets starting at element i (i % 4 == 0, base pointer 16-byte aligned)
+// Targets are decoded from their raw 32-bit halves (no 64-bit arithmetic in the hot loop): four
+// consecutive targets starting at element i (i % 4 == 0, base pointer 16-byte aligned).
 template <int TDT>
-__device__ __forceinline__ void load_targets4(const void* base, int64_t i, int64_t t[4]) {
+__device__ __forceinline__ void load_targets4(const void* base, int64_t i, uint32_t lo[4], uint32_t hi[4]) {
   if constexpr (TDT == TMB_I64) {
     uint4 a = ldg_stream16((const char*)base + i * 8);
     uint4 b = ldg_stream16((const char*)base + i * 8 + 16);
-    t[0] = (int64_t)(((uint64_t)a.y << 32) | a.x);
-    t[1] = (int64_t)(((uint64_t)a.w << 32) | a.z);
-    t[2] = (int64_t)(((uint64_t)b.y << 32) | b.x);
-    t[3] = (int64_t)(((uint64_t)b.w << 32) | b.z);
+    lo[0] = a.x; hi[0] = a.y; lo[1] = a.z; hi[1] = a.w;
+    lo[2] = b.x; hi[2] = b.y; lo[3] = b.z; hi[3] = b.w;
   } else if constexpr (TDT == TMB_I32) {
     uint4 a = ldg_stream16((const char*)base + i * 4);
-    t[0] = (int)a.x; t[1] = (int)a.y; t[2] = (int)a.z; t[3] = (int)a.w;
+    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; lo[3] = a.w;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) hi[e] = (uint32_t)((int)lo[e] >> 31);
   } else {
     uint32_t w = ldg_stream4((const char*)base + i);
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       uint32_t b = (w >> (8 * e)) & 0xffu;
-      t[e] = (TDT == TMB_I8) ? (int64_t)(signed char)b : (int64_t)b;
+      if (TDT == TMB_I8) {
+        lo[e] = (uint32_t)(int)(signed char)b;
+        hi[e] = (uint32_t)((int)lo[e] >> 31);
+      } else {
+        lo[e] = b;
+        hi[e] = 0u;
+      }
     }
   }
 }
@@ -165,16 +172,16 @@ __device__ __forceinline__ void load_preds4(const void* base, int64_t i, float x
 }
 
 struct LaneHist {
-  uint32_t* col;  // this warp's [T+1][32] words
+  uint32_t* col;  // this warp's [T+1][32] words, already offset by the lane
   int lane;
-  unsigned seen;  // samples since the last flush (per lane)
+  unsigned seen;  // upper bound of the samples binned since the last flush (per lane)
 };
 
 __device__ __forceinline__ void lane_flush(const TbArgs& a, LaneHist& h, unsigned long long* gh) {
   __syncwarp();
   for (int k = 0; k <= a.T; ++k) {
-    uint32_t w = h.col[k * 32 + h.lane];
-    h.col[k * 32 + h.lane] = 0;
+    uint32_t w = h.col[k * 32];
+    h.col[k * 32] = 0;
     unsigned neg = __reduce_add_sync(kFull, w & 0xffffu);
     unsigned pos = __reduce_add_sync(kFull, w >> 16);
     if (h.lane == 0) {
@@ -186,46 +193,123 @@ __device__ __forceinline__ void lane_flush(const TbArgs& a, LaneHist& h, unsigne
   __syncwarp();
 }
 
-constexpr int kBatch = 4;             // vectors of 4 samples per thread per iteration
-constexpr int kPer = kBatch * 4;      // samples per thread per iteration
+constexpr int kBatch = 4;         // vectors of 4 samples per thread per iteration
+constexpr int kPer = kBatch * 4;  // samples per thread per iteration
 
-// Classify and bin kPer samples held in registers.  Returns true if pass A saw a value outside [0,1].
+struct Batch {
+  float x[kPer];
+  uint32_t lo[kPer], hi[kPer];
+};
+
+// Filtered exact binning of sigmoid(x) (fp32 only).  The bin only changes when q crosses a threshold, so the
+// exact value of q is needed only near one.  A 4-instruction approximation qa = 1/(1 + 2^(-x*log2e))
+// (FMUL, MUFU.EX2, FADD, MUFU.RCP) comes with a rigorous bound on its distance from q, the value torch's
+// kernel (full-precision expf + IEEE divide) returns:
+//   2^(..) vs e^-x : ex2.approx is good to 2 ulp and the rounding of x*log2e costs |x*log2e| * 2^-24 in the
+//                    exponent, i.e. at most (2 + 1.173|x|) ulp in e  (the bound CUDA documents for __expf)
+//   1 + e          : 0.5 ulp;   approximate reciprocal: 1 ulp
+//   q itself       : torch's expression is within 3 ulp of the true value
+// so |qa - q| <= (6.5 + 1.173|x|) ulp * q.  The margin used is twice that, rel(x) = 1.6e-6 + 2.9e-7|x|, plus
+// 1e-30 absolute for the flushed-to-zero ends (|x| > 87, where both expressions saturate at 0 / 1).  If both
+// neighbours of the guessed bin clear qa by more than the margin the bin is certain; otherwise (about 0.2 % of
+// the samples at T = 200) the sample is re-done with the exact expression.  The result is bit-identical to
+// binning torch's sigmoid at a third of the instructions.
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <int PDT, bool SIG>
-__device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, LaneHist& h, const float (&x)[kPer],
-                                           const int64_t (&t)[kPer], unsigned live, bool& bad_target) {
-  int k[kPer];
+__device__ __noinline__ int exact_bin(const Binner& bn, float x) {
+  return bn.bin(SIG ? sigmoid_as<PDT>(x) : x);
+}
+
+// Classify and bin kPer samples held in registers.  FULL = every slot holds a real sample (no `live` mask).
+// Written stage by stage over all kPer samples (not sample by sample) so that the kPer dependency chains are
+// interleaved: with 8 warps per SM, instruction-level parallelism is what hides the MUFU / LDS latencies.
+// Returns true if pass A saw a value outside [0,1].
+template <int PDT, bool SIG, bool FULL>
+__device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, LaneHist& h, const Batch& s,
+                                           unsigned live, bool& bad_target) {
+  constexpr bool kFiltered = SIG && PDT == TMB_F32;
+  float q[kPer], lowq[kPer], highq[kPer];
+  int g[kPer];
   uint32_t inc[kPer];
-  unsigned recheck = 0;
-  bool outside_any = false;
-  // phase 1: straight-line, 16 independent dependency chains for the scheduler to interleave
+  const float bias = 1.0f - bn.lo * bn.scale;
+  const float top = (float)bn.T;
+
+  // stage 1: the score each sample is binned by
+  if (kFiltered) {
+    float e[kPer];
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) e[i] = ex2_approx(s.x[i] * -1.4426950408889634f);
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) q[i] = rcp_approx(1.0f + e[i]);
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+      const float rel = fmaf(fabsf(s.x[i]), 2.9e-7f, 1.6e-6f);
+      const float margin = fmaf(q[i], rel, 1e-30f);
+      lowq[i] = q[i] - margin;
+      highq[i] = q[i] + margin;
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) q[i] = SIG ? sigmoid_as<PDT>(s.x[i]) : s.x[i];
+  }
+  // stage 2: guessed bin and its two neighbouring thresholds
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) g[i] = (int)fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.0f), top);  // NaN -> 0
+  float below[kPer], above[kPer];
 #pragma unroll
   for (int i = 0; i < kPer; ++i) {
-    const bool is_live = (live >> i) & 1u;
-    const bool ignored = a.has_ignore && t[i] == a.ignore;
-    const bool is_one = t[i] == 1, is_zero = t[i] == 0;
-    const bool counted = is_live && !ignored && (is_one || is_zero);
-    bad_target |= is_live && !ignored && !(is_one || is_zero);
-    if (!SIG) {
-      const bool outside = !(x[i] >= 0.0f && x[i] <= 1.0f);
-      outside_any |= is_live && outside && (!ignored || a.flag_counts_ignored);
-    }
-    const float q = SIG ? sigmoid_as<PDT>(x[i]) : x[i];
-    const int g = bn.guess(q);
-    k[i] = g;
-    if (!bn.verified(g, q)) recheck |= counted ? (1u << i) : 0u;
-    inc[i] = counted ? (is_one ? 0x10000u : 1u) : 0u;
-    h.seen += counted ? 1u : 0u;
+    below[i] = bn.pad[g[i]];
+    above[i] = bn.pad[g[i] + 1];
   }
-  // cold path: a guess that failed verification (non-uniform thresholds, rounding at a grid point)
+  // stage 3: is the guess certain?  which counter does the sample bump?
+  unsigned recheck = 0;
+  unsigned flags = 0;  // bit 0: invalid target seen, bit 1: value outside [0,1] seen (pass A)
+  const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
+    const unsigned is_live = FULL ? 1u : ((live >> i) & 1u);
+    const unsigned ignored = a.has_ignore ? (unsigned)((s.lo[i] == ign_lo) & (s.hi[i] == ign_hi)) : 0u;
+    const unsigned zero_or_one = (unsigned)((s.hi[i] | (s.lo[i] >> 1)) == 0u);
+    const unsigned counted = is_live & (ignored ^ 1u) & zero_or_one;
+    flags |= is_live & (ignored ^ 1u) & (zero_or_one ^ 1u);
+    if (!SIG) {
+      const unsigned outside = (unsigned)!(s.x[i] >= 0.0f && s.x[i] <= 1.0f);
+      flags |= (is_live & outside & ((ignored ^ 1u) | (unsigned)(a.flag_counts_ignored != 0))) << 1;
+    }
+    unsigned sure;
+    if (kFiltered) {
+      // certain for `>=` thresholds and for `>` thresholds alike: q lies strictly between the neighbours
+      sure = (unsigned)((below[i] < lowq[i]) & (highq[i] < above[i]));
+    } else {
+      const unsigned lo_ok = bn.gt ? (unsigned)(below[i] < q[i]) : (unsigned)(below[i] <= q[i]);
+      const unsigned hi_ok = bn.gt ? (unsigned)!(above[i] < q[i]) : (unsigned)!(above[i] <= q[i]);
+      sure = (lo_ok & hi_ok) | (unsigned)((q[i] != q[i]) & (g[i] == 0));
+    }
+    recheck |= ((sure ^ 1u) & counted) << i;
+    inc[i] = counted ? (s.lo[i] * 0xffffu + 1u) : 0u;  // 1 for a negative, 0x10000 for a positive
+  }
+  bad_target |= (flags & 1u) != 0u;
+  // cold path: too close to a threshold for the approximation, or a guess that missed
   if (recheck) {
 #pragma unroll
     for (int i = 0; i < kPer; ++i)
-      if ((recheck >> i) & 1u) k[i] = bn.bisect(SIG ? sigmoid_as<PDT>(x[i]) : x[i]);
+      if ((recheck >> i) & 1u) g[i] = exact_bin<PDT, SIG>(bn, s.x[i]);
   }
-  // phase 2: the read-modify-writes (a lane only ever touches its own bank, so no atomics)
+  // stage 4: the read-modify-writes (a lane only ever touches its own bank, so no atomics)
 #pragma unroll
-  for (int i = 0; i < kPer; ++i) h.col[k[i] * 32 + h.lane] += inc[i];
-  return outside_any;
+  for (int i = 0; i < kPer; ++i) h.col[g[i] * 32] += inc[i];
+  h.seen += kPer;
+  return (flags & 2u) != 0u;
 }
 
 template <int PDT, int TDT, bool SIG>
@@ -239,8 +323,8 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
   const int warp_in_cta = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   uint32_t* cols = sh_u32 + pad_words;
-  LaneHist h{cols + (int64_t)warp_in_cta * (a.T + 1) * 32, lane, 0};
-  for (int k = 0; k <= a.T; ++k) h.col[k * 32 + lane] = 0;
+  LaneHist h{cols + (int64_t)warp_in_cta * (a.T + 1) * 32 + lane, lane, 0};
+  for (int k = 0; k <= a.T; ++k) h.col[k * 32] = 0;
   __syncwarp();
 
   unsigned long long* gh = hist_base(a, SIG ? 1 : 0);
@@ -251,48 +335,71 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
   const int64_t step = gthreads * kBatch;
   bool stop = false, bad_target = false;
 
-  float xa[kPer], xb[kPer];
-  int64_t ta[kPer], tb[kPer];
-  auto fetch = [&](int64_t b, float (&x)[kPer], int64_t (&t)[kPer]) -> unsigned {
+  auto fetch_full = [&](int64_t b, Batch& s) {
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = b + lane + (int64_t)u * gthreads;
+      load_preds4<PDT>(a.preds, v * 4, &s.x[u * 4]);
+      load_targets4<TDT>(a.target, v * 4, &s.lo[u * 4], &s.hi[u * 4]);
+    }
+  };
+  // one batch: bin it, keep the pass-A flag protocol and the 16-bit counters safe
+  auto consume = [&](const Batch& s) {
+    bool mine = lane_batch<PDT, SIG, true>(a, bn, h, s, 0u, bad_target);
+    if (!SIG) {
+      if (mine) raise_flag(a);
+      stop = __any_sync(kFull, mine || flag_up(a));  // once anybody saw a logit the raw histogram is moot
+    }
+    if (h.seen > 65535u - (unsigned)kPer) lane_flush(a, h, gh);  // `seen` is identical in all lanes
+  };
+
+  // Full batches: `b` (the warp's first vector) is warp-uniform and b + 32 + (kBatch-1)*gthreads <= n_vec holds
+  // for every lane, so no masking.  Two register buffers alternate; the next batch is in flight while the
+  // current one is binned.
+  Batch A, B;
+  int64_t b = gtid - lane;
+  const int64_t last_full = n_vec - ((int64_t)(kBatch - 1) * gthreads + 32);  // b <= last_full  <=>  batch is full
+  bool have_a = b <= last_full;
+  if (have_a) fetch_full(b, A);
+  while (have_a && !stop) {
+    const bool have_b = (b + step) <= last_full;
+    if (have_b) fetch_full(b + step, B);
+    consume(A);
+    b += step;
+    if (!have_b || stop) {
+      have_a = false;
+      break;
+    }
+    have_a = (b + step) <= last_full;
+    if (have_a) fetch_full(b + step, A);
+    consume(B);
+    b += step;
+  }
+  // ragged remainder: at most one masked batch per warp
+  if (!stop && b < n_vec) {
+    Batch R;
     unsigned live = 0;
 #pragma unroll
     for (int u = 0; u < kBatch; ++u) {
       const int64_t v = b + lane + (int64_t)u * gthreads;
       if (v < n_vec) {
-        load_preds4<PDT>(a.preds, v * 4, *reinterpret_cast<float(*)[4]>(&x[u * 4]));
-        load_targets4<TDT>(a.target, v * 4, *reinterpret_cast<int64_t(*)[4]>(&t[u * 4]));
+        load_preds4<PDT>(a.preds, v * 4, &R.x[u * 4]);
+        load_targets4<TDT>(a.target, v * 4, &R.lo[u * 4], &R.hi[u * 4]);
         live |= 0xfu << (u * 4);
       } else {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          x[u * 4 + e] = 0.0f;
-          t[u * 4 + e] = 0;
+          R.x[u * 4 + e] = 0.0f;
+          R.lo[u * 4 + e] = 0u;
+          R.hi[u * 4 + e] = 0u;
         }
       }
     }
-    return live;
-  };
-
-  // `b` is warp-uniform so that every lane reaches the warp-collective calls below; the batch after the
-  // current one is fetched before the current one is processed (software pipelining)
-  int64_t b = gtid - lane;
-  unsigned live_a = (b < n_vec) ? fetch(b, xa, ta) : 0u;
-  while (b < n_vec && !stop) {
-    const int64_t b_next = b + step;
-    unsigned live_b = (b_next < n_vec) ? fetch(b_next, xb, tb) : 0u;
-    bool mine = lane_batch<PDT, SIG>(a, bn, h, xa, ta, live_a, bad_target);
+    bool mine = lane_batch<PDT, SIG, false>(a, bn, h, R, live, bad_target);
     if (!SIG) {
       if (mine) raise_flag(a);
-      stop = __any_sync(kFull, mine || flag_up(a));  // once anybody saw a logit the raw histogram is moot
+      stop = __any_sync(kFull, mine || flag_up(a));
     }
-    if (__any_sync(kFull, h.seen > 65535u - (unsigned)kPer)) lane_flush(a, h, gh);
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) {
-      xa[i] = xb[i];
-      ta[i] = tb[i];
-    }
-    live_a = live_b;
-    b = b_next;
   }
   // tail samples (n % 4) — handled by the first threads of CTA 0
   bool tail_stop = false;
@@ -310,8 +417,8 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
         if (t != 0 && t != 1) {
           bad_target = true;
         } else {
-          int k = bn.bin(SIG ? sigmoid_as<PDT>(x) : x);
-          h.col[k * 32 + lane] += t ? 0x10000u : 1u;
+          int k = exact_bin<PDT, SIG>(bn, x);
+          h.col[k * 32] += t ? 0x10000u : 1u;
         }
       }
     }
