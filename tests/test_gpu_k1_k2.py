@@ -432,6 +432,44 @@ def test_sigmoid_bits_match_torch_cuda():
     assert np.array_equal(m.confmat[:, 1, 1].cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("T", [200, 2, 1000])
+def test_binary_curve_saturated_and_special_logits(T):
+    """The filtered sigmoid must stay exact where the approximation is weakest: saturated logits (q within
+    1e-9 of the first / last threshold), huge magnitudes, infinities, NaN, denormal-producing inputs."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(99 + T)
+    n = 2_000_003
+    x = torch.randn(n, generator=g) * 15
+    x[::1001] = float("inf")
+    x[7::1003] = float("-inf")
+    x[11::1009] = float("nan")
+    x[13::1013] = 88.5
+    x[17::1019] = -88.5
+    x[19::1021] = -103.9
+    x[23::1031] = 0.0
+    target = torch.randint(2, (n,), generator=g)
+    m = BinaryPrecisionRecallCurve(thresholds=T, validate_args=False).cuda()
+    m.update(x.cuda(), target.cuda())
+    want = O.binary_curve_binned(x.numpy(), target.numpy(), torch.linspace(0, 1, T).numpy(), sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+
+
+def test_binary_curve_uneven_thresholds_with_logits():
+    """Thresholds off the even grid take the compare-against-the-buffer path of the filtered sigmoid."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(123)
+    n = 1_000_001
+    x = torch.randn(n, generator=g) * 4
+    target = torch.randint(2, (n,), generator=g)
+    thr = torch.sort(torch.rand(150, generator=g) ** 3).values
+    m = BinaryPrecisionRecallCurve(thresholds=thr, validate_args=False).cuda()
+    m.update(x.cuda(), target.cuda())
+    want = O.binary_curve_binned(x.numpy(), target.numpy(), thr.numpy(), sigmoid_fn=cuda_sigmoid)
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+
+
 # ------------------------------------------------------------------------------------------ Metric classes end to end
 def test_collection_config1_matches_oracle():
     """BASELINE config 1: MetricCollection([MulticlassAccuracy, MulticlassConfusionMatrix]), 10 updates."""

@@ -88,6 +88,14 @@ __device__ __forceinline__ uint16_t ldg_stream2(const void* p) {
   return r;
 }
 
+// pull the 128-byte line holding `p` into L2 without occupying a register or a scoreboard slot
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+__host__ __device__ constexpr int label_bytes_dev(int dtype) {
+  return dtype == TMB_I64 ? 8 : (dtype == TMB_I32 ? 4 : (dtype == TMB_I16 ? 2 : 1));
+}
+
 // ---- element decoding ---------------------------------------------------------------------------
 // Every float dtype is widened to fp32 exactly (bf16/f16 -> f32 is lossless), so comparisons give
 // the same answer torch gets when it compares the narrow values.

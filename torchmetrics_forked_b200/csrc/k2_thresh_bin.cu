@@ -67,6 +67,11 @@ struct Binner {
   const float* pad;  // shared or global, T + 2 entries
   int T;
   float lo, scale;  // guess = (q - lo) * scale
+  // u(q) = fmaf(q, scale, 1 - lo*scale) maps threshold j to (nearly) the integer j + 1.  grid_eps is the largest
+  // distance of any u(thr[j]) from j + 1: because u() is monotone in q, a sample whose u lies further than grid_eps
+  // from every integer is on a known side of every threshold — no compare against the buffer needed.  A small
+  // grid_eps means the thresholds are (numerically) evenly spaced, e.g. torch.linspace.
+  float grid_eps;
   bool gt;
   __device__ __forceinline__ bool below(float t, float q) const { return gt ? (t < q) : (t <= q); }
   __device__ __forceinline__ int guess(float q) const {
@@ -78,7 +83,7 @@ struct Binner {
   __device__ __forceinline__ bool verified(int g, float q) const {
     return (below(pad[g], q) && !below(pad[g + 1], q)) || (q != q && g == 0);
   }
-  __device__ __noinline__ int bisect(float q) const {  // cold path: guess was off
+  __device__ __forceinline__ int bisect(float q) const {  // cold path: guess was off
     int lo_i = 0, hi_i = T;
     while (lo_i < hi_i) {
       int mid = (lo_i + hi_i) >> 1;
@@ -110,6 +115,19 @@ __device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_pad, in
   float span = hi - lo;
   b.lo = lo;
   b.scale = (span > 0.0f && a.T > 1) ? (float)(a.T - 1) / span : 0.0f;
+  // how far the thresholds are from the evenly spaced grid, in bins (CTA-wide maximum)
+  __shared__ unsigned grid_eps_bits;
+  if (threadIdx.x == 0) grid_eps_bits = 0u;
+  __syncthreads();
+  const float bias = 1.0f - lo * b.scale;
+  float worst = 0.0f;
+  for (int j = threadIdx.x; j < a.T; j += blockDim.x) {
+    float d = fabsf(fmaf(a.thr[j], b.scale, bias) - (float)(j + 1));
+    worst = (d == d) ? fmaxf(worst, d) : INFINITY;
+  }
+  atomicMax(&grid_eps_bits, __float_as_uint(worst));  // non-negative floats order like their bit patterns
+  __syncthreads();
+  b.grid_eps = (b.scale > 0.0f) ? __uint_as_float(grid_eps_bits) : INFINITY;
   return b;
 }
 
@@ -196,9 +214,16 @@ __device__ __forceinline__ void lane_flush(const TbArgs& a, LaneHist& h, unsigne
 constexpr int kBatch = 4;         // vectors of 4 samples per thread per iteration
 constexpr int kPer = kBatch * 4;  // samples per thread per iteration
 
-struct Batch {
+struct Batch {  // what the loads deliver
   float x[kPer];
   uint32_t lo[kPer], hi[kPer];
+};
+
+struct Decoded {  // what is left of a batch once its registers have been released to the next loads
+  float x[kPer];
+  uint32_t inc[kPer];  // 0 = not counted, 1 = negative, 0x10000 = positive
+  unsigned counted;    // bit i: sample i takes part
+  unsigned flags;      // bit 0: invalid target seen, bit 1: value outside [0,1] seen (pass A)
 };
 
 // Filtered exact binning of sigmoid(x) (fp32 only).  The bin only changes when q crosses a threshold, so the
@@ -210,9 +235,9 @@ struct Batch {
 //   1 + e          : 0.5 ulp;   approximate reciprocal: 1 ulp
 //   q itself       : torch's expression is within 3 ulp of the true value
 // so |qa - q| <= (6.5 + 1.173|x|) ulp * q.  The margin used is twice that, rel(x) = 1.6e-6 + 2.9e-7|x|, plus
-// 1e-30 absolute for the flushed-to-zero ends (|x| > 87, where both expressions saturate at 0 / 1).  If both
-// neighbours of the guessed bin clear qa by more than the margin the bin is certain; otherwise (about 0.2 % of
-// the samples at T = 200) the sample is re-done with the exact expression.  The result is bit-identical to
+// 1e-30 absolute for the flushed-to-zero ends (|x| > 87, where both expressions saturate at 0 / 1).  If the
+// approximate score clears every threshold by more than the margin the bin is certain; otherwise (about 0.2 %
+// of the samples at T = 200) the sample is re-done with the exact expression.  The result is bit-identical to
 // binning torch's sigmoid at a third of the instructions.
 __device__ __forceinline__ float ex2_approx(float x) {
   float y;
@@ -225,22 +250,68 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 
+// Cold path.  Arguments by value so that the caller's Binner stays in registers (a by-reference call put it in
+// local memory and the reloads showed up as long-scoreboard stalls): exact score, then guess / verify / bisect
+// against the threshold buffer.
 template <int PDT, bool SIG>
-__device__ __noinline__ int exact_bin(const Binner& bn, float x) {
-  return bn.bin(SIG ? sigmoid_as<PDT>(x) : x);
+__device__ __noinline__ int exact_bin(const float* pad, int T, float lo, float scale, bool gt, float x) {
+  Binner b;
+  b.pad = pad;
+  b.T = T;
+  b.lo = lo;
+  b.scale = scale;
+  b.gt = gt;
+  b.grid_eps = 0.0f;
+  if (SIG && PDT == TMB_F32) {
+    // The grid test loses its resolution right at the first / last threshold, where saturated sigmoids pile up
+    // (q ~ 1e-9 is certainly above a threshold of 0, yet u(q) rounds onto the integer).  Before paying for the
+    // exact expression, bracket the score: the bin is monotone in q, so if q - margin and q + margin fall into
+    // the same bin of the real threshold buffer, that is the bin.
+    const float q = rcp_approx(1.0f + ex2_approx(x * -1.4426950408889634f));
+    const float margin = fmaf(q, fmaf(fabsf(x), 2.9e-7f, 1.6e-6f), 1e-30f);
+    if (margin < 1.0f) {  // false for NaN / infinite inputs: those go straight to the exact expression
+      const int k_low = b.bin(q - margin), k_high = b.bin(q + margin);
+      if (k_low == k_high) return k_low;
+    }
+  }
+  return b.bin(SIG ? sigmoid_as<PDT>(x) : x);
 }
 
-// Classify and bin kPer samples held in registers.  FULL = every slot holds a real sample (no `live` mask).
-// Written stage by stage over all kPer samples (not sample by sample) so that the kPer dependency chains are
-// interleaved: with 8 warps per SM, instruction-level parallelism is what hides the MUFU / LDS latencies.
-// Returns true if pass A saw a value outside [0,1].
-template <int PDT, bool SIG, bool FULL>
-__device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, LaneHist& h, const Batch& s,
-                                           unsigned live, bool& bad_target) {
+// First touch of a freshly loaded batch: everything that depends on the targets, and a copy of the scores.
+// After this the load registers are dead, so the NEXT batch can be requested into them right away; the wait
+// that precedes this function therefore only ever covers loads that are really needed now.  (With two register
+// buffers the wait for batch i also waited for the just-issued loads of batch i+1 whenever both shared one of
+// the six scoreboard slots — 21 % of the kernel's stall samples sat on that one instruction.)
+template <bool SIG, bool FULL>
+__device__ __forceinline__ void decode_batch(const TbArgs& a, const Batch& s, unsigned live, Decoded& d) {
+  const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
+  d.counted = 0;
+  d.flags = 0;
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
+    const unsigned is_live = FULL ? 1u : ((live >> i) & 1u);
+    const unsigned ignored = a.has_ignore ? (unsigned)((s.lo[i] == ign_lo) & (s.hi[i] == ign_hi)) : 0u;
+    const unsigned zero_or_one = (unsigned)((s.hi[i] | (s.lo[i] >> 1)) == 0u);
+    const unsigned counted = is_live & (ignored ^ 1u) & zero_or_one;
+    d.counted |= counted << i;
+    d.flags |= is_live & (ignored ^ 1u) & (zero_or_one ^ 1u);
+    if (!SIG) {
+      const unsigned outside = (unsigned)!(s.x[i] >= 0.0f && s.x[i] <= 1.0f);
+      d.flags |= (is_live & outside & ((ignored ^ 1u) | (unsigned)(a.flag_counts_ignored != 0))) << 1;
+    }
+    d.inc[i] = counted ? (s.lo[i] * 0xffffu + 1u) : 0u;  // 1 for a negative, 0x10000 for a positive
+    d.x[i] = s.x[i];
+  }
+}
+
+// Bin kPer decoded samples.  Written stage by stage over all kPer samples (not sample by sample) so that the
+// kPer dependency chains are interleaved: with 8 warps per SM, instruction-level parallelism is what hides the
+// MUFU / LDS latencies.  GRID = thresholds on a (numerically) even grid: certainty comes from arithmetic alone.
+template <int PDT, bool SIG, bool GRID>
+__device__ __forceinline__ void bin_batch(const Binner& bn, LaneHist& h, const Decoded& d) {
   constexpr bool kFiltered = SIG && PDT == TMB_F32;
-  float q[kPer], lowq[kPer], highq[kPer];
+  float q[kPer], lowq[kPer], highq[kPer], slack[kPer];
   int g[kPer];
-  uint32_t inc[kPer];
   const float bias = 1.0f - bn.lo * bn.scale;
   const float top = (float)bn.T;
 
@@ -248,46 +319,56 @@ __device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, La
   if (kFiltered) {
     float e[kPer];
 #pragma unroll
-    for (int i = 0; i < kPer; ++i) e[i] = ex2_approx(s.x[i] * -1.4426950408889634f);
+    for (int i = 0; i < kPer; ++i) e[i] = ex2_approx(d.x[i] * -1.4426950408889634f);
 #pragma unroll
     for (int i = 0; i < kPer; ++i) q[i] = rcp_approx(1.0f + e[i]);
 #pragma unroll
     for (int i = 0; i < kPer; ++i) {
-      const float rel = fmaf(fabsf(s.x[i]), 2.9e-7f, 1.6e-6f);
+      const float rel = fmaf(fabsf(d.x[i]), 2.9e-7f, 1.6e-6f);
       const float margin = fmaf(q[i], rel, 1e-30f);
-      lowq[i] = q[i] - margin;
-      highq[i] = q[i] + margin;
+      if (GRID) {
+        // uncertainty of u(q) in bins: the score margin scaled, the grid's own unevenness, 2 ulp of u
+        slack[i] = fmaf(margin, bn.scale, bn.grid_eps + top * 2.4e-7f);
+      } else {
+        lowq[i] = q[i] - margin;
+        highq[i] = q[i] + margin;
+      }
     }
   } else {
 #pragma unroll
-    for (int i = 0; i < kPer; ++i) q[i] = SIG ? sigmoid_as<PDT>(s.x[i]) : s.x[i];
+    for (int i = 0; i < kPer; ++i) q[i] = SIG ? sigmoid_as<PDT>(d.x[i]) : d.x[i];
   }
-  // stage 2: guessed bin and its two neighbouring thresholds
+  // stage 2: guessed bin.  GRID: the distance of u(q) from the nearest integer decides whether the guess is
+  // certain; otherwise its two neighbouring thresholds are fetched and compared.
+  float below[kPer], above[kPer], off_centre[kPer];
+  if (GRID) {
 #pragma unroll
-  for (int i = 0; i < kPer; ++i) g[i] = (int)fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.0f), top);  // NaN -> 0
-  float below[kPer], above[kPer];
-#pragma unroll
-  for (int i = 0; i < kPer; ++i) {
-    below[i] = bn.pad[g[i]];
-    above[i] = bn.pad[g[i] + 1];
-  }
-  // stage 3: is the guess certain?  which counter does the sample bump?
-  unsigned recheck = 0;
-  unsigned flags = 0;  // bit 0: invalid target seen, bit 1: value outside [0,1] seen (pass A)
-  const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
-#pragma unroll
-  for (int i = 0; i < kPer; ++i) {
-    const unsigned is_live = FULL ? 1u : ((live >> i) & 1u);
-    const unsigned ignored = a.has_ignore ? (unsigned)((s.lo[i] == ign_lo) & (s.hi[i] == ign_hi)) : 0u;
-    const unsigned zero_or_one = (unsigned)((s.hi[i] | (s.lo[i] >> 1)) == 0u);
-    const unsigned counted = is_live & (ignored ^ 1u) & zero_or_one;
-    flags |= is_live & (ignored ^ 1u) & (zero_or_one ^ 1u);
-    if (!SIG) {
-      const unsigned outside = (unsigned)!(s.x[i] >= 0.0f && s.x[i] <= 1.0f);
-      flags |= (is_live & outside & ((ignored ^ 1u) | (unsigned)(a.flag_counts_ignored != 0))) << 1;
+    for (int i = 0; i < kPer; ++i) {
+      // below the first / above the last threshold (and NaN) clamp to the middle of the end bins: certain
+      const float u = fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.5f), top + 0.5f);
+      const float fl = floorf(u);
+      g[i] = (int)fl;
+      off_centre[i] = fabsf((u - fl) - 0.5f);  // 0 in the middle of a bin, 0.5 on a threshold
     }
+  } else {
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) g[i] = (int)fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.0f), top);  // NaN -> 0
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+      below[i] = bn.pad[g[i]];
+      above[i] = bn.pad[g[i] + 1];
+    }
+  }
+  // stage 3: is the guess certain?
+  unsigned unsure = 0;
+#pragma unroll
+  for (int i = 0; i < kPer; ++i) {
     unsigned sure;
-    if (kFiltered) {
+    if (GRID) {
+      // exact scores only carry the grid's unevenness; approximate ones add their own margin (see stage 1)
+      const float allowed = kFiltered ? slack[i] : bn.grid_eps;
+      sure = (unsigned)(off_centre[i] + allowed < 0.5f);
+    } else if (kFiltered) {
       // certain for `>=` thresholds and for `>` thresholds alike: q lies strictly between the neighbours
       sure = (unsigned)((below[i] < lowq[i]) & (highq[i] < above[i]));
     } else {
@@ -295,21 +376,37 @@ __device__ __forceinline__ bool lane_batch(const TbArgs& a, const Binner& bn, La
       const unsigned hi_ok = bn.gt ? (unsigned)!(above[i] < q[i]) : (unsigned)!(above[i] <= q[i]);
       sure = (lo_ok & hi_ok) | (unsigned)((q[i] != q[i]) & (g[i] == 0));
     }
-    recheck |= ((sure ^ 1u) & counted) << i;
-    inc[i] = counted ? (s.lo[i] * 0xffffu + 1u) : 0u;  // 1 for a negative, 0x10000 for a positive
+    unsure |= (sure ^ 1u) << i;
   }
-  bad_target |= (flags & 1u) != 0u;
   // cold path: too close to a threshold for the approximation, or a guess that missed
+  const unsigned recheck = unsure & d.counted;
   if (recheck) {
 #pragma unroll
     for (int i = 0; i < kPer; ++i)
-      if ((recheck >> i) & 1u) g[i] = exact_bin<PDT, SIG>(bn, s.x[i]);
+      if ((recheck >> i) & 1u) g[i] = exact_bin<PDT, SIG>(bn.pad, bn.T, bn.lo, bn.scale, bn.gt, d.x[i]);
   }
-  // stage 4: the read-modify-writes (a lane only ever touches its own bank, so no atomics)
+  // stage 4: the read-modify-writes (a lane only ever touches its own bank, so no atomics).  Done four at a
+  // time: the four loads are issued together, a sample whose bin repeats an earlier one of the group takes that
+  // one's updated value instead of its own (stale) load, and the stores go out in order so the last writer of
+  // a bin holds the complete count.  This cuts the LDS->IADD->STS dependency chain from 16 links to 4.
 #pragma unroll
-  for (int i = 0; i < kPer; ++i) h.col[g[i] * 32] += inc[i];
+  for (int i = 0; i < kPer; i += 4) {
+    uint32_t* p0 = h.col + g[i] * 32;
+    uint32_t* p1 = h.col + g[i + 1] * 32;
+    uint32_t* p2 = h.col + g[i + 2] * 32;
+    uint32_t* p3 = h.col + g[i + 3] * 32;
+    const uint32_t v0 = *p0, v1 = *p1, v2 = *p2, v3 = *p3;
+    const uint32_t u0 = v0 + d.inc[i];
+    const uint32_t u1 = (g[i + 1] == g[i] ? u0 : v1) + d.inc[i + 1];
+    const uint32_t u2 = (g[i + 2] == g[i + 1] ? u1 : (g[i + 2] == g[i] ? u0 : v2)) + d.inc[i + 2];
+    const uint32_t u3 =
+        (g[i + 3] == g[i + 2] ? u2 : (g[i + 3] == g[i + 1] ? u1 : (g[i + 3] == g[i] ? u0 : v3))) + d.inc[i + 3];
+    *p0 = u0;
+    *p1 = u1;
+    *p2 = u2;
+    *p3 = u3;
+  }
   h.seen += kPer;
-  return (flags & 2u) != 0u;
 }
 
 template <int PDT, int TDT, bool SIG>
@@ -320,6 +417,7 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
   float* sh_pad = (float*)sh_u32;  // [T + 2] padded thresholds, then the lane histograms
   const int pad_words = (a.T + 2 + 31) / 32 * 32;
   Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);
+  const bool on_grid = bn.grid_eps < 0.01f;  // CTA-uniform: thresholds within 1 % of a bin of an even grid
   const int warp_in_cta = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   uint32_t* cols = sh_u32 + pad_words;
@@ -343,10 +441,11 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
       load_targets4<TDT>(a.target, v * 4, &s.lo[u * 4], &s.hi[u * 4]);
     }
   };
-  // one batch: bin it, keep the pass-A flag protocol and the 16-bit counters safe
-  auto consume = [&](const Batch& s) {
-    bool mine = lane_batch<PDT, SIG, true>(a, bn, h, s, 0u, bad_target);
+  // after a batch is binned: the pass-A flag protocol, and keeping the 16-bit counters from overflowing
+  auto after_batch = [&](const Decoded& d) {
+    bad_target |= (d.flags & 1u) != 0u;
     if (!SIG) {
+      const bool mine = (d.flags & 2u) != 0u;
       if (mine) raise_flag(a);
       stop = __any_sync(kFull, mine || flag_up(a));  // once anybody saw a logit the raw histogram is moot
     }
@@ -354,52 +453,70 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
   };
 
   // Full batches: `b` (the warp's first vector) is warp-uniform and b + 32 + (kBatch-1)*gthreads <= n_vec holds
-  // for every lane, so no masking.  Two register buffers alternate; the next batch is in flight while the
-  // current one is binned.
-  Batch A, B;
+  // for every lane, so no masking.  One load buffer: a batch is decoded (first touch), the next one is requested
+  // into the same registers, then the decoded one is binned while those loads are in flight.
+  Batch S;
+  Decoded D;
   int64_t b = gtid - lane;
   const int64_t last_full = n_vec - ((int64_t)(kBatch - 1) * gthreads + 32);  // b <= last_full  <=>  batch is full
-  bool have_a = b <= last_full;
-  if (have_a) fetch_full(b, A);
-  while (have_a && !stop) {
-    const bool have_b = (b + step) <= last_full;
-    if (have_b) fetch_full(b + step, B);
-    consume(A);
-    b += step;
-    if (!have_b || stop) {
-      have_a = false;
-      break;
+  // With 8 warps per SM one batch of register loads in flight (48 KB per SM) covers only half of the ~90 KB that
+  // HBM latency x bandwidth asks for, and a second register buffer does not help (see decode_batch).  So the
+  // batches further ahead are pulled into L2 with prefetch instructions, which occupy neither registers nor
+  // scoreboard slots; the register loads then only have to hide L2 latency.
+  auto prefetch_batch = [&](int64_t bb) {
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = bb + lane + (int64_t)u * gthreads;
+      const char* pp = (const char*)a.preds + v * 4 * Elem<PDT>::kBytes;
+      const char* tp = (const char*)a.target + v * 4 * label_bytes_dev(TDT);
+      if ((lane & 7) == 0) prefetch_l2(pp);  // one request per 128-byte line is enough
+      if (label_bytes_dev(TDT) == 8 || (lane & 7) == 0) {
+        if (label_bytes_dev(TDT) != 8 || (lane & 3) == 0) prefetch_l2(tp);
+      }
     }
-    have_a = (b + step) <= last_full;
-    if (have_a) fetch_full(b + step, A);
-    consume(B);
+  };
+  constexpr int kAhead = 3;  // batches ahead of the register loads that are requested into L2
+  bool have = b <= last_full;
+  if (have) {
+    fetch_full(b, S);
+#pragma unroll
+    for (int p = 1; p <= kAhead; ++p)
+      if (b + p * step <= last_full) prefetch_batch(b + p * step);
+  }
+  while (have && !stop) {
+    decode_batch<SIG, true>(a, S, 0u, D);
     b += step;
+    have = b <= last_full;
+    if (have) fetch_full(b, S);
+    if (b + kAhead * step <= last_full) prefetch_batch(b + kAhead * step);
+    if (on_grid)
+      bin_batch<PDT, SIG, true>(bn, h, D);
+    else
+      bin_batch<PDT, SIG, false>(bn, h, D);
+    after_batch(D);
   }
   // ragged remainder: at most one masked batch per warp
   if (!stop && b < n_vec) {
-    Batch R;
     unsigned live = 0;
 #pragma unroll
     for (int u = 0; u < kBatch; ++u) {
       const int64_t v = b + lane + (int64_t)u * gthreads;
       if (v < n_vec) {
-        load_preds4<PDT>(a.preds, v * 4, &R.x[u * 4]);
-        load_targets4<TDT>(a.target, v * 4, &R.lo[u * 4], &R.hi[u * 4]);
+        load_preds4<PDT>(a.preds, v * 4, &S.x[u * 4]);
+        load_targets4<TDT>(a.target, v * 4, &S.lo[u * 4], &S.hi[u * 4]);
         live |= 0xfu << (u * 4);
       } else {
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          R.x[u * 4 + e] = 0.0f;
-          R.lo[u * 4 + e] = 0u;
-          R.hi[u * 4 + e] = 0u;
+          S.x[u * 4 + e] = 0.0f;
+          S.lo[u * 4 + e] = 0u;
+          S.hi[u * 4 + e] = 0u;
         }
       }
     }
-    bool mine = lane_batch<PDT, SIG, false>(a, bn, h, R, live, bad_target);
-    if (!SIG) {
-      if (mine) raise_flag(a);
-      stop = __any_sync(kFull, mine || flag_up(a));
-    }
+    decode_batch<SIG, false>(a, S, live, D);
+    bin_batch<PDT, SIG, false>(bn, h, D);
+    after_batch(D);
   }
   // tail samples (n % 4) — handled by the first threads of CTA 0
   bool tail_stop = false;
@@ -417,7 +534,7 @@ __global__ void __launch_bounds__(256, 1) k2_binary_lanes(TbArgs a, int warps_pe
         if (t != 0 && t != 1) {
           bad_target = true;
         } else {
-          int k = exact_bin<PDT, SIG>(bn, x);
+          int k = exact_bin<PDT, SIG>(bn.pad, bn.T, bn.lo, bn.scale, bn.gt, x);
           h.col[k * 32] += t ? 0x10000u : 1u;
         }
       }

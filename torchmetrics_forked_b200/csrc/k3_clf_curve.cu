@@ -90,6 +90,103 @@ __global__ void __launch_bounds__(256) k3_normalize(const void* __restrict__ x, 
   }
 }
 
+// 16-byte vector versions (aligned pointers, every element takes part in the test): U vectors in flight per thread
+template <int DT>
+struct VecIO {
+  static constexpr int kElems = 16 / Elem<DT>::kBytes;
+  __device__ static __forceinline__ void load(const void* base, int64_t v, float (&x)[kElems]) {
+    uint4 r = ldg_stream16((const char*)base + v * 16);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int e = 0; e < kElems; ++e)
+      x[e] = (kElems == 4) ? Elem<DT>::get(w[e], 0) : Elem<DT>::get(w[e >> 1], e & 1);
+  }
+  __device__ static __forceinline__ void store(void* base, int64_t v, const float (&x)[kElems]) {
+    uint32_t w[4];
+    if constexpr (DT == TMB_F32) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) w[e] = __float_as_uint(x[e]);
+    } else if constexpr (DT == TMB_BF16) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        __nv_bfloat162 p = __floats2bfloat162_rn(x[2 * e], x[2 * e + 1]);
+        w[e] = *reinterpret_cast<uint32_t*>(&p);
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        __half2 p = __floats2half2_rn(x[2 * e], x[2 * e + 1]);
+        w[e] = *reinterpret_cast<uint32_t*>(&p);
+      }
+    }
+    *reinterpret_cast<uint4*>((char*)base + v * 16) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
+template <int DT>
+__global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restrict__ x, int64_t n_vec,
+                                                           unsigned long long* flag, unsigned long long gen) {
+  constexpr int E = VecIO<DT>::kElems;
+  constexpr int U = 4;
+  __shared__ int go;
+  if (threadIdx.x == 0) go = *((volatile unsigned long long*)flag) != gen;
+  __syncthreads();
+  if (!go) return;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int lane = threadIdx.x & 31;
+  bool found = false;
+  // the loop variable is warp-uniform so that the vote below is reached by the whole warp
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x - lane; b < n_vec; b += stride * U) {
+    float v[U][E];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = b + lane + (int64_t)u * stride;
+      if (i < n_vec) {
+        VecIO<DT>::load(x, i, v[u]);
+      } else {
+#pragma unroll
+        for (int e = 0; e < E; ++e) v[u][e] = 0.0f;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int e = 0; e < E; ++e) found |= !(v[u][e] >= 0.0f && v[u][e] <= 1.0f);
+    if (__any_sync(kFull, found)) break;
+    if (*((volatile unsigned long long*)flag) == gen) break;  // another CTA already settled it
+  }
+  if (found) atomicMax(flag, gen);
+}
+
+template <int DT>
+__global__ void __launch_bounds__(256) k3_normalize_vec(const void* __restrict__ x, void* __restrict__ out,
+                                                        int64_t n_vec, const unsigned long long* flag,
+                                                        unsigned long long gen) {
+  constexpr int E = VecIO<DT>::kElems;
+  constexpr int U = 4;
+  const bool sig = *flag == gen;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_vec; b += stride * U) {
+    float v[U][E];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = b + (int64_t)u * stride;
+      if (i < n_vec) VecIO<DT>::load(x, i, v[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = b + (int64_t)u * stride;
+      if (i < n_vec) {
+        if (sig) {
+#pragma unroll
+          for (int e = 0; e < E; ++e) v[u][e] = sigmoid_round<DT>(v[u][e]);
+        }
+        VecIO<DT>::store(out, i, v[u]);
+      }
+    }
+  }
+}
+
 // ---- pack: [N, L] row-major -> label-major keys ----------------------------------------------------------------
 template <int DT>
 __global__ void __launch_bounds__(256) k3_pack(const void* __restrict__ preds, const void* __restrict__ target, int tdt,
@@ -458,11 +555,39 @@ static CurvePlan curve_plan(int64_t N, int64_t L) {
 template <int DT>
 static int run_normalize(const void* x, void* out, int64_t n, const void* target, int tdt, int has_ignore,
                          int64_t ignore, unsigned long long* flag, unsigned long long gen, cudaStream_t st) {
-  const int grid = wave_grid((n + 255) / 256, 8);
-  k3_outside_flag<DT><<<grid, 256, 0, st>>>(x, n, target, tdt, has_ignore, ignore, flag, gen);
-  if (int rc = launch_status()) return rc;
-  k3_normalize<DT><<<grid, 256, 0, st>>>(x, out, n, flag, gen);
-  return launch_status();
+  constexpr int E = VecIO<DT>::kElems;
+  constexpr int ES = Elem<DT>::kBytes;
+  const bool aligned = (((uintptr_t)x | (uintptr_t)out) & 15) == 0;
+  const bool test_all = !(target != nullptr && has_ignore);
+  const int64_t n_vec = aligned ? n / E : 0;          // elements [0, n_vec*E) go through the vector kernels
+  const int64_t tail0 = n_vec * E, n_tail = n - tail0;  // the rest through the scalar ones
+  const char* x_tail = (const char*)x + tail0 * ES;
+  char* out_tail = (char*)out + tail0 * ES;
+  const void* t_tail = target ? (const char*)target + tail0 * label_bytes(tdt) : nullptr;
+  // pass A: is any tested element outside [0,1]?
+  if (test_all && n_vec > 0) {
+    auto k = k3_outside_flag_vec<DT>;
+    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 4 - 1) / (256 * 4)), 256, 0, st>>>(x, n_vec, flag, gen);
+    if (int rc = launch_status()) return rc;
+    if (n_tail > 0) {
+      k3_outside_flag<DT><<<1, 256, 0, st>>>(x_tail, n_tail, t_tail, tdt, has_ignore, ignore, flag, gen);
+      if (int rc = launch_status()) return rc;
+    }
+  } else {
+    k3_outside_flag<DT><<<wave_grid((n + 255) / 256, 8), 256, 0, st>>>(x, n, target, tdt, has_ignore, ignore, flag, gen);
+    if (int rc = launch_status()) return rc;
+  }
+  // pass B: copy or sigmoid
+  if (n_vec > 0) {
+    auto k = k3_normalize_vec<DT>;
+    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 4 - 1) / (256 * 4)), 256, 0, st>>>(x, out, n_vec, flag, gen);
+    if (int rc = launch_status()) return rc;
+  }
+  if (n_tail > 0) {
+    k3_normalize<DT><<<wave_grid((n_tail + 255) / 256, 8), 256, 0, st>>>(x_tail, out_tail, n_tail, flag, gen);
+    if (int rc = launch_status()) return rc;
+  }
+  return 0;
 }
 
 }  // namespace tmb
