@@ -269,6 +269,11 @@ def extras_block(device, steps: int, warmup: int, peak: float):
         for _ in range(upd):
             batches.append((torch.randn(n4, L4, generator=g, device=device),
                             torch.randint(2, (n4, L4), generator=g, device=device)))
+        # epoch 0 warms torch's caching allocator (the stored scores are 839 MB per update); epoch 1 is timed
+        for p, t in batches:
+            m.update(p, t)
+        m.compute()
+        m.reset()
         torch.cuda.synchronize()
         for i, (p, t) in enumerate(batches):
             ev[i].record()
@@ -325,6 +330,10 @@ def run_ours(args):
     def tail():  # one compute() per epoch of updates: packed all-reduce of the 8 MB state when world > 1
         result["confmat"] = metric.compute()
 
+    # untimed: one update + compute() so that the NCCL communicator and the allocator are warm before the W warm-up
+    # steps (compute() does not change the local state; the extra update is accounted for in the check below)
+    step()
+    tail()
     with ClockSampler(local) as clocks:
         total_ms, kernel_ms = timed_loop(step, args.steps, args.warmup, world, device, tail=tail)
     clk = clocks.summary()
@@ -335,7 +344,7 @@ def run_ours(args):
 
     # sanity: every sample of every update landed in the state exactly once
     seen = int(result["confmat"].sum().item())
-    expect = rows * world * (args.steps + args.warmup)
+    expect = rows * world * (args.steps + args.warmup + 1)
     assert seen == expect, f"confusion matrix holds {seen} samples, expected {expect}"
 
     # end to end through the public API from pinned host memory
