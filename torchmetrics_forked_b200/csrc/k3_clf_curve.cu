@@ -309,7 +309,7 @@ __global__ void __launch_bounds__(1024) k3_scan_u32(uint32_t* __restrict__ data,
 // sector transaction per 4-byte key).
 constexpr int kScatterSmem = (kSortWarps * 256 + 256 + 256 + kSortTile) * 4;  // 51 200 B, needs the opt-in
 
-__global__ void __launch_bounds__(kSortThreads) k3_sort_scatter(const uint32_t* __restrict__ in,
+__global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_t* __restrict__ in,
                                                                 uint32_t* __restrict__ out, int64_t N, int shift,
                                                                 const uint32_t* __restrict__ scanned, int nb) {
   extern __shared__ uint32_t sm[];
@@ -337,7 +337,15 @@ __global__ void __launch_bounds__(kSortThreads) k3_sort_scatter(const uint32_t* 
   for (int r = 0; r < kSortItems; ++r) {
     const bool valid = (start + r * 32 + lane) < N;
     const uint32_t d = (key[r] >> shift) & 255u;
-    const unsigned peers = __match_any_sync(kFull, valid ? d : (0x100u | lane));
+    // lanes holding the same digit, from eight ballots (one per digit bit).  match.any gives the same mask in one
+    // instruction, but its latency grows with the number of distinct values in the warp (~28 for random digits)
+    // and made the ranking, not the memory traffic, the cost of this kernel.
+    unsigned peers = __ballot_sync(kFull, valid);
+#pragma unroll
+    for (int bit = 0; bit < 8; ++bit) {
+      const unsigned set = __ballot_sync(kFull, (d >> bit) & 1u);
+      peers &= ((d >> bit) & 1u) ? set : ~set;
+    }
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
     if (lane == leader && valid) {
@@ -399,18 +407,31 @@ constexpr int kCurveThreads = 256;
 constexpr int kCurveItems = 16;
 constexpr int kCurveTile = kCurveThreads * kCurveItems;  // 4096
 
+// Shared staging of one tile of sorted keys.  A thread owns 16 CONSECUTIVE positions (the scan needs that), but
+// loading them straight from global memory makes every warp load touch 32 different 64-byte pieces; so the tile
+// (plus the one key after it, for the last boundary test) is brought in with full-width coalesced loads and
+// re-read from shared memory.  Word i lives at i + i/32: with that skew the 32 threads of a warp reading "their
+// j-th key" (stride 16 words) hit 32 different banks.
+constexpr int kKeyWords = kCurveTile + 1 + (kCurveTile + 1) / 32 + 1;
+__device__ __forceinline__ int skew(int i) { return i + (i >> 5); }
+
 struct CurveItems {
   uint32_t pos[kCurveItems];  // 1 for a counted positive
   uint32_t bnd[kCurveItems];  // 1 where a threshold ends
   float score[kCurveItems];
 };
 
-// thread `t` of tile `blk` owns the 16 consecutive sorted positions starting at i0
-__device__ __forceinline__ void curve_load(const uint32_t* __restrict__ k, int64_t N, int64_t nv, int64_t i0,
-                                           CurveItems& it, uint32_t& pos_sum, uint32_t& bnd_sum) {
+// stage tile `blk` of the segment starting at `k`; then thread t decodes positions tile0 + 16 t ... + 15
+__device__ __forceinline__ void curve_load(const uint32_t* __restrict__ k, int64_t N, int64_t nv, int64_t tile0,
+                                           uint32_t* sh_keys, CurveItems& it, uint32_t& pos_sum, uint32_t& bnd_sum) {
+  for (int i = threadIdx.x; i <= kCurveTile; i += kCurveThreads)
+    sh_keys[skew(i)] = (tile0 + i < N) ? k[tile0 + i] : kSentinel;
+  __syncthreads();
+  const int base = threadIdx.x * kCurveItems;
   uint32_t key[kCurveItems + 1];
 #pragma unroll
-  for (int j = 0; j <= kCurveItems; ++j) key[j] = (i0 + j < N) ? k[i0 + j] : kSentinel;
+  for (int j = 0; j <= kCurveItems; ++j) key[j] = sh_keys[skew(base + j)];
+  const int64_t i0 = tile0 + base;
   pos_sum = 0;
   bnd_sum = 0;
 #pragma unroll
@@ -457,19 +478,20 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_b
   return before + incl - v;
 }
 
-// partials[(seg * ntile + tile) * 2 + {0,1}] = positives / boundaries inside the tile
+// pos_part / bnd_part[seg * ntile + tile] = positives / boundaries inside the tile
 __global__ void __launch_bounds__(kCurveThreads) k3_curve_partials(const uint32_t* __restrict__ keys, int64_t N,
                                                                    const unsigned long long* __restrict__ n_valid,
                                                                    uint32_t* __restrict__ pos_part,
                                                                    uint32_t* __restrict__ bnd_part, int ntile) {
   __shared__ uint32_t buf[kCurveThreads / 32];
+  __shared__ uint32_t sh_keys[kKeyWords];
   const int seg = blockIdx.y, blk = blockIdx.x;
   const int64_t nv = (int64_t)n_valid[seg];
-  const int64_t i0 = (int64_t)blk * kCurveTile + (int64_t)threadIdx.x * kCurveItems;
+  const int64_t tile0 = (int64_t)blk * kCurveTile;
   uint32_t ps = 0, bs = 0;
-  if ((int64_t)blk * kCurveTile < nv) {  // CTA-uniform
+  if (tile0 < nv) {  // CTA-uniform
     CurveItems it;
-    curve_load(keys + (int64_t)seg * N, N, nv, i0, it, ps, bs);
+    curve_load(keys + (int64_t)seg * N, N, nv, tile0, sh_keys, it, ps, bs);
   }
   uint32_t tot_p, tot_b;
   block_excl_scan(ps, buf, tot_p);
@@ -480,36 +502,50 @@ __global__ void __launch_bounds__(kCurveThreads) k3_curve_partials(const uint32_
   }
 }
 
+// The curve points of a tile are compacted into shared memory first and written out from there, so that the
+// three output streams leave as full-width coalesced stores.
+constexpr int kEmitSmem = (kKeyWords + 3 * kCurveTile + 16) * 4;  // ~66 KB, needs the opt-in
+
 __global__ void __launch_bounds__(kCurveThreads) k3_curve_emit(const uint32_t* __restrict__ keys, int64_t N,
                                                                const unsigned long long* __restrict__ n_valid,
                                                                const uint32_t* __restrict__ pos_excl,
                                                                const uint32_t* __restrict__ bnd_excl, int ntile,
                                                                float* __restrict__ fps, float* __restrict__ tps,
                                                                float* __restrict__ thr) {
-  __shared__ uint32_t buf[kCurveThreads / 32];
+  extern __shared__ uint32_t sm[];
+  uint32_t* sh_keys = sm;
+  float* sh_f = reinterpret_cast<float*>(sm + kKeyWords);
+  float* sh_t = sh_f + kCurveTile;
+  float* sh_h = sh_t + kCurveTile;
+  uint32_t* buf = reinterpret_cast<uint32_t*>(sh_h + kCurveTile);
   const int seg = blockIdx.y, blk = blockIdx.x;
   const int64_t nv = (int64_t)n_valid[seg];
-  if ((int64_t)blk * kCurveTile >= nv) return;  // CTA-uniform
-  const int64_t i0 = (int64_t)blk * kCurveTile + (int64_t)threadIdx.x * kCurveItems;
+  const int64_t tile0 = (int64_t)blk * kCurveTile;
+  if (tile0 >= nv) return;  // CTA-uniform
   CurveItems it;
   uint32_t ps, bs;
-  curve_load(keys + (int64_t)seg * N, N, nv, i0, it, ps, bs);
-  uint32_t dummy;
+  curve_load(keys + (int64_t)seg * N, N, nv, tile0, sh_keys, it, ps, bs);
+  uint32_t dummy, tile_points;
   uint32_t p_run = pos_excl[(int64_t)seg * ntile + blk] + block_excl_scan(ps, buf, dummy);
-  uint32_t b_run = bnd_excl[(int64_t)seg * ntile + blk] + block_excl_scan(bs, buf, dummy);
-  float* f = fps + (int64_t)seg * N;
-  float* t = tps + (int64_t)seg * N;
-  float* h = thr + (int64_t)seg * N;
+  uint32_t b_loc = block_excl_scan(bs, buf, tile_points);  // position inside this tile's output
+  const int64_t i0 = tile0 + (int64_t)threadIdx.x * kCurveItems;
 #pragma unroll
   for (int j = 0; j < kCurveItems; ++j) {
     p_run += it.pos[j];  // inclusive count of positives up to this position
     if (it.bnd[j]) {
       const float tp = __uint2float_rn(p_run);
-      t[b_run] = tp;
-      f[b_run] = __ll2float_rn(1 + i0 + j) - tp;  // reference: 1 + threshold_idxs - tps, evaluated in float32
-      h[b_run] = it.score[j];
-      b_run += 1;
+      sh_t[b_loc] = tp;
+      sh_f[b_loc] = __ll2float_rn(1 + i0 + j) - tp;  // reference: 1 + threshold_idxs - tps, evaluated in float32
+      sh_h[b_loc] = it.score[j];
+      b_loc += 1;
     }
+  }
+  __syncthreads();
+  const int64_t out0 = (int64_t)seg * N + bnd_excl[(int64_t)seg * ntile + blk];
+  for (int i = threadIdx.x; i < (int)tile_points; i += kCurveThreads) {
+    fps[out0 + i] = sh_f[i];
+    tps[out0 + i] = sh_t[i];
+    thr[out0 + i] = sh_h[i];
   }
 }
 
@@ -724,7 +760,8 @@ extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* ta
     if (int rc = launch_status()) return rc;
     k3_scan_u32<<<L, 1024, 0, st>>>(bnd_part, p.ntile, (long long*)counts);
     if (int rc = launch_status()) return rc;
-    k3_curve_emit<<<grid, kCurveThreads, 0, st>>>(src, n, n_valid, pos_part, bnd_part, p.ntile, fps, tps, thresholds);
+    cudaFuncSetAttribute(k3_curve_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, kEmitSmem);
+    k3_curve_emit<<<grid, kCurveThreads, kEmitSmem, st>>>(src, n, n_valid, pos_part, bnd_part, p.ntile, fps, tps, thresholds);
     if (int rc = launch_status()) return rc;
   }
   return 0;
