@@ -245,7 +245,35 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     tgt = torch.randint(2, (n3,), generator=g, device=device)
     m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(device)
     record("cfg3_probs_int64_targets", lambda: m.update(probs, tgt), n3, n3 * 12, n3 * 4, 4)
-    del logits, probs, tgt, m
+    del probs, m
+    # K1b on the same data: binary stat scores / accuracy (one strict threshold, four counters)
+    from torchmetrics_forked_b200.classification import (
+        BinaryAccuracy,
+        MultilabelPrecisionRecallCurve,
+        MultilabelStatScores,
+        MulticlassStatScores,
+    )
+
+    m = BinaryAccuracy(validate_args=False).to(device)
+    record("k1b_binary_accuracy_2^28_logits", lambda: m.update(logits, tgt), n3, n3 * 12, n3 * 4, 4)
+    del logits, tgt, m
+    torch.cuda.empty_cache()
+    # multilabel: [2^21, 100] fp32 logits + int64 targets, stat scores and binned curve (T = 200)
+    nl, L = 1 << 21, 100
+    ml_p = torch.randn(nl, L, generator=g, device=device)
+    ml_t = torch.randint(2, (nl, L), generator=g, device=device)
+    m = MultilabelStatScores(L, validate_args=False).to(device)
+    record("k1b_multilabel_stat_scores_2^21x100", lambda: m.update(ml_p, ml_t), nl, nl * L * 12, nl * L * 4, 4)
+    m = MultilabelPrecisionRecallCurve(L, thresholds=200, validate_args=False).to(device)
+    record("k2_multilabel_curve_T200_2^21x100", lambda: m.update(ml_p, ml_t), nl, nl * L * 12, nl * L * 4, 4)
+    del ml_p, ml_t, m
+    torch.cuda.empty_cache()
+    # config 2 rows through StatScores (three C-bin histograms instead of the C x C matrix)
+    r2 = 1 << 20
+    p2, t2 = make_cfg2(r2, device, 99)
+    m = MulticlassStatScores(C2_CLASSES, average=None, validate_args=False).to(device)
+    record("cfg2_stat_scores_2^20_rows", lambda: m.update(p2, t2), r2, r2 * 2008, r2 * 2000, 2)
+    del p2, t2, m
     torch.cuda.empty_cache()
 
     # config 5: MulticlassJaccardIndex(150), logits [16,150,512,512]

@@ -191,6 +191,16 @@ int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int t
                    int64_t scratch_bytes, float* fps, float* tps, float* thresholds, int64_t* counts,
                    int32_t* err, void* stream);
 
+/* Area reductions over the curves tmb_clf_curves emitted (same fps / tps buffers, label stride n, counts[l] points
+ * each), replacing the per-label torch chains of
+ *   _binary_roc_compute + _auc_compute_without_check   functional/classification/roc.py:53-78, utilities/compute.py:88-96
+ *   _binary_precision_recall_curve_compute + AP sum     precision_recall_curve.py:274-283, average_precision.py:43-53
+ * out (float64 [num_labels, 4], device) receives per label: the un-normalised trapezoid area under (fps, tps)
+ * starting from (0,0); sum_b (tps_b - tps_{b-1}) * tps_b / (tps_b + fps_b); the last fps; the last tps.
+ * AUROC = out0 / (out2 * out3) (0 when either total is 0), AP = out1 / out3. */
+int tmb_curve_reduce(const float* fps, const float* tps, int64_t n, int64_t num_labels, const int64_t* counts,
+                     double* out, void* stream);
+
 /* Order-preserving removal of the samples whose target equals ignore_index — the boolean-mask indexing of
  * precision_recall_curve.py:178-181 (binary) and auroc.py:317-322 (micro average).  out_* must hold n
  * elements; *count (int64, device) receives how many were kept.  preds is copied bytewise

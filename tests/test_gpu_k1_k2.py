@@ -213,6 +213,31 @@ def test_multiclass_strided_random(shape, dtype, F):
     assert np.array_equal(F.multiclass_confusion_matrix(perm, target.cuda(), C, ignore_index=C - 1).cpu().numpy(), want)
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_multiclass_strided_ties_nan_inf(dtype, F):
+    """torch.argmax's rule on the class-strided layout: first maximum wins, a NaN beats everything (first NaN
+    wins), all -inf gives class 0 — including the packed two-pixels-per-register path of the 16-bit dtypes."""
+    g = torch.Generator().manual_seed(17)
+    C = 40
+    preds = torch.randn(3, C, 32, 64, generator=g).to(dtype)  # 16-bit rounding alone already makes ties
+    preds[0, :, 0, :8] = 0.5  # every class equal -> 0
+    preds[0, 7, 1, :16] = float("nan")  # single NaN -> 7
+    preds[0, 3, 2, :16] = float("nan")
+    preds[0, 30, 2, :16] = float("nan")  # two NaNs -> the first, 3
+    preds[1, :, 3, :] = float("-inf")  # all -inf -> 0
+    preds[1, 5, 4, :] = float("inf")
+    preds[1, 9, 4, :] = float("inf")  # two +inf -> 5
+    preds[2, 11, 5, :] = float("inf")
+    preds[2, 20, 5, :] = float("nan")  # NaN beats +inf -> 20
+    preds[2, 0, 6, :] = -0.0
+    preds[2, 1:, 6, :] = -1.0
+    preds[2, 13, 6, :] = 0.0  # -0.0 == +0.0 -> the first, 0
+    target = torch.randint(C, (3, 32, 64), generator=g)
+    want = O.multiclass_confusion_matrix(preds.float().numpy(), target.numpy(), C)
+    assert np.array_equal(F.multiclass_confusion_matrix(preds.cuda(), target.cuda(), C).cpu().numpy(), want)
+    assert torch.equal(preds.cuda().argmax(1).cpu(), torch.from_numpy(O.argmax_first(preds.float().numpy(), 1)))
+
+
 def test_multiclass_empty_and_errors(F):
     empty = F.multiclass_confusion_matrix(torch.zeros(0, 4).cuda(), torch.zeros(0, dtype=torch.long).cuda(), 4)
     assert empty.shape == (4, 4) and int(empty.sum()) == 0

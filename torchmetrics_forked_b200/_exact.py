@@ -1,12 +1,11 @@
 """Host-side launchers of the exact-curve kernels (K3): conditional sigmoid, ordered ignore-filter, batched
-sort + scan.  Re-exported through :mod:`torchmetrics_forked_b200.kernels`."""
+sort + scan, area reductions.  Re-exported through :mod:`torchmetrics_forked_b200.kernels`."""
 from typing import List, Optional, Tuple
 
 import torch
 from torch import Tensor
 
 from torchmetrics_forked_b200 import _native as nat
-
 
 
 def _as_kernel_input(t: Tensor) -> Tensor:
@@ -70,14 +69,17 @@ def compact_not_ignored(preds: Tensor, target: Tensor, ignore_index: int) -> Tup
     return out_p[:kept], out_t[:kept]
 
 
-def clf_curves(
-    preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int = 1
-) -> Tuple[List[Tensor], List[Tensor], List[Tensor]]:
-    """Per-label ``(fps, tps, thresholds)`` of ``[N, L]`` scores / targets: batched radix sort + scan.
+_SCORE_ERROR = (
+    "exact curves need non-negative scores (probabilities / sigmoid outputs, NaN allowed): the metric's `update` "
+    "always stores such values; negative scores passed directly are not supported"
+)
 
-    Returns three lists of ``L`` 1-d tensors (views into three ``[L, N]`` float32 buffers); thresholds come
-    back in the dtype of ``preds``.  One host read of the ``L`` curve lengths is unavoidable because the
-    outputs have data-dependent sizes.
+
+def _run_curves(preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int):
+    """pack -> batched radix sort -> boundary / prefix scan; everything stays on the device.
+
+    Returns ``(fps, tps, thr)`` as ``[L, N]`` float32 buffers, ``counts`` (int64 ``[L]``, valid prefix of each
+    row) and the int32 error word.
     """
     nat.require_cuda(preds, "preds")
     nat.require_cuda(target, "target")
@@ -102,16 +104,44 @@ def clf_curves(
                 nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts), nat.ptr(err), nat.stream_ptr(dev),
             )  # fmt: skip
         nat.check(rc, "tmb_clf_curves")
-        del scratch
+    return fps, tps, thr, counts, err
+
+
+def clf_curves(
+    preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int = 1
+) -> Tuple[List[Tensor], List[Tensor], List[Tensor]]:
+    """Per-label ``(fps, tps, thresholds)`` of ``[N, L]`` scores / targets: batched radix sort + scan.
+
+    Returns three lists of ``L`` 1-d tensors (views into three ``[L, N]`` float32 buffers); thresholds come
+    back in the dtype of ``preds``.  One host read of the ``L`` curve lengths is unavoidable because the
+    outputs have data-dependent sizes.
+    """
+    fps, tps, thr, counts, err = _run_curves(preds, target, ignore_index, pos_label)
     lengths = counts.cpu().tolist()  # the one synchronisation of the exact compute path
     if int(err.item()) & nat.ERR_SCORE_RANGE:
-        raise RuntimeError(
-            "exact curves need non-negative scores (probabilities / sigmoid outputs, NaN allowed): the metric's "
-            "`update` always stores such values; negative scores passed directly are not supported"
-        )
-    out_dtype = preds.dtype
+        raise RuntimeError(_SCORE_ERROR)
+    num_labels, out_dtype = preds.shape[1], preds.dtype
     f_list = [fps[l, : lengths[l]] for l in range(num_labels)]
     t_list = [tps[l, : lengths[l]] for l in range(num_labels)]
     h_list = [thr[l, : lengths[l]] if out_dtype == torch.float32 else thr[l, : lengths[l]].to(out_dtype)
               for l in range(num_labels)]
     return f_list, t_list, h_list
+
+
+def clf_curve_scores(preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int = 1) -> Tensor:
+    """Per-label area reductions of the exact curves, float64 ``[L, 4]``, without materialising Python lists:
+
+    column 0: trapezoid area under (fps, tps) from (0,0), un-normalised; column 1: ``sum (tps_b - tps_{b-1}) *
+    precision_b``; column 2 / 3: total negatives / positives.  ``AUROC = c0 / (c2 * c3)``, ``AP = c1 / c3``.
+    Nothing is read back to the host here.
+    """
+    fps, tps, _thr, counts, err = _run_curves(preds, target, ignore_index, pos_label)
+    n, num_labels = preds.shape
+    out = torch.empty(num_labels, 4, dtype=torch.float64, device=preds.device)
+    with torch.cuda.device(preds.device):
+        rc = nat.lib().tmb_curve_reduce(
+            nat.ptr(fps), nat.ptr(tps), n, num_labels, nat.ptr(counts), nat.ptr(out), nat.stream_ptr(preds.device)
+        )
+    nat.check(rc, "tmb_curve_reduce")
+    # a negative score poisons the result instead of costing a host sync here: NaN propagates to the metric
+    return torch.where(err.bool(), torch.full_like(out, float("nan")), out)

@@ -196,6 +196,7 @@ struct Packed<TMB_BF16> {
   }
   __device__ static __forceinline__ uint32_t eq_mask(uint32_t a, uint32_t b) { return __heq2_mask(as_v2(a), as_v2(b)); }
   __device__ static __forceinline__ uint32_t nan_mask(uint32_t a) { return __hneu2_mask(as_v2(a), as_v2(a)); }
+  __device__ static __forceinline__ uint32_t gt_mask(uint32_t a, uint32_t b) { return __hgt2_mask(as_v2(a), as_v2(b)); }
   __device__ static __forceinline__ uint32_t splat(float m) {
     return as_u32(__float2bfloat162_rn(m));  // m is one of the row's values: the conversion is exact
   }
@@ -211,6 +212,7 @@ struct Packed<TMB_F16> {
   }
   __device__ static __forceinline__ uint32_t eq_mask(uint32_t a, uint32_t b) { return __heq2_mask(as_v2(a), as_v2(b)); }
   __device__ static __forceinline__ uint32_t nan_mask(uint32_t a) { return __hneu2_mask(as_v2(a), as_v2(a)); }
+  __device__ static __forceinline__ uint32_t gt_mask(uint32_t a, uint32_t b) { return __hgt2_mask(as_v2(a), as_v2(b)); }
   __device__ static __forceinline__ uint32_t splat(float m) { return as_u32(__float2half2_rn(m)); }
 };
 
@@ -398,6 +400,42 @@ __global__ void __launch_bounds__(256) k1_strided(const char* __restrict__ preds
     const int64_t n = g / groups_per_outer;
     const int64_t s0 = (g - n * groups_per_outer) * PPT;
     const char* p0 = preds + (n * h.C * S + s0) * ES;
+    if constexpr (ES == 2 && VB == 16) {
+      // 16-bit scores: keep the running maximum and its class for two pixels per register (the launcher only
+      // picks this variant for C <= 65535).  A plane replaces the incumbent where it is strictly greater, or
+      // where it is the first NaN — torch.argmax's rule — with 3 packed compares and 3 bit-selects per pair.
+      using P = Packed<DT>;
+      uint32_t best2[4], idx2[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        best2[j] = P::kNegInf2;
+        idx2[j] = 0u;
+      }
+      for (int c0 = 0; c0 < h.C; c0 += U) {
+        Vec<VB> r[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (c0 + u < h.C) r[u].load(p0 + (int64_t)(c0 + u) * plane_bytes);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+          if (c0 + u < h.C) {
+            const uint32_t c2 = (uint32_t)(c0 + u) * 0x10001u;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const uint32_t v2 = r[u].w[j];
+              const uint32_t take = P::gt_mask(v2, best2[j]) | (P::nan_mask(v2) & P::eq_mask(best2[j], best2[j]));
+              idx2[j] = (take & c2) | (~take & idx2[j]);
+              best2[j] = (take & v2) | (~take & best2[j]);
+            }
+          }
+      }
+#pragma unroll
+      for (int q = 0; q < PPT; ++q) {
+        int64_t t = load_label(target, target_dtype, n * S + s0 + q);
+        count_sample(h, sh, mi, t, (idx2[q >> 1] >> (16 * (q & 1))) & 0xffffu, false);
+      }
+      continue;
+    }
     Best b[PPT];
 #pragma unroll
     for (int q = 0; q < PPT; ++q) b[q] = best_init();
@@ -582,7 +620,8 @@ static int launch_strided(const void* preds, const void* target, int tdt, int64_
                           const HistArgs& h, cudaStream_t st) {
   constexpr int ES = Elem<DT>::kBytes;
   const int hist_smem = h.sh_bins * (int)sizeof(int);
-  const int vb = vec_bytes(preds, S * ES, ES);
+  int vb = vec_bytes(preds, S * ES, ES);
+  if (ES == 2 && vb == 16 && h.C > 65535) vb = 8;  // the packed 16-byte variant keeps class indices in 16 bits
   const int64_t groups = n_outer * (S / (vb / ES));
   const int block = 256;
   const int64_t ctas = (groups + block - 1) / block;

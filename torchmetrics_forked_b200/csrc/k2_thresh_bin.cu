@@ -478,7 +478,10 @@ __global__ void __launch_bounds__(512, 1) k2_binary_lanes(TbArgs a, int warps_pe
     if (!SIG) {
       const bool mine = d.outside != 0u;
       if (mine) raise_flag(a);
-      stop = __any_sync(kFull, mine || flag_up(a));  // once anybody saw a logit the raw histogram is moot
+      // once anybody saw a logit the raw histogram is moot; other CTAs' flags are polled only now and then (the
+      // poll is a dependent L2 round trip in every iteration otherwise)
+      const bool poll = (h.batches & 7) == 0;
+      stop = __any_sync(kFull, mine || (poll && flag_up(a)));
     }
     if (h.batches >= kFoldEvery) lane_fold(a, h);  // `batches` is identical in all lanes
   };

@@ -62,7 +62,12 @@ __global__ void __launch_bounds__(256) k3_outside_flag(const void* __restrict__ 
     if (__any_sync(__activemask(), found)) break;  // somebody in the warp found one: the answer is known
     if ((i & 0xfffff) < (int64_t)gridDim.x * blockDim.x && *((volatile unsigned long long*)flag) == gen) break;
   }
-  if (found) atomicMax(flag, gen);
+  // one atomic per warp, and none once the flag is known to be up: with logits EVERY thread finds an outside
+  // value at once, and 300 k atomics on one address took longer than the whole sigmoid pass
+  const unsigned voters = __activemask();
+  const bool warp_found = __any_sync(voters, found);
+  if (warp_found && (threadIdx.x & 31) == (__ffs(voters) - 1) && *((volatile unsigned long long*)flag) != gen)
+    atomicMax(flag, gen);
 }
 
 template <int DT>
@@ -155,7 +160,12 @@ __global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restric
     if (__any_sync(kFull, found)) break;
     if (*((volatile unsigned long long*)flag) == gen) break;  // another CTA already settled it
   }
-  if (found) atomicMax(flag, gen);
+  // one atomic per warp, and none once the flag is known to be up: with logits EVERY thread finds an outside
+  // value at once, and 300 k atomics on one address took longer than the whole sigmoid pass
+  const unsigned voters = __activemask();
+  const bool warp_found = __any_sync(voters, found);
+  if (warp_found && (threadIdx.x & 31) == (__ffs(voters) - 1) && *((volatile unsigned long long*)flag) != gen)
+    atomicMax(flag, gen);
 }
 
 template <int DT>
@@ -549,6 +559,56 @@ __global__ void __launch_bounds__(kCurveThreads) k3_curve_emit(const uint32_t* _
   }
 }
 
+// ---- curve -> area reductions ----------------------------------------------------------------------------------------
+// AUROC and average precision straight from the emitted (fps, tps) points, one read of the two arrays, instead
+// of the reference's per-label chain of cat / divide / flip / trapz kernels over 2^24-element tensors
+// (roc.py:53-78, utilities/compute.py:88-96, average_precision.py:43-53).  Per label, accumulated in float64:
+//   out[4l+0] = sum_b (fps_b - fps_{b-1}) * (tps_b + tps_{b-1}) / 2      (trapezoid area before normalisation)
+//   out[4l+1] = sum_b (tps_b - tps_{b-1}) * tps_b / (tps_b + fps_b)      (step-wise precision-recall sum)
+//   out[4l+2] = fps of the last point, out[4l+3] = tps of the last point (the normalisers)
+// with fps_{-1} = tps_{-1} = 0 (the (0,0) point the reference prepends).  `out` must be zero on entry.
+__global__ void __launch_bounds__(256) k3_curve_reduce(const float* __restrict__ fps, const float* __restrict__ tps,
+                                                       int64_t N, const long long* __restrict__ counts,
+                                                       double* __restrict__ out) {
+  const int seg = blockIdx.y;
+  const int64_t D = counts[seg];
+  const float* f = fps + (int64_t)seg * N;
+  const float* t = tps + (int64_t)seg * N;
+  double area = 0.0, ap = 0.0;
+  for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < D; b += (int64_t)gridDim.x * blockDim.x) {
+    const double fb = f[b], tb = t[b];
+    const double fp = b ? (double)f[b - 1] : 0.0, tp = b ? (double)t[b - 1] : 0.0;
+    area += (fb - fp) * (tb + tp) * 0.5;
+    ap += (tb - tp) * (tb / (tb + fb));
+    if (b == D - 1) {
+      out[4 * seg + 2] = fb;
+      out[4 * seg + 3] = tb;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    area += __shfl_xor_sync(kFull, area, d);
+    ap += __shfl_xor_sync(kFull, ap, d);
+  }
+  __shared__ double red[2][8];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    red[0][w] = area;
+    red[1][w] = ap;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, p = 0.0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a += red[0][i];
+      p += red[1][i];
+    }
+    if (a != 0.0) atomicAdd(&out[4 * seg + 0], a);
+    if (p != 0.0) atomicAdd(&out[4 * seg + 1], p);
+  }
+}
+
 // ---- ordered compaction (ignore_index filtering with data-dependent output size) -----------------------------------
 __device__ __forceinline__ void copy_elem(void* dst, int64_t o, const void* src, int64_t i, int size) {
   switch (size) {
@@ -765,6 +825,22 @@ extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* ta
     if (int rc = launch_status()) return rc;
   }
   return 0;
+}
+
+extern "C" int tmb_curve_reduce(const float* fps, const float* tps, int64_t n, int64_t num_labels,
+                                const int64_t* counts, double* out, void* stream) {
+  if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
+  if (!counts || !out) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(out, 0, num_labels * 4 * sizeof(double), st);
+  if (int rc = launch_status()) return rc;
+  if (n == 0) return 0;
+  if (!fps || !tps) return TMB_E_NULL;
+  int64_t gx = (n + 256 * 8 - 1) / (256 * 8);
+  if (gx > 1024) gx = 1024;
+  dim3 grid((unsigned)gx, (unsigned)num_labels);
+  k3_curve_reduce<<<grid, 256, 0, st>>>(fps, tps, n, (const long long*)counts, out);
+  return launch_status();
 }
 
 extern "C" int64_t tmb_compact_scratch_bytes(int64_t n) {

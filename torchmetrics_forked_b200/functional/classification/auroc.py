@@ -20,6 +20,24 @@ from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 from torchmetrics_forked_b200.utilities.prints import rank_zero_warn
 
 
+def _reduce_scores(res: Tensor, average: Optional[str], weights: Optional[Tensor]) -> Tensor:
+    """nan-aware macro / weighted averaging of per-label scores (the tail of the reference's ``_reduce_auroc``)."""
+    if average is None or average == "none":
+        return res
+    if torch.isnan(res).any():
+        rank_zero_warn(
+            f"Average precision score for one or more classes was `nan`. Ignoring these classes in {average}-average",
+            UserWarning,
+        )
+    keep = ~torch.isnan(res)
+    if average == "macro":
+        return res[keep].mean()
+    if average == "weighted" and weights is not None:
+        weights = _safe_divide(weights[keep], weights[keep].sum())
+        return (res[keep] * weights).sum()
+    raise ValueError("Received an incompatible combinations of inputs to make reduction.")
+
+
 def _reduce_auroc(
     fpr: Union[Tensor, List[Tensor]],
     tpr: Union[Tensor, List[Tensor]],
@@ -47,6 +65,35 @@ def _reduce_auroc(
     raise ValueError("Received an incompatible combinations of inputs to make reduction.")
 
 
+def _exact_auroc_from_scores(scores: Tensor) -> Tensor:
+    """Per-label AUROC (float32) from the float64 ``[L, 4]`` reductions of :func:`kernels.clf_curve_scores`.
+
+    Same result as normalising the exact ROC curve and integrating it (reference roc.py:53-78 +
+    utilities/compute.py:88-96) — 0 with a warning when a label has no negative or no positive sample — but
+    from one fused pass over the curve instead of ~12 torch kernels per label.
+    """
+    if bool(torch.isnan(scores).any()):
+        raise RuntimeError(
+            "exact curves need non-negative scores (probabilities / sigmoid outputs): negative scores were found"
+        )
+    area, _, neg, pos = scores.unbind(1)
+    if bool((neg <= 0).any()):
+        rank_zero_warn(
+            "No negative samples in targets, false positive value should be meaningless."
+            " Returning zero tensor in false positive score",
+            UserWarning,
+        )
+    if bool((pos <= 0).any()):
+        rank_zero_warn(
+            "No positive samples in targets, true positive value should be meaningless."
+            " Returning zero tensor in true positive score",
+            UserWarning,
+        )
+    ok = (neg > 0) & (pos > 0)
+    denom = torch.where(ok, neg * pos, torch.ones_like(area))
+    return torch.where(ok, area / denom, torch.zeros_like(area)).to(torch.float32)
+
+
 def _binary_auroc_arg_validation(
     max_fpr: Optional[float] = None,
     thresholds: Optional[Union[int, List[float], Tensor]] = None,
@@ -64,6 +111,15 @@ def _binary_auroc_compute(
     pos_label: int = 1,
 ) -> Tensor:
     """AUROC, optionally the standardised partial area up to ``max_fpr`` (reference :82-106)."""
+    if not (isinstance(state, Tensor) and thresholds is not None) and (max_fpr is None or max_fpr == 1):
+        # exact mode, full area: sort + scan + fused area reduction, no curve is materialised on the host side
+        from torchmetrics_forked_b200 import kernels
+
+        preds, target = state[0], state[1]
+        if preds.ndim > target.ndim:
+            preds = preds[:, 0]
+        scores = kernels.clf_curve_scores(preds.reshape(-1, 1), target.reshape(-1, 1), None, pos_label)
+        return _exact_auroc_from_scores(scores)[0]
     fpr, tpr, _ = _binary_roc_compute(state, thresholds, pos_label)
     if max_fpr is None or max_fpr == 1 or fpr.sum() == 0 or tpr.sum() == 0:
         return _auc_compute_without_check(fpr, tpr, 1.0)
@@ -131,13 +187,14 @@ def _multilabel_auroc_compute(
         if isinstance(state, Tensor) and thresholds is not None:
             return _binary_auroc_compute(state.sum(1), thresholds, max_fpr=None)
         return _binary_auroc_compute(_flatten_valid(state, ignore_index), thresholds, max_fpr=None)
+    if not (isinstance(state, Tensor) and thresholds is not None):
+        # exact mode: all labels in one batched sort + scan + area reduction
+        from torchmetrics_forked_b200 import kernels
+
+        scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1)
+        return _reduce_scores(_exact_auroc_from_scores(scores), average, (state[1] == 1).sum(dim=0).float())
     fpr, tpr, _ = _multilabel_roc_compute(state, num_labels, thresholds, ignore_index)
-    return _reduce_auroc(
-        fpr,
-        tpr,
-        average,
-        weights=(state[1] == 1).sum(dim=0).float() if thresholds is None else state[0][:, 1, :].sum(-1),
-    )
+    return _reduce_auroc(fpr, tpr, average, weights=state[0][:, 1, :].sum(-1))
 
 
 def multilabel_auroc(

@@ -49,9 +49,21 @@ def _reduce_average_precision(
     raise ValueError("Received an incompatible combinations of inputs to make reduction.")
 
 
+def _exact_ap_from_scores(scores: Tensor) -> Tensor:
+    """Per-label average precision (float32) from :func:`kernels.clf_curve_scores`: ``sum (r_b - r_{b-1}) p_b``
+    with ``r = tps / tps_last`` — the reference's flipped step sum (:43-53, :70-75) — NaN without positives."""
+    _, ap_sum, _, pos = scores.unbind(1)
+    return (ap_sum / pos).to(torch.float32)
+
+
 def _binary_average_precision_compute(
     state: Union[Tensor, Tuple[Tensor, Tensor]], thresholds: Optional[Tensor]
 ) -> Tensor:
+    if not (isinstance(state, Tensor) and thresholds is not None):
+        from torchmetrics_forked_b200 import kernels
+
+        scores = kernels.clf_curve_scores(state[0].reshape(-1, 1), state[1].reshape(-1, 1), None, 1)
+        return _exact_ap_from_scores(scores)[0]
     precision, recall, _ = _binary_precision_recall_curve_compute(state, thresholds)
     return -torch.sum((recall[1:] - recall[:-1]) * precision[:-1])
 
@@ -99,13 +111,14 @@ def _multilabel_average_precision_compute(
         else:
             state = _flatten_valid(state, ignore_index)
         return _binary_average_precision_compute(state, thresholds)
+    if not (isinstance(state, Tensor) and thresholds is not None):
+        from torchmetrics_forked_b200 import kernels
+        from torchmetrics_forked_b200.functional.classification.auroc import _reduce_scores
+
+        scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1)
+        return _reduce_scores(_exact_ap_from_scores(scores), average, (state[1] == 1).sum(dim=0).float())
     precision, recall, _ = _multilabel_precision_recall_curve_compute(state, num_labels, thresholds, ignore_index)
-    return _reduce_average_precision(
-        precision,
-        recall,
-        average,
-        weights=(state[1] == 1).sum(dim=0).float() if thresholds is None else state[0][:, 1, :].sum(-1),
-    )
+    return _reduce_average_precision(precision, recall, average, weights=state[0][:, 1, :].sum(-1))
 
 
 def multilabel_average_precision(

@@ -10,7 +10,12 @@ import torch
 from torch import Tensor
 
 from torchmetrics_forked_b200 import _native as nat
-from torchmetrics_forked_b200._exact import clf_curves, compact_not_ignored, sigmoid_normalize  # noqa: F401
+from torchmetrics_forked_b200._exact import (  # noqa: F401
+    clf_curve_scores,
+    clf_curves,
+    compact_not_ignored,
+    sigmoid_normalize,
+)
 
 MC_CONFMAT, MC_STATS, MC_MICRO = nat.MC_CONFMAT, nat.MC_STATS, nat.MC_MICRO
 
