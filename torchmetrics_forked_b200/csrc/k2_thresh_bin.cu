@@ -580,9 +580,149 @@ __global__ void __launch_bounds__(512, 1) k2_binary_lanes(TbArgs a, int warps_pe
   }
 }
 
+// ---- K1b fast path: ONE threshold, [N, L] row-major (binary = L 1) ---------------------------------------------
+// Stat scores / confusion matrices / accuracy / F1 / Jaccard of binary and multilabel tasks compare against a
+// single threshold, so a sample only needs "above or not" — four counters per label.  The grid-stride is a
+// multiple of L vectors of 4 samples, which pins each of a thread's 4 vector slots to ONE label for the whole
+// kernel: the counters live in registers (packed bytes, widened every 255 iterations) and reach memory through
+// 16 atomics per thread at the very end.  No shared memory, no per-sample atomics; HBM-bound.
+template <int PDT, int TDT, bool SIG>
+__global__ void __launch_bounds__(256) k2_single(TbArgs a, int64_t G, int sh_bins) {
+  extern __shared__ uint32_t sh_cnt[];  // [L * 4] when sh_bins > 0
+  if (!pass_enabled(a, SIG)) return;
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) sh_cnt[i] = 0;
+  __syncthreads();
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const float thr = a.thr[0];
+  const bool gt = a.cmp_gt != 0;
+  const int64_t n_vec = a.n_total / 4;
+  const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
+  constexpr bool kFiltered = SIG && PDT == TMB_F32;
+  unsigned long long* gh = hist_base(a, SIG ? 1 : 0);
+  bool bad_target = false, stop = false;
+
+  if (gtid < G) {
+    uint32_t wide[4][4];  // [slot][target * 2 + above]
+    uint32_t packed[4];   // the same four counters as bytes, widened before they can overflow
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      packed[e] = 0;
+#pragma unroll
+      for (int f = 0; f < 4; ++f) wide[e][f] = 0;
+    }
+    auto widen = [&]() {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+#pragma unroll
+        for (int f = 0; f < 4; ++f) wide[e][f] += (packed[e] >> (8 * f)) & 0xffu;
+        packed[e] = 0;
+      }
+    };
+    auto one = [&](float x, uint32_t lo, uint32_t hi, int e) -> bool {  // returns "outside [0,1]" for pass A
+      const bool kept = !(a.has_ignore && lo == ign_lo && hi == ign_hi);
+      const bool zero_or_one = (hi | (lo >> 1)) == 0u;
+      bad_target |= kept && !zero_or_one;
+      bool above;
+      if (kFiltered) {
+        const float q = rcp_approx(1.0f + ex2_approx(x * -1.4426950408889634f));
+        const float margin = fmaf(q, fmaf(fabsf(x), 2.9e-7f, 1.6e-6f), 1e-30f);  // see the filtered sigmoid above
+        above = thr < q;
+        if (!(fabsf(q - thr) > margin)) {  // too close to call (or NaN): exact expression
+          const float qe = sigmoid_as<PDT>(x);
+          above = gt ? (thr < qe) : (thr <= qe);
+        }
+      } else {
+        const float q = SIG ? sigmoid_as<PDT>(x) : x;
+        above = gt ? (thr < q) : (thr <= q);
+      }
+      const uint32_t field = (lo & 1u) * 2u + (above ? 1u : 0u);
+      packed[e] += (kept && zero_or_one) ? (1u << (8 * field)) : 0u;
+      return !SIG && !(x >= 0.0f && x <= 1.0f) && (kept || a.flag_counts_ignored);
+    };
+    int since_widen = 0;
+    constexpr int U = 2;
+    for (int64_t v0 = gtid; v0 < n_vec && !stop; v0 += G * U) {
+      float x[U][4];
+      uint32_t lo[U][4], hi[U][4];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int64_t v = v0 + (int64_t)u * G;
+        if (v < n_vec) {
+          load_preds4<PDT>(a.preds, v * 4, x[u]);
+          load_targets4<TDT>(a.target, v * 4, lo[u], hi[u]);
+        }
+      }
+      bool outside = false;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        if (v0 + (int64_t)u * G < n_vec) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e) outside |= one(x[u][e], lo[u][e], hi[u][e], e);
+        }
+      }
+      since_widen += U;
+      if (since_widen > 255 - U) {
+        widen();
+        since_widen = 0;
+        if (!SIG && flag_up(a)) stop = true;  // another CTA saw a logit: the raw counts are moot
+      }
+      if (outside) {
+        raise_flag(a);
+        stop = true;
+      }
+    }
+    widen();
+    if (!(!SIG && stop)) {
+      // slot e of this thread always saw label (4 * gtid + e) mod L  (G is a multiple of L).  Counters meet in a
+      // CTA-wide shared histogram first when it fits: with L = 1 every thread of the grid would otherwise send
+      // its 16 atomics to the same four addresses.
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int l = (int)((4 * gtid + e) % a.L);
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+          if (wide[e][f]) {
+            if (sh_bins > 0)
+              atomicAdd(&sh_cnt[l * 4 + f], wide[e][f]);
+            else
+              atomicAdd(&gh[(int64_t)l * 4 + f], (unsigned long long)wide[e][f]);  // [l][t][k], T+1 = 2
+          }
+        }
+      }
+    }
+  }
+  if (sh_bins > 0) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
+      const uint32_t v = sh_cnt[i];
+      if (v) atomicAdd(&gh[i], (unsigned long long)v);
+    }
+  }
+  // tail samples (n % 4): a handful, straight to the global counters
+  if (blockIdx.x == 0 && !stop) {
+    const int64_t i = n_vec * 4 + threadIdx.x;
+    if (i < a.n_total) {
+      const float x = load_elem<PDT>(a.preds, i);
+      const int64_t t = load_label(a.target, a.tdt, i);
+      const bool kept = !(a.has_ignore && t == a.ignore);
+      if (!SIG && !(x >= 0.0f && x <= 1.0f) && (kept || a.flag_counts_ignored)) raise_flag(a);
+      if (kept) {
+        if (t != 0 && t != 1) {
+          bad_target = true;
+        } else {
+          const float q = SIG ? sigmoid_as<PDT>(x) : x;
+          const int above = gt ? (thr < q) : (thr <= q);
+          atomicAdd(&gh[(i % a.L) * 4 + t * 2 + above], 1ULL);
+        }
+      }
+    }
+  }
+  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_BINARY);
+}
+
 // ---- generic path: any L / S / T, atomics into shared (small) or global (large) histograms ------------
 template <int PDT, bool SIG, bool LABELS>
-__global__ void __launch_bounds__(256) k2_generic(TbArgs a, int sh_bins, int sh_pad_cap, const float* global_pad) {
+__global__ void __launch_bounds__(1024) k2_generic(TbArgs a, int sh_bins, int sh_pad_cap, const float* global_pad) {
   extern __shared__ uint32_t sh_u32[];
   if (!LABELS) {
     if (!pass_enabled(a, SIG)) return;
@@ -787,18 +927,58 @@ static int launch_binary_lanes_t(const TbArgs& a, int warps, int smem, cudaStrea
   }
 }
 
+template <int PDT, int TDT>
+static int launch_single_pt(const TbArgs& a, cudaStream_t st) {
+  auto ka = k2_single<PDT, TDT, false>;
+  auto kb = k2_single<PDT, TDT, true>;
+  const int block = 256;
+  const int64_t n_vec = a.n_total / 4;
+  const int sh_bins = (int64_t)a.L * 4 <= 8192 ? a.L * 4 : 0;
+  const int smem = sh_bins * 4;
+  const int grid = resident_grid(kb, block, smem, (n_vec + block * 2 - 1) / (block * 2));
+  const int64_t threads = (int64_t)grid * block;
+  const int64_t G = threads / a.L * a.L;  // threads taking part: a multiple of L, so vector slots keep their label
+  if (G < 1) return TMB_E_LIMIT;          // more labels than threads: let the generic path do it
+  ka<<<grid, block, smem, st>>>(a, G, sh_bins);
+  if (int rc = launch_status()) return rc;
+  kb<<<grid, block, smem, st>>>(a, G, sh_bins);
+  return launch_status();
+}
+
+template <int PDT>
+static int launch_single_p(const TbArgs& a, cudaStream_t st) {
+  switch (a.tdt) {
+    case TMB_I64: return launch_single_pt<PDT, TMB_I64>(a, st);
+    case TMB_I32: return launch_single_pt<PDT, TMB_I32>(a, st);
+    case TMB_U8: return launch_single_pt<PDT, TMB_U8>(a, st);
+    default: return launch_single_pt<PDT, TMB_I8>(a, st);
+  }
+}
+
+static int launch_single(const TbArgs& a, cudaStream_t st) {
+  switch (a.pdt) {
+    case TMB_F32: return launch_single_p<TMB_F32>(a, st);
+    case TMB_F16: return launch_single_p<TMB_F16>(a, st);
+    default: return launch_single_p<TMB_BF16>(a, st);
+  }
+}
+
 template <int PDT>
 static int launch_generic(const TbArgs& a, cudaStream_t st) {
   const int64_t bins = (int64_t)a.L * 2 * (a.T + 1);
-  const int sh_bins = bins <= 8192 ? (int)bins : 0;
   const int sh_pad_cap = a.T + 2 <= 4096 ? (a.T + 2 + 31) / 32 * 32 : 0;
+  // privatise the histogram in shared memory whenever it fits the opt-in limit (multilabel L = 100, T = 200 is
+  // 40 200 bins = 157 KB: one big CTA per SM beats 2e8 global atomics)
+  const int64_t sh_room = ((int64_t)dev_info().max_smem_optin - 2048) / 4 - sh_pad_cap;
+  const int sh_bins = bins <= sh_room ? (int)bins : 0;
   const int smem = (sh_pad_cap + sh_bins) * 4;
-  const int block = 256;
+  const int block = smem > 48 * 1024 ? 1024 : 256;
   const int64_t work = (a.n_total + block - 1) / block;
   float* global_pad = (float*)(a.scratch + kHdr + hist_elems(a.L, a.T));
   if (a.preds_is_label) {
     // labels are never sigmoided: they go to histogram variant 0, the one finalize reads while the flag is down
     auto k = k2_generic<TMB_F32, false, true>;
+    if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     k<<<resident_grid(k, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
     return launch_status();
   }
@@ -808,6 +988,10 @@ static int launch_generic(const TbArgs& a, cudaStream_t st) {
   }
   auto ka = k2_generic<PDT, false, false>;
   auto kb = k2_generic<PDT, true, false>;
+  if (smem > 48 * 1024) {
+    cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  }
   ka<<<resident_grid(ka, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
   if (int rc = launch_status()) return rc;
   kb<<<resident_grid(kb, block, smem, work), block, smem, st>>>(a, sh_bins, sh_pad_cap, global_pad);
@@ -857,6 +1041,11 @@ extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int pre
   a.has_ignore = has_ignore;
   a.flag_counts_ignored = flag_counts_ignored;
 
+  // K1b fast path: one threshold, labels along the fastest axis (binary, or multilabel [N, L])
+  if (num_thresholds == 1 && n_inner == 1 && !preds_is_label && target_dtype != TMB_I16 &&
+      ((((uintptr_t)preds | (uintptr_t)target) & 15) == 0)) {
+    if (int rc = launch_single(a, st); rc != TMB_E_LIMIT) return rc;
+  }
   // binary fast path: lane-private histograms need (T+1)*128 B per warp plus the padded thresholds
   const bool aligned = (((uintptr_t)preds | (uintptr_t)target) & 15) == 0;
   const bool tdt_ok = target_dtype != TMB_I16;
