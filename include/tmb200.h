@@ -191,6 +191,31 @@ int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int t
                    int64_t scratch_bytes, float* fps, float* tps, float* thresholds, int64_t* counts,
                    int32_t* err, void* stream);
 
+/* The same, reading the scores / targets from the per-update buffers of the metric state instead of one
+ * concatenated tensor — it also replaces the `dim_zero_cat(self.preds)`, `dim_zero_cat(self.target)` of
+ *   the exact-mode state assembly in compute()   classification/precision_recall_curve.py:175, :373, :563,
+ *                                                classification/auroc.py:122, :425, classification/average_precision.py:116, :428
+ * chunk_table (device memory, 3 * num_chunks + 1 int64):
+ *   [0 .. C]       first row of chunk c, ascending, table[0] = 0 and table[C] = n
+ *   [C+1 .. 2C]    device address of chunk c's scores  ([rows_c, num_labels] row-major, preds_dtype)
+ *   [2C+1 .. 3C]   device address of chunk c's targets ([rows_c, num_labels] row-major, target_dtype)
+ * Empty chunks are allowed.  Everything else as tmb_clf_curves. */
+int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
+                           int64_t n, int64_t num_labels, int has_ignore, int64_t ignore_index, int64_t pos_label,
+                           void* scratch, int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
+                           int64_t* counts, int32_t* err, void* stream);
+
+/* Chunks -> the four per-label area reductions tmb_curve_reduce documents (scores: float64 [num_labels, 4],
+ * device), without writing the curves: pack, sort, then one pass over the sorted keys.  Replaces, for the
+ * exact-mode AUROC / average-precision metrics, tmb_clf_curves + tmb_curve_reduce, i.e.
+ *   _binary_auroc_compute / _multilabel_auroc_compute               functional/classification/auroc.py:82-106, :307-332
+ *   _binary_ / _multilabel_average_precision_compute                functional/classification/average_precision.py:70-75, :284-311
+ * Same scratch size as tmb_clf_curves. */
+int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
+                                 int64_t n, int64_t num_labels, int has_ignore, int64_t ignore_index,
+                                 int64_t pos_label, void* scratch, int64_t scratch_bytes, double* scores,
+                                 int32_t* err, void* stream);
+
 /* Area reductions over the curves tmb_clf_curves emitted (same fps / tps buffers, label stride n, counts[l] points
  * each), replacing the per-label torch chains of
  *   _binary_roc_compute + _auc_compute_without_check   functional/classification/roc.py:53-78, utilities/compute.py:88-96

@@ -311,3 +311,156 @@ def test_multilabel_auroc_config4_scaled():
                                rtol=1e-5)
     np.testing.assert_allclose(float(ap.compute()),
                                np.mean([O.binary_average_precision_exact(f, t) for f, t, _ in curves]), rtol=1e-5)
+
+
+# ------------------------------------------------------------------------------------------ chunked inputs, fused scores
+def _ragged_chunks(n_rows, L, g, quant=None, ignore_frac=0.0, dtype=torch.float32, tdtype=torch.int64):
+    """Per-update buffers of ragged sizes (one of them empty) plus their concatenation."""
+    ps, ts = [], []
+    for n in n_rows:
+        p = torch.rand(n, L, generator=g)
+        if quant:
+            p = (p * quant).round() / quant
+        t = torch.randint(2, (n, L), generator=g)
+        if ignore_frac:
+            t[torch.rand(n, L, generator=g) < ignore_frac] = -1
+        ps.append(p.to(dtype).cuda())
+        ts.append(t.to(tdtype).cuda())
+    return ps, ts, torch.cat(ps), torch.cat(ts)
+
+
+@pytest.mark.parametrize("L", [1, 2, 3, 31, 33, 100, 128, 130, 257])
+def test_chunked_curves_equal_concatenated(L):
+    """tmb_clf_curves_chunked reads the per-update buffers in place: same bits as the concatenated call, and as
+    the oracle, for every label-tile shape of the pack kernel (L below / at / above 32 and 128)."""
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(100 + L)
+    rows = [1, 127, 0, 128, 129, 300, 5] if L > 8 else [1, 4095, 0, 4097, 129, 9000, 5]
+    ps, ts, P, T = _ragged_chunks(rows, L, g, quant=512, ignore_frac=0.1)
+    got = kernels.clf_curves(ps, ts, -1, 1)
+    one = kernels.clf_curves(P, T, -1, 1)
+    for a, b in zip(got, one):
+        for x, y in zip(a, b):
+            assert torch.equal(x, y)
+    _check_curves(got, O.multilabel_clf_curves(P.cpu().numpy(), T.cpu().numpy(), -1))
+
+
+@pytest.mark.parametrize("pdtype,tdtype", [(torch.bfloat16, torch.uint8), (torch.float16, torch.int32)])
+def test_chunked_curves_narrow_dtypes(pdtype, tdtype):
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(77)
+    ps, ts, P, T = _ragged_chunks([700, 1, 2049], 5, g, dtype=pdtype, tdtype=tdtype)
+    got = kernels.clf_curves(ps, ts, None, 1)
+    _check_curves(got, O.multilabel_clf_curves(P.float().cpu().numpy(), T.cpu().numpy()))
+
+
+def _emit_then_reduce(P, T, ignore_index):
+    """The two-step path the fused kernel replaces: tmb_clf_curves + tmb_curve_reduce through the raw C ABI."""
+    from torchmetrics_forked_b200 import _native as nat
+
+    lib, p = nat.lib(), lambda t: ctypes.c_void_p(t.data_ptr())
+    n, L = P.shape
+    scratch = torch.empty(lib.tmb_clf_curve_scratch_bytes(n, L), dtype=torch.uint8, device="cuda")
+    fps, tps, thr = (torch.empty(L, n, device="cuda") for _ in range(3))
+    counts = torch.zeros(L, dtype=torch.int64, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    has = int(ignore_index is not None)
+    assert lib.tmb_clf_curves(p(P), nat.float_code(P), p(T), nat.label_code(T), n, L, has, ignore_index or 0, 1,
+                              p(scratch), scratch.numel(), p(fps), p(tps), p(thr), p(counts), p(err), None) == 0
+    out = torch.empty(L, 4, dtype=torch.float64, device="cuda")
+    assert lib.tmb_curve_reduce(p(fps), p(tps), n, L, p(counts), p(out), None) == 0
+    torch.cuda.synchronize()
+    return out
+
+
+@pytest.mark.parametrize("quant", [None, 4096, 3, 1])
+def test_fused_scores_equal_emit_plus_reduce(quant):
+    """k3_curve_scores (no curve in memory) against curve emit + reduce: same float32 curve points, float64 sums
+    that differ only in summation order.  quant = 3 / 1 makes tie runs that span many 4096-key tiles, i.e. the
+    look-back over tiles without a boundary; one label is ignored entirely (no curve points at all)."""
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(31)
+    ps, ts, P, T = _ragged_chunks([9000, 0, 70_001, 4096], 4, g, quant=quant, ignore_frac=0.05)
+    for t in ts:
+        t[:, 2] = -1
+    T = torch.cat(ts)
+    fused = kernels.clf_curve_scores(ps, ts, -1, 1)
+    want = _emit_then_reduce(P, T, -1)
+    assert torch.equal(fused[:, 2:], want[:, 2:])
+    torch.testing.assert_close(fused[:, :2], want[:, :2], rtol=1e-12, atol=0)
+    assert fused[2].abs().sum() == 0
+    # and against the oracle's float64 areas (the reference itself raises IndexError on a label without samples)
+    keep = [0, 1, 3]
+    curves = O.multilabel_clf_curves(P.cpu().numpy()[:, keep], T.cpu().numpy()[:, keep], -1)
+    for l, (f, t, _) in zip(keep, curves):
+        auroc = float(fused[l, 0] / (fused[l, 2] * fused[l, 3]))
+        np.testing.assert_allclose(auroc, O.binary_auroc_exact(f, t), rtol=1e-6)
+        np.testing.assert_allclose(float(fused[l, 1] / fused[l, 3]), O.binary_average_precision_exact(f, t), rtol=1e-6)
+
+
+def test_fused_scores_single_tensor_and_empty():
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator().manual_seed(32)
+    _, _, P, T = _ragged_chunks([33_333], 7, g)
+    torch.testing.assert_close(kernels.clf_curve_scores(P, T, None, 1), _emit_then_reduce(P, T, None), rtol=1e-12,
+                               atol=0)
+    empty = kernels.clf_curve_scores(P[:0], T[:0], None, 1)
+    assert empty.shape == (7, 4) and float(empty.abs().sum()) == 0
+    with pytest.raises(RuntimeError, match="negative|range|score"):
+        bad = P.clone()
+        bad[5, 3] = -0.5
+        kernels.clf_curves(bad, T, None, 1)
+    assert bool(kernels.clf_curve_scores(bad, T, None, 1).isnan().all())
+
+
+@pytest.mark.parametrize("average", ["macro", "weighted", "micro", "none"])
+def test_multilabel_metrics_over_many_updates(average):
+    """Several updates -> compute() reads the per-update buffers through the chunk table; the state itself stays
+    the list of buffers the reference keeps."""
+    from torchmetrics_forked_b200.classification import MultilabelAUROC, MultilabelAveragePrecision, MultilabelROC
+    from torchmetrics_forked_b200.functional.classification import multilabel_auroc, multilabel_average_precision
+
+    g = torch.Generator().manual_seed(12)
+    L = 6
+    auroc = MultilabelAUROC(L, thresholds=None, average=average, ignore_index=-1).cuda()
+    ap = MultilabelAveragePrecision(L, thresholds=None, average=average, ignore_index=-1).cuda()
+    roc = MultilabelROC(L, thresholds=None, ignore_index=-1).cuda()
+    ps, ts, P, T = _ragged_chunks([500, 4097, 33, 1200], L, g, quant=256, ignore_frac=0.1)
+    for p, t in zip(ps, ts):
+        auroc.update(p, t)
+        ap.update(p, t)
+        roc.update(p, t)
+    assert len(auroc.preds) == 4 and all(torch.equal(a, b) for a, b in zip(auroc.preds, ps))
+    torch.testing.assert_close(auroc.compute(), multilabel_auroc(P, T, L, average=average, ignore_index=-1),
+                               rtol=1e-6, atol=0)
+    torch.testing.assert_close(ap.compute(), multilabel_average_precision(P, T, L, average=average, ignore_index=-1),
+                               rtol=1e-6, atol=0)
+    fpr, tpr, thr = roc.compute()
+    curves = O.multilabel_clf_curves(P.cpu().numpy(), T.cpu().numpy(), -1)
+    for l in range(L):
+        assert np.array_equal(thr[l].cpu().numpy()[1:], curves[l][2])
+        np.testing.assert_allclose(tpr[l].cpu().numpy()[1:], curves[l][1] / curves[l][1][-1], rtol=1e-6)
+    if average == "none":
+        want = [O.binary_auroc_exact(f, t) for f, t, _ in curves]
+        np.testing.assert_allclose(auroc.compute().cpu().numpy(), want, rtol=1e-6)
+
+
+def test_binary_metrics_over_many_updates():
+    from torchmetrics_forked_b200.classification import BinaryAUROC, BinaryAveragePrecision, BinaryROC
+
+    g = torch.Generator().manual_seed(13)
+    chunks = [(torch.rand(n, generator=g).cuda(), torch.randint(2, (n,), generator=g).cuda()) for n in (17, 5000, 1, 812)]
+    P, T = torch.cat([p for p, _ in chunks]), torch.cat([t for _, t in chunks])
+    au, ap, roc = BinaryAUROC(thresholds=None).cuda(), BinaryAveragePrecision(thresholds=None).cuda(), BinaryROC(thresholds=None).cuda()
+    for p, t in chunks:
+        au.update(p, t)
+        ap.update(p, t)
+        roc.update(p, t)
+    f, t, h = O.binary_clf_curve(P.cpu().numpy(), T.cpu().numpy())
+    np.testing.assert_allclose(float(au.compute()), O.binary_auroc_exact(f, t), rtol=1e-6)
+    np.testing.assert_allclose(float(ap.compute()), O.binary_average_precision_exact(f, t), rtol=1e-6)
+    assert np.array_equal(roc.compute()[2].cpu().numpy()[1:], h)

@@ -1,6 +1,6 @@
 """Host-side launchers of the exact-curve kernels (K3): conditional sigmoid, ordered ignore-filter, batched
 sort + scan, area reductions.  Re-exported through :mod:`torchmetrics_forked_b200.kernels`."""
-from typing import List, Optional, Tuple
+from typing import List, Optional, Sequence, Tuple, Union
 
 import torch
 from torch import Tensor
@@ -75,20 +75,56 @@ _SCORE_ERROR = (
 )
 
 
-def _run_curves(preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int):
+Chunks = Union[Tensor, Sequence[Tensor]]
+
+
+def as_columns(x: Chunks) -> Chunks:
+    """1-d (binary) scores / targets, or a list of such chunks, as ``[n, 1]`` column(s)."""
+    if isinstance(x, Tensor):
+        return x.reshape(-1, 1)
+    return [c.reshape(-1, 1) for c in x]
+
+
+def _chunk_lists(preds: Chunks, target: Chunks) -> Tuple[List[Tensor], List[Tensor]]:
+    """Validated, contiguous ``[n_i, L]`` chunk lists (the per-update buffers of an exact-mode state)."""
+    ps = [preds] if isinstance(preds, Tensor) else list(preds)
+    ts = [target] if isinstance(target, Tensor) else list(target)
+    if len(ps) != len(ts) or not ps:
+        raise ValueError("`preds` and `target` must hold the same, non-zero number of chunks")
+    for p, t in zip(ps, ts):
+        nat.require_cuda(p, "preds")
+        nat.require_cuda(t, "target")
+        if p.ndim != 2 or p.shape != t.shape:
+            raise ValueError("`preds` and `target` must both have shape (N, L)")
+        if p.shape[1] != ps[0].shape[1] or p.dtype != ps[0].dtype or t.dtype != ts[0].dtype:
+            raise ValueError("all chunks must agree in the number of labels and in dtype")
+        if p.device != ps[0].device or t.device != ps[0].device:
+            raise ValueError("all chunks must live on one device")
+    return [_as_kernel_input(p) for p in ps], [_as_kernel_input(t) for t in ts]
+
+
+def _chunk_table(ps: List[Tensor], ts: List[Tensor]) -> Tuple[Tensor, int]:
+    """Device table for the chunked entry points (layout: include/tmb200.h) and the total row count."""
+    starts = [0]
+    for p in ps:
+        starts.append(starts[-1] + p.shape[0])
+    table = torch.tensor(
+        starts + [p.data_ptr() for p in ps] + [t.data_ptr() for t in ts], dtype=torch.int64, device=ps[0].device
+    )
+    return table, starts[-1]
+
+
+def _run_curves(preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int):
     """pack -> batched radix sort -> boundary / prefix scan; everything stays on the device.
 
-    Returns ``(fps, tps, thr)`` as ``[L, N]`` float32 buffers, ``counts`` (int64 ``[L]``, valid prefix of each
-    row) and the int32 error word.
+    ``preds`` / ``target`` are ``[N, L]`` tensors or lists of ``[n_i, L]`` chunks (read in place, never
+    concatenated).  Returns ``(fps, tps, thr)`` as ``[L, N]`` float32 buffers, ``counts`` (int64 ``[L]``, valid
+    prefix of each row) and the int32 error word.
     """
-    nat.require_cuda(preds, "preds")
-    nat.require_cuda(target, "target")
-    if preds.ndim != 2 or preds.shape != target.shape:
-        raise ValueError("`preds` and `target` must both have shape (N, L)")
-    preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
-    n, num_labels = preds.shape
-    dev = preds.device
+    ps, ts = _chunk_lists(preds, target)
+    num_labels = ps[0].shape[1]
+    n = sum(p.shape[0] for p in ps)
+    dev = ps[0].device
     fps = torch.empty(num_labels, n, dtype=torch.float32, device=dev)
     tps = torch.empty(num_labels, n, dtype=torch.float32, device=dev)
     thr = torch.empty(num_labels, n, dtype=torch.float32, device=dev)
@@ -97,30 +133,41 @@ def _run_curves(preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_
     has_ign = int(ignore_index is not None)
     if n > 0:
         scratch = torch.empty(int(nat.lib().tmb_clf_curve_scratch_bytes(n, num_labels)), dtype=torch.uint8, device=dev)
+        tail = (
+            n, num_labels, has_ign, int(ignore_index) if has_ign else 0, int(pos_label), nat.ptr(scratch),
+            scratch.numel(), nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts), nat.ptr(err),
+            nat.stream_ptr(dev),
+        )  # fmt: skip
         with torch.cuda.device(dev):
-            rc = nat.lib().tmb_clf_curves(
-                nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target), n, num_labels,
-                has_ign, int(ignore_index) if has_ign else 0, int(pos_label), nat.ptr(scratch), scratch.numel(),
-                nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts), nat.ptr(err), nat.stream_ptr(dev),
-            )  # fmt: skip
-        nat.check(rc, "tmb_clf_curves")
-    return fps, tps, thr, counts, err
+            if len(ps) == 1:
+                rc = nat.lib().tmb_clf_curves(
+                    nat.ptr(ps[0]), nat.float_code(ps[0]), nat.ptr(ts[0]), nat.label_code(ts[0]), *tail
+                )
+                nat.check(rc, "tmb_clf_curves")
+            else:
+                table, _ = _chunk_table(ps, ts)
+                rc = nat.lib().tmb_clf_curves_chunked(
+                    nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), *tail
+                )
+                nat.check(rc, "tmb_clf_curves_chunked")
+    return fps, tps, thr, counts, err, ps[0].dtype
 
 
 def clf_curves(
-    preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int = 1
+    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1
 ) -> Tuple[List[Tensor], List[Tensor], List[Tensor]]:
-    """Per-label ``(fps, tps, thresholds)`` of ``[N, L]`` scores / targets: batched radix sort + scan.
+    """Per-label ``(fps, tps, thresholds)`` of ``[N, L]`` scores / targets (or lists of ``[n_i, L]`` chunks):
+    batched radix sort + scan.
 
     Returns three lists of ``L`` 1-d tensors (views into three ``[L, N]`` float32 buffers); thresholds come
     back in the dtype of ``preds``.  One host read of the ``L`` curve lengths is unavoidable because the
     outputs have data-dependent sizes.
     """
-    fps, tps, thr, counts, err = _run_curves(preds, target, ignore_index, pos_label)
+    fps, tps, thr, counts, err, out_dtype = _run_curves(preds, target, ignore_index, pos_label)
     lengths = counts.cpu().tolist()  # the one synchronisation of the exact compute path
     if int(err.item()) & nat.ERR_SCORE_RANGE:
         raise RuntimeError(_SCORE_ERROR)
-    num_labels, out_dtype = preds.shape[1], preds.dtype
+    num_labels = fps.shape[0]
     f_list = [fps[l, : lengths[l]] for l in range(num_labels)]
     t_list = [tps[l, : lengths[l]] for l in range(num_labels)]
     h_list = [thr[l, : lengths[l]] if out_dtype == torch.float32 else thr[l, : lengths[l]].to(out_dtype)
@@ -128,20 +175,29 @@ def clf_curves(
     return f_list, t_list, h_list
 
 
-def clf_curve_scores(preds: Tensor, target: Tensor, ignore_index: Optional[int], pos_label: int = 1) -> Tensor:
-    """Per-label area reductions of the exact curves, float64 ``[L, 4]``, without materialising Python lists:
+def clf_curve_scores(preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1) -> Tensor:
+    """Per-label area reductions of the exact curves, float64 ``[L, 4]``, straight from the sorted keys — the
+    curves themselves are never written:
 
     column 0: trapezoid area under (fps, tps) from (0,0), un-normalised; column 1: ``sum (tps_b - tps_{b-1}) *
     precision_b``; column 2 / 3: total negatives / positives.  ``AUROC = c0 / (c2 * c3)``, ``AP = c1 / c3``.
-    Nothing is read back to the host here.
+    ``preds`` / ``target`` as in :func:`clf_curves`.  Nothing is read back to the host here.
     """
-    fps, tps, _thr, counts, err = _run_curves(preds, target, ignore_index, pos_label)
-    n, num_labels = preds.shape
-    out = torch.empty(num_labels, 4, dtype=torch.float64, device=preds.device)
-    with torch.cuda.device(preds.device):
-        rc = nat.lib().tmb_curve_reduce(
-            nat.ptr(fps), nat.ptr(tps), n, num_labels, nat.ptr(counts), nat.ptr(out), nat.stream_ptr(preds.device)
-        )
-    nat.check(rc, "tmb_curve_reduce")
+    ps, ts = _chunk_lists(preds, target)
+    num_labels = ps[0].shape[1]
+    dev = ps[0].device
+    table, n = _chunk_table(ps, ts)
+    out = torch.empty(num_labels, 4, dtype=torch.float64, device=dev)
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    has_ign = int(ignore_index is not None)
+    nbytes = int(nat.lib().tmb_clf_curve_scratch_bytes(n, num_labels))
+    scratch = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = nat.lib().tmb_clf_curve_scores_chunked(
+            nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), n, num_labels, has_ign,
+            int(ignore_index) if has_ign else 0, int(pos_label), nat.ptr(scratch), scratch.numel(), nat.ptr(out),
+            nat.ptr(err), nat.stream_ptr(dev),
+        )  # fmt: skip
+    nat.check(rc, "tmb_clf_curve_scores_chunked")
     # a negative score poisons the result instead of costing a host sync here: NaN propagates to the metric
     return torch.where(err.bool(), torch.full_like(out, float("nan")), out)

@@ -64,6 +64,9 @@ class _CurveStateMixin:
 
     def _curve_state(self) -> Union[Tensor, Tuple[Tensor, Tensor]]:
         if self.thresholds is None:
+            if isinstance(self.preds, list) and len(self.preds) > 1:
+                # the per-update buffers go to the kernels as they are (chunk table): no concatenated copy
+                return list(self.preds), list(self.target)
             return dim_zero_cat(self.preds), dim_zero_cat(self.target)
         return self.confmat
 

@@ -198,42 +198,124 @@ __global__ void __launch_bounds__(256) k3_normalize_vec(const void* __restrict__
 }
 
 // ---- pack: [N, L] row-major -> label-major keys ----------------------------------------------------------------
+// The scores / targets of an exact-mode metric live in one buffer per `update` call (the reference concatenates
+// them in compute(): classification/precision_recall_curve.py:159 `dim_zero_cat`).  The pack kernel reads the
+// chunks where they lie through a device table, so the concatenated copy (a second 12 bytes per label-sample of
+// traffic and of HBM) never exists.
+//   table[0 .. C]        first row of chunk c (table[C] = N)
+//   table[C+1 .. 2C]     address of chunk c's scores   ([rows_c, L] row-major, dtype DT)
+//   table[2C+1 .. 3C]    address of chunk c's targets  ([rows_c, L] row-major, dtype tdt)
+struct PackSrc {
+  const void* preds;       // used when table == nullptr: one chunk
+  const void* target;
+  const long long* table;  // device memory, 3 C + 1 entries
+  int num_chunks;
+};
+
+constexpr int kPackRows = 128;    // rows per CTA: every label leaves as one 512-byte run of keys
+constexpr int kPackLabels = 128;  // labels per CTA
+constexpr int kPackThreads = 256;
+constexpr int kPackUnroll = 4;
+__host__ __device__ constexpr int pack_stride(int labels) {
+  // words between two label rows of the staging tile.  A warp stores 32 consecutive (row, label) elements: with
+  // >= 32 labels they differ in the label, bank (label + row) % 32 is conflict-free with stride = 1 mod 32; with
+  // few labels the warp spans 32 / labels rows and the stride has to be that many banks.
+  return kPackRows + (labels >= 32 ? 1 : ((32 + labels - 1) / labels) % 32);
+}
+
+// A CTA reads rows [n0, n0 + 128) x labels [l0, l0 + lt): with lt == L (any L <= 128) that is ONE contiguous
+// 128 L-element region per chunk, read with full-width coalesced loads whatever L is (the earlier 32 x 32
+// transpose tile fetched 1.7x the algorithmic bytes at L = 100: 400-byte rows cut into 128-byte pieces that
+// straddle sectors).  Element e of the region -> (row, label) by a multiply-high with ceil(2^32 / lt).
 template <int DT>
-__global__ void __launch_bounds__(256) k3_pack(const void* __restrict__ preds, const void* __restrict__ target, int tdt,
-                                               int64_t N, int L, int has_ignore, int64_t ignore, int64_t pos_label,
-                                               uint32_t* __restrict__ keys, unsigned long long* n_valid, int* err) {
-  __shared__ uint32_t tile[32][33];
-  __shared__ int cnt[32];
-  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const int64_t n0 = (int64_t)blockIdx.x * 32;
-  const int l0 = blockIdx.y * 32;
-  if (threadIdx.x < 32) cnt[threadIdx.x] = 0;
-  bool negative = false;
-  for (int j = ty; j < 32; j += 8) {
-    const int64_t n = n0 + j;
-    const int l = l0 + tx;
-    uint32_t key = kSentinel;
-    if (n < N && l < L) {
-      const int64_t idx = n * L + l;
-      const int64_t t = load_label(target, tdt, idx);
-      if (!(has_ignore && t == ignore)) key = make_key(load_elem<DT>(preds, idx), t == pos_label, negative);
+__global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, int64_t N, int L, int has_ignore,
+                                                        int64_t ignore, int64_t pos_label, uint32_t* __restrict__ keys,
+                                                        unsigned long long* n_valid, int* err) {
+  extern __shared__ uint32_t tile[];  // [lt][stride]
+  __shared__ int sh_chunk;
+  __shared__ int cnt[kPackLabels];
+  const int lane = threadIdx.x & 31;
+  const int64_t n0 = (int64_t)blockIdx.x * kPackRows;
+  const int l0 = blockIdx.y * kPackLabels;
+  const int lt = min(kPackLabels, L - l0);
+  const int rows = (int)min((int64_t)kPackRows, N - n0);
+  const int stride = pack_stride(lt);
+  const uint32_t magic = lt > 1 ? (uint32_t)(0x100000000ull / (unsigned)lt) + 1u : 0u;  // e / lt for e * lt < 2^32
+  const int C = src.num_chunks;
+  if (threadIdx.x < kPackLabels) cnt[threadIdx.x] = 0;
+  if (src.table != nullptr) {
+    if (threadIdx.x == 0) {  // last chunk that starts at or before n0
+      int lo = 0, hi = C - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (src.table[mid] <= n0) lo = mid; else hi = mid - 1;
+      }
+      sh_chunk = lo;
     }
-    tile[j][tx] = key;
-  }
-  if (negative) atomicOr(err, TMB_ERR_SCORE_RANGE);
-  __syncthreads();
-  for (int j = ty; j < 32; j += 8) {  // j is warp-uniform: every lane reaches the ballot
-    const int l = l0 + j;
-    const int64_t n = n0 + tx;
-    const bool in_range = (l < L) && (n < N);
-    const uint32_t key = in_range ? tile[tx][j] : kSentinel;
-    if (in_range) keys[(int64_t)l * N + n] = key;
-    const unsigned b = __ballot_sync(kFull, in_range && key_valid(key));
-    if (tx == 0 && b) atomicAdd(&cnt[j], __popc(b));
   }
   __syncthreads();
-  if (threadIdx.x < 32 && l0 + (int)threadIdx.x < L && cnt[threadIdx.x])
-    atomicAdd(&n_valid[l0 + threadIdx.x], (unsigned long long)cnt[threadIdx.x]);
+  int c = src.table != nullptr ? sh_chunk : 0;
+  bool negative = false;
+  const int total = rows * lt;
+  for (int e0 = threadIdx.x; e0 < total; e0 += kPackThreads * kPackUnroll) {
+    float v[kPackUnroll];
+    int64_t t[kPackUnroll];
+    int slot[kPackUnroll];
+#pragma unroll
+    for (int q = 0; q < kPackUnroll; ++q) {
+      const int e = e0 + q * kPackThreads;
+      slot[q] = -1;
+      if (e < total) {
+        const int r = lt > 1 ? (int)__umulhi((uint32_t)e, magic) : e;
+        const int col = e - r * lt;
+        const int64_t n = n0 + r;
+        const void* pb = src.preds;
+        const void* tb = src.target;
+        int64_t row = n;
+        if (src.table != nullptr) {
+          while (n >= src.table[c + 1]) ++c;  // rows only grow along e: c never goes back
+          row = n - src.table[c];
+          pb = (const void*)src.table[C + 1 + c];
+          tb = (const void*)src.table[2 * C + 1 + c];
+        }
+        const int64_t idx = row * L + l0 + col;
+        v[q] = load_elem<DT>(pb, idx);
+        t[q] = load_label(tb, tdt, idx);
+        slot[q] = col * stride + r;
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < kPackUnroll; ++q) {
+      if (slot[q] >= 0) {
+        uint32_t key = kSentinel;
+        if (!(has_ignore && t[q] == ignore)) key = make_key(v[q], t[q] == pos_label, negative);
+        tile[slot[q]] = key;
+      }
+    }
+  }
+  __syncthreads();
+  if (__any_sync(kFull, negative) && lane == 0) atomicOr(err, TMB_ERR_SCORE_RANGE);
+  // write-out: 128 consecutive keys per label; a warp stays inside one label (128 % 32 == 0)
+  for (int o = threadIdx.x; o < lt * kPackRows; o += kPackThreads) {
+    const int col = o >> 7, r = o & (kPackRows - 1);
+    const bool in_range = r < rows;
+    uint32_t key = kSentinel;
+    if (in_range) {
+      key = tile[col * stride + r];
+      keys[(int64_t)(l0 + col) * N + n0 + r] = key;
+    }
+    if (has_ignore) {
+      const unsigned b = __ballot_sync(kFull, in_range && key_valid(key));
+      if (lane == 0 && b) atomicAdd(&cnt[col], __popc(b));
+    }
+  }
+  if (has_ignore) {
+    __syncthreads();
+    if (threadIdx.x < lt && cnt[threadIdx.x])
+      atomicAdd(&n_valid[l0 + threadIdx.x], (unsigned long long)cnt[threadIdx.x]);
+  } else if (blockIdx.x == 0 && threadIdx.x < lt) {
+    n_valid[l0 + threadIdx.x] = (unsigned long long)N;  // nothing is ignored: every label counts all N rows
+  }
 }
 
 // ---- radix sort ----------------------------------------------------------------------------------------------
@@ -249,15 +331,19 @@ __global__ void __launch_bounds__(kSortThreads) k3_sort_hist(const uint32_t* __r
   __shared__ uint32_t wh[kSortWarps][256];
   const int seg = blockIdx.y, blk = blockIdx.x;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) (&wh[0][0])[i] = 0;
-  __syncthreads();
   const uint32_t* k = keys + (int64_t)seg * N;
   const int64_t start = (int64_t)blk * kSortTile + w * kWarpSpan;
+  const int span = (int)min((int64_t)kWarpSpan, N - start);  // <= 0 for a warp past the end
+  // all 16 loads first: interleaved with the shared-memory atomics the compiler kept them in program order and
+  // every warp paid 16 DRAM latencies back to back
+  uint32_t key[kSortItems];
 #pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const int64_t idx = start + r * 32 + lane;
-    if (idx < N) atomicAdd(&wh[w][(k[idx] >> shift) & 255u], 1u);
-  }
+  for (int r = 0; r < kSortItems; ++r) key[r] = (r * 32 + lane < span) ? ldg_stream4(k + start + r * 32 + lane) : 0u;
+  for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) (&wh[0][0])[i] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < kSortItems; ++r)
+    if (r * 32 + lane < span) atomicAdd(&wh[w][(key[r] >> shift) & 255u], 1u);
   __syncthreads();
   if (threadIdx.x < 256) {
     uint32_t s = 0;
@@ -310,6 +396,23 @@ __global__ void __launch_bounds__(1024) k3_scan_u32(uint32_t* __restrict__ data,
   if (totals != nullptr && threadIdx.x == 0) totals[blockIdx.x] = (long long)carry;
 }
 
+// peers & (lanes whose `bit` of v equals mine): one step of an 8-ballot match over the digit
+__device__ __forceinline__ unsigned match_bit(unsigned peers, uint32_t v, uint32_t bit) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      ".reg .b32 t, s, m;\n\t"
+      "and.b32 t, %1, %2;\n\t"
+      "setp.ne.u32 p, t, 0;\n\t"
+      "vote.sync.ballot.b32 s, p, 0xffffffff;\n\t"
+      "selp.b32 m, 0, 0xffffffff, p;\n\t"
+      "lop3.b32 %0, %0, s, m, 0x60;\n\t"  // peers & (s ^ m): s where my bit is set, ~s where it is clear
+      "}"
+      : "+r"(peers)
+      : "r"(v), "r"(bit));
+  return peers;
+}
+
 // stable scatter of one tile.  Ranking inside a warp: lanes holding the same digit find each other with
 // match_any, the lowest such lane bumps the warp's digit counter for the whole group, each lane adds its
 // position inside the group.  Order = (warp, round, lane) = memory order, so the pass is stable.
@@ -335,36 +438,32 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
   const int64_t tile0 = (int64_t)blk * kSortTile;
   const int64_t start = tile0 + w * kWarpSpan;
   const int tile_n = (int)min((int64_t)kSortTile, N - tile0);
+  const int span = (int)min((int64_t)kWarpSpan, N - start);  // <= 0 for a warp past the end
   const unsigned lt_mask = (1u << lane) - 1u;
+  // Positions past the end of the segment carry key 0xffffffff: digit 255 in every pass, and — being the last
+  // positions of the tile — they rank behind every real key of that digit, so they land at the very end of the
+  // digit-ordered tile (local index >= tile_n) and are never written.  No validity test in the loops below.
   uint32_t key[kSortItems];
   uint32_t rank[kSortItems];
 #pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const int64_t idx = start + r * 32 + lane;
-    key[r] = (idx < N) ? k[idx] : 0u;
-  }
+  for (int r = 0; r < kSortItems; ++r)
+    key[r] = (r * 32 + lane < span) ? ldg_stream4(k + start + r * 32 + lane) : 0xffffffffu;
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    const bool valid = (start + r * 32 + lane) < N;
-    const uint32_t d = (key[r] >> shift) & 255u;
+    const uint32_t dk = key[r] >> shift;
     // lanes holding the same digit, from eight ballots (one per digit bit).  match.any gives the same mask in one
     // instruction, but its latency grows with the number of distinct values in the warp (~28 for random digits)
     // and made the ranking, not the memory traffic, the cost of this kernel.
-    unsigned peers = __ballot_sync(kFull, valid);
+    // Four instructions per bit (test, vote, select, and-xor), pinned in PTX: from the C form the compiler
+    // derived the predicate twice and spent six.
+    unsigned peers = kFull;
 #pragma unroll
-    for (int bit = 0; bit < 8; ++bit) {
-      const unsigned set = __ballot_sync(kFull, (d >> bit) & 1u);
-      peers &= ((d >> bit) & 1u) ? set : ~set;
-    }
+    for (int bit = 0; bit < 8; ++bit) peers = match_bit(peers, dk, 1u << bit);
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
-    if (lane == leader && valid) {
-      old = wh[w][d];
-      wh[w][d] = old + __popc(peers);
-    }
-    old = __shfl_sync(kFull, old, leader);
+    if (lane == leader) old = atomicAdd(&wh[w][dk & 255u], (uint32_t)__popc(peers));
+    old = __shfl_sync(kFull, old, leader);  // also keeps the rounds in order: round r + 1 sees round r's counts
     rank[r] = old + __popc(peers & lt_mask);
-    __syncwarp();
   }
   __syncthreads();
   // per digit: prefix over the warps, tile total; then an exclusive scan of the totals over the 256 digits
@@ -399,10 +498,8 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
-    if ((start + r * 32 + lane) < N) {
-      const uint32_t d = (key[r] >> shift) & 255u;
-      sorted[tile_off[d] + wh[w][d] + rank[r]] = key[r];
-    }
+    const uint32_t d = (key[r] >> shift) & 255u;
+    sorted[tile_off[d] + wh[w][d] + rank[r]] = key[r];
   }
   __syncthreads();
   uint32_t* o = out + (int64_t)seg * N;
@@ -465,6 +562,30 @@ __device__ __forceinline__ void curve_load(const uint32_t* __restrict__ k, int64
   }
 }
 
+// the same staging, but the thread keeps only two 16-bit masks (bit j: position base + j is a counted positive /
+// ends a threshold) — all the partial sums and the area reductions need
+__device__ __forceinline__ void curve_load_bits(const uint32_t* __restrict__ k, int64_t N, int64_t nv, int64_t tile0,
+                                                uint32_t* sh_keys, uint32_t& pos_bits, uint32_t& bnd_bits) {
+  for (int i = threadIdx.x; i <= kCurveTile; i += kCurveThreads)
+    sh_keys[skew(i)] = (tile0 + i < N) ? k[tile0 + i] : kSentinel;
+  __syncthreads();
+  const int base = threadIdx.x * kCurveItems;
+  const int64_t i0 = tile0 + base;
+  pos_bits = 0;
+  bnd_bits = 0;
+  uint32_t key = sh_keys[skew(base)];
+#pragma unroll
+  for (int j = 0; j < kCurveItems; ++j) {
+    const uint32_t next = sh_keys[skew(base + j + 1)];
+    if (i0 + j < nv) {
+      const bool boundary = (i0 + j == nv - 1) || !(key_score(next) - key_score(key) == 0.0f);
+      pos_bits |= key_positive(key) << j;
+      bnd_bits |= (boundary ? 1u : 0u) << j;
+    }
+    key = next;
+  }
+}
+
 // block-wide exclusive prefix of one uint32 per thread (256 threads), also returns the block total
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_buf, uint32_t& total) {
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -488,27 +609,40 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* warp_b
   return before + incl - v;
 }
 
-// pos_part / bnd_part[seg * ntile + tile] = positives / boundaries inside the tile
+// pos_part / bnd_part[seg * ntile + tile] = positives / boundaries inside the tile;
+// tile_last[...] = 0 if the tile holds no boundary, else ((local position of its last boundary + 1) << 16) |
+// (positives of the tile up to and including that position) — what the next tile needs to know about "the
+// previous curve point" in k3_curve_scores
 __global__ void __launch_bounds__(kCurveThreads) k3_curve_partials(const uint32_t* __restrict__ keys, int64_t N,
                                                                    const unsigned long long* __restrict__ n_valid,
                                                                    uint32_t* __restrict__ pos_part,
-                                                                   uint32_t* __restrict__ bnd_part, int ntile) {
+                                                                   uint32_t* __restrict__ bnd_part,
+                                                                   uint32_t* __restrict__ tile_last, int ntile) {
   __shared__ uint32_t buf[kCurveThreads / 32];
   __shared__ uint32_t sh_keys[kKeyWords];
   const int seg = blockIdx.y, blk = blockIdx.x;
   const int64_t nv = (int64_t)n_valid[seg];
   const int64_t tile0 = (int64_t)blk * kCurveTile;
-  uint32_t ps = 0, bs = 0;
-  if (tile0 < nv) {  // CTA-uniform
-    CurveItems it;
-    curve_load(keys + (int64_t)seg * N, N, nv, tile0, sh_keys, it, ps, bs);
-  }
+  uint32_t pb = 0, bb = 0;
+  if (tile0 < nv) curve_load_bits(keys + (int64_t)seg * N, N, nv, tile0, sh_keys, pb, bb);  // CTA-uniform
   uint32_t tot_p, tot_b;
-  block_excl_scan(ps, buf, tot_p);
-  block_excl_scan(bs, buf, tot_b);
+  const uint32_t pe = block_excl_scan(__popc(pb), buf, tot_p);
+  block_excl_scan(__popc(bb), buf, tot_b);
+  uint32_t cand = 0;
+  if (bb) {
+    const int j = 31 - __clz(bb);
+    cand = ((threadIdx.x * kCurveItems + j + 1) << 16) | (pe + __popc(pb & ((2u << j) - 1u)));
+  }
+  cand = __reduce_max_sync(kFull, cand);
+  if ((threadIdx.x & 31) == 0) buf[threadIdx.x >> 5] = cand;
+  __syncthreads();
   if (threadIdx.x == 0) {
+    uint32_t last = 0;
+#pragma unroll
+    for (int ww = 0; ww < kCurveThreads / 32; ++ww) last = max(last, buf[ww]);
     pos_part[(int64_t)seg * ntile + blk] = tot_p;
     bnd_part[(int64_t)seg * ntile + blk] = tot_b;
+    tile_last[(int64_t)seg * ntile + blk] = last;
   }
 }
 
@@ -556,6 +690,115 @@ __global__ void __launch_bounds__(kCurveThreads) k3_curve_emit(const uint32_t* _
     fps[out0 + i] = sh_f[i];
     tps[out0 + i] = sh_t[i];
     thr[out0 + i] = sh_h[i];
+  }
+}
+
+// ---- sorted keys -> area reductions, no curve in memory ----------------------------------------------------------
+// AUROC / average precision need sums over consecutive curve points only, so the fused metrics never write the
+// three [L, N] float32 curves (12 bytes per label-sample) just to read two of them back: every thread walks its
+// 16 sorted positions, and at a boundary adds the term of that curve point.  The previous curve point of a
+// thread's first boundary comes from an exclusive max-scan of (position + 1) << 32 | tps over the CTA, seeded
+// with the last boundary of the nearest earlier tile that has one (tile_last).  The float32 roundings are the
+// ones the emitted curve would carry (tps = float32(count), fps = float32(1 + idx) - tps), the accumulation is
+// float64 — same values as k3_curve_emit + k3_curve_reduce; `out` as documented there, zero on entry.
+__global__ void __launch_bounds__(kCurveThreads) k3_curve_scores(const uint32_t* __restrict__ keys, int64_t N,
+                                                                 const unsigned long long* __restrict__ n_valid,
+                                                                 const uint32_t* __restrict__ pos_excl,
+                                                                 const uint32_t* __restrict__ tile_last, int ntile,
+                                                                 double* __restrict__ out) {
+  __shared__ uint32_t buf[kCurveThreads / 32];
+  __shared__ uint32_t sh_keys[kKeyWords];
+  __shared__ unsigned long long wmax[kCurveThreads / 32];
+  __shared__ unsigned long long sh_carry;
+  __shared__ double red[2][kCurveThreads / 32];
+  const int seg = blockIdx.y, blk = blockIdx.x;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t nv = (int64_t)n_valid[seg];
+  const int64_t tile0 = (int64_t)blk * kCurveTile;
+  if (tile0 >= nv) return;  // CTA-uniform
+  uint32_t pb, bb;
+  curve_load_bits(keys + (int64_t)seg * N, N, nv, tile0, sh_keys, pb, bb);
+  if (w == 0) {  // nearest earlier tile with a boundary, 32 tiles per step (ties spanning whole tiles are rare)
+    unsigned long long carry = 0;
+    for (int base = blk - 1; base >= 0; base -= 32) {
+      const int j = base - lane;
+      const uint32_t tl = j >= 0 ? tile_last[(int64_t)seg * ntile + j] : 0u;
+      const unsigned found = __ballot_sync(kFull, tl != 0u);
+      if (found) {  // warp-uniform
+        const int src = __ffs(found) - 1;
+        const uint32_t v = __shfl_sync(kFull, tl, src);
+        const int jj = base - src;
+        const unsigned long long idx1 = (unsigned long long)jj * kCurveTile + (v >> 16);
+        carry = (idx1 << 32) | (unsigned long long)(pos_excl[(int64_t)seg * ntile + jj] + (v & 0xffffu));
+        break;
+      }
+    }
+    if (lane == 0) sh_carry = carry;
+  }
+  uint32_t dummy;
+  const uint32_t pe = pos_excl[(int64_t)seg * ntile + blk] + block_excl_scan(__popc(pb), buf, dummy);
+  const int64_t i0 = tile0 + (int64_t)threadIdx.x * kCurveItems;
+  unsigned long long mine = 0;
+  if (bb) {
+    const int j = 31 - __clz(bb);
+    mine = ((unsigned long long)(i0 + j + 1) << 32) | (unsigned long long)(pe + __popc(pb & ((2u << j) - 1u)));
+  }
+  unsigned long long incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const unsigned long long o = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl = max(incl, o);
+  }
+  if (lane == 31) wmax[w] = incl;
+  __syncthreads();  // also orders sh_carry (written before the scan's barriers) — kept explicit for wmax
+  unsigned long long prev = sh_carry;
+#pragma unroll
+  for (int ww = 0; ww < kCurveThreads / 32; ++ww)
+    if (ww < w) prev = max(prev, wmax[ww]);
+  {
+    const unsigned long long up = __shfl_up_sync(kFull, incl, 1);
+    if (lane > 0) prev = max(prev, up);
+  }
+  float ptf = __uint2float_rn((uint32_t)prev);
+  float pff = __ll2float_rn((long long)(prev >> 32)) - ptf;
+  uint32_t p_run = pe;
+  double area = 0.0, ap = 0.0;
+#pragma unroll
+  for (int j = 0; j < kCurveItems; ++j) {
+    p_run += (pb >> j) & 1u;
+    if ((bb >> j) & 1u) {
+      const float tf = __uint2float_rn(p_run);
+      const float ff = __ll2float_rn(1 + i0 + j) - tf;
+      const double fb = ff, tb = tf, fp = pff, tp = ptf;
+      area += (fb - fp) * (tb + tp) * 0.5;
+      ap += (tb - tp) * (tb / (tb + fb));
+      if (i0 + j == nv - 1) {
+        out[4 * seg + 2] = fb;
+        out[4 * seg + 3] = tb;
+      }
+      ptf = tf;
+      pff = ff;
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    area += __shfl_xor_sync(kFull, area, d);
+    ap += __shfl_xor_sync(kFull, ap, d);
+  }
+  if (lane == 0) {
+    red[0][w] = area;
+    red[1][w] = ap;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, p = 0.0;
+#pragma unroll
+    for (int i = 0; i < kCurveThreads / 32; ++i) {
+      a += red[0][i];
+      p += red[1][i];
+    }
+    if (a != 0.0) atomicAdd(&out[4 * seg + 0], a);
+    if (p != 0.0) atomicAdd(&out[4 * seg + 1], p);
   }
 }
 
@@ -665,7 +908,7 @@ static int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 struct CurvePlan {
   int64_t N, L;
   int nb, ntile;
-  int64_t off_keys_a, off_keys_b, off_counts, off_pos, off_bnd, off_nvalid, total;
+  int64_t off_keys_a, off_keys_b, off_counts, off_pos, off_bnd, off_last, off_nvalid, total;
 };
 
 static CurvePlan curve_plan(int64_t N, int64_t L) {
@@ -680,6 +923,7 @@ static CurvePlan curve_plan(int64_t N, int64_t L) {
   p.off_counts = off; off = align_up(off + L * 256 * (int64_t)p.nb * 4, 256);
   p.off_pos = off; off = align_up(off + L * (int64_t)p.ntile * 4, 256);
   p.off_bnd = off; off = align_up(off + L * (int64_t)p.ntile * 4, 256);
+  p.off_last = off; off = align_up(off + L * (int64_t)p.ntile * 4, 256);
   p.off_nvalid = off; off = align_up(off + L * 8, 256);
   p.total = off;
   return p;
@@ -751,12 +995,91 @@ extern "C" int64_t tmb_clf_curve_scratch_bytes(int64_t n, int64_t num_labels) {
   return curve_plan(n, num_labels).total;
 }
 
-extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n,
-                              int64_t num_labels, int has_ignore, int64_t ignore_index, int64_t pos_label,
-                              void* scratch, int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
-                              int64_t* counts, int32_t* err, void* stream) {
+namespace tmb {
+
+struct CurveBufs {
+  uint32_t *keys_a, *keys_b, *cnt, *pos_part, *bnd_part, *tile_last;
+  unsigned long long* n_valid;
+};
+
+static CurveBufs curve_bufs(const CurvePlan& p, void* scratch) {
+  char* base = (char*)scratch;
+  CurveBufs b;
+  b.keys_a = (uint32_t*)(base + p.off_keys_a);
+  b.keys_b = (uint32_t*)(base + p.off_keys_b);
+  b.cnt = (uint32_t*)(base + p.off_counts);
+  b.pos_part = (uint32_t*)(base + p.off_pos);
+  b.bnd_part = (uint32_t*)(base + p.off_bnd);
+  b.tile_last = (uint32_t*)(base + p.off_last);
+  b.n_valid = (unsigned long long*)(base + p.off_nvalid);
+  return b;
+}
+
+template <int DT>
+static int launch_pack(const PackSrc& src, int tdt, int64_t n, int L, int has_ignore, int64_t ignore,
+                       int64_t pos_label, const CurveBufs& b, int32_t* err, cudaStream_t st) {
+  const int lt_full = L < kPackLabels ? L : kPackLabels;
+  const int lt_last = L % kPackLabels ? L % kPackLabels : lt_full;
+  int words = lt_full * pack_stride(lt_full);
+  if (lt_last * pack_stride(lt_last) > words) words = lt_last * pack_stride(lt_last);
+  auto k = k3_pack<DT>;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kPackLabels * pack_stride(kPackLabels) * 4);
+  dim3 grid((unsigned)((n + kPackRows - 1) / kPackRows), (unsigned)((L + kPackLabels - 1) / kPackLabels));
+  k<<<grid, kPackThreads, words * 4, st>>>(src, tdt, n, L, has_ignore, ignore, pos_label, b.keys_a, b.n_valid, err);
+  return launch_status();
+}
+
+// pack + 4 sort passes; the sorted keys end up in b.keys_a
+static int pack_and_sort(const PackSrc& src, int preds_dtype, int target_dtype, int64_t n, int L, int has_ignore,
+                         int64_t ignore, int64_t pos_label, const CurvePlan& p, const CurveBufs& b, int32_t* err,
+                         cudaStream_t st) {
+  cudaMemsetAsync(b.n_valid, 0, (size_t)L * 8, st);
+  int rc;
+  switch (preds_dtype) {
+    case TMB_F32: rc = launch_pack<TMB_F32>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
+    case TMB_F16: rc = launch_pack<TMB_F16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
+    default: rc = launch_pack<TMB_BF16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
+  }
+  if (rc) return rc;
+  uint32_t* src_keys = b.keys_a;
+  uint32_t* dst_keys = b.keys_b;
+  cudaFuncSetAttribute(k3_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 8 * pass;
+    dim3 grid((unsigned)p.nb, (unsigned)L);
+    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src_keys, n, shift, b.cnt, p.nb);
+    if ((rc = launch_status())) return rc;
+    k3_scan_u32<<<L, 1024, 0, st>>>(b.cnt, (int64_t)256 * p.nb, nullptr);
+    if ((rc = launch_status())) return rc;
+    k3_sort_scatter<<<grid, kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, shift, b.cnt, p.nb);
+    if ((rc = launch_status())) return rc;
+    uint32_t* tmp = src_keys;
+    src_keys = dst_keys;
+    dst_keys = tmp;
+  }
+  return 0;  // an even number of passes: the result is back in keys_a
+}
+
+static int curve_tile_sums(int64_t n, int L, const CurvePlan& p, const CurveBufs& b, long long* counts,
+                           cudaStream_t st) {
+  dim3 grid((unsigned)p.ntile, (unsigned)L);
+  k3_curve_partials<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.bnd_part, b.tile_last,
+                                                    p.ntile);
+  if (int rc = launch_status()) return rc;
+  k3_scan_u32<<<L, 1024, 0, st>>>(b.pos_part, p.ntile, nullptr);
+  if (int rc = launch_status()) return rc;
+  if (counts != nullptr) {  // the curve lengths / output offsets are only needed when the curve is written
+    k3_scan_u32<<<L, 1024, 0, st>>>(b.bnd_part, p.ntile, counts);
+    if (int rc = launch_status()) return rc;
+  }
+  return 0;
+}
+
+static int curves_impl(const PackSrc& src, int preds_dtype, int target_dtype, int64_t n, int64_t num_labels,
+                       int has_ignore, int64_t ignore_index, int64_t pos_label, void* scratch, int64_t scratch_bytes,
+                       float* fps, float* tps, float* thresholds, int64_t* counts, int32_t* err, void* stream) {
   if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
-  if (n < 0 || num_labels < 1 || num_labels > 65535 * 32) return TMB_E_SHAPE;
+  if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
   if (n >= ((int64_t)1 << 31)) return TMB_E_LIMIT;  // 32-bit ranks / prefix counts per label
   if (!counts || !err) return TMB_E_NULL;
   cudaStream_t st = (cudaStream_t)stream;
@@ -764,67 +1087,73 @@ extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* ta
     cudaMemsetAsync(counts, 0, num_labels * 8, st);
     return launch_status();
   }
-  if (!preds || !target || !scratch || !fps || !tps || !thresholds) return TMB_E_NULL;
+  if (!scratch || !fps || !tps || !thresholds) return TMB_E_NULL;
   const CurvePlan p = curve_plan(n, num_labels);
   if (scratch_bytes < p.total) return TMB_E_SCRATCH;
-  char* base = (char*)scratch;
-  uint32_t* keys_a = (uint32_t*)(base + p.off_keys_a);
-  uint32_t* keys_b = (uint32_t*)(base + p.off_keys_b);
-  uint32_t* cnt = (uint32_t*)(base + p.off_counts);
-  uint32_t* pos_part = (uint32_t*)(base + p.off_pos);
-  uint32_t* bnd_part = (uint32_t*)(base + p.off_bnd);
-  unsigned long long* n_valid = (unsigned long long*)(base + p.off_nvalid);
+  const CurveBufs b = curve_bufs(p, scratch);
   const int L = (int)num_labels;
+  if (int rc = pack_and_sort(src, preds_dtype, target_dtype, n, L, has_ignore, ignore_index, pos_label, p, b, err, st))
+    return rc;
+  if (int rc = curve_tile_sums(n, L, p, b, (long long*)counts, st)) return rc;
+  dim3 grid((unsigned)p.ntile, (unsigned)L);
+  cudaFuncSetAttribute(k3_curve_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, kEmitSmem);
+  k3_curve_emit<<<grid, kCurveThreads, kEmitSmem, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.bnd_part, p.ntile, fps,
+                                                       tps, thresholds);
+  return launch_status();
+}
 
-  cudaMemsetAsync(n_valid, 0, num_labels * 8, st);
-  {
-    dim3 grid((unsigned)((n + 31) / 32), (unsigned)((L + 31) / 32));
-    switch (preds_dtype) {
-      case TMB_F32:
-        k3_pack<TMB_F32><<<grid, 256, 0, st>>>(preds, target, target_dtype, n, L, has_ignore, ignore_index, pos_label,
-                                               keys_a, n_valid, err);
-        break;
-      case TMB_F16:
-        k3_pack<TMB_F16><<<grid, 256, 0, st>>>(preds, target, target_dtype, n, L, has_ignore, ignore_index, pos_label,
-                                               keys_a, n_valid, err);
-        break;
-      default:
-        k3_pack<TMB_BF16><<<grid, 256, 0, st>>>(preds, target, target_dtype, n, L, has_ignore, ignore_index, pos_label,
-                                                keys_a, n_valid, err);
-        break;
-    }
-    if (int rc = launch_status()) return rc;
-  }
-  uint32_t* src = keys_a;
-  uint32_t* dst = keys_b;
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 8 * pass;
-    dim3 grid((unsigned)p.nb, (unsigned)L);
-    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src, n, shift, cnt, p.nb);
-    if (int rc = launch_status()) return rc;
-    k3_scan_u32<<<L, 1024, 0, st>>>(cnt, (int64_t)256 * p.nb, nullptr);
-    if (int rc = launch_status()) return rc;
-    cudaFuncSetAttribute(k3_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
-    k3_sort_scatter<<<grid, kSortThreads, kScatterSmem, st>>>(src, dst, n, shift, cnt, p.nb);
-    if (int rc = launch_status()) return rc;
-    uint32_t* tmp = src;
-    src = dst;
-    dst = tmp;
-  }
-  // after 4 passes the sorted keys are back in keys_a (== src)
-  {
-    dim3 grid((unsigned)p.ntile, (unsigned)L);
-    k3_curve_partials<<<grid, kCurveThreads, 0, st>>>(src, n, n_valid, pos_part, bnd_part, p.ntile);
-    if (int rc = launch_status()) return rc;
-    k3_scan_u32<<<L, 1024, 0, st>>>(pos_part, p.ntile, nullptr);
-    if (int rc = launch_status()) return rc;
-    k3_scan_u32<<<L, 1024, 0, st>>>(bnd_part, p.ntile, (long long*)counts);
-    if (int rc = launch_status()) return rc;
-    cudaFuncSetAttribute(k3_curve_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, kEmitSmem);
-    k3_curve_emit<<<grid, kCurveThreads, kEmitSmem, st>>>(src, n, n_valid, pos_part, bnd_part, p.ntile, fps, tps, thresholds);
-    if (int rc = launch_status()) return rc;
-  }
-  return 0;
+static bool chunk_table_ok(const int64_t* table, int64_t num_chunks) {
+  return table != nullptr && num_chunks >= 1 && num_chunks < ((int64_t)1 << 24);
+}
+
+}  // namespace tmb
+
+extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n,
+                              int64_t num_labels, int has_ignore, int64_t ignore_index, int64_t pos_label,
+                              void* scratch, int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
+                              int64_t* counts, int32_t* err, void* stream) {
+  if (n > 0 && (!preds || !target)) return TMB_E_NULL;
+  const PackSrc src{preds, target, nullptr, 1};
+  return curves_impl(src, preds_dtype, target_dtype, n, num_labels, has_ignore, ignore_index, pos_label, scratch,
+                     scratch_bytes, fps, tps, thresholds, counts, err, stream);
+}
+
+extern "C" int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
+                                      int target_dtype, int64_t n, int64_t num_labels, int has_ignore,
+                                      int64_t ignore_index, int64_t pos_label, void* scratch, int64_t scratch_bytes,
+                                      float* fps, float* tps, float* thresholds, int64_t* counts, int32_t* err,
+                                      void* stream) {
+  if (n > 0 && !chunk_table_ok(chunk_table, num_chunks)) return chunk_table ? TMB_E_SHAPE : TMB_E_NULL;
+  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks};
+  return curves_impl(src, preds_dtype, target_dtype, n, num_labels, has_ignore, ignore_index, pos_label, scratch,
+                     scratch_bytes, fps, tps, thresholds, counts, err, stream);
+}
+
+extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
+                                            int target_dtype, int64_t n, int64_t num_labels, int has_ignore,
+                                            int64_t ignore_index, int64_t pos_label, void* scratch,
+                                            int64_t scratch_bytes, double* scores, int32_t* err, void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
+  if (n >= ((int64_t)1 << 31)) return TMB_E_LIMIT;
+  if (!scores || !err) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(scores, 0, num_labels * 4 * sizeof(double), st);
+  if (int rc = launch_status()) return rc;
+  if (n == 0) return 0;
+  if (!chunk_table_ok(chunk_table, num_chunks)) return chunk_table ? TMB_E_SHAPE : TMB_E_NULL;
+  if (!scratch) return TMB_E_NULL;
+  const CurvePlan p = curve_plan(n, num_labels);
+  if (scratch_bytes < p.total) return TMB_E_SCRATCH;
+  const CurveBufs b = curve_bufs(p, scratch);
+  const int L = (int)num_labels;
+  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks};
+  if (int rc = pack_and_sort(src, preds_dtype, target_dtype, n, L, has_ignore, ignore_index, pos_label, p, b, err, st))
+    return rc;
+  if (int rc = curve_tile_sums(n, L, p, b, nullptr, st)) return rc;
+  dim3 grid((unsigned)p.ntile, (unsigned)L);
+  k3_curve_scores<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.tile_last, p.ntile, scores);
+  return launch_status();
 }
 
 extern "C" int tmb_curve_reduce(const float* fps, const float* tps, int64_t n, int64_t num_labels,

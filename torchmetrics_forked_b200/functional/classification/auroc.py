@@ -116,9 +116,9 @@ def _binary_auroc_compute(
         from torchmetrics_forked_b200 import kernels
 
         preds, target = state[0], state[1]
-        if preds.ndim > target.ndim:
+        if isinstance(preds, Tensor) and preds.ndim > target.ndim:
             preds = preds[:, 0]
-        scores = kernels.clf_curve_scores(preds.reshape(-1, 1), target.reshape(-1, 1), None, pos_label)
+        scores = kernels.clf_curve_scores(kernels.as_columns(preds), kernels.as_columns(target), None, pos_label)
         return _exact_auroc_from_scores(scores)[0]
     fpr, tpr, _ = _binary_roc_compute(state, thresholds, pos_label)
     if max_fpr is None or max_fpr == 1 or fpr.sum() == 0 or tpr.sum() == 0:
@@ -167,6 +167,9 @@ def _multilabel_auroc_arg_validation(
 
 def _flatten_valid(state: Tuple[Tensor, Tensor], ignore_index: Optional[int]) -> Tuple[Tensor, Tensor]:
     """Micro averaging in exact mode: every (sample, label) pair becomes one binary sample."""
+    if not isinstance(state[0], Tensor):  # per-update chunks: flatten (and filter) each one where it lies
+        pairs = [_flatten_valid((p, t), ignore_index) for p, t in zip(state[0], state[1])]
+        return [p for p, _ in pairs], [t for _, t in pairs]
     preds, target = state[0].flatten(), state[1].flatten()
     if ignore_index is not None:
         from torchmetrics_forked_b200 import kernels
@@ -192,7 +195,8 @@ def _multilabel_auroc_compute(
         from torchmetrics_forked_b200 import kernels
 
         scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1)
-        return _reduce_scores(_exact_auroc_from_scores(scores), average, (state[1] == 1).sum(dim=0).float())
+        # weights: the reference counts (target == 1) per label (:331); column 3 is that count already
+        return _reduce_scores(_exact_auroc_from_scores(scores), average, scores[:, 3].float())
     fpr, tpr, _ = _multilabel_roc_compute(state, num_labels, thresholds, ignore_index)
     return _reduce_auroc(fpr, tpr, average, weights=state[0][:, 1, :].sum(-1))
 

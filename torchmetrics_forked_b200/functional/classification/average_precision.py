@@ -62,7 +62,7 @@ def _binary_average_precision_compute(
     if not (isinstance(state, Tensor) and thresholds is not None):
         from torchmetrics_forked_b200 import kernels
 
-        scores = kernels.clf_curve_scores(state[0].reshape(-1, 1), state[1].reshape(-1, 1), None, 1)
+        scores = kernels.clf_curve_scores(kernels.as_columns(state[0]), kernels.as_columns(state[1]), None, 1)
         return _exact_ap_from_scores(scores)[0]
     precision, recall, _ = _binary_precision_recall_curve_compute(state, thresholds)
     return -torch.sum((recall[1:] - recall[:-1]) * precision[:-1])
@@ -116,7 +116,8 @@ def _multilabel_average_precision_compute(
         from torchmetrics_forked_b200.functional.classification.auroc import _reduce_scores
 
         scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1)
-        return _reduce_scores(_exact_ap_from_scores(scores), average, (state[1] == 1).sum(dim=0).float())
+        # weights: the reference counts (target == 1) per label (:308); column 3 is that count already
+        return _reduce_scores(_exact_ap_from_scores(scores), average, scores[:, 3].float())
     precision, recall, _ = _multilabel_precision_recall_curve_compute(state, num_labels, thresholds, ignore_index)
     return _reduce_average_precision(precision, recall, average, weights=state[0][:, 1, :].sum(-1))
 

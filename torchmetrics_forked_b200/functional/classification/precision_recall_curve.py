@@ -77,9 +77,9 @@ def _binary_clf_curve(
     """
     if sample_weights is not None:
         raise NotImplementedError("`sample_weights` is not used on the metric path and is not supported here")
-    if preds.ndim > target.ndim:
+    if isinstance(preds, Tensor) and preds.ndim > target.ndim:
         preds = preds[:, 0]
-    fps, tps, thr = kernels.clf_curves(preds.reshape(-1, 1), target.reshape(-1, 1), None, pos_label)
+    fps, tps, thr = kernels.clf_curves(kernels.as_columns(preds), kernels.as_columns(target), None, pos_label)
     return fps[0], tps[0], thr[0]
 
 

@@ -11,6 +11,7 @@ from torch import Tensor
 
 from torchmetrics_forked_b200 import _native as nat
 from torchmetrics_forked_b200._exact import (  # noqa: F401
+    as_columns,
     clf_curve_scores,
     clf_curves,
     compact_not_ignored,
