@@ -210,11 +210,12 @@ int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int p
  * exact-mode AUROC / average-precision metrics, tmb_clf_curves + tmb_curve_reduce, i.e.
  *   _binary_auroc_compute / _multilabel_auroc_compute               functional/classification/auroc.py:82-106, :307-332
  *   _binary_ / _multilabel_average_precision_compute                functional/classification/average_precision.py:70-75, :284-311
- * Same scratch size as tmb_clf_curves. */
+ * want_ap = 0 skips the average-precision sum (column 1 stays 0; it costs a float64 division per curve point
+ * that AUROC does not need).  Same scratch size as tmb_clf_curves. */
 int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
                                  int64_t n, int64_t num_labels, int has_ignore, int64_t ignore_index,
-                                 int64_t pos_label, void* scratch, int64_t scratch_bytes, double* scores,
-                                 int32_t* err, void* stream);
+                                 int64_t pos_label, int want_ap, void* scratch, int64_t scratch_bytes,
+                                 double* scores, int32_t* err, void* stream);
 
 /* Area reductions over the curves tmb_clf_curves emitted (same fps / tps buffers, label stride n, counts[l] points
  * each), replacing the per-label torch chains of

@@ -464,3 +464,23 @@ def test_binary_metrics_over_many_updates():
     np.testing.assert_allclose(float(au.compute()), O.binary_auroc_exact(f, t), rtol=1e-6)
     np.testing.assert_allclose(float(ap.compute()), O.binary_average_precision_exact(f, t), rtol=1e-6)
     assert np.array_equal(roc.compute()[2].cpu().numpy()[1:], h)
+
+
+def test_fused_scores_float32_rounding_path_beyond_2p24():
+    """From 2^24 rows on, float32(1 + idx) - float32(tps) rounds (as in the reference's float32 curves): the
+    integer fast path is off and the fused kernel must still reproduce emit + reduce."""
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator(device="cuda").manual_seed(33)
+    n = (1 << 24) + 4099
+    P = torch.rand(n, 1, generator=g, device="cuda")
+    T = torch.randint(2, (n, 1), generator=g, device="cuda")
+    fused = kernels.clf_curve_scores([P[:5_000_000], P[5_000_000:]], [T[:5_000_000], T[5_000_000:]], None, 1)
+    want = _emit_then_reduce(P, T, None)
+    assert torch.equal(fused[:, 2:], want[:, 2:])
+    torch.testing.assert_close(fused[:, :2], want[:, :2], rtol=1e-12, atol=0)
+    no_ap = kernels.clf_curve_scores(P, T, None, 1, want_ap=False)
+    assert torch.equal(no_ap[:, 0], fused[:, 0]) and float(no_ap[0, 1]) == 0.0
+    small = kernels.clf_curve_scores(P[:100_000], T[:100_000], None, 1, want_ap=False)
+    torch.testing.assert_close(small[:, 0], _emit_then_reduce(P[:100_000].contiguous(), T[:100_000].contiguous(), None)[:, 0],
+                               rtol=0, atol=0)

@@ -175,13 +175,16 @@ def clf_curves(
     return f_list, t_list, h_list
 
 
-def clf_curve_scores(preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1) -> Tensor:
+def clf_curve_scores(
+    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1, want_ap: bool = True
+) -> Tensor:
     """Per-label area reductions of the exact curves, float64 ``[L, 4]``, straight from the sorted keys — the
     curves themselves are never written:
 
     column 0: trapezoid area under (fps, tps) from (0,0), un-normalised; column 1: ``sum (tps_b - tps_{b-1}) *
     precision_b``; column 2 / 3: total negatives / positives.  ``AUROC = c0 / (c2 * c3)``, ``AP = c1 / c3``.
-    ``preds`` / ``target`` as in :func:`clf_curves`.  Nothing is read back to the host here.
+    ``preds`` / ``target`` as in :func:`clf_curves`; ``want_ap=False`` leaves column 1 at zero (AUROC does not need
+    its float64 division per curve point).  Nothing is read back to the host here.
     """
     ps, ts = _chunk_lists(preds, target)
     num_labels = ps[0].shape[1]
@@ -195,8 +198,8 @@ def clf_curve_scores(preds: Chunks, target: Chunks, ignore_index: Optional[int],
     with torch.cuda.device(dev):
         rc = nat.lib().tmb_clf_curve_scores_chunked(
             nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), n, num_labels, has_ign,
-            int(ignore_index) if has_ign else 0, int(pos_label), nat.ptr(scratch), scratch.numel(), nat.ptr(out),
-            nat.ptr(err), nat.stream_ptr(dev),
+            int(ignore_index) if has_ign else 0, int(pos_label), int(want_ap), nat.ptr(scratch), scratch.numel(),
+            nat.ptr(out), nat.ptr(err), nat.stream_ptr(dev),
         )  # fmt: skip
     nat.check(rc, "tmb_clf_curve_scores_chunked")
     # a negative score poisons the result instead of costing a host sync here: NaN propagates to the metric

@@ -73,8 +73,8 @@ SIGNATURES = {
     ),
     "tmb_clf_curve_scores_chunked": (
         c_int,
-        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p,
-         c_void_p, c_void_p],
+        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_int64,
+         c_void_p, c_void_p, c_void_p],
     ),
     "tmb_curve_reduce": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_compact_scratch_bytes": (c_int64, [c_int64]),

@@ -215,7 +215,7 @@ struct PackSrc {
 constexpr int kPackRows = 128;    // rows per CTA: every label leaves as one 512-byte run of keys
 constexpr int kPackLabels = 128;  // labels per CTA
 constexpr int kPackThreads = 256;
-constexpr int kPackUnroll = 4;
+constexpr int kPackUnroll = 8;
 __host__ __device__ constexpr int pack_stride(int labels) {
   // words between two label rows of the staging tile.  A warp stores 32 consecutive (row, label) elements: with
   // >= 32 labels they differ in the label, bank (label + row) % 32 is conflict-free with stride = 1 mod 32; with
@@ -254,44 +254,54 @@ __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, in
     }
   }
   __syncthreads();
+  // The tile's rows are walked chunk by chunk (CTA-uniform outer loop, normally one trip): inside, the base
+  // pointers are loop constants and the element loop contains no load but the data loads.  (A per-element
+  // "did the row cross into the next chunk?" test with the table read in its rare branch made every element
+  // wait for the previous element's data: the branch's load and the data loads shared a scoreboard.)
   int c = src.table != nullptr ? sh_chunk : 0;
   bool negative = false;
-  const int total = rows * lt;
-  for (int e0 = threadIdx.x; e0 < total; e0 += kPackThreads * kPackUnroll) {
-    float v[kPackUnroll];
-    int64_t t[kPackUnroll];
-    int slot[kPackUnroll];
+  int r_begin = 0;
+  while (r_begin < rows) {
+    int64_t c_begin = 0, c_end = N;
+    const void* pb = src.preds;
+    const void* tb = src.target;
+    if (src.table != nullptr) {
+      while (src.table[c + 1] <= n0 + r_begin) ++c;  // skips empty chunks too
+      c_begin = src.table[c];
+      c_end = src.table[c + 1];
+      pb = (const void*)src.table[C + 1 + c];
+      tb = (const void*)src.table[2 * C + 1 + c];
+    }
+    const int r_end = (int)min((int64_t)rows, c_end - n0);
+    const int64_t base_off = (n0 - c_begin) * L + l0;  // element offset of (row n0, label l0) inside the chunk
+    const int e_end = r_end * lt;
+    for (int e0 = r_begin * lt + threadIdx.x; e0 < e_end; e0 += kPackThreads * kPackUnroll) {
+      float v[kPackUnroll];
+      int64_t t[kPackUnroll];
+      int slot[kPackUnroll];
 #pragma unroll
-    for (int q = 0; q < kPackUnroll; ++q) {
-      const int e = e0 + q * kPackThreads;
-      slot[q] = -1;
-      if (e < total) {
-        const int r = lt > 1 ? (int)__umulhi((uint32_t)e, magic) : e;
-        const int col = e - r * lt;
-        const int64_t n = n0 + r;
-        const void* pb = src.preds;
-        const void* tb = src.target;
-        int64_t row = n;
-        if (src.table != nullptr) {
-          while (n >= src.table[c + 1]) ++c;  // rows only grow along e: c never goes back
-          row = n - src.table[c];
-          pb = (const void*)src.table[C + 1 + c];
-          tb = (const void*)src.table[2 * C + 1 + c];
+      for (int q = 0; q < kPackUnroll; ++q) {
+        const int e = e0 + q * kPackThreads;
+        slot[q] = -1;
+        if (e < e_end) {
+          const int r = lt > 1 ? (int)__umulhi((uint32_t)e, magic) : e;
+          const int col = e - r * lt;
+          const int64_t idx = base_off + (r * L + col);
+          v[q] = load_elem<DT>(pb, idx);
+          t[q] = load_label(tb, tdt, idx);
+          slot[q] = col * stride + r;
         }
-        const int64_t idx = row * L + l0 + col;
-        v[q] = load_elem<DT>(pb, idx);
-        t[q] = load_label(tb, tdt, idx);
-        slot[q] = col * stride + r;
       }
-    }
 #pragma unroll
-    for (int q = 0; q < kPackUnroll; ++q) {
-      if (slot[q] >= 0) {
-        uint32_t key = kSentinel;
-        if (!(has_ignore && t[q] == ignore)) key = make_key(v[q], t[q] == pos_label, negative);
-        tile[slot[q]] = key;
+      for (int q = 0; q < kPackUnroll; ++q) {
+        if (slot[q] >= 0) {
+          uint32_t key = kSentinel;
+          if (!(has_ignore && t[q] == ignore)) key = make_key(v[q], t[q] == pos_label, negative);
+          tile[slot[q]] = key;
+        }
       }
     }
+    r_begin = r_end;
   }
   __syncthreads();
   if (__any_sync(kFull, negative) && lane == 0) atomicOr(err, TMB_ERR_SCORE_RANGE);
@@ -413,6 +423,13 @@ __device__ __forceinline__ unsigned match_bit(unsigned peers, uint32_t v, uint32
   return peers;
 }
 
+__device__ __forceinline__ void put_rank(uint32_t* rank2, int r, uint32_t v) {  // r is a compile-time constant
+  if (r & 1) rank2[r >> 1] |= v << 16; else rank2[r >> 1] = v;
+}
+__device__ __forceinline__ uint32_t get_rank(const uint32_t* rank2, int r) {
+  return (r & 1) ? rank2[r >> 1] >> 16 : rank2[r >> 1] & 0xffffu;
+}
+
 // stable scatter of one tile.  Ranking inside a warp: lanes holding the same digit find each other with
 // match_any, the lowest such lane bumps the warp's digit counter for the whole group, each lane adds its
 // position inside the group.  Order = (warp, round, lane) = memory order, so the pass is stable.
@@ -420,19 +437,20 @@ __device__ __forceinline__ unsigned match_bit(unsigned peers, uint32_t v, uint32
 // neighbouring keys of one digit run (32 keys = 128 B on average), so a warp store touches a few sectors instead
 // of 32 (writing straight from the ranking registers cost 2.6 ms per pass at 2^21 x 100 keys — one 32-byte
 // sector transaction per 4-byte key).
-constexpr int kScatterSmem = (kSortWarps * 256 + 256 + 256 + kSortTile) * 4;  // 51 200 B, needs the opt-in
+constexpr int kScatterSmem = (kSortWarps * 256 + 256 + kSortTile) * 4;  // 50 176 B, needs the opt-in
 
 __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_t* __restrict__ in,
                                                                 uint32_t* __restrict__ out, int64_t N, int shift,
                                                                 const uint32_t* __restrict__ scanned, int nb) {
   extern __shared__ uint32_t sm[];
   uint32_t(*wh)[256] = reinterpret_cast<uint32_t(*)[256]>(sm);  // [kSortWarps][256]: counts, then warp prefixes
-  uint32_t* tile_off = sm + kSortWarps * 256;                    // [256] first local position of each digit
-  uint32_t* gdelta = tile_off + 256;                             // [256] global position minus local position
+  uint32_t* gdelta = sm + kSortWarps * 256;                      // [256] global position minus local position
   uint32_t* sorted = gdelta + 256;                               // [kSortTile] the tile in digit order
   const int seg = blockIdx.y, blk = blockIdx.x;
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) sm[i] = 0;
+  // global position of this tile's first key of digit threadIdx.x; fetched now, needed after the ranking
+  const uint32_t digit_base = threadIdx.x < 256 ? scanned[((int64_t)seg * 256 + threadIdx.x) * nb + blk] : 0u;
   __syncthreads();
   const uint32_t* k = in + (int64_t)seg * N;
   const int64_t tile0 = (int64_t)blk * kSortTile;
@@ -444,10 +462,17 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
   // positions of the tile — they rank behind every real key of that digit, so they land at the very end of the
   // digit-ordered tile (local index >= tile_n) and are never written.  No validity test in the loops below.
   uint32_t key[kSortItems];
-  uint32_t rank[kSortItems];
+  uint32_t rank2[kSortItems / 2];  // two 16-bit ranks per register (a warp rank is below 512 + 32)
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r)
     key[r] = (r * 32 + lane < span) ? ldg_stream4(k + start + r * 32 + lane) : 0xffffffffu;
+  // The leader's atomic returns the warp's running count of the digit; its consumer (the shuffle that hands the
+  // count to the group) is issued one round later, behind the next round's eight votes, so the warp does not
+  // sit on the shared-memory round trip 16 times.  Same-warp atomics reach shared memory in issue order, which
+  // is what keeps round r + 1 behind round r on a common digit.
+  uint32_t prev_old = 0;
+  unsigned prev_peers = 0;
+  int prev_leader = 0;
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) {
     const uint32_t dk = key[r] >> shift;
@@ -462,19 +487,19 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
     const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
     if (lane == leader) old = atomicAdd(&wh[w][dk & 255u], (uint32_t)__popc(peers));
-    old = __shfl_sync(kFull, old, leader);  // also keeps the rounds in order: round r + 1 sees round r's counts
-    rank[r] = old + __popc(peers & lt_mask);
+    if (r > 0) put_rank(rank2, r - 1, __shfl_sync(kFull, prev_old, prev_leader) + __popc(prev_peers & lt_mask));
+    prev_old = old;
+    prev_peers = peers;
+    prev_leader = leader;
   }
+  put_rank(rank2, kSortItems - 1, __shfl_sync(kFull, prev_old, prev_leader) + __popc(prev_peers & lt_mask));
   __syncthreads();
-  // per digit: prefix over the warps, tile total; then an exclusive scan of the totals over the 256 digits
+  // per digit: tile total -> exclusive scan over the 256 digits -> wh[warp][digit] becomes the local position of
+  // the warp's first key with that digit (digit start + keys of earlier warps)
   uint32_t total = 0;
   if (threadIdx.x < 256) {
 #pragma unroll
-    for (int ww = 0; ww < kSortWarps; ++ww) {
-      uint32_t t = wh[ww][threadIdx.x];
-      wh[ww][threadIdx.x] = total;
-      total += t;
-    }
+    for (int ww = 0; ww < kSortWarps; ++ww) total += wh[ww][threadIdx.x];
   }
   {
     uint32_t incl = total;  // threads >= 256 carry 0 and only take part in the shuffles
@@ -491,16 +516,19 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
 #pragma unroll
       for (int ww = 0; ww < 8; ++ww) before += (ww < w) ? warp_tot[ww] : 0u;
       const uint32_t first = before + incl - total;  // local position of the first key with this digit
-      tile_off[threadIdx.x] = first;
-      gdelta[threadIdx.x] = scanned[((int64_t)seg * 256 + threadIdx.x) * nb + blk] - first;
+      gdelta[threadIdx.x] = digit_base - first;
+      uint32_t run = first;
+#pragma unroll
+      for (int ww = 0; ww < kSortWarps; ++ww) {
+        const uint32_t t = wh[ww][threadIdx.x];
+        wh[ww][threadIdx.x] = run;
+        run += t;
+      }
     }
   }
   __syncthreads();
 #pragma unroll
-  for (int r = 0; r < kSortItems; ++r) {
-    const uint32_t d = (key[r] >> shift) & 255u;
-    sorted[tile_off[d] + wh[w][d] + rank[r]] = key[r];
-  }
+  for (int r = 0; r < kSortItems; ++r) sorted[wh[w][(key[r] >> shift) & 255u] + get_rank(rank2, r)] = key[r];
   __syncthreads();
   uint32_t* o = out + (int64_t)seg * N;
   for (int i = threadIdx.x; i < tile_n; i += kSortThreads) {
@@ -522,6 +550,22 @@ constexpr int kCurveTile = kCurveThreads * kCurveItems;  // 4096
 constexpr int kKeyWords = kCurveTile + 1 + (kCurveTile + 1) / 32 + 1;
 __device__ __forceinline__ int skew(int i) { return i + (i >> 5); }
 
+// all 16 loads of a thread are issued before the first store (a plain copy loop ran load -> store -> load ...
+// and the curve kernels spent half their stall samples on that one shared-memory store)
+__device__ __forceinline__ void stage_tile(const uint32_t* __restrict__ k, int64_t N, int64_t tile0, uint32_t* sh_keys) {
+  const int n_load = (int)min((int64_t)kCurveTile + 1, N - tile0);
+  uint32_t v[kCurveItems];
+#pragma unroll
+  for (int q = 0; q < kCurveItems; ++q) {
+    const int i = threadIdx.x + q * kCurveThreads;
+    v[q] = i < n_load ? ldg_stream4(k + tile0 + i) : kSentinel;
+  }
+#pragma unroll
+  for (int q = 0; q < kCurveItems; ++q) sh_keys[skew(threadIdx.x + q * kCurveThreads)] = v[q];
+  if (threadIdx.x == 0) sh_keys[skew(kCurveTile)] = kCurveTile < n_load ? ldg_stream4(k + tile0 + kCurveTile) : kSentinel;
+  __syncthreads();
+}
+
 struct CurveItems {
   uint32_t pos[kCurveItems];  // 1 for a counted positive
   uint32_t bnd[kCurveItems];  // 1 where a threshold ends
@@ -531,9 +575,7 @@ struct CurveItems {
 // stage tile `blk` of the segment starting at `k`; then thread t decodes positions tile0 + 16 t ... + 15
 __device__ __forceinline__ void curve_load(const uint32_t* __restrict__ k, int64_t N, int64_t nv, int64_t tile0,
                                            uint32_t* sh_keys, CurveItems& it, uint32_t& pos_sum, uint32_t& bnd_sum) {
-  for (int i = threadIdx.x; i <= kCurveTile; i += kCurveThreads)
-    sh_keys[skew(i)] = (tile0 + i < N) ? k[tile0 + i] : kSentinel;
-  __syncthreads();
+  stage_tile(k, N, tile0, sh_keys);
   const int base = threadIdx.x * kCurveItems;
   uint32_t key[kCurveItems + 1];
 #pragma unroll
@@ -566,24 +608,25 @@ __device__ __forceinline__ void curve_load(const uint32_t* __restrict__ k, int64
 // ends a threshold) — all the partial sums and the area reductions need
 __device__ __forceinline__ void curve_load_bits(const uint32_t* __restrict__ k, int64_t N, int64_t nv, int64_t tile0,
                                                 uint32_t* sh_keys, uint32_t& pos_bits, uint32_t& bnd_bits) {
-  for (int i = threadIdx.x; i <= kCurveTile; i += kCurveThreads)
-    sh_keys[skew(i)] = (tile0 + i < N) ? k[tile0 + i] : kSentinel;
-  __syncthreads();
+  stage_tile(k, N, tile0, sh_keys);
   const int base = threadIdx.x * kCurveItems;
-  const int64_t i0 = tile0 + base;
+  const int64_t left = nv - (tile0 + base);  // counted positions from this thread's first one on
+  const int n_mine = left >= kCurveItems ? kCurveItems : (left > 0 ? (int)left : 0);
+  const int last_j = left <= kCurveItems ? (int)left - 1 : -1;  // where the curve's final point sits, if here
   pos_bits = 0;
   bnd_bits = 0;
   uint32_t key = sh_keys[skew(base)];
 #pragma unroll
   for (int j = 0; j < kCurveItems; ++j) {
     const uint32_t next = sh_keys[skew(base + j + 1)];
-    if (i0 + j < nv) {
-      const bool boundary = (i0 + j == nv - 1) || !(key_score(next) - key_score(key) == 0.0f);
-      pos_bits |= key_positive(key) << j;
-      bnd_bits |= (boundary ? 1u : 0u) << j;
-    }
+    const bool boundary = (j == last_j) || !(key_score(next) - key_score(key) == 0.0f);
+    pos_bits |= key_positive(key) << j;
+    bnd_bits |= (boundary ? 1u : 0u) << j;
     key = next;
   }
+  const uint32_t mine = (1u << n_mine) - 1u;  // n_mine <= 16
+  pos_bits &= mine;
+  bnd_bits &= mine;
 }
 
 // block-wide exclusive prefix of one uint32 per thread (256 threads), also returns the block total
@@ -701,6 +744,8 @@ __global__ void __launch_bounds__(kCurveThreads) k3_curve_emit(const uint32_t* _
 // with the last boundary of the nearest earlier tile that has one (tile_last).  The float32 roundings are the
 // ones the emitted curve would carry (tps = float32(count), fps = float32(1 + idx) - tps), the accumulation is
 // float64 — same values as k3_curve_emit + k3_curve_reduce; `out` as documented there, zero on entry.
+// kAP = false leaves column 1 (the average-precision sum, one float64 division per curve point) at zero.
+template <bool kExact, bool kAP>
 __global__ void __launch_bounds__(kCurveThreads) k3_curve_scores(const uint32_t* __restrict__ keys, int64_t N,
                                                                  const unsigned long long* __restrict__ n_valid,
                                                                  const uint32_t* __restrict__ pos_excl,
@@ -759,25 +804,50 @@ __global__ void __launch_bounds__(kCurveThreads) k3_curve_scores(const uint32_t*
     const unsigned long long up = __shfl_up_sync(kFull, incl, 1);
     if (lane > 0) prev = max(prev, up);
   }
-  float ptf = __uint2float_rn((uint32_t)prev);
-  float pff = __ll2float_rn((long long)(prev >> 32)) - ptf;
   uint32_t p_run = pe;
   double area = 0.0, ap = 0.0;
+  if constexpr (kExact) {
+    // N < 2^24: every float32 curve value is an exact integer, so the trapezoid terms are integers too —
+    // 2 * area accumulates in 64-bit integer arithmetic (< 2^49) and equals the float64 sum bit for bit
+    uint32_t p_tps = (uint32_t)prev, p_idx1 = (uint32_t)(prev >> 32);
+    unsigned long long area2 = 0;
+    const uint32_t i1 = (uint32_t)i0 + 1u;
 #pragma unroll
-  for (int j = 0; j < kCurveItems; ++j) {
-    p_run += (pb >> j) & 1u;
-    if ((bb >> j) & 1u) {
-      const float tf = __uint2float_rn(p_run);
-      const float ff = __ll2float_rn(1 + i0 + j) - tf;
-      const double fb = ff, tb = tf, fp = pff, tp = ptf;
-      area += (fb - fp) * (tb + tp) * 0.5;
-      ap += (tb - tp) * (tb / (tb + fb));
-      if (i0 + j == nv - 1) {
-        out[4 * seg + 2] = fb;
-        out[4 * seg + 3] = tb;
+    for (int j = 0; j < kCurveItems; ++j) {
+      p_run += (pb >> j) & 1u;
+      if ((bb >> j) & 1u) {
+        const uint32_t idx1 = i1 + j;
+        const uint32_t df = (idx1 - p_run) - (p_idx1 - p_tps);
+        area2 += (unsigned long long)df * (p_run + p_tps);
+        if constexpr (kAP) ap += (double)(p_run - p_tps) * ((double)p_run / (double)idx1);
+        p_tps = p_run;
+        p_idx1 = idx1;
       }
-      ptf = tf;
-      pff = ff;
+    }
+    area = (double)area2 * 0.5;
+    if (p_idx1 == (uint32_t)nv && bb) {  // this thread holds the curve's last point
+      out[4 * seg + 2] = (double)(p_idx1 - p_tps);
+      out[4 * seg + 3] = (double)p_tps;
+    }
+  } else {
+    float ptf = __uint2float_rn((uint32_t)prev);
+    float pff = __ll2float_rn((long long)(prev >> 32)) - ptf;
+#pragma unroll
+    for (int j = 0; j < kCurveItems; ++j) {
+      p_run += (pb >> j) & 1u;
+      if ((bb >> j) & 1u) {
+        const float tf = __uint2float_rn(p_run);
+        const float ff = __ll2float_rn(1 + i0 + j) - tf;
+        const double fb = ff, tb = tf, fp = pff, tp = ptf;
+        area += (fb - fp) * (tb + tp) * 0.5;
+        if constexpr (kAP) ap += (tb - tp) * (tb / (tb + fb));
+        if (i0 + j == nv - 1) {
+          out[4 * seg + 2] = fb;
+          out[4 * seg + 3] = tb;
+        }
+        ptf = tf;
+        pff = ff;
+      }
     }
   }
 #pragma unroll
@@ -1131,7 +1201,7 @@ extern "C" int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_ch
 
 extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
                                             int target_dtype, int64_t n, int64_t num_labels, int has_ignore,
-                                            int64_t ignore_index, int64_t pos_label, void* scratch,
+                                            int64_t ignore_index, int64_t pos_label, int want_ap, void* scratch,
                                             int64_t scratch_bytes, double* scores, int32_t* err, void* stream) {
   if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
   if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
@@ -1152,7 +1222,10 @@ extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t 
     return rc;
   if (int rc = curve_tile_sums(n, L, p, b, nullptr, st)) return rc;
   dim3 grid((unsigned)p.ntile, (unsigned)L);
-  k3_curve_scores<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.tile_last, p.ntile, scores);
+  const bool exact = n < ((int64_t)1 << 24), ap = want_ap != 0;
+  auto k = exact ? (ap ? k3_curve_scores<true, true> : k3_curve_scores<true, false>)
+                 : (ap ? k3_curve_scores<false, true> : k3_curve_scores<false, false>);
+  k<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.tile_last, p.ntile, scores);
   return launch_status();
 }
 

@@ -118,7 +118,9 @@ def _binary_auroc_compute(
         preds, target = state[0], state[1]
         if isinstance(preds, Tensor) and preds.ndim > target.ndim:
             preds = preds[:, 0]
-        scores = kernels.clf_curve_scores(kernels.as_columns(preds), kernels.as_columns(target), None, pos_label)
+        scores = kernels.clf_curve_scores(
+            kernels.as_columns(preds), kernels.as_columns(target), None, pos_label, want_ap=False
+        )
         return _exact_auroc_from_scores(scores)[0]
     fpr, tpr, _ = _binary_roc_compute(state, thresholds, pos_label)
     if max_fpr is None or max_fpr == 1 or fpr.sum() == 0 or tpr.sum() == 0:
@@ -194,7 +196,7 @@ def _multilabel_auroc_compute(
         # exact mode: all labels in one batched sort + scan + area reduction
         from torchmetrics_forked_b200 import kernels
 
-        scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1)
+        scores = kernels.clf_curve_scores(state[0], state[1], ignore_index, 1, want_ap=False)
         # weights: the reference counts (target == 1) per label (:331); column 3 is that count already
         return _reduce_scores(_exact_auroc_from_scores(scores), average, scores[:, 3].float())
     fpr, tpr, _ = _multilabel_roc_compute(state, num_labels, thresholds, ignore_index)
