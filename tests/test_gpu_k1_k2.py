@@ -567,3 +567,35 @@ def test_jaccard_config5_scaled():
     confmat = O.multiclass_confusion_matrix(preds.numpy(), target.numpy(), 150)
     assert np.array_equal(m.confmat.cpu().numpy(), confmat)
     np.testing.assert_allclose(m.compute().cpu().numpy(), O.jaccard_reduce(confmat, "macro"), rtol=RTOL)
+
+
+@pytest.mark.parametrize("L", [4, 5, 7, 100, 251])
+@pytest.mark.parametrize("kind", ["logits", "probs", "outlier"])
+def test_multilabel_curve_shared_histogram_kernel(L, kind, F):
+    """k2_multi ([N, L] row-major, CTA-wide shared histogram): label wrap-around inside a vector of 4 (L not a
+    multiple of 4), ragged element counts, ignore_index, uneven thresholds, both passes of the sigmoid protocol
+    and accumulation over two updates, against the oracle bit for bit."""
+    from torchmetrics_forked_b200.classification import MultilabelPrecisionRecallCurve
+
+    g = torch.Generator().manual_seed(1000 + L)
+    thr_even = torch.linspace(0, 1, 50)
+    thr_uneven = torch.sort(torch.rand(37, generator=g)).values
+    for thr, tdtype, pdtype in [(thr_even, torch.int64, torch.float32), (thr_uneven, torch.uint8, torch.float32),
+                                (thr_even, torch.int32, torch.bfloat16)]:
+        m = MultilabelPrecisionRecallCurve(L, thresholds=thr, ignore_index=None if tdtype == torch.uint8 else -1).cuda()
+        ign = m.ignore_index
+        want = None
+        for n in (3001, 77):  # n * L is odd for odd L: exercises the ragged batch and the n % 4 tail
+            x = torch.randn(n, L, generator=g) * 2 if kind != "probs" else torch.rand(n, L, generator=g)
+            if kind == "outlier":
+                x = torch.rand(n, L, generator=g)
+                x[n // 2, L // 2] = 1.25  # one value outside [0,1] flips the whole batch to sigmoid (H1)
+            x = x.to(pdtype)
+            t = torch.randint(2, (n, L), generator=g)
+            if ign is not None:
+                t[torch.rand(n, L, generator=g) < 0.2] = ign
+            m.update(x.cuda(), t.to(tdtype).cuda())
+            part = O.multilabel_curve_binned(x.float().numpy(), t.numpy(), L, thr.numpy(), ign,
+                                             sigmoid_fn=lambda a, d=pdtype: torch.from_numpy(a).to(d).cuda().sigmoid().float().cpu().numpy())
+            want = part if want is None else want + part
+        assert np.array_equal(m.confmat.cpu().numpy(), want), (L, kind, tdtype, pdtype)

@@ -322,14 +322,13 @@ __device__ __forceinline__ void decode_batch(const TbArgs& a, const Batch& s, un
   }
 }
 
-// Bin kPer decoded samples.  Written stage by stage over all kPer samples (not sample by sample) so that the
+// Bins of kPer decoded samples.  Written stage by stage over all kPer samples (not sample by sample) so that the
 // dependency chains of different samples interleave.  GRID = thresholds on a (numerically) even grid: certainty
 // comes from arithmetic alone; otherwise the two neighbouring thresholds of the guess are fetched and compared.
 template <int PDT, bool SIG, bool GRID>
-__device__ __forceinline__ void bin_batch(const Binner& bn, LaneHist& h, const Decoded& d) {
+__device__ __forceinline__ void batch_bins(const Binner& bn, const Decoded& d, int (&g)[kPer]) {
   constexpr bool kFiltered = SIG && PDT == TMB_F32;
   float q[kPer], lowq[kPer], highq[kPer], slack[kPer];
-  int g[kPer];
   const float bias = 1.0f - bn.lo * bn.scale;
   const float top = (float)bn.T;
 
@@ -401,6 +400,12 @@ __device__ __forceinline__ void bin_batch(const Binner& bn, LaneHist& h, const D
     for (int i = 0; i < kPer; ++i)
       if ((recheck >> i) & 1u) g[i] = exact_bin<PDT, SIG>(bn.pad, bn.T, bn.lo, bn.scale, bn.gt, d.x[i]);
   }
+}
+
+template <int PDT, bool SIG, bool GRID>
+__device__ __forceinline__ void bin_batch(const Binner& bn, LaneHist& h, const Decoded& d) {
+  int g[kPer];
+  batch_bins<PDT, SIG, GRID>(bn, d, g);
   // stage 4: the read-modify-writes on this lane's own bytes.  Done four at a time: the four loads are issued
   // together, a sample whose counter repeats an earlier one of the group takes that one's updated value instead
   // of its own (stale) load, and the stores go out in order so the last writer holds the complete count.  This
@@ -577,6 +582,178 @@ __global__ void __launch_bounds__(512, 1) k2_binary_lanes(TbArgs a, int warps_pe
   for (int r = threadIdx.x; r < rows; r += blockDim.x) {
     const uint32_t v = cta_hist[r];
     if (v) atomicAdd(&gh[(r & 1) * (a.T + 1) + (r >> 1)], (unsigned long long)v);  // row r = k*2 + t
+  }
+}
+
+// ---- multilabel binned curves: [N, L] row-major, CTA-wide shared histogram ---------------------------------------
+// Same load / decode / filtered-sigmoid pipeline as k2_binary_lanes; what differs is where the counts go.  With L
+// labels the lane-private byte counters would need L times the space, so the CTA keeps ONE 32-bit histogram
+// [L][2][T+1] in shared memory (161 KB at L = 100, T = 200: one CTA per SM) and every counted sample is one
+// shared-memory atomic.  The earlier generic kernel did the same atomics but one sample per loop trip — load,
+// exact sigmoid, compare, atomic, next load — and was bound by that latency chain (27 % of the HBM roofline),
+// not by the atomics.  A thread's vector of 4 consecutive elements covers 4 consecutive labels (wrapping at L);
+// the label of its first element advances by a constant from batch to batch, so no division in the loop.
+template <int PDT, int TDT, bool SIG>
+__global__ void __launch_bounds__(512, 1) k2_multi(TbArgs a) {
+  extern __shared__ uint32_t sh_u32[];
+  if (!pass_enabled(a, SIG)) return;
+  float* sh_pad = (float*)sh_u32;
+  const int pad_words = (a.T + 2 + 31) / 32 * 32;
+  const int kbins = a.T + 1;
+  const int nbins = a.L * 2 * kbins;
+  uint32_t* hist = sh_u32 + pad_words;
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x) hist[i] = 0;
+  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
+  const bool on_grid = bn.grid_eps < 0.01f;
+  const int lane = threadIdx.x & 31;
+  const int L = a.L;
+
+  const int64_t n = a.n_total;
+  const int64_t n_vec = n / 4;
+  const int64_t gthreads = (int64_t)gridDim.x * blockDim.x;
+  const int64_t gtid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t step = gthreads * kBatch;
+  bool stop = false, bad_target = false;
+  int batches = 0;
+  // label of the first element of this thread's vector u of the current batch, and its advance per batch
+  int lab[kBatch];
+#pragma unroll
+  for (int u = 0; u < kBatch; ++u) lab[u] = (int)(((gtid + (int64_t)u * gthreads) * 4) % L);
+  const int dlab = (int)((step * 4) % L);
+
+  auto fetch_full = [&](int64_t b, Batch& s) {
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = b + lane + (int64_t)u * gthreads;
+      load_preds4<PDT>(a.preds, v * 4, &s.x[u * 4]);
+      load_targets4<TDT>(a.target, v * 4, &s.lo[u * 4], &s.hi[u * 4]);
+    }
+  };
+  auto prefetch_batch = [&](int64_t bb) {
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = bb + lane + (int64_t)u * gthreads;
+      const char* pp = (const char*)a.preds + v * 4 * Elem<PDT>::kBytes;
+      const char* tp = (const char*)a.target + v * 4 * label_bytes_dev(TDT);
+      if ((lane & 7) == 0) prefetch_l2(pp);
+      if (label_bytes_dev(TDT) == 8 ? (lane & 3) == 0 : (lane & 7) == 0) prefetch_l2(tp);
+    }
+  };
+  auto process = [&](const Batch& s, unsigned live, bool full, Decoded& d) {
+    if (full) {
+      if (a.has_ignore) decode_batch<SIG, true, true>(a, s, 0u, d);
+      else decode_batch<SIG, true, false>(a, s, 0u, d);
+    } else {
+      if (a.has_ignore) decode_batch<SIG, false, true>(a, s, live, d);
+      else decode_batch<SIG, false, false>(a, s, live, d);
+    }
+  };
+  // count the batch (labels of the CURRENT batch), then move the labels on to the next one
+  auto count = [&](const Decoded& d, const int (&g)[kPer]) {
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int i = u * 4 + e;
+        int l = lab[u] + e;
+        l -= (l >= L) ? L : 0;
+        if (d.inc[i]) atomicAdd(&hist[(l * 2 + (int)(d.toff[i] >> 5)) * kbins + g[i]], 1u);
+      }
+      lab[u] += dlab;
+      lab[u] -= (lab[u] >= L) ? L : 0;
+    }
+  };
+  auto after_batch = [&](const Decoded& d) {
+    bad_target |= d.bad != 0u;
+    batches += 1;
+    if (!SIG) {
+      const bool mine = d.outside != 0u;
+      if (mine) raise_flag(a);
+      const bool poll = (batches & 7) == 0;
+      stop = __any_sync(kFull, mine || (poll && flag_up(a)));
+    }
+  };
+
+  Batch S;
+  Decoded D;
+  int g[kPer];
+  constexpr int kAhead = 4;
+  int64_t b = gtid - lane;
+  const int64_t last_full = n_vec - ((int64_t)(kBatch - 1) * gthreads + 32);
+  bool have = b <= last_full;
+  if (have) {
+    fetch_full(b, S);
+#pragma unroll
+    for (int p = 1; p <= kAhead; ++p)
+      if (b + p * step <= last_full) prefetch_batch(b + p * step);
+  }
+  while (have && !stop) {
+    process(S, 0u, true, D);
+    b += step;
+    have = b <= last_full;
+    if (have) fetch_full(b, S);
+    if (b + kAhead * step <= last_full) prefetch_batch(b + kAhead * step);
+    if (on_grid)
+      batch_bins<PDT, SIG, true>(bn, D, g);
+    else
+      batch_bins<PDT, SIG, false>(bn, D, g);
+    count(D, g);
+    after_batch(D);
+  }
+  // ragged remainder: at most one masked batch per warp
+  if (!stop && b < n_vec) {
+    unsigned live = 0;
+#pragma unroll
+    for (int u = 0; u < kBatch; ++u) {
+      const int64_t v = b + lane + (int64_t)u * gthreads;
+      if (v < n_vec) {
+        load_preds4<PDT>(a.preds, v * 4, &S.x[u * 4]);
+        load_targets4<TDT>(a.target, v * 4, &S.lo[u * 4], &S.hi[u * 4]);
+        live |= 0xfu << (u * 4);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          S.x[u * 4 + e] = 0.0f;
+          S.lo[u * 4 + e] = 0u;
+          S.hi[u * 4 + e] = 0u;
+        }
+      }
+    }
+    process(S, live, false, D);
+    batch_bins<PDT, SIG, false>(bn, D, g);
+    count(D, g);
+    after_batch(D);
+  }
+  // tail elements (n % 4) — handled by the first threads of CTA 0
+  bool tail_stop = false;
+  if (!stop && blockIdx.x == 0) {
+    const int64_t i = n_vec * 4 + threadIdx.x;
+    if (i < n) {
+      const float x = load_elem<PDT>(a.preds, i);
+      const int64_t t = load_label(a.target, a.tdt, i);
+      const bool ignored = a.has_ignore && t == a.ignore;
+      if (!SIG && !(x >= 0.0f && x <= 1.0f) && (!ignored || a.flag_counts_ignored)) {
+        tail_stop = true;
+        raise_flag(a);
+      }
+      if (!ignored) {
+        if (t != 0 && t != 1) {
+          bad_target = true;
+        } else {
+          const int k = exact_bin<PDT, SIG>(bn.pad, bn.T, bn.lo, bn.scale, bn.gt, x);
+          atomicAdd(&hist[((int)(i % L) * 2 + (int)t) * kbins + k], 1u);
+        }
+      }
+    }
+  }
+  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_BINARY);
+  const bool dead = !SIG && __syncthreads_or(stop || tail_stop);
+  if (SIG) __syncthreads();
+  if (dead || (!SIG && flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
+  unsigned long long* gh = hist_base(a, SIG ? 1 : 0);
+  for (int i = threadIdx.x; i < nbins; i += blockDim.x) {
+    const uint32_t v = hist[i];
+    if (v) atomicAdd(&gh[i], (unsigned long long)v);
   }
 }
 
@@ -928,6 +1105,31 @@ static int launch_binary_lanes_t(const TbArgs& a, int warps, int smem, cudaStrea
 }
 
 template <int PDT, int TDT>
+static int launch_multi_pt(const TbArgs& a, int smem, cudaStream_t st) {
+  auto ka = k2_multi<PDT, TDT, false>;
+  auto kb = k2_multi<PDT, TDT, true>;
+  cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int block = 512;
+  const int64_t work = (a.n_total / 4 + (int64_t)block * kBatch - 1) / ((int64_t)block * kBatch);
+  const int grid = resident_grid(kb, block, smem, work);
+  ka<<<grid, block, smem, st>>>(a);
+  if (int rc = launch_status()) return rc;
+  kb<<<grid, block, smem, st>>>(a);
+  return launch_status();
+}
+
+template <int PDT>
+static int launch_multi_p(const TbArgs& a, int smem, cudaStream_t st) {
+  switch (a.tdt) {
+    case TMB_I64: return launch_multi_pt<PDT, TMB_I64>(a, smem, st);
+    case TMB_I32: return launch_multi_pt<PDT, TMB_I32>(a, smem, st);
+    case TMB_U8: return launch_multi_pt<PDT, TMB_U8>(a, smem, st);
+    default: return launch_multi_pt<PDT, TMB_I8>(a, smem, st);
+  }
+}
+
+template <int PDT, int TDT>
 static int launch_single_pt(const TbArgs& a, cudaStream_t st) {
   auto ka = k2_single<PDT, TDT, false>;
   auto kb = k2_single<PDT, TDT, true>;
@@ -1063,6 +1265,17 @@ extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int pre
         case TMB_F32: return launch_binary_lanes_t<TMB_F32>(a, warps, smem, st);
         case TMB_F16: return launch_binary_lanes_t<TMB_F16>(a, warps, smem, st);
         default: return launch_binary_lanes_t<TMB_BF16>(a, warps, smem, st);
+      }
+    }
+  }
+  // multilabel [N, L] curves: CTA-wide shared histogram, batched loads (needs the histogram to fit one SM)
+  if (num_labels >= 4 && n_inner == 1 && !preds_is_label && aligned && tdt_ok) {
+    const int64_t smem = ((int64_t)(a.T + 2 + 31) / 32 * 32 + (int64_t)a.L * 2 * (a.T + 1)) * 4;
+    if (smem <= (int64_t)dev_info().max_smem_optin - 1024) {
+      switch (preds_dtype) {
+        case TMB_F32: return launch_multi_p<TMB_F32>(a, (int)smem, st);
+        case TMB_F16: return launch_multi_p<TMB_F16>(a, (int)smem, st);
+        default: return launch_multi_p<TMB_BF16>(a, (int)smem, st);
       }
     }
   }
