@@ -46,6 +46,51 @@ from torchmetrics_forked_b200.classification.stat_scores import (
     StatScores,
 )
 
+from torchmetrics_forked_b200.classification.cohen_kappa import BinaryCohenKappa, CohenKappa, MulticlassCohenKappa
+from torchmetrics_forked_b200.classification.hamming import (
+    BinaryHammingDistance,
+    HammingDistance,
+    MulticlassHammingDistance,
+    MultilabelHammingDistance,
+)
+from torchmetrics_forked_b200.classification.matthews_corrcoef import (
+    BinaryMatthewsCorrCoef,
+    MatthewsCorrCoef,
+    MulticlassMatthewsCorrCoef,
+    MultilabelMatthewsCorrCoef,
+)
+from torchmetrics_forked_b200.classification.precision_fixed_recall import (
+    BinaryPrecisionAtFixedRecall,
+    MultilabelPrecisionAtFixedRecall,
+    PrecisionAtFixedRecall,
+)
+from torchmetrics_forked_b200.classification.precision_recall import (
+    BinaryPrecision,
+    BinaryRecall,
+    MulticlassPrecision,
+    MulticlassRecall,
+    MultilabelPrecision,
+    MultilabelRecall,
+    Precision,
+    Recall,
+)
+from torchmetrics_forked_b200.classification.recall_fixed_precision import (
+    BinaryRecallAtFixedPrecision,
+    MultilabelRecallAtFixedPrecision,
+    RecallAtFixedPrecision,
+)
+from torchmetrics_forked_b200.classification.specificity import (
+    BinarySpecificity,
+    MulticlassSpecificity,
+    MultilabelSpecificity,
+    Specificity,
+)
+from torchmetrics_forked_b200.classification.specificity_sensitivity import (
+    BinarySpecificityAtSensitivity,
+    MultilabelSpecificityAtSensitivity,
+    SpecificityAtSensitivity,
+)
+
 __all__ = [
     "Accuracy", "BinaryAccuracy", "MulticlassAccuracy", "MultilabelAccuracy",
     "AUROC", "BinaryAUROC", "MultilabelAUROC",
@@ -57,4 +102,5 @@ __all__ = [
     "BinaryPrecisionRecallCurve", "MultilabelPrecisionRecallCurve", "PrecisionRecallCurve",
     "ROC", "BinaryROC", "MultilabelROC",
     "BinaryStatScores", "MulticlassStatScores", "MultilabelStatScores", "StatScores",
+    "BinaryCohenKappa", "CohenKappa", "MulticlassCohenKappa", "BinaryHammingDistance", "HammingDistance", "MulticlassHammingDistance", "MultilabelHammingDistance", "BinaryMatthewsCorrCoef", "MatthewsCorrCoef", "MulticlassMatthewsCorrCoef", "MultilabelMatthewsCorrCoef", "BinaryPrecisionAtFixedRecall", "MultilabelPrecisionAtFixedRecall", "PrecisionAtFixedRecall", "BinaryPrecision", "BinaryRecall", "MulticlassPrecision", "MulticlassRecall", "MultilabelPrecision", "MultilabelRecall", "Precision", "Recall", "BinaryRecallAtFixedPrecision", "MultilabelRecallAtFixedPrecision", "RecallAtFixedPrecision", "BinarySpecificity", "MulticlassSpecificity", "MultilabelSpecificity", "Specificity", "BinarySpecificityAtSensitivity", "MultilabelSpecificityAtSensitivity", "SpecificityAtSensitivity",
 ]  # fmt: skip

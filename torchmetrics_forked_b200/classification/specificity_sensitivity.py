@@ -1,0 +1,99 @@
+"""SpecificityAtSensitivity metric classes: the precision-recall-curve state (K2 binned / K3 exact kernels) and one operating
+point of the curve at ``compute`` (reference: classification/specificity_sensitivity.py: binary :46, multilabel :232, wrapper :330)."""
+from typing import Any, List, Optional, Tuple, Union
+
+from torch import Tensor
+from typing_extensions import Literal
+
+from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
+from torchmetrics_forked_b200.classification.precision_recall_curve import (
+    BinaryPrecisionRecallCurve,
+    MultilabelPrecisionRecallCurve,
+)
+from torchmetrics_forked_b200.functional.classification._fixed_point import (
+    _binary_roc_point,
+    _check_level,
+    _multilabel_roc_point,
+)
+from torchmetrics_forked_b200.metric import Metric
+from torchmetrics_forked_b200.utilities.enums import ClassificationTask
+
+
+class BinarySpecificityAtSensitivity(BinaryPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+
+    def __init__(
+        self,
+        min_sensitivity: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(thresholds, ignore_index, validate_args=validate_args, **kwargs)
+        if validate_args:
+            _check_level("min_sensitivity", min_sensitivity)
+        self.min_sensitivity = min_sensitivity
+
+    def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
+        return _binary_roc_point(self._curve_state(), self.thresholds, self.min_sensitivity)
+
+
+class MultilabelSpecificityAtSensitivity(MultilabelPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Label"
+
+    def __init__(
+        self,
+        num_labels: int,
+        min_sensitivity: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(num_labels, thresholds, ignore_index, validate_args=validate_args, **kwargs)
+        if validate_args:
+            _check_level("min_sensitivity", min_sensitivity)
+        self.min_sensitivity = min_sensitivity
+
+    def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
+        return _multilabel_roc_point(
+            self._curve_state(), self.num_labels, self.thresholds, self.ignore_index, self.min_sensitivity
+        )
+
+
+class SpecificityAtSensitivity(_ClassificationTaskWrapper):
+    """``SpecificityAtSensitivity(task=...)``; the multiclass form needs the multiclass curves (row f2, not built yet)."""
+
+    def __new__(  # type: ignore[misc]
+        cls,
+        task: Literal["binary", "multiclass", "multilabel"],
+        min_sensitivity: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        num_classes: Optional[int] = None,
+        num_labels: Optional[int] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> Metric:
+        task = ClassificationTask.from_str(task)
+        if task == ClassificationTask.BINARY:
+            return BinarySpecificityAtSensitivity(min_sensitivity, thresholds, ignore_index, validate_args, **kwargs)
+        if task == ClassificationTask.MULTICLASS:
+            if not isinstance(num_classes, int):
+                raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+            raise NotImplementedError("MulticlassSpecificityAtSensitivity needs the multiclass (softmax) curves: not built yet")
+        if task == ClassificationTask.MULTILABEL:
+            if not isinstance(num_labels, int):
+                raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
+            return MultilabelSpecificityAtSensitivity(num_labels, min_sensitivity, thresholds, ignore_index, validate_args, **kwargs)
+        raise ValueError(f"Task {task} not supported!")

@@ -46,6 +46,56 @@ from torchmetrics_forked_b200.functional.classification.stat_scores import (
     stat_scores,
 )
 
+from torchmetrics_forked_b200.functional.classification.cohen_kappa import (
+    binary_cohen_kappa,
+    cohen_kappa,
+    multiclass_cohen_kappa,
+)
+from torchmetrics_forked_b200.functional.classification.hamming import (
+    binary_hamming_distance,
+    hamming_distance,
+    multiclass_hamming_distance,
+    multilabel_hamming_distance,
+)
+from torchmetrics_forked_b200.functional.classification.matthews_corrcoef import (
+    binary_matthews_corrcoef,
+    matthews_corrcoef,
+    multiclass_matthews_corrcoef,
+    multilabel_matthews_corrcoef,
+)
+from torchmetrics_forked_b200.functional.classification.precision_fixed_recall import (
+    binary_precision_at_fixed_recall,
+    multilabel_precision_at_fixed_recall,
+    precision_at_fixed_recall,
+)
+from torchmetrics_forked_b200.functional.classification.precision_recall import (
+    binary_precision,
+    binary_recall,
+    multiclass_precision,
+    multiclass_recall,
+    multilabel_precision,
+    multilabel_recall,
+    precision,
+    recall,
+)
+from torchmetrics_forked_b200.functional.classification.recall_fixed_precision import (
+    binary_recall_at_fixed_precision,
+    multilabel_recall_at_fixed_precision,
+    recall_at_fixed_precision,
+)
+from torchmetrics_forked_b200.functional.classification.specificity import (
+    binary_specificity,
+    multiclass_specificity,
+    multilabel_specificity,
+    specificity,
+)
+from torchmetrics_forked_b200.functional.classification.specificity_sensitivity import (
+    binary_specificity_at_sensitivity,
+    multilabel_specificity_at_sensitivity,
+    specicity_at_sensitivity,
+    specificity_at_sensitivity,
+)
+
 __all__ = [
     "accuracy", "binary_accuracy", "multiclass_accuracy", "multilabel_accuracy",
     "auroc", "binary_auroc", "multilabel_auroc",
@@ -57,4 +107,5 @@ __all__ = [
     "binary_precision_recall_curve", "multilabel_precision_recall_curve", "precision_recall_curve",
     "binary_roc", "multilabel_roc", "roc",
     "binary_stat_scores", "multiclass_stat_scores", "multilabel_stat_scores", "stat_scores",
+    "binary_cohen_kappa", "cohen_kappa", "multiclass_cohen_kappa", "binary_hamming_distance", "hamming_distance", "multiclass_hamming_distance", "multilabel_hamming_distance", "binary_matthews_corrcoef", "matthews_corrcoef", "multiclass_matthews_corrcoef", "multilabel_matthews_corrcoef", "binary_precision_at_fixed_recall", "multilabel_precision_at_fixed_recall", "precision_at_fixed_recall", "binary_precision", "binary_recall", "multiclass_precision", "multiclass_recall", "multilabel_precision", "multilabel_recall", "precision", "recall", "binary_recall_at_fixed_precision", "multilabel_recall_at_fixed_precision", "recall_at_fixed_precision", "binary_specificity", "multiclass_specificity", "multilabel_specificity", "specificity", "binary_specificity_at_sensitivity", "multilabel_specificity_at_sensitivity", "specicity_at_sensitivity", "specificity_at_sensitivity",
 ]  # fmt: skip

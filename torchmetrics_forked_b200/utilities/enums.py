@@ -1,16 +1,12 @@
-"""Task enum used by the `task=` wrapper classes (reference: utilities/enums.py:19-53, 108-122)."""
+"""Task enums used by the `task=` wrapper classes (reference: utilities/enums.py:19-53, 108-156)."""
 from enum import Enum
 
 
-class ClassificationTask(str, Enum):
-    """The three classification tasks; compares equal to its lower-case string value."""
-
-    BINARY = "binary"
-    MULTICLASS = "multiclass"
-    MULTILABEL = "multilabel"
+class _TaskEnum(str, Enum):
+    """Compares equal to its lower-case string value; ``from_str`` is a case-insensitive lookup by member name."""
 
     @classmethod
-    def from_str(cls, value: str) -> "ClassificationTask":
+    def from_str(cls, value: str) -> "_TaskEnum":
         """Case-insensitive lookup by member name; dashes count as underscores."""
         if isinstance(value, cls):
             return value
@@ -31,3 +27,18 @@ class ClassificationTask(str, Enum):
 
     def __str__(self) -> str:
         return self.value
+
+
+class ClassificationTask(_TaskEnum):
+    """The three classification tasks."""
+
+    BINARY = "binary"
+    MULTICLASS = "multiclass"
+    MULTILABEL = "multilabel"
+
+
+class ClassificationTaskNoMultilabel(_TaskEnum):
+    """Tasks of the metrics that have no multilabel form (Cohen's kappa)."""
+
+    BINARY = "binary"
+    MULTICLASS = "multiclass"
