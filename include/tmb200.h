@@ -176,6 +176,27 @@ int tmb_sigmoid_normalize(const void* preds, int preds_dtype, int64_t n, const v
                           int target_dtype, int has_ignore, int64_t ignore_index, void* out, int64_t* flag,
                           int64_t generation, void* stream);
 
+/* ---- K5: multiclass curves --------------------------------------------------------------
+ *
+ * The conditional row softmax of
+ *   _multiclass_precision_recall_curve_format   functional/classification/precision_recall_curve.py:423-458
+ * ("if not torch.all((preds >= 0) * (preds <= 1)): preds = preds.softmax(1)", evaluated after the rows with
+ * target == ignore_index were dropped), in the two-call flag protocol of tmb_sigmoid_normalize:
+ *
+ * tmb_rows_outside_flag: preds [n_rows, num_classes] row-major; raises *flag to `generation` if any element of a
+ *   row whose target (one integer per row; NULL = every row counts) differs from ignore_index lies outside [0,1]
+ *   or is NaN.  Any num_classes.
+ * tmb_softmax_rows: out = softmax(preds, dim=1) if *flag == generation, else a copy; same dtype as preds.  The
+ *   result is bit-identical to torch.softmax on the device for num_classes <= 1024 (its persistent warp kernel's
+ *   lane layout, reduction order, expf and IEEE division are reproduced); wider rows return TMB_E_LIMIT and the
+ *   caller keeps torch's own kernel for them.
+ */
+int tmb_rows_outside_flag(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes,
+                          const void* target, int target_dtype, int has_ignore, int64_t ignore_index,
+                          int64_t* flag, int64_t generation, void* stream);
+int tmb_softmax_rows(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes, void* out,
+                     const int64_t* flag, int64_t generation, void* stream);
+
 /* tmb_clf_curves replaces, for all labels at once,
  *   _binary_clf_curve                          functional/classification/precision_recall_curve.py:28-80
  *   the per-label loops that call it           same file :819-829, functional/classification/roc.py:345-355

@@ -40,6 +40,52 @@ def sigmoid_normalize(preds: Tensor, target: Optional[Tensor], ignore_index: Opt
     return out
 
 
+SOFTMAX_MAX_CLASSES = 1024  # rows up to here go through tmb_softmax_rows (bit-equal to torch); wider ones through torch
+
+
+def softmax_normalize(
+    preds: Tensor, target: Optional[Tensor] = None, ignore_index: Optional[int] = None
+) -> Tensor:
+    """``preds.softmax(1)`` of an ``[M, C]`` matrix if any element of a row that is not ignored lies outside [0,1],
+    else a copy — the multiclass twin of :func:`sigmoid_normalize`, decided on the device.
+
+    ``target`` holds one class index per row; rows with ``target == ignore_index`` take no part in the test (the
+    reference removes them before it looks, precision_recall_curve.py:445-452).
+    """
+    nat.require_cuda(preds, "preds")
+    if preds.ndim != 2:
+        raise ValueError("`preds` must have shape (M, C)")
+    preds = _as_kernel_input(preds)
+    rows, num_classes = preds.shape
+    if preds.numel() == 0:
+        return torch.empty_like(preds)
+    dev = preds.device
+    flag = torch.zeros(1, dtype=torch.int64, device=dev)
+    has_ign = int(target is not None and ignore_index is not None)
+    if has_ign:
+        nat.require_cuda(target, "target")
+        target = _as_kernel_input(target.reshape(-1))
+        if target.numel() != rows:
+            raise ValueError("`target` must hold one class index per row of `preds`")
+    with torch.cuda.device(dev):
+        rc = nat.lib().tmb_rows_outside_flag(
+            nat.ptr(preds), nat.float_code(preds), rows, num_classes, nat.ptr(target) if has_ign else 0,
+            nat.label_code(target) if has_ign else 0, has_ign, int(ignore_index) if has_ign else 0, nat.ptr(flag), 1,
+            nat.stream_ptr(dev),
+        )  # fmt: skip
+        nat.check(rc, "tmb_rows_outside_flag")
+        if num_classes > SOFTMAX_MAX_CLASSES:
+            # torch uses a different (block-reduction) kernel for wide rows; keep its bits by keeping its kernel
+            return torch.where(flag.bool(), preds.softmax(1), preds)
+        out = torch.empty_like(preds)
+        rc = nat.lib().tmb_softmax_rows(
+            nat.ptr(preds), nat.float_code(preds), rows, num_classes, nat.ptr(out), nat.ptr(flag), 1,
+            nat.stream_ptr(dev),
+        )
+        nat.check(rc, "tmb_softmax_rows")
+    return out
+
+
 def compact_not_ignored(preds: Tensor, target: Tensor, ignore_index: int) -> Tuple[Tensor, Tensor]:
     """``preds[target != ignore_index], target[target != ignore_index]`` (1-d), order preserved.
 

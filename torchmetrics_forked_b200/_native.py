@@ -61,6 +61,11 @@ SIGNATURES = {
         c_int, [c_void_p, c_int, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int64, c_void_p]
     ),
     "tmb_clf_curve_scratch_bytes": (c_int64, [c_int64, c_int64]),
+    "tmb_rows_outside_flag": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p],
+    ),
+    "tmb_softmax_rows": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p]),
     "tmb_clf_curves": (
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p,

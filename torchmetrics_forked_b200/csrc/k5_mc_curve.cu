@@ -1,0 +1,200 @@
+// K5 — multiclass curves: the row softmax of
+//   _multiclass_precision_recall_curve_format   functional/classification/precision_recall_curve.py:423-458
+// (`if not torch.all((preds >= 0) * (preds <= 1)): preds = preds.softmax(1)`, evaluated AFTER the rows with
+// target == ignore_index were removed) as a conditional, bit-exact kernel.
+//
+// Threshold compares and sort order are decided by the low bits of the probabilities, so the softmax has to
+// return what torch's CUDA kernel returns.  For a contiguous [M, C] matrix with C <= 1024 that kernel is the
+// "persistent warp softmax" (aten/src/ATen/native/cuda/PersistentSoftmax.cuh, softmax_warp_forward); its result
+// is fixed by four things, all reproduced here:
+//   * P = next power of two >= C, W = min(32, P) lanes per row, element c lives in lane c % W, slot c / W;
+//     slots past C hold -inf
+//   * max: per lane over its slots in slot order with `m > e ? m : e`, then an xor butterfly over the W lanes
+//     (offsets W/2 .. 1) with `a < b ? b : a`
+//   * e = expf(x - max) (full-precision expf), per-lane sum in slot order starting from 0, same butterfly with +
+//   * result e / sum (IEEE division), rounded to the input dtype for bf16 / f16
+// Rows wider than 1024 use a different torch kernel (block reduction); the host side keeps torch's own softmax
+// for those and only takes the in/out-of-range decision from here.
+#include "common.cuh"
+
+namespace tmb {
+
+constexpr int kSoftmaxMaxClasses = 1024;
+constexpr int kSoftmaxSlots = kSoftmaxMaxClasses / 32;
+
+template <int DT>
+__device__ __forceinline__ void store_elem(void* out, int64_t i, float v) {
+  if constexpr (DT == TMB_F32) {
+    ((float*)out)[i] = v;
+  } else if constexpr (DT == TMB_BF16) {
+    ((__nv_bfloat16*)out)[i] = __float2bfloat16_rn(v);
+  } else {
+    ((__half*)out)[i] = __float2half_rn(v);
+  }
+}
+
+struct RowMap {  // how rows are laid over a warp
+  int W;         // lanes per row (power of two, <= 32)
+  int log2W;
+  int slots;     // elements per lane: P / W
+};
+
+static RowMap row_map(int C) {
+  int P = 1;
+  while (P < C) P <<= 1;
+  RowMap m;
+  m.W = P < 32 ? P : 32;
+  m.log2W = 0;
+  while ((1 << m.log2W) < m.W) ++m.log2W;
+  m.slots = P / m.W;
+  return m;
+}
+
+// pass A: atomicMax(flag, gen) as soon as a value outside [0,1] (NaN included) shows up in a row that is not
+// ignored.  Same flag protocol as k3_outside_flag.
+template <int DT>
+__global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restrict__ x, int64_t rows, int C, RowMap rm,
+                                                            const void* __restrict__ target, int tdt,
+                                                            int has_ignore, int64_t ignore, unsigned long long* flag,
+                                                            unsigned long long gen) {
+  __shared__ int go;
+  if (threadIdx.x == 0) go = *((volatile unsigned long long*)flag) != gen;
+  __syncthreads();
+  if (!go) return;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
+  const int rows_per_warp = 32 >> rm.log2W;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  bool found = false;
+  int trip = 0;
+  for (int64_t r0 = warp * rows_per_warp; r0 < rows; r0 += nwarps * rows_per_warp, ++trip) {  // warp-uniform
+    const int64_t r = r0 + sub;
+    bool counted = r < rows;
+    if (counted && has_ignore && target != nullptr) counted = load_label(target, tdt, r) != ignore;
+    if (counted) {
+      for (int c = j; c < C; c += rm.W) {
+        const float v = load_elem<DT>(x, r * C + c);
+        found |= !(v >= 0.0f && v <= 1.0f);
+      }
+    }
+    if (__any_sync(kFull, found)) break;
+    if ((trip & 63) == 63 && *((volatile unsigned long long*)flag) == gen) break;
+  }
+  if (__any_sync(kFull, found) && lane == 0 && *((volatile unsigned long long*)flag) != gen) atomicMax(flag, gen);
+}
+
+// pass B: out = (flag == gen) ? softmax(x, dim=1) : x
+template <int DT>
+__global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ x, void* __restrict__ out,
+                                                       int64_t rows, int C, RowMap rm,
+                                                       const unsigned long long* __restrict__ flag,
+                                                       unsigned long long gen) {
+  const bool soft = *flag == gen;
+  const int lane = threadIdx.x & 31;
+  const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
+  const int rows_per_warp = 32 >> rm.log2W;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r0 = warp * rows_per_warp; r0 < rows; r0 += nwarps * rows_per_warp) {  // warp-uniform trip count
+    const int64_t r = r0 + sub;
+    const bool active = r < rows;
+    const int64_t base = r * C;
+    float e[kSoftmaxSlots];
+#pragma unroll
+    for (int it = 0; it < kSoftmaxSlots; ++it) {
+      const int c = it * rm.W + j;
+      e[it] = (it < rm.slots && active && c < C) ? load_elem<DT>(x, base + c) : -INFINITY;
+    }
+    if (soft) {
+      float m = e[0];
+#pragma unroll
+      for (int it = 1; it < kSoftmaxSlots; ++it)
+        if (it < rm.slots) m = (m > e[it]) ? m : e[it];
+      for (int off = rm.W >> 1; off > 0; off >>= 1) {
+        const float b = __shfl_xor_sync(kFull, m, off, rm.W);
+        m = (m < b) ? b : m;
+      }
+      float s = 0.0f;
+#pragma unroll
+      for (int it = 0; it < kSoftmaxSlots; ++it) {
+        if (it < rm.slots) {
+          e[it] = expf(e[it] - m);
+          s += e[it];
+        }
+      }
+      for (int off = rm.W >> 1; off > 0; off >>= 1) s += __shfl_xor_sync(kFull, s, off, rm.W);
+#pragma unroll
+      for (int it = 0; it < kSoftmaxSlots; ++it)
+        if (it < rm.slots) e[it] = e[it] / s;
+    }
+#pragma unroll
+    for (int it = 0; it < kSoftmaxSlots; ++it) {
+      const int c = it * rm.W + j;
+      if (it < rm.slots && active && c < C) store_elem<DT>(out, base + c, e[it]);
+    }
+  }
+}
+
+template <int DT>
+static int launch_rows_flag(const void* x, int64_t rows, int C, const void* target, int tdt, int has_ignore,
+                            int64_t ignore, unsigned long long* flag, unsigned long long gen, cudaStream_t st) {
+  const RowMap rm = row_map(C < kSoftmaxMaxClasses ? C : kSoftmaxMaxClasses);  // wider rows: 32 lanes stride over C
+  auto k = k5_rows_outside_flag<DT>;
+  const int64_t work = (rows * rm.W + 255) / 256;
+  k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, rows, C, rm, target, tdt, has_ignore, ignore, flag, gen);
+  return launch_status();
+}
+
+template <int DT>
+static int launch_softmax_rows(const void* x, void* out, int64_t rows, int C, const unsigned long long* flag,
+                               unsigned long long gen, cudaStream_t st) {
+  const RowMap rm = row_map(C);
+  auto k = k5_softmax_rows<DT>;
+  const int64_t work = (rows * rm.W + 255) / 256;
+  k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, out, rows, C, rm, flag, gen);
+  return launch_status();
+}
+
+}  // namespace tmb
+
+using namespace tmb;
+
+extern "C" int tmb_rows_outside_flag(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes,
+                                     const void* target, int target_dtype, int has_ignore, int64_t ignore_index,
+                                     int64_t* flag, int64_t generation, void* stream) {
+  if (float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (target != nullptr && label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_rows < 0 || num_classes < 1 || num_classes > (1 << 30) || generation < 1) return TMB_E_SHAPE;
+  if (!flag) return TMB_E_NULL;
+  if (n_rows == 0) return 0;
+  if (!preds) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* f = (unsigned long long*)flag;
+  const unsigned long long gen = (unsigned long long)generation;
+  const int C = (int)num_classes;
+  switch (preds_dtype) {
+    case TMB_F32: return launch_rows_flag<TMB_F32>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+    case TMB_F16: return launch_rows_flag<TMB_F16>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+    default: return launch_rows_flag<TMB_BF16>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+  }
+}
+
+extern "C" int tmb_softmax_rows(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes, void* out,
+                                const int64_t* flag, int64_t generation, void* stream) {
+  if (float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (n_rows < 0 || num_classes < 1 || generation < 1) return TMB_E_SHAPE;
+  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;
+  if (!flag) return TMB_E_NULL;
+  if (n_rows == 0) return 0;
+  if (!preds || !out) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned long long* f = (const unsigned long long*)flag;
+  const unsigned long long gen = (unsigned long long)generation;
+  const int C = (int)num_classes;
+  switch (preds_dtype) {
+    case TMB_F32: return launch_softmax_rows<TMB_F32>(preds, out, n_rows, C, f, gen, st);
+    case TMB_F16: return launch_softmax_rows<TMB_F16>(preds, out, n_rows, C, f, gen, st);
+    default: return launch_softmax_rows<TMB_BF16>(preds, out, n_rows, C, f, gen, st);
+  }
+}

@@ -16,6 +16,7 @@ from torchmetrics_forked_b200._exact import (  # noqa: F401
     clf_curves,
     compact_not_ignored,
     sigmoid_normalize,
+    softmax_normalize,
 )
 
 MC_CONFMAT, MC_STATS, MC_MICRO = nat.MC_CONFMAT, nat.MC_STATS, nat.MC_MICRO
