@@ -197,6 +197,21 @@ int tmb_rows_outside_flag(const void* preds, int preds_dtype, int64_t n_rows, in
 int tmb_softmax_rows(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes, void* out,
                      const int64_t* flag, int64_t generation, void* stream);
 
+/* tmb_mc_curve_update: the binned multiclass curve update,
+ *   _multiclass_precision_recall_curve_format + _update (+_vectorized / _loop)
+ *       functional/classification/precision_recall_curve.py:423-527
+ * in one pass over the logits: conditional softmax (as above, ignored rows excluded from the range test), every
+ * (row, class) probability binned against thr[0..T) with `>=`, one-hot target `class == target[row]`.
+ * preds [n_rows, num_classes] row-major (2 <= num_classes <= 1024, else TMB_E_LIMIT), target one integer per row
+ * (outside [0, num_classes) and not ignored: TMB_ERR_TARGET_RANGE).  micro != 0 folds all classes into one binary
+ * task (average="micro").  scratch: tmb_thresh_bin_scratch_elems(micro ? 1 : num_classes, T), zero before first
+ * use; follow with tmb_thresh_bin_finalize(num_labels = micro ? 1 : num_classes, layout TMB_TB_CURVE), which adds
+ * into the int64 [T, num_classes, 2, 2] (micro: [T, 2, 2]) state and re-zeroes the scratch. */
+int tmb_mc_curve_update(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n_rows,
+                        int64_t num_classes, const float* thr, int64_t num_thresholds, int has_ignore,
+                        int64_t ignore_index, int micro, int64_t* scratch, int64_t scratch_elems, int32_t* err,
+                        void* stream);
+
 /* tmb_clf_curves replaces, for all labels at once,
  *   _binary_clf_curve                          functional/classification/precision_recall_curve.py:28-80
  *   the per-label loops that call it           same file :819-829, functional/classification/roc.py:345-355
@@ -220,11 +235,14 @@ int tmb_clf_curves(const void* preds, int preds_dtype, const void* target, int t
  *   [0 .. C]       first row of chunk c, ascending, table[0] = 0 and table[C] = n
  *   [C+1 .. 2C]    device address of chunk c's scores  ([rows_c, num_labels] row-major, preds_dtype)
  *   [2C+1 .. 3C]   device address of chunk c's targets ([rows_c, num_labels] row-major, target_dtype)
- * Empty chunks are allowed.  Everything else as tmb_clf_curves. */
+ * Empty chunks are allowed.  class_targets != 0 is the multiclass form (the per-class loop of
+ * _multiclass_precision_recall_curve_compute, precision_recall_curve.py:548-555, `pos_label=i`): the target chunks
+ * then hold ONE class index per row ([rows_c]) and label l is positive where target == l (pos_label unused).
+ * Everything else as tmb_clf_curves. */
 int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
                            int64_t n, int64_t num_labels, int has_ignore, int64_t ignore_index, int64_t pos_label,
-                           void* scratch, int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
-                           int64_t* counts, int32_t* err, void* stream);
+                           int class_targets, void* scratch, int64_t scratch_bytes, float* fps, float* tps,
+                           float* thresholds, int64_t* counts, int32_t* err, void* stream);
 
 /* Chunks -> the four per-label area reductions tmb_curve_reduce documents (scores: float64 [num_labels, 4],
  * device), without writing the curves: pack, sort, then one pass over the sorted keys.  Replaces, for the
@@ -235,8 +253,8 @@ int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int p
  * that AUROC does not need).  Same scratch size as tmb_clf_curves. */
 int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
                                  int64_t n, int64_t num_labels, int has_ignore, int64_t ignore_index,
-                                 int64_t pos_label, int want_ap, void* scratch, int64_t scratch_bytes,
-                                 double* scores, int32_t* err, void* stream);
+                                 int64_t pos_label, int class_targets, int want_ap, void* scratch,
+                                 int64_t scratch_bytes, double* scores, int32_t* err, void* stream);
 
 /* Area reductions over the curves tmb_clf_curves emitted (same fps / tps buffers, label stride n, counts[l] points
  * each), replacing the per-label torch chains of

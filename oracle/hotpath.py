@@ -270,6 +270,53 @@ def multilabel_curve_binned(
     return out
 
 
+# ------------------------------------------------------------------------------------------ K5: multiclass curves (row f2)
+def torch_cpu_softmax(x: Array) -> Array:
+    """Row softmax with the bits of torch's CPU kernel (what the golden vectors of the CPU reference contain)."""
+    import torch
+
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).softmax(1).numpy()
+
+
+def multiclass_rows(preds: Array, target: Array, num_classes: int, ignore_index: Optional[int] = None,
+                    softmax_fn: SigmoidFn = torch_cpu_softmax) -> Tuple[Array, Array]:
+    """`_multiclass_precision_recall_curve_format` (precision_recall_curve.py:423-458) up to the softmax:
+    `[M', C]` float32 probabilities and `[M']` targets — extra dimensions folded into the rows, rows with
+    `target == ignore_index` REMOVED first, softmax over the classes iff any remaining value is outside [0,1]."""
+    q = np.moveaxis(np.asarray(preds).astype(np.float32), 1, -1).reshape(-1, num_classes)
+    t = np.asarray(target).astype(np.int64).reshape(-1)
+    if ignore_index is not None:
+        keep = t != ignore_index
+        q, t = q[keep], t[keep]
+    if q.size and _needs_sigmoid(q):
+        q = softmax_fn(np.ascontiguousarray(q))
+    return q, t
+
+
+def multiclass_curve_binned(preds: Array, target: Array, num_classes: int, thresholds: Array,
+                            ignore_index: Optional[int] = None, softmax_fn: SigmoidFn = torch_cpu_softmax,
+                            micro: bool = False) -> Array:
+    """`_multiclass_precision_recall_curve_update` (:461-527) -> `[T, C, 2, 2]`: class c against the one-hot target
+    `target == c`; `micro` -> the flattened binary task, `[T, 2, 2]` (:453-455, :473-474)."""
+    q, t = multiclass_rows(preds, target, num_classes, ignore_index, softmax_fn)
+    hot = (t[:, None] == np.arange(num_classes)[None, :]).astype(np.int64)
+    if micro:
+        return _bin_counts(q.reshape(-1), hot.reshape(-1), thresholds)
+    T = np.asarray(thresholds).size
+    out = np.zeros((T, num_classes, 2, 2), dtype=np.int64)
+    for c in range(num_classes):
+        out[:, c] = _bin_counts(q[:, c], hot[:, c], thresholds)
+    return out
+
+
+def multiclass_clf_curves(probs: Array, target: Array) -> List[Tuple[Array, Array, Array]]:
+    """The per-class loop of `_multiclass_precision_recall_curve_compute` (:548-555): column c of the stored
+    probabilities against `pos_label = c`."""
+    probs = np.asarray(probs)
+    target = np.asarray(target)
+    return [binary_clf_curve(probs[:, c], target, pos_label=c) for c in range(probs.shape[1])]
+
+
 # ------------------------------------------------------------------------------------------ K3: exact curves
 def exact_state(preds: Array, sigmoid_fn: SigmoidFn = torch_cpu_sigmoid) -> Array:
     """The scores `update` stores in exact mode: sigmoid over the whole batch iff any value is outside

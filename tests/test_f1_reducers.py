@@ -95,8 +95,8 @@ def test_task_wrappers_and_argument_errors():
         C.CohenKappa(task="multilabel", num_labels=3)
     with pytest.raises(ValueError, match="weight"):
         C.BinaryCohenKappa(weights="cubic")
-    with pytest.raises(NotImplementedError):
-        C.RecallAtFixedPrecision(task="multiclass", min_precision=0.5, num_classes=3)
+    m = C.RecallAtFixedPrecision(task="multiclass", min_precision=0.5, num_classes=3, thresholds=4)
+    assert type(m).__name__ == "MulticlassRecallAtFixedPrecision" and m.confmat.shape == (4, 3, 2, 2)
     assert F.specicity_at_sensitivity is F.specificity_at_sensitivity  # the reference's spelling is kept as an alias
     import inspect
 

@@ -50,3 +50,143 @@ def test_softmax_normalize_decision_and_special_rows():
     wide = torch.randn(17, 3000, generator=g, device="cuda")
     assert torch.equal(kernels.softmax_normalize(wide), wide.softmax(1))
     assert kernels.softmax_normalize(probs[:0]).shape == (0, 10)
+
+
+# ------------------------------------------------------------------------------------------ binned states
+from conftest import golden_names, ignore_of, load_golden  # noqa: E402
+
+import hotpath as O  # noqa: E402
+
+
+def cuda_softmax(x: np.ndarray) -> np.ndarray:
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).cuda().softmax(1).cpu().numpy()
+
+
+def _cuda(x):
+    return torch.from_numpy(np.ascontiguousarray(x)).cuda()
+
+
+@pytest.mark.parametrize("name", golden_names("f2_mccurve_"))
+def test_multiclass_curve_golden(name):
+    """Binned [T, C, 2, 2] / micro [T, 2, 2] states bit for bit against the oracle fed with the DEVICE softmax (H5:
+    CPU and CUDA softmax differ in low bits), and against the reference's own states where no softmax is involved;
+    exact-mode state, curves and the scalar metrics against the reference's golden values."""
+    from torchmetrics_forked_b200 import classification as C
+    from torchmetrics_forked_b200 import functional as F
+    from torchmetrics_forked_b200 import kernels
+
+    c = load_golden(name)
+    nC, ign = int(c["num_classes"]), ignore_of(c)
+    thr = torch.from_numpy(c["thresholds"])
+    preds, target = _cuda(c["preds"]), _cuda(c["target"])
+    softmaxed = "logits" in name or name.endswith(("multidim", "wide"))
+    for micro in (False, True):
+        m = C.MulticlassPrecisionRecallCurve(nC, thresholds=thr, average="micro" if micro else None,
+                                             ignore_index=ign).cuda()
+        h = preds.shape[0] // 3
+        m.update(preds[:h], target[:h])
+        m.update(preds[h:], target[h:])
+        # two updates decide the softmax independently, like two reference updates: build the oracle the same way
+        want = sum(O.multiclass_curve_binned(c["preds"][s], c["target"][s], nC, c["thresholds"], ign, cuda_softmax, micro)
+                   for s in (slice(0, h), slice(h, None)))
+        assert np.array_equal(m.confmat.cpu().numpy(), want), (name, micro)
+    got = F.multiclass_precision_recall_curve(preds, target, nC, thresholds=thr, ignore_index=ign)
+    state = O.multiclass_curve_binned(c["preds"], c["target"], nC, c["thresholds"], ign, cuda_softmax)
+    if not softmaxed:
+        assert np.array_equal(state, c["state"])
+    tps, fps, fns = state[:, :, 1, 1], state[:, :, 0, 1], state[:, :, 1, 0]
+    with np.errstate(invalid="ignore", divide="ignore"):
+        prec = np.where(tps + fps == 0, 0.0, tps / np.maximum(tps + fps, 1))
+    np.testing.assert_allclose(got[0].cpu().numpy()[:, :-1], prec.T, rtol=1e-6)
+    # exact mode
+    e = C.MulticlassPrecisionRecallCurve(nC, thresholds=None, ignore_index=ign).cuda()
+    e.update(preds, target)
+    want_probs, want_t = O.multiclass_rows(c["preds"], c["target"], nC, ign, cuda_softmax)
+    assert np.array_equal(e.preds[0].cpu().numpy(), want_probs) and np.array_equal(e.target[0].cpu().numpy(), want_t)
+    fps_l, tps_l, thr_l = kernels.clf_curves(e.preds[0], e.target[0], None, class_targets=True)
+    for k, (wf, wt, wh) in enumerate(O.multiclass_clf_curves(want_probs, want_t)):
+        assert np.array_equal(fps_l[k].cpu().numpy(), wf) and np.array_equal(tps_l[k].cpu().numpy(), wt)
+        assert np.array_equal(thr_l[k].cpu().numpy(), wh)
+        if not softmaxed:
+            assert np.array_equal(wf, c[f"fps_{k}"]) and np.array_equal(wh, c[f"thr_{k}"])
+    tol = dict(rtol=2e-5, atol=1e-6) if softmaxed else dict(rtol=1e-6, atol=1e-7)
+    for avg in ("macro", "weighted", "none"):
+        for T_, tag in ((None, "exact"), (len(thr), "binned")):
+            a = F.multiclass_auroc(preds, target, nC, average=avg, thresholds=T_, ignore_index=ign)
+            np.testing.assert_allclose(a.cpu().numpy(), c[f"auroc_{avg}_{tag}"], **tol)
+            a = F.multiclass_average_precision(preds, target, nC, average=avg, thresholds=T_, ignore_index=ign)
+            np.testing.assert_allclose(a.cpu().numpy(), c[f"ap_{avg}_{tag}"], **tol)
+    au = C.AUROC(task="multiclass", num_classes=nC, average="macro", thresholds=None, ignore_index=ign).cuda()
+    ap = C.MulticlassAveragePrecision(nC, average="weighted", thresholds=None, ignore_index=ign).cuda()
+    for s in (slice(0, 100), slice(100, None)):
+        au.update(preds[s], target[s])
+        ap.update(preds[s], target[s])
+    if not softmaxed:  # per-update softmax decisions coincide only when no update needs one
+        np.testing.assert_allclose(float(au.compute()), c["auroc_macro_exact"], **tol)
+        np.testing.assert_allclose(float(ap.compute()), c["ap_weighted_exact"], **tol)
+    if not softmaxed:
+        for stem, kw in (("recall_at_fixed_precision", "min_precision"), ("precision_at_fixed_recall", "min_recall"),
+                         ("specificity_at_sensitivity", "min_sensitivity")):
+            for T_, tag in ((None, "exact"), (len(thr), "binned")):
+                a, b = getattr(F, f"multiclass_{stem}")(preds, target, nC, **{kw: 0.4}, thresholds=T_, ignore_index=ign)
+                np.testing.assert_allclose(a.cpu().numpy(), c[f"{stem}_{tag}"][0], rtol=1e-6, atol=1e-7)
+                np.testing.assert_allclose(b.cpu().numpy(), c[f"{stem}_{tag}"][1], rtol=1e-6, atol=1e-7)
+        for avg in ("macro", "micro"):
+            pr = F.multiclass_precision_recall_curve(preds, target, nC, thresholds=len(thr), average=avg, ignore_index=ign)
+            roc = C.MulticlassROC(nC, thresholds=len(thr), average=avg, ignore_index=ign).cuda()
+            roc.update(preds, target)
+            for k, v in zip(("p", "r", "t"), pr):
+                np.testing.assert_allclose(v.cpu().numpy(), c[f"prc_{avg}_{k}"], rtol=1e-6, atol=1e-7)
+            for k, v in zip(("f", "t", "h"), roc.compute()):
+                np.testing.assert_allclose(v.cpu().numpy(), c[f"roc_{avg}_{k}"], rtol=1e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("C", [2, 3, 10, 33, 100, 1000])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_multiclass_curve_fused_kernel_random(C, dtype):
+    """k2_mc_rows over every lane layout, ragged rows, ignore_index, uneven thresholds and 16-bit scores, against
+    the oracle with the device softmax; C = 1000, T = 200 does not fit one SM's shared memory (global atomics)."""
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(400 + C)
+    n = 4099 if C <= 100 else 517
+    for thr in (torch.linspace(0, 1, 200), torch.sort(torch.rand(23, generator=g)).values):
+        preds = (torch.randn(n, C, generator=g) * 3).to(dtype)
+        target = torch.randint(C, (n,), generator=g)
+        target[torch.rand(n, generator=g) < 0.1] = -1
+        m = M.MulticlassPrecisionRecallCurve(C, thresholds=thr, ignore_index=-1).cuda()
+        m.update(preds.cuda(), target.cuda())
+        sm = lambda a: torch.from_numpy(a).to(dtype).cuda().softmax(1).float().cpu().numpy()  # noqa: E731
+        # 16-bit scores: above 1e6 comparisons the reference loops over thresholds and `preds >= thresholds[i]`
+        # (0-d threshold) is evaluated in the dtype of preds, i.e. against the ROUNDED threshold (:472, :518)
+        kept = int((target != -1).sum())
+        thr_seen = thr.to(dtype).float() if dtype != torch.float32 and kept * C * C > 1_000_000 else thr
+        want = O.multiclass_curve_binned(preds.float().numpy(), target.numpy(), C, thr_seen.numpy(), -1, sm)
+        assert np.array_equal(m.confmat.cpu().numpy(), want), (C, dtype, len(thr))
+    # probabilities: pass A only; out-of-range target is reported
+    probs = torch.rand(300, C, generator=g).softmax(1)
+    m = M.MulticlassPrecisionRecallCurve(C, thresholds=50).cuda()
+    tgt = torch.randint(C, (300,), generator=g)
+    m.update(probs.cuda(), tgt.cuda())
+    want = O.multiclass_curve_binned(probs.numpy(), tgt.numpy(), C, torch.linspace(0, 1, 50).numpy())
+    assert np.array_equal(m.confmat.cpu().numpy(), want)
+    bad = tgt.clone()
+    bad[5] = C
+    with pytest.raises(RuntimeError, match="target"):
+        M.MulticlassPrecisionRecallCurve(C, thresholds=50).cuda().update(probs.cuda(), bad.cuda())
+
+
+def test_multiclass_curve_wide_rows_fallback():
+    """C > 1024: torch's softmax behind the device-side decision, one-hot binning through the multilabel kernels."""
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(9)
+    C, n = 1500, 200
+    preds, target = torch.randn(n, C, generator=g), torch.randint(C, (n,), generator=g)
+    target[::7] = -1
+    for micro in (False, True):
+        m = M.MulticlassPrecisionRecallCurve(C, thresholds=9, average="micro" if micro else None, ignore_index=-1).cuda()
+        m.update(preds.cuda(), target.cuda())
+        want = O.multiclass_curve_binned(preds.numpy(), target.numpy(), C, torch.linspace(0, 1, 9).numpy(), -1,
+                                         cuda_softmax, micro)
+        assert np.array_equal(m.confmat.cpu().numpy(), want)

@@ -131,8 +131,9 @@ def as_columns(x: Chunks) -> Chunks:
     return [c.reshape(-1, 1) for c in x]
 
 
-def _chunk_lists(preds: Chunks, target: Chunks) -> Tuple[List[Tensor], List[Tensor]]:
-    """Validated, contiguous ``[n_i, L]`` chunk lists (the per-update buffers of an exact-mode state)."""
+def _chunk_lists(preds: Chunks, target: Chunks, class_targets: bool = False) -> Tuple[List[Tensor], List[Tensor]]:
+    """Validated, contiguous ``[n_i, L]`` chunk lists (the per-update buffers of an exact-mode state); with
+    ``class_targets`` the target chunks are ``[n_i]`` class indices."""
     ps = [preds] if isinstance(preds, Tensor) else list(preds)
     ts = [target] if isinstance(target, Tensor) else list(target)
     if len(ps) != len(ts) or not ps:
@@ -140,7 +141,10 @@ def _chunk_lists(preds: Chunks, target: Chunks) -> Tuple[List[Tensor], List[Tens
     for p, t in zip(ps, ts):
         nat.require_cuda(p, "preds")
         nat.require_cuda(t, "target")
-        if p.ndim != 2 or p.shape != t.shape:
+        if class_targets:
+            if p.ndim != 2 or t.ndim != 1 or t.shape[0] != p.shape[0]:
+                raise ValueError("`preds` must have shape (N, C) and `target` shape (N,)")
+        elif p.ndim != 2 or p.shape != t.shape:
             raise ValueError("`preds` and `target` must both have shape (N, L)")
         if p.shape[1] != ps[0].shape[1] or p.dtype != ps[0].dtype or t.dtype != ts[0].dtype:
             raise ValueError("all chunks must agree in the number of labels and in dtype")
@@ -160,14 +164,16 @@ def _chunk_table(ps: List[Tensor], ts: List[Tensor]) -> Tuple[Tensor, int]:
     return table, starts[-1]
 
 
-def _run_curves(preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int):
+def _run_curves(
+    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int, class_targets: bool = False
+):
     """pack -> batched radix sort -> boundary / prefix scan; everything stays on the device.
 
     ``preds`` / ``target`` are ``[N, L]`` tensors or lists of ``[n_i, L]`` chunks (read in place, never
     concatenated).  Returns ``(fps, tps, thr)`` as ``[L, N]`` float32 buffers, ``counts`` (int64 ``[L]``, valid
     prefix of each row) and the int32 error word.
     """
-    ps, ts = _chunk_lists(preds, target)
+    ps, ts = _chunk_lists(preds, target, class_targets)
     num_labels = ps[0].shape[1]
     n = sum(p.shape[0] for p in ps)
     dev = ps[0].device
@@ -179,37 +185,39 @@ def _run_curves(preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_
     has_ign = int(ignore_index is not None)
     if n > 0:
         scratch = torch.empty(int(nat.lib().tmb_clf_curve_scratch_bytes(n, num_labels)), dtype=torch.uint8, device=dev)
+        head = (n, num_labels, has_ign, int(ignore_index) if has_ign else 0, int(pos_label))
         tail = (
-            n, num_labels, has_ign, int(ignore_index) if has_ign else 0, int(pos_label), nat.ptr(scratch),
-            scratch.numel(), nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts), nat.ptr(err),
-            nat.stream_ptr(dev),
+            nat.ptr(scratch), scratch.numel(), nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts),
+            nat.ptr(err), nat.stream_ptr(dev),
         )  # fmt: skip
         with torch.cuda.device(dev):
-            if len(ps) == 1:
+            if len(ps) == 1 and not class_targets:
                 rc = nat.lib().tmb_clf_curves(
-                    nat.ptr(ps[0]), nat.float_code(ps[0]), nat.ptr(ts[0]), nat.label_code(ts[0]), *tail
+                    nat.ptr(ps[0]), nat.float_code(ps[0]), nat.ptr(ts[0]), nat.label_code(ts[0]), *head, *tail
                 )
                 nat.check(rc, "tmb_clf_curves")
             else:
                 table, _ = _chunk_table(ps, ts)
                 rc = nat.lib().tmb_clf_curves_chunked(
-                    nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), *tail
+                    nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), *head,
+                    int(class_targets), *tail
                 )
                 nat.check(rc, "tmb_clf_curves_chunked")
     return fps, tps, thr, counts, err, ps[0].dtype
 
 
 def clf_curves(
-    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1
+    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1, class_targets: bool = False
 ) -> Tuple[List[Tensor], List[Tensor], List[Tensor]]:
     """Per-label ``(fps, tps, thresholds)`` of ``[N, L]`` scores / targets (or lists of ``[n_i, L]`` chunks):
-    batched radix sort + scan.
+    batched radix sort + scan.  ``class_targets=True``: multiclass form, ``target`` chunks are ``[n_i]`` class
+    indices and label ``l`` is positive where ``target == l``.
 
     Returns three lists of ``L`` 1-d tensors (views into three ``[L, N]`` float32 buffers); thresholds come
     back in the dtype of ``preds``.  One host read of the ``L`` curve lengths is unavoidable because the
     outputs have data-dependent sizes.
     """
-    fps, tps, thr, counts, err, out_dtype = _run_curves(preds, target, ignore_index, pos_label)
+    fps, tps, thr, counts, err, out_dtype = _run_curves(preds, target, ignore_index, pos_label, class_targets)
     lengths = counts.cpu().tolist()  # the one synchronisation of the exact compute path
     if int(err.item()) & nat.ERR_SCORE_RANGE:
         raise RuntimeError(_SCORE_ERROR)
@@ -222,8 +230,9 @@ def clf_curves(
 
 
 def clf_curve_scores(
-    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1, want_ap: bool = True
-) -> Tensor:
+    preds: Chunks, target: Chunks, ignore_index: Optional[int], pos_label: int = 1, want_ap: bool = True,
+    class_targets: bool = False,
+) -> Tensor:  # fmt: skip
     """Per-label area reductions of the exact curves, float64 ``[L, 4]``, straight from the sorted keys — the
     curves themselves are never written:
 
@@ -232,7 +241,7 @@ def clf_curve_scores(
     ``preds`` / ``target`` as in :func:`clf_curves`; ``want_ap=False`` leaves column 1 at zero (AUROC does not need
     its float64 division per curve point).  Nothing is read back to the host here.
     """
-    ps, ts = _chunk_lists(preds, target)
+    ps, ts = _chunk_lists(preds, target, class_targets)
     num_labels = ps[0].shape[1]
     dev = ps[0].device
     table, n = _chunk_table(ps, ts)
@@ -244,7 +253,8 @@ def clf_curve_scores(
     with torch.cuda.device(dev):
         rc = nat.lib().tmb_clf_curve_scores_chunked(
             nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), n, num_labels, has_ign,
-            int(ignore_index) if has_ign else 0, int(pos_label), int(want_ap), nat.ptr(scratch), scratch.numel(),
+            int(ignore_index) if has_ign else 0, int(pos_label), int(class_targets), int(want_ap), nat.ptr(scratch),
+            scratch.numel(),
             nat.ptr(out), nat.ptr(err), nat.stream_ptr(dev),
         )  # fmt: skip
     nat.check(rc, "tmb_clf_curve_scores_chunked")

@@ -66,6 +66,11 @@ SIGNATURES = {
         [c_void_p, c_int, c_int64, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p],
     ),
     "tmb_softmax_rows": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p]),
+    "tmb_mc_curve_update": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_void_p, c_int64, c_int, c_int64, c_int, c_void_p,
+         c_int64, c_void_p, c_void_p],
+    ),
     "tmb_clf_curves": (
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p,
@@ -73,13 +78,13 @@ SIGNATURES = {
     ),
     "tmb_clf_curves_chunked": (
         c_int,
-        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_void_p, c_int64, c_void_p,
-         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_int64,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
     ),
     "tmb_clf_curve_scores_chunked": (
         c_int,
-        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_int64,
-         c_void_p, c_void_p, c_void_p],
+        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_int, c_void_p,
+         c_int64, c_void_p, c_void_p, c_void_p],
     ),
     "tmb_curve_reduce": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_compact_scratch_bytes": (c_int64, [c_int64]),

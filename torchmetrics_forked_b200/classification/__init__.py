@@ -5,10 +5,11 @@ from torchmetrics_forked_b200.classification.accuracy import (
     MulticlassAccuracy,
     MultilabelAccuracy,
 )
-from torchmetrics_forked_b200.classification.auroc import AUROC, BinaryAUROC, MultilabelAUROC
+from torchmetrics_forked_b200.classification.auroc import AUROC, BinaryAUROC, MulticlassAUROC, MultilabelAUROC
 from torchmetrics_forked_b200.classification.average_precision import (
     AveragePrecision,
     BinaryAveragePrecision,
+    MulticlassAveragePrecision,
     MultilabelAveragePrecision,
 )
 from torchmetrics_forked_b200.classification.confusion_matrix import (
@@ -35,10 +36,11 @@ from torchmetrics_forked_b200.classification.jaccard import (
 )
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
     PrecisionRecallCurve,
 )
-from torchmetrics_forked_b200.classification.roc import ROC, BinaryROC, MultilabelROC
+from torchmetrics_forked_b200.classification.roc import ROC, BinaryROC, MulticlassROC, MultilabelROC
 from torchmetrics_forked_b200.classification.stat_scores import (
     BinaryStatScores,
     MulticlassStatScores,
@@ -61,6 +63,7 @@ from torchmetrics_forked_b200.classification.matthews_corrcoef import (
 )
 from torchmetrics_forked_b200.classification.precision_fixed_recall import (
     BinaryPrecisionAtFixedRecall,
+    MulticlassPrecisionAtFixedRecall,
     MultilabelPrecisionAtFixedRecall,
     PrecisionAtFixedRecall,
 )
@@ -76,6 +79,7 @@ from torchmetrics_forked_b200.classification.precision_recall import (
 )
 from torchmetrics_forked_b200.classification.recall_fixed_precision import (
     BinaryRecallAtFixedPrecision,
+    MulticlassRecallAtFixedPrecision,
     MultilabelRecallAtFixedPrecision,
     RecallAtFixedPrecision,
 )
@@ -87,6 +91,7 @@ from torchmetrics_forked_b200.classification.specificity import (
 )
 from torchmetrics_forked_b200.classification.specificity_sensitivity import (
     BinarySpecificityAtSensitivity,
+    MulticlassSpecificityAtSensitivity,
     MultilabelSpecificityAtSensitivity,
     SpecificityAtSensitivity,
 )
@@ -103,4 +108,5 @@ __all__ = [
     "ROC", "BinaryROC", "MultilabelROC",
     "BinaryStatScores", "MulticlassStatScores", "MultilabelStatScores", "StatScores",
     "BinaryCohenKappa", "CohenKappa", "MulticlassCohenKappa", "BinaryHammingDistance", "HammingDistance", "MulticlassHammingDistance", "MultilabelHammingDistance", "BinaryMatthewsCorrCoef", "MatthewsCorrCoef", "MulticlassMatthewsCorrCoef", "MultilabelMatthewsCorrCoef", "BinaryPrecisionAtFixedRecall", "MultilabelPrecisionAtFixedRecall", "PrecisionAtFixedRecall", "BinaryPrecision", "BinaryRecall", "MulticlassPrecision", "MulticlassRecall", "MultilabelPrecision", "MultilabelRecall", "Precision", "Recall", "BinaryRecallAtFixedPrecision", "MultilabelRecallAtFixedPrecision", "RecallAtFixedPrecision", "BinarySpecificity", "MulticlassSpecificity", "MultilabelSpecificity", "Specificity", "BinarySpecificityAtSensitivity", "MultilabelSpecificityAtSensitivity", "SpecificityAtSensitivity",
+    "MulticlassAUROC", "MulticlassROC", "MulticlassAveragePrecision", "MulticlassPrecisionRecallCurve", "MulticlassPrecisionAtFixedRecall", "MulticlassRecallAtFixedPrecision", "MulticlassSpecificityAtSensitivity",
 ]  # fmt: skip

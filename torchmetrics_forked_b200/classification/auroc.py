@@ -7,11 +7,14 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
 from torchmetrics_forked_b200.functional.classification.auroc import (
     _binary_auroc_arg_validation,
     _binary_auroc_compute,
+    _multiclass_auroc_arg_validation,
+    _multiclass_auroc_compute,
     _multilabel_auroc_arg_validation,
     _multilabel_auroc_compute,
 )
@@ -41,6 +44,35 @@ class BinaryAUROC(BinaryPrecisionRecallCurve):
 
     def compute(self) -> Tensor:  # type: ignore[override]
         return _binary_auroc_compute(self._curve_state(), self.thresholds, self.max_fpr)
+
+
+class MulticlassAUROC(MulticlassPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: bool = True
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Class"
+
+    def __init__(
+        self,
+        num_classes: int,
+        average: Optional[Literal["macro", "weighted", "none"]] = "macro",
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(
+            num_classes=num_classes, thresholds=thresholds, ignore_index=ignore_index, validate_args=False, **kwargs
+        )
+        if validate_args:
+            _multiclass_auroc_arg_validation(num_classes, average, thresholds, ignore_index)
+        self.average = average  # the curve base class stores None here; this metric's averaging is over the scores
+        self.validate_args = validate_args
+
+    def compute(self) -> Tensor:  # type: ignore[override]
+        return _multiclass_auroc_compute(self._curve_state(), self.num_classes, self.average, self.thresholds)
 
 
 class MultilabelAUROC(MultilabelPrecisionRecallCurve):
@@ -92,7 +124,9 @@ class AUROC(_ClassificationTaskWrapper):
         if task == ClassificationTask.BINARY:
             return BinaryAUROC(max_fpr, **kwargs)
         if task == ClassificationTask.MULTICLASS:
-            raise NotImplementedError("multiclass AUROC is not part of the sm_100a update path yet")
+            if not isinstance(num_classes, int):
+                raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+            return MulticlassAUROC(num_classes, average, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

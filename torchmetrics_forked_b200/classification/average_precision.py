@@ -8,10 +8,13 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
 from torchmetrics_forked_b200.functional.classification.average_precision import (
     _binary_average_precision_compute,
+    _multiclass_average_precision_arg_validation,
+    _multiclass_average_precision_compute,
     _multilabel_average_precision_arg_validation,
     _multilabel_average_precision_compute,
 )
@@ -28,6 +31,35 @@ class BinaryAveragePrecision(BinaryPrecisionRecallCurve):
 
     def compute(self) -> Tensor:  # type: ignore[override]
         return _binary_average_precision_compute(self._curve_state(), self.thresholds)
+
+
+class MulticlassAveragePrecision(MulticlassPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: bool = True
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Class"
+
+    def __init__(
+        self,
+        num_classes: int,
+        average: Optional[Literal["macro", "weighted", "none"]] = "macro",
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(
+            num_classes=num_classes, thresholds=thresholds, ignore_index=ignore_index, validate_args=False, **kwargs
+        )
+        if validate_args:
+            _multiclass_average_precision_arg_validation(num_classes, average, thresholds, ignore_index)
+        self.average = average  # the curve base class stores None here; this metric's averaging is over the scores
+        self.validate_args = validate_args
+
+    def compute(self) -> Tensor:  # type: ignore[override]
+        return _multiclass_average_precision_compute(self._curve_state(), self.num_classes, self.average, self.thresholds)
 
 
 class MultilabelAveragePrecision(MultilabelPrecisionRecallCurve):
@@ -78,7 +110,9 @@ class AveragePrecision(_ClassificationTaskWrapper):
         if task == ClassificationTask.BINARY:
             return BinaryAveragePrecision(**kwargs)
         if task == ClassificationTask.MULTICLASS:
-            raise NotImplementedError("multiclass average precision is not part of the sm_100a update path yet")
+            if not isinstance(num_classes, int):
+                raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+            return MulticlassAveragePrecision(num_classes, average, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

@@ -8,11 +8,13 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
 from torchmetrics_forked_b200.functional.classification._fixed_point import (
     _binary_pr_point,
     _check_level,
+    _multiclass_pr_point,
     _multilabel_pr_point,
     _precision_at_recall,
 )
@@ -44,6 +46,35 @@ class BinaryPrecisionAtFixedRecall(BinaryPrecisionRecallCurve):
         return _binary_pr_point(self._curve_state(), self.thresholds, self.min_recall, _precision_at_recall)
 
 
+class MulticlassPrecisionAtFixedRecall(MulticlassPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Class"
+
+    def __init__(
+        self,
+        num_classes: int,
+        min_recall: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(
+            num_classes=num_classes, thresholds=thresholds, ignore_index=ignore_index, validate_args=validate_args,
+            **kwargs,
+        )  # fmt: skip
+        if validate_args:
+            _check_level("min_recall", min_recall)
+        self.min_recall = min_recall
+
+    def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
+        return _multiclass_pr_point(self._curve_state(), self.num_classes, self.thresholds, self.min_recall, _precision_at_recall)
+
+
 class MultilabelPrecisionAtFixedRecall(MultilabelPrecisionRecallCurve):
     is_differentiable: bool = False
     higher_is_better: Optional[bool] = None
@@ -73,7 +104,7 @@ class MultilabelPrecisionAtFixedRecall(MultilabelPrecisionRecallCurve):
 
 
 class PrecisionAtFixedRecall(_ClassificationTaskWrapper):
-    """``PrecisionAtFixedRecall(task=...)``; the multiclass form needs the multiclass curves (row f2, not built yet)."""
+    """``PrecisionAtFixedRecall(task=...)``."""
 
     def __new__(  # type: ignore[misc]
         cls,
@@ -92,7 +123,7 @@ class PrecisionAtFixedRecall(_ClassificationTaskWrapper):
         if task == ClassificationTask.MULTICLASS:
             if not isinstance(num_classes, int):
                 raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
-            raise NotImplementedError("MulticlassPrecisionAtFixedRecall needs the multiclass (softmax) curves: not built yet")
+            return MulticlassPrecisionAtFixedRecall(num_classes, min_recall, thresholds, ignore_index, validate_args, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

@@ -21,6 +21,11 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_format_exact,
     _binary_precision_recall_curve_tensor_validation,
     _binary_precision_recall_curve_update_,
+    _multiclass_precision_recall_curve_arg_validation,
+    _multiclass_precision_recall_curve_compute,
+    _multiclass_precision_recall_curve_format_exact,
+    _multiclass_precision_recall_curve_tensor_validation,
+    _multiclass_precision_recall_curve_update_,
     _multilabel_precision_recall_curve_arg_validation,
     _multilabel_precision_recall_curve_compute,
     _multilabel_precision_recall_curve_format_exact,
@@ -116,6 +121,68 @@ class BinaryPrecisionRecallCurve(_CurveStateMixin, Metric):
         return _binary_precision_recall_curve_compute(self._curve_state(), self.thresholds)
 
 
+class MulticlassPrecisionRecallCurve(_CurveStateMixin, Metric):
+    """One-vs-rest curves of a multiclass task (reference :200-385).
+
+    Binned mode keeps the int64 ``[T, C, 2, 2]`` state updated in place by the fused softmax + binning kernel;
+    exact mode stores the (conditionally softmaxed) ``[M, C]`` scores and ``[M]`` targets per update.  With
+    ``average="micro"`` the binned state is ``[T, 2, 2]`` (the reference declares ``[T, C, 2, 2]`` and then adds
+    a ``[T, 2, 2]`` update to it, which only broadcasts when ``T == C``).
+    """
+
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+
+    preds: List[Tensor]
+    target: List[Tensor]
+    confmat: Tensor
+
+    def __init__(
+        self,
+        num_classes: int,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        average: Optional[Literal["micro", "macro"]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(**kwargs)
+        if validate_args:
+            _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index, average)
+        self.num_classes = num_classes
+        self.average = average
+        self.ignore_index = ignore_index
+        self.validate_args = validate_args
+        self._init_curve_state(thresholds, (2, 2) if average == "micro" else (num_classes, 2, 2))
+
+    def update(self, preds: Tensor, target: Tensor) -> None:
+        if self.validate_args:
+            _multiclass_precision_recall_curve_tensor_validation(preds, target, self.num_classes, self.ignore_index)
+        dev = preds.device
+        if self.thresholds is None:
+            p, t = _multiclass_precision_recall_curve_format_exact(
+                preds, target, self.num_classes, self.ignore_index, self.average, self.validate_args
+            )
+            self.preds.append(p)
+            self.target.append(t)
+            return
+        err = self._error_word(dev)
+        thr, perm = self._bin_plan(dev)
+        labels = 1 if self.average == "micro" else self.num_classes
+        scratch = self._scratch_buffer("tb", kernels.thresh_bin_scratch_numel(labels, thr.numel()), dev)
+        _multiclass_precision_recall_curve_update_(
+            preds, target, self.num_classes, thr, perm, self.ignore_index, self.average, self.confmat, scratch, err
+        )
+        if self.validate_args:
+            self._raise_on_data_errors()
+
+    def compute(self) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+        return _multiclass_precision_recall_curve_compute(
+            self._curve_state(), self.num_classes, self.thresholds, self.average
+        )
+
+
 class MultilabelPrecisionRecallCurve(_CurveStateMixin, Metric):
     is_differentiable: bool = False
     higher_is_better: Optional[bool] = None
@@ -168,7 +235,7 @@ class MultilabelPrecisionRecallCurve(_CurveStateMixin, Metric):
 
 
 class PrecisionRecallCurve(_ClassificationTaskWrapper):
-    """``PrecisionRecallCurve(task=...)`` (reference :643-675); multiclass curves are a later row of SURVEY §8."""
+    """``PrecisionRecallCurve(task=...)`` (reference :643-675)."""
 
     def __new__(  # type: ignore[misc]
         cls,
@@ -185,7 +252,9 @@ class PrecisionRecallCurve(_ClassificationTaskWrapper):
         if task == ClassificationTask.BINARY:
             return BinaryPrecisionRecallCurve(**kwargs)
         if task == ClassificationTask.MULTICLASS:
-            raise NotImplementedError("multiclass precision-recall curves are not part of the sm_100a update path yet")
+            if not isinstance(num_classes, int):
+                raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+            return MulticlassPrecisionRecallCurve(num_classes, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

@@ -8,11 +8,13 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
 from torchmetrics_forked_b200.functional.classification._fixed_point import (
     _binary_pr_point,
     _check_level,
+    _multiclass_pr_point,
     _multilabel_pr_point,
     _recall_at_precision,
 )
@@ -44,6 +46,35 @@ class BinaryRecallAtFixedPrecision(BinaryPrecisionRecallCurve):
         return _binary_pr_point(self._curve_state(), self.thresholds, self.min_precision, _recall_at_precision)
 
 
+class MulticlassRecallAtFixedPrecision(MulticlassPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Class"
+
+    def __init__(
+        self,
+        num_classes: int,
+        min_precision: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(
+            num_classes=num_classes, thresholds=thresholds, ignore_index=ignore_index, validate_args=validate_args,
+            **kwargs,
+        )  # fmt: skip
+        if validate_args:
+            _check_level("min_precision", min_precision)
+        self.min_precision = min_precision
+
+    def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
+        return _multiclass_pr_point(self._curve_state(), self.num_classes, self.thresholds, self.min_precision, _recall_at_precision)
+
+
 class MultilabelRecallAtFixedPrecision(MultilabelPrecisionRecallCurve):
     is_differentiable: bool = False
     higher_is_better: Optional[bool] = None
@@ -73,7 +104,7 @@ class MultilabelRecallAtFixedPrecision(MultilabelPrecisionRecallCurve):
 
 
 class RecallAtFixedPrecision(_ClassificationTaskWrapper):
-    """``RecallAtFixedPrecision(task=...)``; the multiclass form needs the multiclass curves (row f2, not built yet)."""
+    """``RecallAtFixedPrecision(task=...)``."""
 
     def __new__(  # type: ignore[misc]
         cls,
@@ -92,7 +123,7 @@ class RecallAtFixedPrecision(_ClassificationTaskWrapper):
         if task == ClassificationTask.MULTICLASS:
             if not isinstance(num_classes, int):
                 raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
-            raise NotImplementedError("MulticlassRecallAtFixedPrecision needs the multiclass (softmax) curves: not built yet")
+            return MulticlassRecallAtFixedPrecision(num_classes, min_precision, thresholds, ignore_index, validate_args, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

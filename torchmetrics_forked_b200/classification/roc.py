@@ -1,6 +1,6 @@
 """ROC metric classes: same state and update as the precision-recall curve, different ``compute``.
 
-Reference: classification/roc.py (binary :42-156, multilabel :339-466).
+Reference: classification/roc.py (binary :42-156, multiclass :159-336, multilabel :339-466).
 """
 from typing import Any, List, Optional, Tuple, Union
 
@@ -10,9 +10,14 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
-from torchmetrics_forked_b200.functional.classification.roc import _binary_roc_compute, _multilabel_roc_compute
+from torchmetrics_forked_b200.functional.classification.roc import (
+    _binary_roc_compute,
+    _multiclass_roc_compute,
+    _multilabel_roc_compute,
+)
 from torchmetrics_forked_b200.metric import Metric
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
@@ -20,6 +25,11 @@ from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 class BinaryROC(BinaryPrecisionRecallCurve):
     def compute(self) -> Tuple[Tensor, Tensor, Tensor]:  # type: ignore[override]
         return _binary_roc_compute(self._curve_state(), self.thresholds)
+
+
+class MulticlassROC(MulticlassPrecisionRecallCurve):
+    def compute(self) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+        return _multiclass_roc_compute(self._curve_state(), self.num_classes, self.thresholds, self.average)
 
 
 class MultilabelROC(MultilabelPrecisionRecallCurve):
@@ -43,7 +53,9 @@ class ROC(_ClassificationTaskWrapper):
         if task == ClassificationTask.BINARY:
             return BinaryROC(**kwargs)
         if task == ClassificationTask.MULTICLASS:
-            raise NotImplementedError("multiclass ROC is not part of the sm_100a update path yet")
+            if not isinstance(num_classes, int):
+                raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+            return MulticlassROC(num_classes, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

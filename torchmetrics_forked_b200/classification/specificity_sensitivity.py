@@ -8,11 +8,13 @@ from typing_extensions import Literal
 from torchmetrics_forked_b200.classification.base import _ClassificationTaskWrapper
 from torchmetrics_forked_b200.classification.precision_recall_curve import (
     BinaryPrecisionRecallCurve,
+    MulticlassPrecisionRecallCurve,
     MultilabelPrecisionRecallCurve,
 )
 from torchmetrics_forked_b200.functional.classification._fixed_point import (
     _binary_roc_point,
     _check_level,
+    _multiclass_roc_point,
     _multilabel_roc_point,
 )
 from torchmetrics_forked_b200.metric import Metric
@@ -41,6 +43,35 @@ class BinarySpecificityAtSensitivity(BinaryPrecisionRecallCurve):
 
     def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
         return _binary_roc_point(self._curve_state(), self.thresholds, self.min_sensitivity)
+
+
+class MulticlassSpecificityAtSensitivity(MulticlassPrecisionRecallCurve):
+    is_differentiable: bool = False
+    higher_is_better: Optional[bool] = None
+    full_state_update: bool = False
+    plot_lower_bound: float = 0.0
+    plot_upper_bound: float = 1.0
+    plot_legend_name: str = "Class"
+
+    def __init__(
+        self,
+        num_classes: int,
+        min_sensitivity: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+        **kwargs: Any,
+    ) -> None:
+        super().__init__(
+            num_classes=num_classes, thresholds=thresholds, ignore_index=ignore_index, validate_args=validate_args,
+            **kwargs,
+        )  # fmt: skip
+        if validate_args:
+            _check_level("min_sensitivity", min_sensitivity)
+        self.min_sensitivity = min_sensitivity
+
+    def compute(self) -> Tuple[Tensor, Tensor]:  # type: ignore[override]
+        return _multiclass_roc_point(self._curve_state(), self.num_classes, self.thresholds, self.min_sensitivity)
 
 
 class MultilabelSpecificityAtSensitivity(MultilabelPrecisionRecallCurve):
@@ -72,7 +103,7 @@ class MultilabelSpecificityAtSensitivity(MultilabelPrecisionRecallCurve):
 
 
 class SpecificityAtSensitivity(_ClassificationTaskWrapper):
-    """``SpecificityAtSensitivity(task=...)``; the multiclass form needs the multiclass curves (row f2, not built yet)."""
+    """``SpecificityAtSensitivity(task=...)``."""
 
     def __new__(  # type: ignore[misc]
         cls,
@@ -91,7 +122,7 @@ class SpecificityAtSensitivity(_ClassificationTaskWrapper):
         if task == ClassificationTask.MULTICLASS:
             if not isinstance(num_classes, int):
                 raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
-            raise NotImplementedError("MulticlassSpecificityAtSensitivity needs the multiclass (softmax) curves: not built yet")
+            return MulticlassSpecificityAtSensitivity(num_classes, min_sensitivity, thresholds, ignore_index, validate_args, **kwargs)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

@@ -24,6 +24,7 @@
 // 16-bit pairs, made that fit) cover the rest.  Loads: one register batch ahead plus L2 prefetches four
 // batches ahead.
 #include "common.cuh"
+#include "softmax_rows.cuh"
 
 namespace tmb {
 
@@ -757,6 +758,102 @@ __global__ void __launch_bounds__(512, 1) k2_multi(TbArgs a) {
   }
 }
 
+// ---- multiclass binned curves: row softmax fused into the binning ------------------------------
+// _multiclass_precision_recall_curve_format/_update (precision_recall_curve.py:423-527): softmax over the classes
+// if any kept value is outside [0,1], then every (row, class) element is binned against the thresholds with the
+// one-hot target `class == target[row]`.  The reference materialises the probabilities and an N x C x T
+// comparison (or loops T times over N x C); here a sub-warp keeps a row in registers in the lane layout of
+// torch's persistent softmax (softmax_rows.cuh: bit-identical probabilities), bins its elements and adds them to
+// the CTA-wide [C][2][T+1] histogram in shared memory — the logits are read once, nothing is written but counts.
+// `micro` folds all classes into label 0 (the reference flattens preds and one-hot targets into one binary task).
+// Histograms that do not fit one SM go to global memory with one atomic per element.
+template <int PDT, bool SOFT>
+__global__ void __launch_bounds__(512, 1) k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro,
+                                                     int sh_bins) {
+  extern __shared__ uint32_t sh_u32[];
+  if (!pass_enabled(a, SOFT)) return;
+  float* sh_pad = (float*)sh_u32;
+  const int pad_words = (a.T + 2 + 31) / 32 * 32;
+  const int kbins = a.T + 1;
+  uint32_t* hist = sh_u32 + pad_words;
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
+  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
+  const bool on_grid = bn.grid_eps < 0.01f;
+  unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
+  const int lane = threadIdx.x & 31;
+  const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
+  const int rows_per_warp = 32 >> rm.log2W;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  bool stop = false, bad_target = false;
+  int trip = 0;
+  for (int64_t r0 = warp * rows_per_warp; r0 < rows && !stop; r0 += nwarps * rows_per_warp, ++trip) {  // warp-uniform
+    const int64_t r = r0 + sub;
+    const bool active = r < rows;
+    const int64_t t = active ? load_label(a.target, a.tdt, r) : 0;
+    const bool counted = active && !(a.has_ignore && t == a.ignore);
+    if (counted && (t < 0 || t >= C)) bad_target = true;
+    const int64_t base = r * C;
+    float e[kSoftmaxSlots];
+#pragma unroll
+    for (int it = 0; it < kSoftmaxSlots; ++it) {
+      const int c = it * rm.W + j;
+      e[it] = (it < rm.slots && counted && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
+    }
+    if (!SOFT) {
+      bool mine = false;
+#pragma unroll
+      for (int it = 0; it < kSoftmaxSlots; ++it)
+        if (it < rm.slots && counted && it * rm.W + j < C) mine |= !(e[it] >= 0.0f && e[it] <= 1.0f);
+      if (mine) raise_flag(a);
+      stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
+      if (stop) break;
+    } else {
+      softmax_row_inplace<PDT>(e, rm);
+    }
+#pragma unroll
+    for (int g0 = 0; g0 < kSoftmaxSlots; g0 += kPer) {
+      if (g0 < rm.slots) {  // warp-uniform
+        Decoded d;
+        d.bad = 0;
+        d.outside = 0;
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+          const int c = (g0 + i) * rm.W + j;
+          const bool valid = counted && (g0 + i) < rm.slots && c < C;
+          d.x[i] = valid ? e[g0 + i] : 0.5f;
+          d.inc[i] = valid ? 1u : 0u;
+          d.toff[i] = 0u;
+        }
+        int g[kPer];
+        if (on_grid)
+          batch_bins<PDT, false, true>(bn, d, g);
+        else
+          batch_bins<PDT, false, false>(bn, d, g);
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+          if (d.inc[i]) {
+            const int c = (g0 + i) * rm.W + j;
+            const int bin = ((micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0)) * kbins + g[i];
+            if (sh_bins > 0)
+              atomicAdd(&hist[bin], 1u);
+            else
+              atomicAdd(&gh[bin], 1ULL);
+          }
+        }
+      }
+    }
+  }
+  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_RANGE);
+  const bool dead = !SOFT && __syncthreads_or(stop);
+  if (SOFT) __syncthreads();
+  if (dead || (!SOFT && flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
+    const uint32_t v = hist[i];
+    if (v) atomicAdd(&gh[i], (unsigned long long)v);
+  }
+}
+
 // ---- K1b fast path: ONE threshold, [N, L] row-major (binary = L 1) ---------------------------------------------
 // Stat scores / confusion matrices / accuracy / F1 / Jaccard of binary and multilabel tasks compare against a
 // single threshold, so a sample only needs "above or not" — four counters per label.  The grid-stride is a
@@ -1129,6 +1226,27 @@ static int launch_multi_p(const TbArgs& a, int smem, cudaStream_t st) {
   }
 }
 
+template <int PDT>
+static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaStream_t st) {
+  const RowMap rm = row_map(C);
+  const int64_t pad_bytes = (int64_t)(a.T + 2 + 31) / 32 * 32 * 4;
+  const int64_t bins = (int64_t)a.L * 2 * (a.T + 1);
+  const bool fits = pad_bytes + bins * 4 <= (int64_t)dev_info().max_smem_optin - 1024;
+  const int sh_bins = fits ? (int)bins : 0;
+  const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
+  auto ka = k2_mc_rows<PDT, false>;
+  auto kb = k2_mc_rows<PDT, true>;
+  cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int block = 512;
+  const int64_t work = (rows * rm.W + block - 1) / block;
+  const int grid = resident_grid(kb, block, smem, work);
+  ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+  if (int rc = launch_status()) return rc;
+  kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+  return launch_status();
+}
+
 template <int PDT, int TDT>
 static int launch_single_pt(const TbArgs& a, cudaStream_t st) {
   auto ka = k2_single<PDT, TDT, false>;
@@ -1284,6 +1402,44 @@ extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int pre
     case TMB_F32: return launch_generic<TMB_F32>(a, st);
     case TMB_F16: return launch_generic<TMB_F16>(a, st);
     default: return launch_generic<TMB_BF16>(a, st);
+  }
+}
+
+extern "C" int tmb_mc_curve_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                   int64_t n_rows, int64_t num_classes, const float* thr, int64_t num_thresholds,
+                                   int has_ignore, int64_t ignore_index, int micro, int64_t* scratch,
+                                   int64_t scratch_elems, int32_t* err, void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_rows < 0 || num_classes < 2) return TMB_E_SHAPE;
+  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;
+  if (num_thresholds < 1 || num_thresholds > (1 << 26)) return TMB_E_SHAPE;
+  if (!scratch || !err || !thr) return TMB_E_NULL;
+  const int64_t labels = micro ? 1 : num_classes;
+  if (scratch_elems < scratch_elems_for(labels, num_thresholds)) return TMB_E_SCRATCH;
+  if (n_rows == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  TbArgs a;
+  a.preds = preds;
+  a.target = target;
+  a.thr = thr;
+  a.scratch = (unsigned long long*)scratch;
+  a.err = err;
+  a.n_total = n_rows * num_classes;
+  a.S = 1;
+  a.ignore = ignore_index;
+  a.L = (int)labels;
+  a.T = (int)num_thresholds;
+  a.pdt = preds_dtype;
+  a.tdt = target_dtype;
+  a.preds_is_label = 0;
+  a.cmp_gt = 0;
+  a.has_ignore = has_ignore;
+  a.flag_counts_ignored = 0;
+  switch (preds_dtype) {
+    case TMB_F32: return launch_mc_rows<TMB_F32>(a, n_rows, (int)num_classes, micro, st);
+    case TMB_F16: return launch_mc_rows<TMB_F16>(a, n_rows, (int)num_classes, micro, st);
+    default: return launch_mc_rows<TMB_BF16>(a, n_rows, (int)num_classes, micro, st);
   }
 }
 

@@ -210,6 +210,7 @@ struct PackSrc {
   const void* target;
   const long long* table;  // device memory, 3 C + 1 entries
   int num_chunks;
+  int class_targets;       // 1: targets hold ONE class index per row ([rows_c]); label l is positive where it equals l
 };
 
 constexpr int kPackRows = 128;    // rows per CTA: every label leaves as one 512-byte run of keys
@@ -273,7 +274,8 @@ __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, in
       tb = (const void*)src.table[2 * C + 1 + c];
     }
     const int r_end = (int)min((int64_t)rows, c_end - n0);
-    const int64_t base_off = (n0 - c_begin) * L + l0;  // element offset of (row n0, label l0) inside the chunk
+    const int64_t row_off = n0 - c_begin;            // row n0 inside the chunk
+    const int64_t base_off = row_off * L + l0;        // element offset of (row n0, label l0) inside the chunk
     const int e_end = r_end * lt;
     for (int e0 = r_begin * lt + threadIdx.x; e0 < e_end; e0 += kPackThreads * kPackUnroll) {
       float v[kPackUnroll];
@@ -288,16 +290,20 @@ __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, in
           const int col = e - r * lt;
           const int64_t idx = base_off + (r * L + col);
           v[q] = load_elem<DT>(pb, idx);
-          t[q] = load_label(tb, tdt, idx);
-          slot[q] = col * stride + r;
+          t[q] = load_label(tb, tdt, src.class_targets ? row_off + r : idx);
+          slot[q] = (col << 8) | r;  // r < 128
         }
       }
 #pragma unroll
       for (int q = 0; q < kPackUnroll; ++q) {
         if (slot[q] >= 0) {
+          const int col = slot[q] >> 8, r = slot[q] & 255;
           uint32_t key = kSentinel;
-          if (!(has_ignore && t[q] == ignore)) key = make_key(v[q], t[q] == pos_label, negative);
-          tile[slot[q]] = key;
+          if (!(has_ignore && t[q] == ignore)) {
+            const int64_t positive_value = src.class_targets ? (int64_t)(l0 + col) : pos_label;
+            key = make_key(v[q], t[q] == positive_value, negative);
+          }
+          tile[col * stride + r] = key;
         }
       }
     }
@@ -1183,26 +1189,27 @@ extern "C" int tmb_clf_curves(const void* preds, int preds_dtype, const void* ta
                               void* scratch, int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
                               int64_t* counts, int32_t* err, void* stream) {
   if (n > 0 && (!preds || !target)) return TMB_E_NULL;
-  const PackSrc src{preds, target, nullptr, 1};
+  const PackSrc src{preds, target, nullptr, 1, 0};
   return curves_impl(src, preds_dtype, target_dtype, n, num_labels, has_ignore, ignore_index, pos_label, scratch,
                      scratch_bytes, fps, tps, thresholds, counts, err, stream);
 }
 
 extern "C" int tmb_clf_curves_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
                                       int target_dtype, int64_t n, int64_t num_labels, int has_ignore,
-                                      int64_t ignore_index, int64_t pos_label, void* scratch, int64_t scratch_bytes,
-                                      float* fps, float* tps, float* thresholds, int64_t* counts, int32_t* err,
-                                      void* stream) {
+                                      int64_t ignore_index, int64_t pos_label, int class_targets, void* scratch,
+                                      int64_t scratch_bytes, float* fps, float* tps, float* thresholds,
+                                      int64_t* counts, int32_t* err, void* stream) {
   if (n > 0 && !chunk_table_ok(chunk_table, num_chunks)) return chunk_table ? TMB_E_SHAPE : TMB_E_NULL;
-  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks};
+  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks, class_targets ? 1 : 0};
   return curves_impl(src, preds_dtype, target_dtype, n, num_labels, has_ignore, ignore_index, pos_label, scratch,
                      scratch_bytes, fps, tps, thresholds, counts, err, stream);
 }
 
 extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
                                             int target_dtype, int64_t n, int64_t num_labels, int has_ignore,
-                                            int64_t ignore_index, int64_t pos_label, int want_ap, void* scratch,
-                                            int64_t scratch_bytes, double* scores, int32_t* err, void* stream) {
+                                            int64_t ignore_index, int64_t pos_label, int class_targets,
+                                            int want_ap, void* scratch, int64_t scratch_bytes, double* scores,
+                                            int32_t* err, void* stream) {
   if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
   if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
   if (n >= ((int64_t)1 << 31)) return TMB_E_LIMIT;
@@ -1217,7 +1224,7 @@ extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t 
   if (scratch_bytes < p.total) return TMB_E_SCRATCH;
   const CurveBufs b = curve_bufs(p, scratch);
   const int L = (int)num_labels;
-  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks};
+  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks, class_targets ? 1 : 0};
   if (int rc = pack_and_sort(src, preds_dtype, target_dtype, n, L, has_ignore, ignore_index, pos_label, p, b, err, st))
     return rc;
   if (int rc = curve_tile_sums(n, L, p, b, nullptr, st)) return rc;

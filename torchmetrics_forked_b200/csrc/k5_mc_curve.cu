@@ -15,40 +15,9 @@
 //   * result e / sum (IEEE division), rounded to the input dtype for bf16 / f16
 // Rows wider than 1024 use a different torch kernel (block reduction); the host side keeps torch's own softmax
 // for those and only takes the in/out-of-range decision from here.
-#include "common.cuh"
+#include "softmax_rows.cuh"
 
 namespace tmb {
-
-constexpr int kSoftmaxMaxClasses = 1024;
-constexpr int kSoftmaxSlots = kSoftmaxMaxClasses / 32;
-
-template <int DT>
-__device__ __forceinline__ void store_elem(void* out, int64_t i, float v) {
-  if constexpr (DT == TMB_F32) {
-    ((float*)out)[i] = v;
-  } else if constexpr (DT == TMB_BF16) {
-    ((__nv_bfloat16*)out)[i] = __float2bfloat16_rn(v);
-  } else {
-    ((__half*)out)[i] = __float2half_rn(v);
-  }
-}
-
-struct RowMap {  // how rows are laid over a warp
-  int W;         // lanes per row (power of two, <= 32)
-  int log2W;
-  int slots;     // elements per lane: P / W
-};
-
-static RowMap row_map(int C) {
-  int P = 1;
-  while (P < C) P <<= 1;
-  RowMap m;
-  m.W = P < 32 ? P : 32;
-  m.log2W = 0;
-  while ((1 << m.log2W) < m.W) ++m.log2W;
-  m.slots = P / m.W;
-  return m;
-}
 
 // pass A: atomicMax(flag, gen) as soon as a value outside [0,1] (NaN included) shows up in a row that is not
 // ignored.  Same flag protocol as k3_outside_flag.
@@ -106,28 +75,7 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
       const int c = it * rm.W + j;
       e[it] = (it < rm.slots && active && c < C) ? load_elem<DT>(x, base + c) : -INFINITY;
     }
-    if (soft) {
-      float m = e[0];
-#pragma unroll
-      for (int it = 1; it < kSoftmaxSlots; ++it)
-        if (it < rm.slots) m = (m > e[it]) ? m : e[it];
-      for (int off = rm.W >> 1; off > 0; off >>= 1) {
-        const float b = __shfl_xor_sync(kFull, m, off, rm.W);
-        m = (m < b) ? b : m;
-      }
-      float s = 0.0f;
-#pragma unroll
-      for (int it = 0; it < kSoftmaxSlots; ++it) {
-        if (it < rm.slots) {
-          e[it] = expf(e[it] - m);
-          s += e[it];
-        }
-      }
-      for (int off = rm.W >> 1; off > 0; off >>= 1) s += __shfl_xor_sync(kFull, s, off, rm.W);
-#pragma unroll
-      for (int it = 0; it < kSoftmaxSlots; ++it)
-        if (it < rm.slots) e[it] = e[it] / s;
-    }
+    if (soft) softmax_row_inplace<DT>(e, rm);
 #pragma unroll
     for (int it = 0; it < kSoftmaxSlots; ++it) {
       const int c = it * rm.W + j;

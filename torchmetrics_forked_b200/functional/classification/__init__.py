@@ -5,10 +5,11 @@ from torchmetrics_forked_b200.functional.classification.accuracy import (
     multiclass_accuracy,
     multilabel_accuracy,
 )
-from torchmetrics_forked_b200.functional.classification.auroc import auroc, binary_auroc, multilabel_auroc
+from torchmetrics_forked_b200.functional.classification.auroc import auroc, binary_auroc, multiclass_auroc, multilabel_auroc
 from torchmetrics_forked_b200.functional.classification.average_precision import (
     average_precision,
     binary_average_precision,
+    multiclass_average_precision,
     multilabel_average_precision,
 )
 from torchmetrics_forked_b200.functional.classification.confusion_matrix import (
@@ -35,10 +36,11 @@ from torchmetrics_forked_b200.functional.classification.jaccard import (
 )
 from torchmetrics_forked_b200.functional.classification.precision_recall_curve import (
     binary_precision_recall_curve,
+    multiclass_precision_recall_curve,
     multilabel_precision_recall_curve,
     precision_recall_curve,
 )
-from torchmetrics_forked_b200.functional.classification.roc import binary_roc, multilabel_roc, roc
+from torchmetrics_forked_b200.functional.classification.roc import binary_roc, multiclass_roc, multilabel_roc, roc
 from torchmetrics_forked_b200.functional.classification.stat_scores import (
     binary_stat_scores,
     multiclass_stat_scores,
@@ -65,6 +67,7 @@ from torchmetrics_forked_b200.functional.classification.matthews_corrcoef import
 )
 from torchmetrics_forked_b200.functional.classification.precision_fixed_recall import (
     binary_precision_at_fixed_recall,
+    multiclass_precision_at_fixed_recall,
     multilabel_precision_at_fixed_recall,
     precision_at_fixed_recall,
 )
@@ -80,6 +83,7 @@ from torchmetrics_forked_b200.functional.classification.precision_recall import 
 )
 from torchmetrics_forked_b200.functional.classification.recall_fixed_precision import (
     binary_recall_at_fixed_precision,
+    multiclass_recall_at_fixed_precision,
     multilabel_recall_at_fixed_precision,
     recall_at_fixed_precision,
 )
@@ -91,6 +95,7 @@ from torchmetrics_forked_b200.functional.classification.specificity import (
 )
 from torchmetrics_forked_b200.functional.classification.specificity_sensitivity import (
     binary_specificity_at_sensitivity,
+    multiclass_specificity_at_sensitivity,
     multilabel_specificity_at_sensitivity,
     specicity_at_sensitivity,
     specificity_at_sensitivity,
@@ -108,4 +113,5 @@ __all__ = [
     "binary_roc", "multilabel_roc", "roc",
     "binary_stat_scores", "multiclass_stat_scores", "multilabel_stat_scores", "stat_scores",
     "binary_cohen_kappa", "cohen_kappa", "multiclass_cohen_kappa", "binary_hamming_distance", "hamming_distance", "multiclass_hamming_distance", "multilabel_hamming_distance", "binary_matthews_corrcoef", "matthews_corrcoef", "multiclass_matthews_corrcoef", "multilabel_matthews_corrcoef", "binary_precision_at_fixed_recall", "multilabel_precision_at_fixed_recall", "precision_at_fixed_recall", "binary_precision", "binary_recall", "multiclass_precision", "multiclass_recall", "multilabel_precision", "multilabel_recall", "precision", "recall", "binary_recall_at_fixed_precision", "multilabel_recall_at_fixed_precision", "recall_at_fixed_precision", "binary_specificity", "multiclass_specificity", "multilabel_specificity", "specificity", "binary_specificity_at_sensitivity", "multilabel_specificity_at_sensitivity", "specicity_at_sensitivity", "specificity_at_sensitivity",
+    "multiclass_auroc", "multiclass_roc", "multiclass_average_precision", "multiclass_precision_recall_curve", "multiclass_precision_at_fixed_recall", "multiclass_recall_at_fixed_precision", "multiclass_specificity_at_sensitivity",
 ]  # fmt: skip

@@ -19,12 +19,20 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_compute,
     _binary_precision_recall_curve_tensor_validation,
     _binary_state_functional,
+    _multiclass_precision_recall_curve_arg_validation,
+    _multiclass_precision_recall_curve_compute,
+    _multiclass_precision_recall_curve_tensor_validation,
+    _multiclass_state_functional,
     _multilabel_precision_recall_curve_arg_validation,
     _multilabel_precision_recall_curve_compute,
     _multilabel_precision_recall_curve_tensor_validation,
     _multilabel_state_functional,
 )
-from torchmetrics_forked_b200.functional.classification.roc import _binary_roc_compute, _multilabel_roc_compute
+from torchmetrics_forked_b200.functional.classification.roc import (
+    _binary_roc_compute,
+    _multiclass_roc_compute,
+    _multilabel_roc_compute,
+)
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
 State = Union[Tensor, Tuple[Tensor, Tensor]]
@@ -133,8 +141,32 @@ def _multilabel_roc_point(
     )
 
 
+def _multiclass_pr_point(
+    state: State, num_classes: int, thresholds: Optional[Tensor], level: float, select: Selector
+) -> Tuple[Tensor, Tensor]:
+    precision, recall, thr = _multiclass_precision_recall_curve_compute(state, num_classes, thresholds)
+    shared = isinstance(state, Tensor)
+    return _stack_points(
+        [select(precision[i], recall[i], thr if shared else thr[i], level) for i in range(num_classes)]
+    )
+
+
+def _multiclass_roc_point(
+    state: State, num_classes: int, thresholds: Optional[Tensor], level: float
+) -> Tuple[Tensor, Tensor]:
+    fpr, sensitivity, thr = _multiclass_roc_compute(state, num_classes, thresholds)
+    shared = isinstance(state, Tensor)
+    return _stack_points(
+        [
+            _specificity_at_sensitivity(1 - fpr[i], sensitivity[i], thr if shared else thr[i], level)
+            for i in range(num_classes)
+        ]
+    )
+
+
 def fixed_point_family(stem: str, level_name: str, select: Optional[Selector]):
-    """``(binary_<stem>, multilabel_<stem>, <stem>)``; ``select=None`` means the ROC based specificity metric."""
+    """``(binary_<stem>, multiclass_<stem>, multilabel_<stem>, <stem>)``; ``select=None`` means the ROC based
+    specificity metric."""
 
     def binary(
         preds: Tensor,
@@ -153,6 +185,27 @@ def fixed_point_family(stem: str, level_name: str, select: Optional[Selector]):
         if select is None:
             return _binary_roc_point(state, thresholds, level)
         return _binary_pr_point(state, thresholds, level, select)
+
+    def multiclass(
+        preds: Tensor,
+        target: Tensor,
+        num_classes: int,
+        level: float,
+        thresholds: Optional[Union[int, List[float], Tensor]] = None,
+        ignore_index: Optional[int] = None,
+        validate_args: bool = True,
+    ) -> Tuple[Tensor, Tensor]:
+        if validate_args:
+            _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index)
+            _check_level(level_name, level)
+            _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
+        thresholds = _adjust_threshold_arg(thresholds, preds.device)
+        state = _multiclass_state_functional(
+            preds, target, num_classes, thresholds, ignore_index, None, validate_args, f"multiclass_{stem}"
+        )
+        if select is None:
+            return _multiclass_roc_point(state, num_classes, thresholds, level)
+        return _multiclass_pr_point(state, num_classes, thresholds, level, select)
 
     def multilabel(
         preds: Tensor,
@@ -192,9 +245,7 @@ def fixed_point_family(stem: str, level_name: str, select: Optional[Selector]):
         if task == ClassificationTask.MULTICLASS:
             if not isinstance(num_classes, int):
                 raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
-            raise NotImplementedError(
-                f"multiclass_{stem} needs the multiclass (softmax) curves — row f2 of the hot-path scope, not built yet"
-            )
+            return multiclass(preds, target, num_classes, level, thresholds, ignore_index, validate_args)
         if task == ClassificationTask.MULTILABEL:
             if not isinstance(num_labels, int):
                 raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")
@@ -220,4 +271,9 @@ def fixed_point_family(stem: str, level_name: str, select: Optional[Selector]):
         wrapper.__doc__ = f"``{name}``: curve state (K2 / K3 kernels), then one operating point of the curve."
         return wrapper
 
-    return rename(binary, f"binary_{stem}"), rename(multilabel, f"multilabel_{stem}"), rename(by_task, stem)
+    return (
+        rename(binary, f"binary_{stem}"),
+        rename(multiclass, f"multiclass_{stem}"),
+        rename(multilabel, f"multilabel_{stem}"),
+        rename(by_task, stem),
+    )

@@ -10,11 +10,18 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_arg_validation,
     _binary_precision_recall_curve_tensor_validation,
     _binary_state_functional,
+    _multiclass_precision_recall_curve_arg_validation,
+    _multiclass_precision_recall_curve_tensor_validation,
+    _multiclass_state_functional,
     _multilabel_precision_recall_curve_arg_validation,
     _multilabel_precision_recall_curve_tensor_validation,
     _multilabel_state_functional,
 )
-from torchmetrics_forked_b200.functional.classification.roc import _binary_roc_compute, _multilabel_roc_compute
+from torchmetrics_forked_b200.functional.classification.roc import (
+    _binary_roc_compute,
+    _multiclass_roc_compute,
+    _multilabel_roc_compute,
+)
 from torchmetrics_forked_b200.utilities.compute import _auc_compute_without_check, _safe_divide
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 from torchmetrics_forked_b200.utilities.prints import rank_zero_warn
@@ -167,6 +174,55 @@ def _multilabel_auroc_arg_validation(
         raise ValueError(f"Expected argument `average` to be one of {allowed_average} but got {average}")
 
 
+def _multiclass_auroc_arg_validation(
+    num_classes: int,
+    average: Optional[str] = "macro",
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    ignore_index: Optional[int] = None,
+) -> None:
+    _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index)
+    allowed_average = ("macro", "weighted", "none", None)
+    if average not in allowed_average:
+        raise ValueError(f"Expected argument `average` to be one of {allowed_average} but got {average}")
+
+
+def _multiclass_auroc_compute(
+    state: Union[Tensor, Tuple[Tensor, Tensor]],
+    num_classes: int,
+    average: Optional[str] = "macro",
+    thresholds: Optional[Tensor] = None,
+) -> Tensor:
+    """One-vs-rest AUROC per class, then averaging (reference auroc.py:192-204)."""
+    if not (isinstance(state, Tensor) and thresholds is not None):
+        # exact mode: all classes in one batched sort + scan + area reduction; column 3 (positives per class) is
+        # the reference's `_bincount(target, minlength=num_classes)` weight
+        from torchmetrics_forked_b200 import kernels
+
+        scores = kernels.clf_curve_scores(state[0], state[1], None, want_ap=False, class_targets=True)
+        return _reduce_scores(_exact_auroc_from_scores(scores), average, scores[:, 3].float())
+    fpr, tpr, _ = _multiclass_roc_compute(state, num_classes, thresholds)
+    return _reduce_auroc(fpr, tpr, average, weights=state[0][:, 1, :].sum(-1))
+
+
+def multiclass_auroc(
+    preds: Tensor,
+    target: Tensor,
+    num_classes: int,
+    average: Optional[Literal["macro", "weighted", "none"]] = "macro",
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    ignore_index: Optional[int] = None,
+    validate_args: bool = True,
+) -> Tensor:
+    """Reference: auroc.py:207-292."""
+    if validate_args:
+        _multiclass_auroc_arg_validation(num_classes, average, thresholds, ignore_index)
+        _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
+    thresholds = _adjust_threshold_arg(thresholds, preds.device)
+    state = _multiclass_state_functional(preds, target, num_classes, thresholds, ignore_index, None, validate_args,
+                                         "multiclass_auroc")
+    return _multiclass_auroc_compute(state, num_classes, average, thresholds)
+
+
 def _flatten_valid(state: Tuple[Tensor, Tensor], ignore_index: Optional[int]) -> Tuple[Tensor, Tensor]:
     """Micro averaging in exact mode: every (sample, label) pair becomes one binary sample."""
     if not isinstance(state[0], Tensor):  # per-update chunks: flatten (and filter) each one where it lies
@@ -239,7 +295,9 @@ def auroc(
     if task == ClassificationTask.BINARY:
         return binary_auroc(preds, target, max_fpr, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTICLASS:
-        raise NotImplementedError("multiclass AUROC is not part of the sm_100a update path yet")
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        return multiclass_auroc(preds, target, num_classes, average, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTILABEL:
         if not isinstance(num_labels, int):
             raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

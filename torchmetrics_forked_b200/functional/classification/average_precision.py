@@ -12,6 +12,10 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_compute,
     _binary_precision_recall_curve_tensor_validation,
     _binary_state_functional,
+    _multiclass_precision_recall_curve_arg_validation,
+    _multiclass_precision_recall_curve_compute,
+    _multiclass_precision_recall_curve_tensor_validation,
+    _multiclass_state_functional,
     _multilabel_precision_recall_curve_arg_validation,
     _multilabel_precision_recall_curve_compute,
     _multilabel_precision_recall_curve_tensor_validation,
@@ -83,6 +87,54 @@ def binary_average_precision(
     state = _binary_state_functional(preds, target, thresholds, ignore_index, validate_args,
                                      "binary_average_precision")
     return _binary_average_precision_compute(state, thresholds)
+
+
+def _multiclass_average_precision_arg_validation(
+    num_classes: int,
+    average: Optional[str] = "macro",
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    ignore_index: Optional[int] = None,
+) -> None:
+    _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index)
+    allowed_average = ("macro", "weighted", "none", None)
+    if average not in allowed_average:
+        raise ValueError(f"Expected argument `average` to be one of {allowed_average} but got {average}")
+
+
+def _multiclass_average_precision_compute(
+    state: Union[Tensor, Tuple[Tensor, Tensor]],
+    num_classes: int,
+    average: Optional[str] = "macro",
+    thresholds: Optional[Tensor] = None,
+) -> Tensor:
+    """One-vs-rest average precision per class, then averaging (reference average_precision.py:164-176)."""
+    if not (isinstance(state, Tensor) and thresholds is not None):
+        from torchmetrics_forked_b200 import kernels
+        from torchmetrics_forked_b200.functional.classification.auroc import _reduce_scores
+
+        scores = kernels.clf_curve_scores(state[0], state[1], None, class_targets=True)
+        return _reduce_scores(_exact_ap_from_scores(scores), average, scores[:, 3].float())
+    precision, recall, _ = _multiclass_precision_recall_curve_compute(state, num_classes, thresholds)
+    return _reduce_average_precision(precision, recall, average, weights=state[0][:, 1, :].sum(-1))
+
+
+def multiclass_average_precision(
+    preds: Tensor,
+    target: Tensor,
+    num_classes: int,
+    average: Optional[Literal["macro", "weighted", "none"]] = "macro",
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    ignore_index: Optional[int] = None,
+    validate_args: bool = True,
+) -> Tensor:
+    """Reference: average_precision.py:179-269."""
+    if validate_args:
+        _multiclass_average_precision_arg_validation(num_classes, average, thresholds, ignore_index)
+        _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
+    thresholds = _adjust_threshold_arg(thresholds, preds.device)
+    state = _multiclass_state_functional(preds, target, num_classes, thresholds, ignore_index, None, validate_args,
+                                         "multiclass_average_precision")
+    return _multiclass_average_precision_compute(state, num_classes, average, thresholds)
 
 
 def _multilabel_average_precision_arg_validation(
@@ -157,7 +209,9 @@ def average_precision(
     if task == ClassificationTask.BINARY:
         return binary_average_precision(preds, target, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTICLASS:
-        raise NotImplementedError("multiclass average precision is not part of the sm_100a update path yet")
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        return multiclass_average_precision(preds, target, num_classes, average, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTILABEL:
         if not isinstance(num_labels, int):
             raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

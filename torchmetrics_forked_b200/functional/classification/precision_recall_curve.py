@@ -20,7 +20,7 @@ from typing_extensions import Literal
 
 from torchmetrics_forked_b200 import kernels
 from torchmetrics_forked_b200.utilities.checks import _check_same_shape
-from torchmetrics_forked_b200.utilities.compute import _safe_divide
+from torchmetrics_forked_b200.utilities.compute import _safe_divide, interp
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
 _LOOP_SWITCH = 50_000  # above this many samples the reference compares in the dtype of `preds` (:203-207)
@@ -329,6 +329,189 @@ def multilabel_precision_recall_curve(
     return _multilabel_precision_recall_curve_compute(state, num_labels, thresholds, ignore_index)
 
 
+# ------------------------------------------------------------------------------------------ multiclass (row f2)
+_MC_VECTOR_SWITCH = 1_000_000  # reference :472: above this many comparisons it loops over thresholds (0-d compare)
+
+
+def _multiclass_precision_recall_curve_arg_validation(
+    num_classes: int,
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    ignore_index: Optional[int] = None,
+    average: Optional[str] = None,
+) -> None:
+    """Reference: precision_recall_curve.py:360-377."""
+    if not isinstance(num_classes, int) or num_classes < 2:
+        raise ValueError(f"Expected argument `num_classes` to be an integer larger than 1, but got {num_classes}")
+    if average not in (None, "micro", "macro"):
+        raise ValueError(f"Expected argument `average` to be one of None, 'micro' or 'macro', but got {average}")
+    _binary_precision_recall_curve_arg_validation(thresholds, ignore_index)
+
+
+def _multiclass_precision_recall_curve_tensor_validation(
+    preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int] = None
+) -> None:
+    """Shape / dtype checks of :380-420; the range check of the targets (the reference counts unique values, a
+    host synchronisation) is done by the kernels through the error word."""
+    if not preds.ndim == target.ndim + 1:
+        raise ValueError(
+            f"Expected `preds` to have one more dimension than `target` but got {preds.ndim} and {target.ndim}"
+        )
+    if target.is_floating_point():
+        raise ValueError(
+            f"Expected argument `target` to be an int or long tensor, but got tensor with dtype {target.dtype}"
+        )
+    if not preds.is_floating_point():
+        raise ValueError(f"Expected `preds` to be a float tensor, but got {preds.dtype}")
+    if preds.shape[1] != num_classes:
+        raise ValueError(
+            "Expected `preds.shape[1]` to be equal to the number of classes but"
+            f" got {preds.shape[1]} and {num_classes}."
+        )
+    if preds.shape[0] != target.shape[0] or preds.shape[2:] != target.shape[1:]:
+        raise ValueError(
+            "Expected the shape of `preds` should be (N, C, ...) and the shape of `target` should be (N, ...)"
+            f" but got {preds.shape} and {target.shape}"
+        )
+
+
+def _multiclass_rows(preds: Tensor, target: Tensor, num_classes: int) -> Tuple[Tensor, Tensor]:
+    """``[M, C]`` scores and ``[M]`` class indices, extra dimensions folded into the rows (reference :439-440).
+    For ``[N, C]`` inputs this is a view; inputs with extra dimensions are transposed by torch."""
+    return preds.transpose(0, 1).reshape(num_classes, -1).T, target.flatten()
+
+
+def _multiclass_precision_recall_curve_update_(
+    preds: Tensor, target: Tensor, num_classes: int, thr_sorted: Tensor, perm: Optional[Tensor],
+    ignore_index: Optional[int], average: Optional[str], confmat: Tensor, scratch: Tensor, err: Tensor,
+) -> None:  # fmt: skip
+    """Binned mode: ``confmat[t, class, class == target, softmax(preds)[class] >= thr_t] += 1`` in place
+    (reference :423-527); ``average="micro"`` folds the classes into one binary ``[T, 2, 2]`` state.
+
+    Rows with ``target == ignore_index`` are dropped and take no part in the softmax decision (:442-448).
+    """
+    rows, tgt = _multiclass_rows(preds, target, num_classes)
+    micro = average == "micro"
+    comparisons = rows.numel() if micro else rows.numel() * num_classes
+    thr = _curve_thresholds_for(rows, thr_sorted, comparisons <= (_LOOP_SWITCH if micro else _MC_VECTOR_SWITCH))
+    labels = 1 if micro else num_classes
+    if num_classes <= kernels.MC_CURVE_MAX_CLASSES:
+        kernels.mc_curve_update(rows, tgt, thr, ignore_index, micro, scratch, err)
+    else:
+        # rows wider than the register-resident kernel: torch's own softmax (its wide-row kernel has another
+        # reduction order) behind the device-side range decision, then the multilabel binning with one-hot targets
+        probs = kernels.softmax_normalize(rows, tgt, ignore_index)
+        keep = None if ignore_index is None else tgt != ignore_index
+        safe = tgt if keep is None else torch.where(keep, tgt, torch.zeros_like(tgt))
+        hot = torch.nn.functional.one_hot(safe.long().clamp(0, num_classes - 1), num_classes)
+        if keep is not None:
+            hot = torch.where(keep.unsqueeze(1), hot, torch.full_like(hot, ignore_index))
+        if micro:
+            kernels.thresh_bin_update(probs.flatten(), hot.flatten(), 1, True, thr, False, ignore_index, False, scratch, err)
+        else:
+            kernels.thresh_bin_update(probs, hot, num_classes, False, thr, False, ignore_index, False, scratch, err)
+    kernels.thresh_bin_finalize(scratch, labels, thr.numel(), perm, kernels.TB_CURVE, (confmat,))
+
+
+def _multiclass_precision_recall_curve_format_exact(
+    preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int], average: Optional[str],
+    validate_args: bool = False,
+) -> Tuple[Tensor, Tensor]:  # fmt: skip
+    """Exact mode: the ``[M', C]`` (conditionally softmaxed) scores and ``[M']`` targets to store; ``micro``
+    stores them flattened with one-hot targets (reference :439-456)."""
+    rows, tgt = _multiclass_rows(preds, target, num_classes)
+    if ignore_index is not None:
+        keep = tgt != ignore_index  # boolean-mask indexing: data-dependent size, synchronises like the reference
+        rows, tgt = rows[keep], tgt[keep]
+    if validate_args and bool(((tgt < 0) | (tgt >= num_classes)).any()):
+        raise RuntimeError(
+            "Detected more unique values in `target` than `num_classes`: `target` contains values outside"
+            f" [0, {num_classes}) that are not `ignore_index`."
+        )
+    probs = kernels.softmax_normalize(rows)
+    if average == "micro":
+        return probs.flatten(), torch.nn.functional.one_hot(tgt.long(), num_classes=num_classes).flatten()
+    return probs, tgt
+
+
+def _multiclass_state_functional(
+    preds: Tensor, target: Tensor, num_classes: int, thresholds: Optional[Tensor], ignore_index: Optional[int],
+    average: Optional[str], validate_args: bool, where: str,
+) -> Union[Tensor, Tuple[Tensor, Tensor]]:  # fmt: skip
+    dev = preds.device
+    if thresholds is None:
+        return _multiclass_precision_recall_curve_format_exact(
+            preds, target, num_classes, ignore_index, average, validate_args
+        )
+    err = torch.zeros(1, dtype=torch.int32, device=dev)
+    thr_sorted, perm = _threshold_plan(thresholds, dev)
+    labels = 1 if average == "micro" else num_classes
+    shape = (len(thresholds), 2, 2) if average == "micro" else (len(thresholds), num_classes, 2, 2)
+    state = torch.zeros(*shape, dtype=torch.long, device=dev)
+    scratch = torch.zeros(kernels.thresh_bin_scratch_numel(labels, len(thresholds)), dtype=torch.long, device=dev)
+    _multiclass_precision_recall_curve_update_(
+        preds, target, num_classes, thr_sorted, perm, ignore_index, average, state, scratch, err
+    )
+    if validate_args:
+        kernels.raise_on_error_word(err, where)
+    return state
+
+
+def _macro_curve(
+    xs: Sequence[Tensor], ys: Sequence[Tensor], thresholds: Tensor, descending_thresholds: bool
+) -> Tuple[Tensor, Tensor, Tensor]:
+    """``average="macro"``: all classes' x values merged and sorted, y = mean of the per-class curves interpolated
+    there (reference :557-571, roc.py:189-200)."""
+    merged = torch.cat(list(xs), 0).sort().values
+    mean_y = torch.zeros_like(merged)
+    for x, y in zip(xs, ys):
+        mean_y += interp(merged, x, y)
+    mean_y /= len(xs)
+    return merged, mean_y, thresholds.sort(descending=descending_thresholds).values
+
+
+def _multiclass_precision_recall_curve_compute(
+    state: Union[Tensor, Tuple[Tensor, Tensor]], num_classes: int, thresholds: Optional[Tensor],
+    average: Optional[str] = None,
+) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:  # fmt: skip
+    """Reference: precision_recall_curve.py:530-575."""
+    if average == "micro":
+        return _binary_precision_recall_curve_compute(state, thresholds)
+    binned = isinstance(state, Tensor) and thresholds is not None
+    if binned:
+        precision, recall = _curve_from_counts(
+            state[:, :, 1, 1], state[:, :, 0, 1], state[:, :, 1, 0], (1, num_classes)
+        )
+        precision, recall = precision.T, recall.T
+        if average == "macro":
+            return _macro_curve(list(precision), list(recall), thresholds.repeat(num_classes), False)
+        return precision, recall, thresholds
+    fps, tps, thr = kernels.clf_curves(state[0], state[1], None, class_targets=True)
+    curves = [_exact_pr_from_curve(fps[i], tps[i], thr[i]) for i in range(num_classes)]
+    precision_list, recall_list, thres_list = ([c[k] for c in curves] for k in range(3))
+    if average == "macro":
+        return _macro_curve(precision_list, recall_list, torch.cat(thres_list, 0), False)
+    return precision_list, recall_list, thres_list
+
+
+def multiclass_precision_recall_curve(
+    preds: Tensor,
+    target: Tensor,
+    num_classes: int,
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    average: Optional[Literal["micro", "macro"]] = None,
+    ignore_index: Optional[int] = None,
+    validate_args: bool = True,
+) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+    """One-vs-rest ``(precision, recall, thresholds)`` per class (reference :578-689)."""
+    if validate_args:
+        _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index, average)
+        _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
+    thresholds = _adjust_threshold_arg(thresholds, preds.device)
+    state = _multiclass_state_functional(preds, target, num_classes, thresholds, ignore_index, average,
+                                         validate_args, "multiclass_precision_recall_curve")
+    return _multiclass_precision_recall_curve_compute(state, num_classes, thresholds, average)
+
+
 def precision_recall_curve(
     preds: Tensor,
     target: Tensor,
@@ -344,7 +527,11 @@ def precision_recall_curve(
     if task == ClassificationTask.BINARY:
         return binary_precision_recall_curve(preds, target, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTICLASS:
-        raise NotImplementedError("multiclass precision-recall curves are not part of the sm_100a update path yet")
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        return multiclass_precision_recall_curve(
+            preds, target, num_classes, thresholds, None, ignore_index, validate_args
+        )
     if task == ClassificationTask.MULTILABEL:
         if not isinstance(num_labels, int):
             raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

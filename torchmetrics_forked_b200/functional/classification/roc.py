@@ -14,11 +14,16 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_arg_validation,
     _binary_precision_recall_curve_tensor_validation,
     _binary_state_functional,
+    _macro_curve,
+    _multiclass_precision_recall_curve_arg_validation,
+    _multiclass_precision_recall_curve_tensor_validation,
+    _multiclass_state_functional,
     _multilabel_clf_curves,
     _multilabel_precision_recall_curve_arg_validation,
     _multilabel_precision_recall_curve_tensor_validation,
     _multilabel_state_functional,
 )
+from torchmetrics_forked_b200 import kernels
 from torchmetrics_forked_b200.utilities.compute import _safe_divide
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 from torchmetrics_forked_b200.utilities.prints import rank_zero_warn
@@ -78,6 +83,48 @@ def binary_roc(
     return _binary_roc_compute(state, thresholds)
 
 
+def _multiclass_roc_compute(
+    state: Union[Tensor, Tuple[Tensor, Tensor]], num_classes: int, thresholds: Optional[Tensor],
+    average: Optional[str] = None,
+) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:  # fmt: skip
+    """One-vs-rest ROC per class (reference :162-204)."""
+    if average == "micro":
+        return _binary_roc_compute(state, thresholds, pos_label=1)
+    if isinstance(state, Tensor) and thresholds is not None:
+        tps, fps, fns, tns = state[:, :, 1, 1], state[:, :, 0, 1], state[:, :, 1, 0], state[:, :, 0, 0]
+        tpr = _safe_divide(tps, tps + fns).flip(0).T
+        fpr = _safe_divide(fps, fps + tns).flip(0).T
+        thres = thresholds.flip(0)
+        if average == "macro":
+            return _macro_curve(list(fpr), list(tpr), thres.repeat(num_classes), True)
+        return fpr, tpr, thres
+    fps_l, tps_l, thr_l = kernels.clf_curves(state[0], state[1], None, class_targets=True)
+    curves = [_roc_from_curve(fps_l[i], tps_l[i], thr_l[i]) for i in range(num_classes)]
+    fpr, tpr, thres = ([c[k] for c in curves] for k in range(3))
+    if average == "macro":
+        return _macro_curve(fpr, tpr, torch.cat(thres, 0), True)
+    return fpr, tpr, thres
+
+
+def multiclass_roc(
+    preds: Tensor,
+    target: Tensor,
+    num_classes: int,
+    thresholds: Optional[Union[int, List[float], Tensor]] = None,
+    average: Optional[Literal["micro", "macro"]] = None,
+    ignore_index: Optional[int] = None,
+    validate_args: bool = True,
+) -> Union[Tuple[Tensor, Tensor, Tensor], Tuple[List[Tensor], List[Tensor], List[Tensor]]]:
+    """Per-class ``(fpr, tpr, thresholds)`` (reference :207-326)."""
+    if validate_args:
+        _multiclass_precision_recall_curve_arg_validation(num_classes, thresholds, ignore_index, average)
+        _multiclass_precision_recall_curve_tensor_validation(preds, target, num_classes, ignore_index)
+    thresholds = _adjust_threshold_arg(thresholds, preds.device)
+    state = _multiclass_state_functional(preds, target, num_classes, thresholds, ignore_index, average,
+                                         validate_args, "multiclass_roc")
+    return _multiclass_roc_compute(state, num_classes, thresholds, average)
+
+
 def _multilabel_roc_compute(
     state: Union[Tensor, Tuple[Tensor, Tensor]],
     num_labels: int,
@@ -132,7 +179,9 @@ def roc(
     if task == ClassificationTask.BINARY:
         return binary_roc(preds, target, thresholds, ignore_index, validate_args)
     if task == ClassificationTask.MULTICLASS:
-        raise NotImplementedError("multiclass ROC is not part of the sm_100a update path yet")
+        if not isinstance(num_classes, int):
+            raise ValueError(f"`num_classes` is expected to be `int` but `{type(num_classes)} was passed.`")
+        return multiclass_roc(preds, target, num_classes, thresholds, None, ignore_index, validate_args)
     if task == ClassificationTask.MULTILABEL:
         if not isinstance(num_labels, int):
             raise ValueError(f"`num_labels` is expected to be `int` but `{type(num_labels)} was passed.`")

@@ -4,8 +4,8 @@ from torchmetrics_forked_b200.functional.classification._fixed_point import (  #
     fixed_point_family,
 )
 
-(binary_specificity_at_sensitivity, multilabel_specificity_at_sensitivity,
+(binary_specificity_at_sensitivity, multiclass_specificity_at_sensitivity, multilabel_specificity_at_sensitivity,
  specificity_at_sensitivity) = fixed_point_family("specificity_at_sensitivity", "min_sensitivity", None)
-for _f in (binary_specificity_at_sensitivity, multilabel_specificity_at_sensitivity, specificity_at_sensitivity):
+for _f in (binary_specificity_at_sensitivity, multiclass_specificity_at_sensitivity, multilabel_specificity_at_sensitivity, specificity_at_sensitivity):
     _f.__module__ = __name__
 specicity_at_sensitivity = specificity_at_sensitivity  # the reference exports the dispatcher under this spelling

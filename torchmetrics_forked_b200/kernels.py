@@ -201,6 +201,42 @@ def thresh_bin_update(
     nat.check(rc, "tmb_thresh_bin_update")
 
 
+MC_CURVE_MAX_CLASSES = 1024  # row width the fused softmax + binning kernel keeps in registers
+
+
+def mc_curve_update(
+    preds: Tensor,
+    target: Tensor,
+    thresholds: Tensor,
+    ignore_index: Optional[int],
+    micro: bool,
+    scratch: Tensor,
+    err: Tensor,
+) -> None:
+    """One pass of (conditional row softmax +) threshold binning of ``[M, C]`` multiclass scores with one-hot
+    targets ``class == target[row]`` into the int64 ``scratch`` histogram (``C`` labels, or 1 with ``micro``).
+    Follow with :func:`thresh_bin_finalize`."""
+    nat.require_cuda(preds, "preds")
+    nat.require_cuda(target, "target")
+    nat.require_cuda(thresholds, "thresholds")
+    if preds.ndim != 2 or target.ndim != 1 or target.shape[0] != preds.shape[0]:
+        raise ValueError("`preds` must have shape (M, C) and `target` shape (M,)")
+    if thresholds.dtype != torch.float32 or not thresholds.is_contiguous():
+        raise ValueError("`thresholds` must be a contiguous float32 tensor")
+    preds = _as_kernel_input(preds)
+    target = _as_kernel_input(target)
+    if preds.numel() == 0:
+        return
+    has_ign, ign = _ignore_args(ignore_index)
+    with torch.cuda.device(preds.device):
+        rc = nat.lib().tmb_mc_curve_update(
+            nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target), preds.shape[0],
+            preds.shape[1], nat.ptr(thresholds), thresholds.numel(), has_ign, ign, int(micro), nat.ptr(scratch),
+            scratch.numel(), nat.ptr(err), nat.stream_ptr(preds.device),
+        )  # fmt: skip
+    nat.check(rc, "tmb_mc_curve_update")
+
+
 def thresh_bin_finalize(
     scratch: Tensor, num_labels: int, num_thresholds: int, perm: Optional[Tensor], layout: int, out
 ) -> None:
