@@ -268,6 +268,17 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     record("k2_multilabel_curve_T200_2^21x100", lambda: m.update(ml_p, ml_t), nl, nl * L * 12, nl * L * 4, 4)
     del ml_p, ml_t, m
     torch.cuda.empty_cache()
+    # row f2: multiclass binned curves, fused row softmax + binning (MulticlassAUROC(thresholds=200) update)
+    from torchmetrics_forked_b200.classification import MulticlassAUROC
+
+    for rows_mc, C_mc in ((1 << 21, 100), (1 << 24, 10), (1 << 18, 1000)):
+        mc_p = torch.randn(rows_mc, C_mc, generator=g, device=device)
+        mc_t = torch.randint(C_mc, (rows_mc,), generator=g, device=device)
+        m = MulticlassAUROC(C_mc, thresholds=200, validate_args=False).to(device)
+        record(f"f2_multiclass_curve_T200_{rows_mc}x{C_mc}", lambda: m.update(mc_p, mc_t), rows_mc,
+               rows_mc * (C_mc * 4 + 8), rows_mc * C_mc * 4, 4)
+        del mc_p, mc_t, m
+        torch.cuda.empty_cache()
     # config 2 rows through StatScores (three C-bin histograms instead of the C x C matrix)
     r2 = 1 << 20
     p2, t2 = make_cfg2(r2, device, 99)

@@ -13,7 +13,7 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 
 which = sys.argv[1] if len(sys.argv) > 1 else "k1"
-reps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+reps = int(sys.argv[2]) if len(sys.argv) > 2 and which != "f2" else 4
 dev = torch.device("cuda")
 g = torch.Generator(device=dev).manual_seed(0)
 
@@ -53,5 +53,14 @@ elif which == "k3":
     for _ in range(2):
         m.update(torch.randn(n, L, generator=g, device=dev), torch.randint(2, (n, L), generator=g, device=dev))
     print(float(m.compute()))
+elif which == "f2":
+    from torchmetrics_forked_b200.classification import MulticlassAUROC
+
+    n, C = (1 << 21, 100) if len(sys.argv) < 4 else (int(sys.argv[2]), int(sys.argv[3]))
+    p = torch.randn(n, C, generator=g, device=dev)
+    t = torch.randint(C, (n,), generator=g, device=dev)
+    m = MulticlassAUROC(C, thresholds=200, validate_args=False).to(dev)
+    for _ in range(3):
+        m.update(p, t)
 torch.cuda.synchronize()
 print("done", which)

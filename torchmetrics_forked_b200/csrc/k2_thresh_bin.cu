@@ -767,9 +767,9 @@ __global__ void __launch_bounds__(512, 1) k2_multi(TbArgs a) {
 // the CTA-wide [C][2][T+1] histogram in shared memory — the logits are read once, nothing is written but counts.
 // `micro` folds all classes into label 0 (the reference flattens preds and one-hot targets into one binary task).
 // Histograms that do not fit one SM go to global memory with one atomic per element.
-template <int PDT, bool SOFT>
-__global__ void __launch_bounds__(512, 1) k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro,
-                                                     int sh_bins) {
+template <int PDT, bool SOFT, int SLOTS>
+__global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
+    k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro, int sh_bins) {
   extern __shared__ uint32_t sh_u32[];
   if (!pass_enabled(a, SOFT)) return;
   float* sh_pad = (float*)sh_u32;
@@ -785,6 +785,7 @@ __global__ void __launch_bounds__(512, 1) k2_mc_rows(TbArgs a, RowMap rm, int64_
   const int rows_per_warp = 32 >> rm.log2W;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  constexpr int kGroups = (SLOTS + kPer - 1) / kPer;  // bins are taken kPer elements at a time
   bool stop = false, bad_target = false;
   int trip = 0;
   for (int64_t r0 = warp * rows_per_warp; r0 < rows && !stop; r0 += nwarps * rows_per_warp, ++trip) {  // warp-uniform
@@ -794,52 +795,52 @@ __global__ void __launch_bounds__(512, 1) k2_mc_rows(TbArgs a, RowMap rm, int64_
     const bool counted = active && !(a.has_ignore && t == a.ignore);
     if (counted && (t < 0 || t >= C)) bad_target = true;
     const int64_t base = r * C;
-    float e[kSoftmaxSlots];
+    float e[SLOTS];
 #pragma unroll
-    for (int it = 0; it < kSoftmaxSlots; ++it) {
+    for (int it = 0; it < SLOTS; ++it) {
       const int c = it * rm.W + j;
-      e[it] = (it < rm.slots && counted && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
+      e[it] = (counted && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
     }
     if (!SOFT) {
       bool mine = false;
 #pragma unroll
-      for (int it = 0; it < kSoftmaxSlots; ++it)
-        if (it < rm.slots && counted && it * rm.W + j < C) mine |= !(e[it] >= 0.0f && e[it] <= 1.0f);
+      for (int it = 0; it < SLOTS; ++it)
+        if (counted && it * rm.W + j < C) mine |= !(e[it] >= 0.0f && e[it] <= 1.0f);
       if (mine) raise_flag(a);
       stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
       if (stop) break;
     } else {
-      softmax_row_inplace<PDT>(e, rm);
+      softmax_row_inplace<PDT, SLOTS>(e, rm);
     }
 #pragma unroll
-    for (int g0 = 0; g0 < kSoftmaxSlots; g0 += kPer) {
-      if (g0 < rm.slots) {  // warp-uniform
-        Decoded d;
-        d.bad = 0;
-        d.outside = 0;
+    for (int gi = 0; gi < kGroups; ++gi) {
+      Decoded d;
+      d.bad = 0;
+      d.outside = 0;
 #pragma unroll
-        for (int i = 0; i < kPer; ++i) {
-          const int c = (g0 + i) * rm.W + j;
-          const bool valid = counted && (g0 + i) < rm.slots && c < C;
-          d.x[i] = valid ? e[g0 + i] : 0.5f;
-          d.inc[i] = valid ? 1u : 0u;
-          d.toff[i] = 0u;
-        }
-        int g[kPer];
-        if (on_grid)
-          batch_bins<PDT, false, true>(bn, d, g);
-        else
-          batch_bins<PDT, false, false>(bn, d, g);
+      for (int i = 0; i < kPer; ++i) {
+        const int it = gi * kPer + i;
+        const int c = it * rm.W + j;
+        const bool valid = it < SLOTS && counted && c < C;
+        d.x[i] = valid ? e[it < SLOTS ? it : 0] : 0.5f;
+        d.inc[i] = valid ? 1u : 0u;
+        d.toff[i] = 0u;
+      }
+      int g[kPer];
+      if (on_grid)
+        batch_bins<PDT, false, true>(bn, d, g);
+      else
+        batch_bins<PDT, false, false>(bn, d, g);
 #pragma unroll
-        for (int i = 0; i < kPer; ++i) {
-          if (d.inc[i]) {
-            const int c = (g0 + i) * rm.W + j;
-            const int bin = ((micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0)) * kbins + g[i];
-            if (sh_bins > 0)
-              atomicAdd(&hist[bin], 1u);
-            else
-              atomicAdd(&gh[bin], 1ULL);
-          }
+      for (int i = 0; i < kPer; ++i) {
+        const int it = gi * kPer + i;
+        if (it < SLOTS && d.inc[i]) {
+          const int c = it * rm.W + j;
+          const int bin = ((micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0)) * kbins + g[i];
+          if (sh_bins > 0)
+            atomicAdd(&hist[bin], 1u);
+          else
+            atomicAdd(&gh[bin], 1ULL);
         }
       }
     }
@@ -1234,17 +1235,23 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
   const bool fits = pad_bytes + bins * 4 <= (int64_t)dev_info().max_smem_optin - 1024;
   const int sh_bins = fits ? (int)bins : 0;
   const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
-  auto ka = k2_mc_rows<PDT, false>;
-  auto kb = k2_mc_rows<PDT, true>;
-  cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  const int block = 512;
-  const int64_t work = (rows * rm.W + block - 1) / block;
-  const int grid = resident_grid(kb, block, smem, work);
-  ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
-  if (int rc = launch_status()) return rc;
-  kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
-  return launch_status();
+  int rc = 0;
+  TMB_DISPATCH_SLOTS(rm.slots, {
+    auto ka = k2_mc_rows<PDT, false, SLOTS>;
+    auto kb = k2_mc_rows<PDT, true, SLOTS>;
+    cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int block = SLOTS <= 8 ? 1024 : 512;
+    const int64_t work = (rows * rm.W + block - 1) / block;
+    const int grid = resident_grid(kb, block, smem, work);
+    ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+    rc = launch_status();
+    if (rc == 0) {
+      kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+      rc = launch_status();
+    }
+  })
+  return rc;
 }
 
 template <int PDT, int TDT>

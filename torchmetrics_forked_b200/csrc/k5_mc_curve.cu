@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restri
 }
 
 // pass B: out = (flag == gen) ? softmax(x, dim=1) : x
-template <int DT>
+template <int DT, int SLOTS>
 __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ x, void* __restrict__ out,
                                                        int64_t rows, int C, RowMap rm,
                                                        const unsigned long long* __restrict__ flag,
@@ -69,17 +69,17 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
     const int64_t r = r0 + sub;
     const bool active = r < rows;
     const int64_t base = r * C;
-    float e[kSoftmaxSlots];
+    float e[SLOTS];
 #pragma unroll
-    for (int it = 0; it < kSoftmaxSlots; ++it) {
+    for (int it = 0; it < SLOTS; ++it) {
       const int c = it * rm.W + j;
-      e[it] = (it < rm.slots && active && c < C) ? load_elem<DT>(x, base + c) : -INFINITY;
+      e[it] = (active && c < C) ? load_elem<DT>(x, base + c) : -INFINITY;
     }
-    if (soft) softmax_row_inplace<DT>(e, rm);
+    if (soft) softmax_row_inplace<DT, SLOTS>(e, rm);
 #pragma unroll
-    for (int it = 0; it < kSoftmaxSlots; ++it) {
+    for (int it = 0; it < SLOTS; ++it) {
       const int c = it * rm.W + j;
-      if (it < rm.slots && active && c < C) store_elem<DT>(out, base + c, e[it]);
+      if (active && c < C) store_elem<DT>(out, base + c, e[it]);
     }
   }
 }
@@ -98,9 +98,11 @@ template <int DT>
 static int launch_softmax_rows(const void* x, void* out, int64_t rows, int C, const unsigned long long* flag,
                                unsigned long long gen, cudaStream_t st) {
   const RowMap rm = row_map(C);
-  auto k = k5_softmax_rows<DT>;
   const int64_t work = (rows * rm.W + 255) / 256;
-  k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, out, rows, C, rm, flag, gen);
+  TMB_DISPATCH_SLOTS(rm.slots, {
+    auto k = k5_softmax_rows<DT, SLOTS>;
+    k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, out, rows, C, rm, flag, gen);
+  })
   return launch_status();
 }
 
