@@ -767,9 +767,16 @@ __global__ void __launch_bounds__(512, 1) k2_multi(TbArgs a) {
 // the CTA-wide [C][2][T+1] histogram in shared memory — the logits are read once, nothing is written but counts.
 // `micro` folds all classes into label 0 (the reference flattens preds and one-hot targets into one binary task).
 // Histograms that do not fit one SM go to global memory with one atomic per element.
+// A lane takes kPer elements per trip through the binning code: SLOTS elements of each of ROWS = kPer / SLOTS rows
+// when a row gives it fewer than kPer (C <= 128), so narrow rows (C = 10: one element per lane and row) still fill
+// the batch and keep ROWS loads in flight.  When the [C][2][T+1] histogram does not fit one SM (C = 1000, T = 200
+// is 1.6 MB) only the lowest `low_k` bins of every (class, target) pair live in shared memory — softmax mass of a
+// wide row sits near 0 — and the rest goes to global memory with one atomic per element.
 template <int PDT, bool SOFT, int SLOTS>
 __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
-    k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro, int sh_bins) {
+    k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro, int sh_bins, int low_k) {
+  constexpr int ROWS = SLOTS < kPer ? kPer / SLOTS : 1;
+  constexpr int kGroups = (SLOTS + kPer - 1) / kPer;
   extern __shared__ uint32_t sh_u32[];
   if (!pass_enabled(a, SOFT)) return;
   float* sh_pad = (float*)sh_u32;
@@ -783,46 +790,72 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   const int lane = threadIdx.x & 31;
   const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
   const int rows_per_warp = 32 >> rm.log2W;
+  const int64_t rows_per_trip = (int64_t)rows_per_warp * ROWS;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  constexpr int kGroups = (SLOTS + kPer - 1) / kPer;  // bins are taken kPer elements at a time
   bool stop = false, bad_target = false;
   int trip = 0;
-  for (int64_t r0 = warp * rows_per_warp; r0 < rows && !stop; r0 += nwarps * rows_per_warp, ++trip) {  // warp-uniform
-    const int64_t r = r0 + sub;
-    const bool active = r < rows;
-    const int64_t t = active ? load_label(a.target, a.tdt, r) : 0;
-    const bool counted = active && !(a.has_ignore && t == a.ignore);
-    if (counted && (t < 0 || t >= C)) bad_target = true;
-    const int64_t base = r * C;
-    float e[SLOTS];
+  auto count = [&](int c, bool hot, int k) {
+    const int pair = (micro ? 0 : c) * 2 + (hot ? 1 : 0);
+    if (low_k == 0) {
+      atomicAdd(&hist[pair * kbins + k], 1u);  // the whole histogram is in shared memory
+    } else if (k < low_k) {
+      atomicAdd(&hist[pair * low_k + k], 1u);
+    } else {
+      atomicAdd(&gh[pair * kbins + k], 1ULL);
+    }
+  };
+  for (int64_t r0 = warp * rows_per_trip; r0 < rows && !stop; r0 += nwarps * rows_per_trip, ++trip) {  // warp-uniform
+    {  // the rows of this warp's NEXT trip are one contiguous region of at most 4 KB: one L2 prefetch per 128-byte
+       // line, so that the register loads of that trip wait for L2, not for DRAM (half of all stall samples)
+      const int64_t rn = r0 + nwarps * rows_per_trip;
+      const int64_t first = rn * C * Elem<PDT>::kBytes, end = min(rn + rows_per_trip, rows) * C * Elem<PDT>::kBytes;
+      const int64_t mine = (first & ~(int64_t)127) + (int64_t)lane * 128;
+      if (rn < rows && mine < end) prefetch_l2((const char*)a.preds + mine);
+    }
+    float e[ROWS][SLOTS];
+    int64_t t[ROWS];
+    bool counted[ROWS];
 #pragma unroll
-    for (int it = 0; it < SLOTS; ++it) {
-      const int c = it * rm.W + j;
-      e[it] = (counted && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
+    for (int q = 0; q < ROWS; ++q) {
+      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
+      const bool active = r < rows;
+      t[q] = active ? load_label(a.target, a.tdt, r) : 0;
+      counted[q] = active && !(a.has_ignore && t[q] == a.ignore);
+      if (counted[q] && (t[q] < 0 || t[q] >= C)) bad_target = true;
+      const int64_t base = r * C;
+#pragma unroll
+      for (int it = 0; it < SLOTS; ++it) {
+        const int c = it * rm.W + j;
+        e[q][it] = (counted[q] && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
+      }
     }
     if (!SOFT) {
       bool mine = false;
 #pragma unroll
-      for (int it = 0; it < SLOTS; ++it)
-        if (counted && it * rm.W + j < C) mine |= !(e[it] >= 0.0f && e[it] <= 1.0f);
+      for (int q = 0; q < ROWS; ++q)
+#pragma unroll
+        for (int it = 0; it < SLOTS; ++it)
+          if (counted[q] && it * rm.W + j < C) mine |= !(e[q][it] >= 0.0f && e[q][it] <= 1.0f);
       if (mine) raise_flag(a);
       stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
       if (stop) break;
     } else {
-      softmax_row_inplace<PDT, SLOTS>(e, rm);
+#pragma unroll
+      for (int q = 0; q < ROWS; ++q) softmax_row_inplace<PDT, SLOTS>(e[q], rm);
     }
 #pragma unroll
     for (int gi = 0; gi < kGroups; ++gi) {
       Decoded d;
       d.bad = 0;
       d.outside = 0;
+      // element i of the batch: (row q, slot it) — ROWS > 1 means SLOTS < kPer and one group
 #pragma unroll
       for (int i = 0; i < kPer; ++i) {
-        const int it = gi * kPer + i;
-        const int c = it * rm.W + j;
-        const bool valid = it < SLOTS && counted && c < C;
-        d.x[i] = valid ? e[it < SLOTS ? it : 0] : 0.5f;
+        const int q = ROWS > 1 ? i / SLOTS : 0;
+        const int it = ROWS > 1 ? i % SLOTS : gi * kPer + i;
+        const bool valid = it < SLOTS && counted[q] && it * rm.W + j < C;
+        d.x[i] = valid ? e[q][it < SLOTS ? it : 0] : 0.5f;
         d.inc[i] = valid ? 1u : 0u;
         d.toff[i] = 0u;
       }
@@ -833,14 +866,11 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
         batch_bins<PDT, false, false>(bn, d, g);
 #pragma unroll
       for (int i = 0; i < kPer; ++i) {
-        const int it = gi * kPer + i;
+        const int q = ROWS > 1 ? i / SLOTS : 0;
+        const int it = ROWS > 1 ? i % SLOTS : gi * kPer + i;
         if (it < SLOTS && d.inc[i]) {
           const int c = it * rm.W + j;
-          const int bin = ((micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0)) * kbins + g[i];
-          if (sh_bins > 0)
-            atomicAdd(&hist[bin], 1u);
-          else
-            atomicAdd(&gh[bin], 1ULL);
+          count(c, c == (int)t[q], g[i]);
         }
       }
     }
@@ -851,7 +881,10 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   if (dead || (!SOFT && flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
     const uint32_t v = hist[i];
-    if (v) atomicAdd(&gh[i], (unsigned long long)v);
+    if (v) {
+      const int64_t dst = low_k == 0 ? (int64_t)i : (int64_t)(i / low_k) * kbins + (i % low_k);
+      atomicAdd(&gh[dst], (unsigned long long)v);
+    }
   }
 }
 
@@ -1231,9 +1264,18 @@ template <int PDT>
 static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaStream_t st) {
   const RowMap rm = row_map(C);
   const int64_t pad_bytes = (int64_t)(a.T + 2 + 31) / 32 * 32 * 4;
-  const int64_t bins = (int64_t)a.L * 2 * (a.T + 1);
-  const bool fits = pad_bytes + bins * 4 <= (int64_t)dev_info().max_smem_optin - 1024;
-  const int sh_bins = fits ? (int)bins : 0;
+  const int64_t pairs = (int64_t)a.L * 2, kbins = a.T + 1;
+  const int64_t room = ((int64_t)dev_info().max_smem_optin - 1024 - pad_bytes) / 4;  // 32-bit counters that fit
+  int sh_bins, low_k;
+  if (pairs * kbins <= room) {
+    sh_bins = (int)(pairs * kbins);
+    low_k = 0;
+  } else {
+    low_k = (int)(room / pairs);  // 0 for an absurd class count: everything goes to global memory
+    if (low_k > kbins) low_k = (int)kbins;
+    sh_bins = (int)(pairs * low_k);
+    if (low_k == 0) low_k = -1;  // "nothing in shared memory": k < low_k never holds
+  }
   const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
   int rc = 0;
   TMB_DISPATCH_SLOTS(rm.slots, {
@@ -1242,12 +1284,13 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
     cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     const int block = SLOTS <= 8 ? 1024 : 512;
-    const int64_t work = (rows * rm.W + block - 1) / block;
+    constexpr int kRowsPerLane = SLOTS < kPer ? kPer / SLOTS : 1;
+    const int64_t work = (rows * rm.W / kRowsPerLane + block - 1) / block + 1;
     const int grid = resident_grid(kb, block, smem, work);
-    ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+    ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins, low_k);
     rc = launch_status();
     if (rc == 0) {
-      kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins);
+      kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins, low_k);
       rc = launch_status();
     }
   })
