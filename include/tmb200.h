@@ -86,6 +86,18 @@ int tmb_mc_label_hist(const void* preds, int preds_dtype, const void* target, in
                       int64_t n, int64_t num_classes, int has_ignore, int64_t ignore_index, int mode,
                       int64_t* out, int32_t* err, void* stream);
 
+/* tmb_mc_topk_hist: the top_k > 1 branch of
+ *   _multiclass_stat_scores_update      functional/classification/stat_scores.py:363-393
+ *   select_topk (torch.topk + scatter)  utilities/data.py:115-139
+ * preds [n_rows, num_classes] row-major float scores (2 <= num_classes <= 1024, else TMB_E_LIMIT), target one
+ * integer per row.  Adds into `scratch` (int64 [3 * num_classes], the TMB_MC_STATS layout: rows per target class |
+ * rows with the class among the top_k scores | rows whose target is among its top_k); follow with
+ * tmb_mc_stats_finalize(mode TMB_MC_STATS).  Ties at the k-th score go to the lower class index, NaN ranks highest
+ * (torch.topk's CUDA order).  Rows with target == ignore_index are dropped. */
+int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* target, int target_dtype, int64_t n_rows,
+                     int64_t num_classes, int64_t top_k, int has_ignore, int64_t ignore_index, int64_t* scratch,
+                     int32_t* err, void* stream);
+
 /* Turns the TMB_MC_STATS / TMB_MC_MICRO scratch into `tp/fp/tn/fn += ...`
  * (functional/classification/stat_scores.py:401-404 and :414-418) and re-zeroes the scratch so the
  * next update needs no memset.  tp/fp/tn/fn are int64 [C] (STATS) or [1] (MICRO). */

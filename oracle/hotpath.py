@@ -270,6 +270,41 @@ def multilabel_curve_binned(
     return out
 
 
+# ------------------------------------------------------------------------------------------ top-k stat scores (row f3)
+def topk_sets(rows: Array, k: int) -> Array:
+    """`select_topk` (utilities/data.py:115-139) as a boolean [M, C] membership matrix: the k largest scores of a row,
+    NaN ranking highest, -0.0 below +0.0, ties broken towards the lower class index (what torch.topk's CUDA
+    radix select + gather picks; the CPU order only differs when there IS a tie at the k-th place)."""
+    rows = np.ascontiguousarray(rows, dtype=np.float32)
+    bits = rows.view(np.uint32).astype(np.int64)
+    # torch's radix-select key (TopKTypeConfig<float>::convert): flip all bits of negatives, the sign bit of the
+    # rest, NaN -> all ones; so -0.0 ranks below +0.0
+    key = np.where(bits & 0x80000000, bits ^ 0xFFFFFFFF, bits | 0x80000000)
+    key = np.where(np.isnan(rows), 0xFFFFFFFF, key)
+    order = np.argsort(-key, axis=1, kind="stable")  # stable: equal keys keep ascending class order
+    member = np.zeros(rows.shape, dtype=bool)
+    np.put_along_axis(member, order[:, :k], True, axis=1)
+    return member
+
+
+def multiclass_stat_scores_topk(preds: Array, target: Array, num_classes: int, top_k: int,
+                                ignore_index: Optional[int] = None) -> Tuple[Array, Array, Array, Array]:
+    """`_multiclass_stat_scores_update` with `top_k > 1`, global (stat_scores.py:363-393): k-hot prediction against
+    the one-hot target, per class; rows whose target is ignored leave all four counts."""
+    q = np.moveaxis(np.asarray(preds).astype(np.float32), 1, -1).reshape(-1, num_classes)
+    t = np.asarray(target).astype(np.int64).reshape(-1)
+    if ignore_index is not None:
+        keep = t != ignore_index
+        q, t = q[keep], t[keep]
+    member = topk_sets(q, top_k)
+    hot = t[:, None] == np.arange(num_classes)[None, :]
+    tp = (hot & member).sum(0).astype(np.int64)
+    fn = (hot & ~member).sum(0).astype(np.int64)
+    fp = (~hot & member).sum(0).astype(np.int64)
+    tn = (~hot & ~member).sum(0).astype(np.int64)
+    return tp, fp, tn, fn
+
+
 # ------------------------------------------------------------------------------------------ K5: multiclass curves (row f2)
 def torch_cpu_softmax(x: Array) -> Array:
     """Row softmax with the bits of torch's CPU kernel (what the golden vectors of the CPU reference contain)."""

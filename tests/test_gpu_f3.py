@@ -1,0 +1,89 @@
+"""GPU parity for SURVEY §8 row f3: stat scores with `top_k > 1` (top-k selection kernel) against the reference's
+golden vectors, the oracle, and — for ties and NaNs — torch.topk on the device."""
+import numpy as np
+import pytest
+import torch
+from conftest import golden_names, ignore_of, load_golden
+
+import hotpath as O
+
+pytestmark = pytest.mark.gpu
+AVERAGES = ("micro", "macro", "weighted", "none")
+
+
+@pytest.mark.parametrize("name", golden_names("f3_topk_"))
+def test_topk_golden(name):
+    from torchmetrics_forked_b200 import classification as C
+    from torchmetrics_forked_b200 import functional as F
+
+    c = load_golden(name)
+    nC, k, ign = int(c["num_classes"]), int(c["top_k"]), ignore_of(c)
+    preds, target = torch.from_numpy(c["preds"]).cuda(), torch.from_numpy(c["target"]).cuda()
+    for avg in AVERAGES:
+        got = F.multiclass_stat_scores(preds, target, nC, average=avg, top_k=k, ignore_index=ign)
+        want = c[f"stat_scores_{avg}"]
+        if avg in ("micro", "none"):
+            assert np.array_equal(got.cpu().numpy(), want), (name, avg)
+        else:
+            np.testing.assert_allclose(got.cpu().numpy(), want, rtol=1e-6)
+        for fn in ("accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+            got = getattr(F, f"multiclass_{fn}")(preds, target, nC, average=avg, top_k=k, ignore_index=ign)
+            np.testing.assert_allclose(got.cpu().numpy(), c[f"{fn}_{avg}"], rtol=1e-6, atol=1e-7, err_msg=f"{fn} {avg}")
+    # module API, two updates; the micro state stays per class for top_k > 1 (reference :318-320)
+    m = C.MulticlassAccuracy(nC, top_k=k, average="micro", ignore_index=ign).cuda()
+    s = C.StatScores(task="multiclass", num_classes=nC, top_k=k, average="none", ignore_index=ign).cuda()
+    h = preds.shape[0] // 3
+    for sl in (slice(0, h), slice(h, None)):
+        m.update(preds[sl], target[sl])
+        s.update(preds[sl], target[sl])
+    assert m.tp.shape == (nC,)
+    np.testing.assert_allclose(float(m.compute()), c["accuracy_micro"], rtol=1e-6)
+    assert np.array_equal(s.compute().cpu().numpy(), c["stat_scores_none"])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("C,k", [(2, 2), (5, 2), (33, 7), (100, 5), (1000, 5), (1024, 20)])
+def test_topk_ties_and_special_values_follow_torch_topk(C, k, dtype):
+    """Heavily tied scores (16-bit dtypes, quantised values), NaN and +-inf entries: the selected sets must be the
+    ones torch.topk picks on this device, and the oracle's rule (value desc, index asc, NaN first) must agree."""
+    from torchmetrics_forked_b200 import functional as F
+
+    g = torch.Generator().manual_seed(C * 31 + k)
+    n = 3001 if C <= 100 else 257
+    preds = ((torch.randn(n, C, generator=g) * 2).round() / 2).to(dtype)  # few distinct values: ties everywhere
+    preds[0, 0] = float("nan")
+    preds[1, C - 1] = float("inf")
+    preds[2, :] = float("-inf")
+    preds[3, :] = 0.0
+    if C > 1:
+        preds[3, 1] = -0.0
+    target = torch.randint(C, (n,), generator=g)
+    target[::11] = -1
+    dp, dt = preds.cuda(), target.cuda()
+    got = F.multiclass_stat_scores(dp, dt, C, average="none", top_k=k, ignore_index=-1).cpu().numpy()
+    # torch.topk on the device -> k-hot -> the reference's one-hot arithmetic
+    keep = dt != -1
+    member = torch.zeros(n, C, dtype=torch.bool, device="cuda").scatter_(1, dp.topk(k, dim=1).indices, True)[keep]
+    hot = torch.nn.functional.one_hot(dt[keep], C).bool()
+    want = torch.stack([(hot & member).sum(0), (~hot & member).sum(0), (~hot & ~member).sum(0), (hot & ~member).sum(0),
+                        hot.sum(0)], -1).cpu().numpy()
+    assert np.array_equal(got, want), (C, k, dtype)
+    tp, fp, tn, fn = O.multiclass_stat_scores_topk(preds.float().numpy(), target.numpy(), C, k, -1)
+    assert np.array_equal(got, np.stack([tp, fp, tn, fn, tp + fn], -1))
+
+
+def test_topk_argument_handling():
+    from torchmetrics_forked_b200 import classification as C
+    from torchmetrics_forked_b200 import functional as F
+
+    p, t = torch.randn(10, 4).cuda(), torch.randint(4, (10,)).cuda()
+    with pytest.raises(ValueError, match="top_k"):
+        F.multiclass_accuracy(p, t, 4, top_k=5)
+    with pytest.raises(ValueError, match="top_k"):
+        F.multiclass_accuracy(t, t, 4, top_k=2)  # label-valued preds cannot be ranked
+    with pytest.raises(NotImplementedError):
+        C.MulticlassStatScores(4, multidim_average="samplewise")
+    bad = t.clone()
+    bad[0] = 9
+    with pytest.raises(RuntimeError, match="target"):
+        F.multiclass_accuracy(p, bad, 4, top_k=2)

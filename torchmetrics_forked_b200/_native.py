@@ -38,6 +38,10 @@ SIGNATURES = {
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p,
          c_void_p],
     ),
+    "tmb_mc_topk_hist": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p],
+    ),
     "tmb_mc_label_hist": (
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p],

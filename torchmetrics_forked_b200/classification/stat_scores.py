@@ -20,6 +20,7 @@ from torchmetrics_forked_b200.functional.classification.stat_scores import (
     _multiclass_stat_scores_compute,
     _multiclass_stat_scores_tensor_validation,
     _multiclass_stat_scores_update_,
+    _multiclass_stats_mode,
     _multilabel_stat_scores_arg_validation,
     _multilabel_stat_scores_compute,
     _multilabel_stat_scores_tensor_validation,
@@ -136,11 +137,11 @@ class MulticlassStatScores(_AbstractStatScores):
             )
         dev = preds.device
         tp, fp, tn, fn = self._states_on(dev)
-        mode = kernels.MC_MICRO if self.average == "micro" else kernels.MC_STATS
+        mode = _multiclass_stats_mode(self.average, self.top_k)
         scratch = self._scratch_buffer(f"mc{mode}", kernels.mc_scratch_numel(self.num_classes, mode), dev)
         _multiclass_stat_scores_update_(
             preds, target, self.num_classes, self.average, self.ignore_index, tp, fp, tn, fn, scratch,
-            self._error_word(dev),
+            self._error_word(dev), self.top_k,
         )  # fmt: skip
         if self.validate_args:
             self._raise_on_data_errors()

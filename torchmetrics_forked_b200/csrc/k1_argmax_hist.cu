@@ -13,6 +13,7 @@
 // C*sizeof(elem) + sizeof(target), there is no reuse, so the only shared-memory use is the coalescing
 // stage of rows_thread and the privatised histogram for small C.
 #include "common.cuh"
+#include "softmax_rows.cuh"
 
 namespace tmb {
 
@@ -647,6 +648,91 @@ static int launch_strided(const void* preds, const void* target, int tdt, int64_
   return launch_status();
 }
 
+// ---- top-k rows: stat scores with top_k > 1 -------------------------------------------------------
+// _multiclass_stat_scores_update with top_k != 1 (functional/classification/stat_scores.py:363-393): select_topk
+// (utilities/data.py:115-139, torch.topk) turns a row into a k-hot prediction, the target into a one-hot, and
+// per class  tp = target & pred,  fn = target & !pred,  fp = !target & pred,  tn = the rest; rows whose target is
+// ignored drop out of all four.  That is three histograms per batch — T[c] rows with target c, P[c] rows with c
+// among the top k, M[c] rows with target c among the top k — in the layout k1_stats_finalize already reduces
+// (tn = n - T - P + M holds for any k).  A warp keeps the row in registers (element c in lane c % 32, slot c / 32)
+// as the order-preserving unsigned keys of torch's radix select (NaN largest, -0.0 below +0.0) and extracts the maximum k times:
+// lane-local best in slot order, REDUX.MAX over the warp, REDUX.MIN over the indices of the lanes that hold it —
+// i.e. ties go to the lowest class index, the order torch's radix-select gather produces.
+__device__ __forceinline__ uint32_t topk_key(float v) {
+  if (v != v) return 0xffffffffu;
+  const uint32_t b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);  // >= 0x007fffff for every non-NaN: 0 marks "taken / padding"
+}
+
+template <int DT, int SLOTS>
+__global__ void __launch_bounds__(256) k1_rows_topk(const void* __restrict__ preds, const void* __restrict__ target,
+                                                    int tdt, int64_t rows, int C, int top_k, int has_ignore,
+                                                    int64_t ignore, unsigned long long* __restrict__ out, int* err) {
+  extern __shared__ int sh_topk[];  // [3 * C]: T | P | M
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nwarps) {  // warp-uniform
+    const int64_t t = load_label(target, tdt, r);
+    if (has_ignore && t == ignore) continue;
+    if (t < 0 || t >= C) {
+      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      continue;
+    }
+    uint32_t key[SLOTS];
+#pragma unroll
+    for (int it = 0; it < SLOTS; ++it) {
+      const int c = it * 32 + lane;
+      key[it] = c < C ? topk_key(load_elem<DT>(preds, r * C + c)) : 0u;
+    }
+    bool hit = false;
+    for (int round = 0; round < top_k; ++round) {
+      uint32_t best = 0;
+      int best_it = 0;
+#pragma unroll
+      for (int it = 0; it < SLOTS; ++it) {
+        if (key[it] > best) {  // strictly greater: the lowest slot (= lowest class of this lane) wins a tie
+          best = key[it];
+          best_it = it;
+        }
+      }
+      const uint32_t top = __reduce_max_sync(kFull, best);
+      const uint32_t cand = (best == top) ? (uint32_t)(best_it * 32 + lane) : 0xffffffffu;
+      const uint32_t cls = __reduce_min_sync(kFull, cand);
+#pragma unroll
+      for (int it = 0; it < SLOTS; ++it)
+        if ((uint32_t)(it * 32 + lane) == cls) key[it] = 0u;  // taken
+      if (lane == 0) atomicAdd(&sh_topk[C + (int)cls], 1);
+      hit |= (int64_t)cls == t;
+    }
+    if (lane == 0) {
+      atomicAdd(&sh_topk[(int)t], 1);
+      if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const int v = sh_topk[i];
+    if (v) atomicAdd(&out[i], (unsigned long long)v);
+  }
+}
+
+template <int DT>
+static int launch_rows_topk(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
+                            int has_ignore, int64_t ignore, unsigned long long* out, int* err, cudaStream_t st) {
+  const RowMap rm = row_map(C < 32 ? 32 : C);  // always 32 lanes per row here; slots = next_pow2(C) / 32
+  const int smem = 3 * C * (int)sizeof(int);
+  const int64_t work = (rows * 32 + 255) / 256;
+  TMB_DISPATCH_SLOTS(rm.slots, {
+    auto k = k1_rows_topk<DT, SLOTS>;
+    k<<<resident_grid(k, 256, smem, work), 256, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore, ignore,
+                                                           out, err);
+  })
+  return launch_status();
+}
+
 }  // namespace tmb
 
 using namespace tmb;
@@ -680,6 +766,25 @@ extern "C" int tmb_mc_argmax_hist(const void* preds, int preds_dtype, const void
     case TMB_F32: return launch_strided<TMB_F32>(preds, target, target_dtype, n_outer, n_inner, h, st);
     case TMB_F16: return launch_strided<TMB_F16>(preds, target, target_dtype, n_outer, n_inner, h, st);
     default: return launch_strided<TMB_BF16>(preds, target, target_dtype, n_outer, n_inner, h, st);
+  }
+}
+
+extern "C" int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                int64_t n_rows, int64_t num_classes, int64_t top_k, int has_ignore,
+                                int64_t ignore_index, int64_t* scratch, int32_t* err, void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_rows < 0 || num_classes < 2 || top_k < 1 || top_k > num_classes) return TMB_E_SHAPE;
+  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;  // the row lives in 32 registers per lane
+  if (!scratch || !err) return TMB_E_NULL;
+  if (n_rows == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* out = (unsigned long long*)scratch;
+  const int C = (int)num_classes, k = (int)top_k;
+  switch (preds_dtype) {
+    case TMB_F32: return launch_rows_topk<TMB_F32>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
+    case TMB_F16: return launch_rows_topk<TMB_F16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
+    default: return launch_rows_topk<TMB_BF16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
   }
 }
 

@@ -114,7 +114,7 @@ def functional_family(stem: str, reducer: Reducer) -> Tuple[Callable, Callable, 
             _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
         _require_global(multidim_average, top_k)
         tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-            preds, target, num_classes, average, ignore_index, validate_args, f"multiclass_{stem}"
+            preds, target, num_classes, average, ignore_index, validate_args, f"multiclass_{stem}", top_k
         )
         return reducer(tp, fp, tn, fn, average=average, multidim_average=multidim_average)
 

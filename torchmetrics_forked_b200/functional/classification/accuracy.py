@@ -82,7 +82,7 @@ def multiclass_accuracy(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_accuracy"
+        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_accuracy", top_k
     )
     return _accuracy_reduce(tp, fp, tn, fn, average=average, multidim_average=multidim_average)
 

@@ -115,7 +115,7 @@ def multiclass_fbeta_score(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_fbeta_score"
+        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_fbeta_score", top_k
     )
     return _fbeta_reduce(tp, fp, tn, fn, beta, average=average, multidim_average=multidim_average)
 

@@ -10,7 +10,8 @@ fused kernel per task that adds into the int64 ``tp/fp/tn/fn`` states in place:
 * binary / multilabel: conditional sigmoid + strict ``> threshold`` + four counters per label (:90-131,
   :647-681).
 
-``multidim_average="samplewise"`` and ``top_k > 1`` (:363-393) are outside the hot path.
+``top_k > 1`` (:363-393) goes through the top-k selection kernel (row f3); ``multidim_average="samplewise"``
+is not built.
 """
 from typing import Optional, Tuple
 
@@ -37,10 +38,10 @@ def _check_multidim(multidim_average: str) -> None:
 
 
 def _require_global(multidim_average: str, top_k: int = 1) -> None:
-    if multidim_average != "global" or top_k != 1:
+    if multidim_average != "global":
         raise NotImplementedError(
-            "The sm_100a update path covers `multidim_average='global'` with `top_k=1`; the samplewise / top-k"
-            " branches of the reference (functional/classification/stat_scores.py:363-393) are not part of it."
+            "The sm_100a update path covers `multidim_average='global'`; the samplewise branch of the reference"
+            " (functional/classification/stat_scores.py:363-393) is not part of it."
         )
 
 
@@ -162,13 +163,23 @@ def _multiclass_stat_scores_tensor_validation(
             )
 
 
+def _multiclass_stats_mode(average: Optional[str], top_k: int = 1) -> int:
+    """Scalar match counters for ``micro`` with ``top_k == 1`` (reference :394-403), per-class histograms otherwise
+    (``top_k > 1`` keeps per-class states even for ``micro``, classification/stat_scores.py:318-320)."""
+    return kernels.MC_MICRO if (average == "micro" and top_k == 1) else kernels.MC_STATS
+
+
 def _multiclass_stat_scores_update_(
     preds: Tensor, target: Tensor, num_classes: int, average: Optional[str], ignore_index: Optional[int],
-    tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, scratch: Tensor, err: Tensor,
+    tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, scratch: Tensor, err: Tensor, top_k: int = 1,
 ) -> None:  # fmt: skip
-    """In-place ``tp/fp/tn/fn += counts`` for ``top_k=1``, global averaging (reference :325-341, :394-418)."""
-    mode = kernels.MC_MICRO if average == "micro" else kernels.MC_STATS
-    _multiclass_hist_update_(preds, target, num_classes, ignore_index, mode, scratch, err)
+    """In-place ``tp/fp/tn/fn += counts``, global averaging (reference :325-341, :394-418; ``top_k > 1``:
+    :363-393 through the top-k selection kernel)."""
+    mode = _multiclass_stats_mode(average, top_k)
+    if top_k > 1:
+        kernels.mc_topk_hist(preds, target, num_classes, top_k, ignore_index, scratch, err)
+    else:
+        _multiclass_hist_update_(preds, target, num_classes, ignore_index, mode, scratch, err)
     kernels.mc_stats_finalize(scratch, num_classes, mode, tp, fp, tn, fn)
 
 
@@ -195,25 +206,27 @@ def multiclass_stat_scores(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(preds, target, num_classes, average, ignore_index,
-                                                              validate_args, "multiclass_stat_scores")
+                                                              validate_args, "multiclass_stat_scores", top_k)
     return _multiclass_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
 def _multiclass_stat_scores_functional_state(
     preds: Tensor, target: Tensor, num_classes: int, average: Optional[str], ignore_index: Optional[int],
-    validate_args: bool, where: str,
+    validate_args: bool, where: str, top_k: int = 1,
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:  # fmt: skip
     """Fresh zero states + one fused update; shared by the functional accuracy / f-beta entry points."""
     dev = preds.device
-    size = 1 if average == "micro" else num_classes
+    mode = _multiclass_stats_mode(average, top_k)
+    size = 1 if mode == kernels.MC_MICRO else num_classes
     tp, fp, tn, fn = (torch.zeros(size, dtype=torch.long, device=dev) for _ in range(4))
-    mode = kernels.MC_MICRO if average == "micro" else kernels.MC_STATS
     scratch = torch.zeros(kernels.mc_scratch_numel(num_classes, mode), dtype=torch.long, device=dev)
     err = torch.zeros(1, dtype=torch.int32, device=dev)
-    _multiclass_stat_scores_update_(preds, target, num_classes, average, ignore_index, tp, fp, tn, fn, scratch, err)
+    _multiclass_stat_scores_update_(
+        preds, target, num_classes, average, ignore_index, tp, fp, tn, fn, scratch, err, top_k
+    )
     if validate_args:
         kernels.raise_on_error_word(err, where)
-    if average == "micro":
+    if mode == kernels.MC_MICRO:
         tp, fp, tn, fn = tp.squeeze(0), fp.squeeze(0), tn.squeeze(0), fn.squeeze(0)
     return tp, fp, tn, fn
 

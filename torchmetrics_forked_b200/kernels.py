@@ -75,6 +75,38 @@ def mc_argmax_hist(
     nat.check(rc, "tmb_mc_argmax_hist")
 
 
+TOPK_MAX_CLASSES = 1024  # row width the top-k kernel keeps in registers
+
+
+def mc_topk_hist(
+    preds: Tensor, target: Tensor, num_classes: int, top_k: int, ignore_index: Optional[int], out: Tensor, err: Tensor
+) -> None:
+    """Top-k selection over dim 1 of float ``preds [N, C, ...]`` + the three ``MC_STATS`` histograms against
+    ``target [N, ...]`` (rows per target class | rows with the class in the top k | hits), added into ``out``."""
+    nat.require_cuda(preds, "preds")
+    nat.require_cuda(target, "target")
+    nat.require_cuda(out, "state")
+    if preds.ndim < 2 or preds.shape[1] != num_classes or not preds.is_floating_point():
+        raise ValueError("`top_k > 1` needs float `preds` of shape (N, C, ...) with C equal to `num_classes`")
+    if num_classes > TOPK_MAX_CLASSES:
+        raise NotImplementedError(f"`top_k > 1` is built for up to {TOPK_MAX_CLASSES} classes, got {num_classes}")
+    if preds.ndim > 2:  # extra dimensions become rows (torch transposes; the reference's one-hot does the same)
+        preds = preds.movedim(1, -1).reshape(-1, num_classes)
+    preds = _as_kernel_input(preds)
+    target = _as_kernel_input(target.reshape(-1))
+    if target.numel() != preds.shape[0]:
+        raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+    if preds.shape[0] == 0:
+        return
+    has_ign, ign = _ignore_args(ignore_index)
+    with torch.cuda.device(preds.device):
+        rc = nat.lib().tmb_mc_topk_hist(
+            nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target), preds.shape[0],
+            int(num_classes), int(top_k), has_ign, ign, nat.ptr(out), nat.ptr(err), nat.stream_ptr(preds.device),
+        )  # fmt: skip
+    nat.check(rc, "tmb_mc_topk_hist")
+
+
 def mc_label_hist(
     preds: Tensor,
     target: Tensor,
