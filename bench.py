@@ -268,6 +268,15 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     record("k2_multilabel_curve_T200_2^21x100", lambda: m.update(ml_p, ml_t), nl, nl * L * 12, nl * L * 4, 4)
     del ml_p, ml_t, m
     torch.cuda.empty_cache()
+    # row f3: top-5 accuracy at the config-2 row shape (bf16 [2^20, 1000])
+    from torchmetrics_forked_b200.classification import MulticlassAccuracy
+
+    r5 = 1 << 20
+    p5, t5 = make_cfg2(r5, device, 77)
+    m = MulticlassAccuracy(C2_CLASSES, top_k=5, average="micro", validate_args=False).to(device)
+    record("f3_top5_accuracy_2^20_rows", lambda: m.update(p5, t5), r5, r5 * 2008, r5 * 2000, 2)
+    del p5, t5, m
+    torch.cuda.empty_cache()
     # row f2: multiclass binned curves, fused row softmax + binning (MulticlassAUROC(thresholds=200) update)
     from torchmetrics_forked_b200.classification import MulticlassAUROC
 

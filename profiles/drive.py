@@ -62,5 +62,14 @@ elif which == "f2":
     m = MulticlassAUROC(C, thresholds=200, validate_args=False).to(dev)
     for _ in range(3):
         m.update(p, t)
+elif which == "f3":
+    from torchmetrics_forked_b200.classification import MulticlassAccuracy
+
+    rows = 1 << 20
+    t = torch.randint(1000, (rows,), generator=g, device=dev)
+    p = torch.randn(rows, 1000, generator=g, device=dev).bfloat16()
+    m = MulticlassAccuracy(1000, top_k=5, average="micro", validate_args=False).to(dev)
+    for _ in range(3):
+        m.update(p, t)
 torch.cuda.synchronize()
 print("done", which)

@@ -675,6 +675,12 @@ __global__ void __launch_bounds__(256) k1_rows_topk(const void* __restrict__ pre
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   for (int64_t r = warp; r < rows; r += nwarps) {  // warp-uniform
+    {  // this warp's next row -> L2 (one request per 128-byte line): its register loads then wait for L2, not DRAM
+      const int64_t rn = r + nwarps;
+      const int64_t first = rn * C * Elem<DT>::kBytes, end = first + (int64_t)C * Elem<DT>::kBytes;
+      const int64_t mine = (first & ~(int64_t)127) + (int64_t)lane * 128;
+      if (rn < rows && mine < end) prefetch_l2((const char*)preds + mine);
+    }
     const int64_t t = load_label(target, tdt, r);
     if (has_ignore && t == ignore) continue;
     if (t < 0 || t >= C) {
