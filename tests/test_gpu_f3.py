@@ -42,7 +42,7 @@ def test_topk_golden(name):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16, torch.float16])
-@pytest.mark.parametrize("C,k", [(2, 2), (5, 2), (33, 7), (100, 5), (1000, 5), (1024, 20)])
+@pytest.mark.parametrize("C,k", [(2, 2), (5, 2), (8, 3), (33, 7), (100, 5), (264, 9), (520, 5), (1000, 5), (1024, 20)])
 def test_topk_ties_and_special_values_follow_torch_topk(C, k, dtype):
     """Heavily tied scores (16-bit dtypes, quantised values), NaN and +-inf entries: the selected sets must be the
     ones torch.topk picks on this device, and the oracle's rule (value desc, index asc, NaN first) must agree."""

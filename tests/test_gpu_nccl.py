@@ -46,6 +46,7 @@ def _worker(rank: int, port: int, out_dir: str) -> None:
     from torchmetrics_forked_b200.classification import (
         BinaryPrecisionRecallCurve,
         MulticlassAccuracy,
+        MulticlassAUROC,
         MulticlassConfusionMatrix,
         MultilabelAUROC,
     )
@@ -85,6 +86,22 @@ def _worker(rank: int, port: int, out_dir: str) -> None:
         np.testing.assert_allclose(got, [O.binary_auroc_exact(f, t) for f, t, _ in curves], rtol=1e-5)
         with auroc.sync_context():  # rank-ordered concatenation of the uneven shards
             assert np.array_equal(auroc.preds.cpu().numpy(), cat("ml_preds"))
+        # rows f2 / f3 through the same sync: exact multiclass AUROC over two updates per rank (a list state of
+        # [n, C] chunks and one of [n] class indices), and top-k accuracy (per-class sum states)
+        probs = lambda s: s["mc_preds"][:4000].softmax(1)  # noqa: E731  (in [0,1]: stored as they are)
+        mca = MulticlassAUROC(50, thresholds=None, average="none").to(dev)
+        mine_probs = probs(_shard(rank)).to(dev)
+        mca.update(mine_probs[:1500], mine["mc_target"][:1500])
+        mca.update(mine_probs[1500:], mine["mc_target"][1500:4000])
+        got = mca.compute().cpu().numpy()
+        all_probs = torch.cat([probs(s) for s in every]).numpy()
+        all_t = torch.cat([s["mc_target"][:4000] for s in every]).numpy()
+        want = [O.binary_auroc_exact(f, t) for f, t, _ in O.multiclass_clf_curves(all_probs, all_t)]
+        np.testing.assert_allclose(got, want, rtol=1e-5)
+        top3 = MulticlassAccuracy(50, top_k=3, average="micro").to(dev)
+        top3.update(mine["mc_preds"], mine["mc_target"])
+        tp, fp, tn, fn = O.multiclass_stat_scores_topk(cat("mc_preds"), cat("mc_target"), 50, 3)
+        assert abs(float(top3.compute()) - tp.sum() / (tp.sum() + fn.sum())) < 1e-6
         Path(out_dir, f"ok{rank}").write_text("ok")
     finally:
         dist.destroy_process_group()

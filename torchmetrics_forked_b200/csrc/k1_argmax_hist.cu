@@ -725,12 +725,107 @@ __global__ void __launch_bounds__(256) k1_rows_topk(const void* __restrict__ pre
   }
 }
 
+// 16-bit scores leave 16 spare bits in a 32-bit key: value key in the high half, 0xffff - class in the low half.
+// One integer max per slot then finds value AND lowest class at once, one REDUX.MAX per round finishes the warp,
+// and the row arrives as 16-byte vectors (8 scores each, vector v of the row in lane v % 32) instead of 32 two-byte
+// loads per lane.  Needs C % 8 == 0 (16-byte aligned rows) and C <= 1024; other shapes take k1_rows_topk.
+template <int DT>
+__device__ __forceinline__ uint32_t topk_key16(uint32_t b) {  // b: the raw 16-bit pattern
+  constexpr uint32_t kExpAll = DT == TMB_BF16 ? 0x7f80u : 0x7c00u;
+  if ((b & 0x7fffu) > kExpAll) return 0xffffu;            // NaN ranks highest
+  return (b & 0x8000u) ? (~b & 0xffffu) : (b | 0x8000u);  // torch's TopKTypeConfig<half / bfloat16>::convert
+}
+
+template <int DT, int VECS>
+__global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ preds, const void* __restrict__ target,
+                                                      int tdt, int64_t rows, int C, int top_k, int has_ignore,
+                                                      int64_t ignore, unsigned long long* __restrict__ out, int* err) {
+  extern __shared__ int sh_topk[];  // [3 * C]: T | P | M
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int n_vec = C >> 3;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  uint4 raw[VECS];
+  auto fetch = [&](int64_t r) {
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      const int v = lane + 32 * q;
+      raw[q] = v < n_vec ? ldg_stream16((const char*)preds + (r * C + (int64_t)v * 8) * 2) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  int64_t r = warp;
+  if (r < rows) fetch(r);
+  for (; r < rows; r += nwarps) {  // warp-uniform
+    const int64_t t = load_label(target, tdt, r);
+    uint32_t key[VECS * 8];
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      const int v = lane + 32 * q;
+      const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const uint32_t bits = (e & 1) ? (w[e >> 1] >> 16) : (w[e >> 1] & 0xffffu);
+        const uint32_t idx = (uint32_t)v * 8u + e;
+        key[q * 8 + e] = v < n_vec ? (topk_key16<DT>(bits) << 16) | (0xffffu - idx) : 0u;
+      }
+    }
+    if (r + nwarps < rows) fetch(r + nwarps);  // the next row travels while this one is ranked
+    if (has_ignore && t == ignore) continue;
+    if (t < 0 || t >= C) {
+      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      continue;
+    }
+    bool hit = false;
+    for (int round = 0; round < top_k; ++round) {
+      uint32_t best = 0;
+#pragma unroll
+      for (int i = 0; i < VECS * 8; ++i) best = max(best, key[i]);
+      const uint32_t top = __reduce_max_sync(kFull, best);
+      const int cls = (int)(0xffffu - (top & 0xffffu));
+#pragma unroll
+      for (int i = 0; i < VECS * 8; ++i) key[i] = key[i] == top ? 0u : key[i];  // keys are unique: only the owner's
+      if (lane == 0) atomicAdd(&sh_topk[C + cls], 1);
+      hit |= (int64_t)cls == t;
+    }
+    if (lane == 0) {
+      atomicAdd(&sh_topk[(int)t], 1);
+      if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const int v = sh_topk[i];
+    if (v) atomicAdd(&out[i], (unsigned long long)v);
+  }
+}
+
 template <int DT>
 static int launch_rows_topk(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
                             int has_ignore, int64_t ignore, unsigned long long* out, int* err, cudaStream_t st) {
   const RowMap rm = row_map(C < 32 ? 32 : C);  // always 32 lanes per row here; slots = next_pow2(C) / 32
   const int smem = 3 * C * (int)sizeof(int);
   const int64_t work = (rows * 32 + 255) / 256;
+  if constexpr (DT != TMB_F32) {
+    if (C % 8 == 0 && (((uintptr_t)preds) & 15) == 0) {  // 16-byte aligned rows: packed keys, vector loads
+      const int vecs = (C / 8 + 31) / 32;  // 16-byte vectors per lane: 1 .. 4
+#define TMB_LAUNCH_TOPK16(V)                                                                                   \
+  {                                                                                                            \
+    auto k = k1_rows_topk16<DT, V>;                                                                            \
+    k<<<resident_grid(k, 256, smem, work), 256, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore,   \
+                                                           ignore, out, err);                                 \
+  }
+      switch (vecs) {
+        case 1: TMB_LAUNCH_TOPK16(1) break;
+        case 2: TMB_LAUNCH_TOPK16(2) break;
+        case 3: TMB_LAUNCH_TOPK16(3) break;
+        default: TMB_LAUNCH_TOPK16(4) break;
+      }
+#undef TMB_LAUNCH_TOPK16
+      return launch_status();
+    }
+  }
   TMB_DISPATCH_SLOTS(rm.slots, {
     auto k = k1_rows_topk<DT, SLOTS>;
     k<<<resident_grid(k, 256, smem, work), 256, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore, ignore,
