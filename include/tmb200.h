@@ -58,6 +58,7 @@ extern "C" {
 #define TMB_MC_CONFMAT 0 /* out = int64 state [C, C], row = target, col = pred                    */
 #define TMB_MC_STATS 1   /* out = int64 scratch [3C]: hist_target[C] hist_pred[C] match[C]        */
 #define TMB_MC_MICRO 2   /* out = int64 scratch [2]: number of matches, number of counted samples */
+#define TMB_MC_BOTH 3    /* out = int64 scratch [C*C + 3C]: the batch's confusion matrix, then the STATS layout */
 
 /* Library / build identification: returns the compiled-for SM (100) and writes nothing. */
 int tmb_build_arch(void);
@@ -103,6 +104,17 @@ int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* target, int
  * next update needs no memset.  tp/fp/tn/fn are int64 [C] (STATS) or [1] (MICRO). */
 int tmb_mc_stats_finalize(int64_t* scratch, int64_t num_classes, int mode, int64_t* tp, int64_t* fp,
                           int64_t* tn, int64_t* fn, void* stream);
+
+/* One argmax for a whole MetricCollection (collections.py:200-226 calls every compute group's
+ * update, so Accuracy + ConfusionMatrix read the logits twice and run argmax twice): tmb_mc_argmax_hist /
+ * tmb_mc_label_hist with mode TMB_MC_BOTH fill one scratch, then
+ *   tmb_mc_shared_confmat  adds scratch[0 .. C*C) into the int64 [C, C] confusion-matrix state and zeroes it;
+ *   tmb_mc_shared_stats    adds the stat scores into tp/fp/tn/fn — int64 [C], or [1] summed over classes when
+ *                          micro != 0 (functional/classification/stat_scores.py:394-418) — once per subscribing
+ *                          metric; pass clear != 0 on the last call to zero the histograms. */
+int tmb_mc_shared_confmat(int64_t* scratch, int64_t num_classes, int64_t* confmat, void* stream);
+int tmb_mc_shared_stats(int64_t* scratch, int64_t num_classes, int micro, int clear, int64_t* tp, int64_t* fp,
+                        int64_t* tn, int64_t* fn, void* stream);
 
 /* Scratch size in bytes for a mode (0 for TMB_MC_CONFMAT). Host only. */
 int64_t tmb_mc_scratch_bytes(int64_t num_classes, int mode);

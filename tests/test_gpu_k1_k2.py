@@ -599,3 +599,54 @@ def test_multilabel_curve_shared_histogram_kernel(L, kind, F):
                                              sigmoid_fn=lambda a, d=pdtype: torch.from_numpy(a).to(d).cuda().sigmoid().float().cpu().numpy())
             want = part if want is None else want + part
         assert np.array_equal(m.confmat.cpu().numpy(), want), (L, kind, tdtype, pdtype)
+
+
+@pytest.mark.parametrize("case", ["logits", "labels", "strided_bf16", "ignore", "wide"])
+def test_collection_shares_one_argmax(case):
+    """a confusion-matrix family head and the stat-score family heads of a MetricCollection are
+    fed by ONE pass over the logits (mode TMB_MC_BOTH + the shared finalize kernels).  Every state must equal the
+    state of the same metric updated on its own, bit for bit; data errors still surface; other metrics of the
+    collection are untouched."""
+    from torchmetrics_forked_b200 import MetricCollection
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(77)
+    C = 300 if case == "wide" else 7
+    ign = 2 if case == "ignore" else None
+
+    def make():
+        return [M.MulticlassAccuracy(C, average="micro", ignore_index=ign), M.MulticlassF1Score(C, average="macro", ignore_index=ign),
+                M.MulticlassRecall(C, average="none", ignore_index=ign), M.MulticlassConfusionMatrix(C, ignore_index=ign),
+                M.MulticlassJaccardIndex(C, ignore_index=ign), M.MulticlassAccuracy(C, top_k=2 if case != "labels" else 1, ignore_index=ign)]
+
+    names = ["acc", "f1", "rec", "cm", "iou", "top2"]
+    coll = MetricCollection(dict(zip(names, make()))).cuda()
+    alone = {k: m.cuda() for k, m in zip(names, make())}
+    for step in range(4):
+        if case == "labels":
+            preds, target = torch.randint(C, (501,), generator=g), torch.randint(C, (501,), generator=g)
+        elif case == "strided_bf16":
+            preds, target = torch.randn(6, C, 5, 9, generator=g).bfloat16(), torch.randint(C, (6, 5, 9), generator=g)
+        else:
+            preds, target = torch.randn(1003, C, generator=g), torch.randint(C, (1003,), generator=g)
+        coll.update(preds.cuda(), target.cuda())
+        for m in alone.values():
+            m.update(preds.cuda(), target.cuda())
+        if step == 0:
+            continue
+        plan = coll._shared_plan_cache
+        assert plan is not None and plan[0] == "cm" and sorted(plan[1]) == (["acc", "f1"] if case != "labels" else ["acc", "f1"])
+    # "rec" (average none) shares f1's [C] states, "iou" shares cm's, "top2" is its own group (top_k = 2)
+    for k in names:
+        a, b = coll[k], alone[k]
+        for state in a._defaults:
+            assert torch.equal(getattr(a, state), getattr(b, state)), (case, k, state)
+        assert a._update_count == b._update_count == 4
+    out = coll.compute()
+    for k in names:
+        assert torch.equal(out[k], alone[k].compute()), (case, k)
+    # a bad target is still reported, by whichever participant validates
+    bad_p, bad_t = (torch.randint(C, (10,)), torch.full((10,), C)) if case == "labels" else (torch.randn(10, C), torch.full((10,), C))
+    if case != "strided_bf16":
+        with pytest.raises(RuntimeError, match="target"):
+            coll.update(bad_p.cuda(), bad_t.cuda())

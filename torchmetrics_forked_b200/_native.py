@@ -18,7 +18,7 @@ c_void_p, c_int, c_int64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64
 FLOAT_CODES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 LABEL_CODES = {torch.int64: 0, torch.int32: 1, torch.int16: 2, torch.uint8: 3, torch.bool: 3, torch.int8: 4}
 
-MC_CONFMAT, MC_STATS, MC_MICRO = 0, 1, 2
+MC_CONFMAT, MC_STATS, MC_MICRO, MC_BOTH = 0, 1, 2, 3
 ERR_TARGET_RANGE, ERR_PREDS_RANGE, ERR_TARGET_BINARY, ERR_SCORE_RANGE = 1, 2, 4, 8
 
 _ARG_ERRORS = {
@@ -37,6 +37,10 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p,
          c_void_p],
+    ),
+    "tmb_mc_shared_confmat": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "tmb_mc_shared_stats": (
+        c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
     ),
     "tmb_mc_topk_hist": (
         c_int,

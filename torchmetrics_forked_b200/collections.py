@@ -59,6 +59,7 @@ class MetricCollection(ModuleDict):
         self._enable_compute_groups = compute_groups
         self._groups_checked: bool = False
         self._state_is_copy: bool = False
+        self._shared_plan_cache: Any = "unset"  # see _shared_argmax_plan; recomputed whenever the groups change
         self.add_metrics(metrics, *additional_metrics)
 
     # ------------------------------------------------------------------ the four verbs
@@ -70,9 +71,11 @@ class MetricCollection(ModuleDict):
     def update(self, *args: Any, **kwargs: Any) -> None:
         """``update`` of every metric (of one member per compute group once groups are known)."""
         if self._groups_checked:
+            shared = self._shared_argmax_update(args, kwargs)
             for members in self._groups.values():
                 head = getattr(self, members[0])
-                head.update(*args, **head._filter_kwargs(**kwargs))
+                if members[0] not in shared:
+                    head.update(*args, **head._filter_kwargs(**kwargs))
                 # the followers see the new state through the shared tensors, so their cached results are
                 # stale too (the 1.3.0dev reference keeps serving the old value here; deliberate deviation)
                 for name in members[1:]:
@@ -97,6 +100,83 @@ class MetricCollection(ModuleDict):
             m.reset()
         if self._enable_compute_groups and self._groups_checked:
             self._compute_groups_create_state_ref()
+
+    # ------------------------------------------------------------------ one argmax per collection
+    def _shared_argmax_plan(self) -> Optional[Tuple[str, List[str]]]:
+        """``(confusion-matrix head, [stat-score heads])`` that can be fed by ONE pass over the logits.
+
+        The reference updates every compute group separately (collections.py:200-226), so e.g. ``Accuracy`` +
+        ``ConfusionMatrix`` (different states, hence different groups) read ``preds`` twice and run argmax twice.
+        A multiclass confusion-matrix family head (ConfusionMatrix, JaccardIndex, CohenKappa, MatthewsCorrCoef) and
+        every multiclass stat-scores family head (StatScores, Accuracy, FBeta / F1, Precision, Recall, Specificity,
+        HammingDistance; ``top_k == 1``, global averaging) with the same ``num_classes`` and ``ignore_index`` are
+        updated together instead: the kernel fills the batch confusion matrix and the three stat-score histograms
+        in one launch, small finalize kernels add them into each metric's own states.
+        """
+        from torchmetrics_forked_b200.classification.confusion_matrix import MulticlassConfusionMatrix
+        from torchmetrics_forked_b200.classification.stat_scores import MulticlassStatScores
+
+        heads = [members[0] for members in self._groups.values()]
+        for name in heads:
+            cm = getattr(self, name)
+            if not isinstance(cm, MulticlassConfusionMatrix) or cm.num_classes > 2048:
+                continue
+            subs = [
+                n for n in heads
+                if isinstance(getattr(self, n), MulticlassStatScores)
+                and getattr(self, n).top_k == 1 and getattr(self, n).multidim_average == "global"
+                and getattr(self, n).num_classes == cm.num_classes and getattr(self, n).ignore_index == cm.ignore_index
+            ]  # fmt: skip
+            if subs:
+                return name, subs
+        return None
+
+    def _shared_argmax_update(self, args: Tuple[Any, ...], kwargs: Dict[str, Any]) -> List[str]:
+        """Run the shared update if the collection and this call qualify; returns the heads it has served."""
+        if self._shared_plan_cache == "unset":
+            self._shared_plan_cache = self._shared_argmax_plan()
+        plan = self._shared_plan_cache
+        if plan is None or kwargs or len(args) != 2:
+            return []
+        preds, target = args
+        if not (isinstance(preds, Tensor) and isinstance(target, Tensor) and preds.is_cuda and target.is_cuda):
+            return []
+        from torchmetrics_forked_b200 import kernels
+        from torchmetrics_forked_b200.functional.classification.confusion_matrix import (
+            _multiclass_confusion_matrix_tensor_validation,
+            _multiclass_hist_update_,
+        )
+        from torchmetrics_forked_b200.functional.classification.stat_scores import (
+            _multiclass_stat_scores_tensor_validation,
+        )
+
+        cm = getattr(self, plan[0])
+        subs = [getattr(self, n) for n in plan[1]]
+        if any(m.compute_on_cpu or m.dist_sync_on_step for m in (cm, *subs)):
+            return []
+        dev, C = preds.device, cm.num_classes
+        if cm.confmat.device != dev or any(m.tp.device != dev for m in subs):
+            return []  # let the individual updates raise their usual device error
+        if cm.validate_args:
+            _multiclass_confusion_matrix_tensor_validation(preds, target, C, cm.ignore_index)
+        for m in subs:
+            if m.validate_args:
+                _multiclass_stat_scores_tensor_validation(preds, target, C, m.multidim_average, m.ignore_index)
+        for m in (cm, *subs):  # what Metric._wrap_update does around an update
+            m._computed = None
+            m._update_count += 1
+        with torch.no_grad():
+            scratch = cm._scratch_buffer("both", kernels.mc_scratch_numel(C, kernels.MC_BOTH), dev)
+            err = cm._error_word(dev)
+            _multiclass_hist_update_(preds, target, C, cm.ignore_index, kernels.MC_BOTH, scratch, err)
+            kernels.mc_shared_confmat(scratch, C, cm.confmat)
+            for i, m in enumerate(subs):
+                kernels.mc_shared_stats(
+                    scratch, C, m.average == "micro", i == len(subs) - 1, m.tp, m.fp, m.tn, m.fn
+                )
+        if cm.validate_args or any(m.validate_args for m in subs):
+            cm._raise_on_data_errors()
+        return [plan[0], *plan[1]]
 
     # ------------------------------------------------------------------ compute groups
     def _merge_compute_groups(self) -> None:
@@ -128,10 +208,16 @@ class MetricCollection(ModuleDict):
             s1, s2 = getattr(metric1, key), getattr(metric2, key)
             if type(s1) != type(s2):  # noqa: E721
                 return False
+            # EVERY state has to agree.  The reference returns from inside this loop (collections.py:281-285), i.e.
+            # it only ever compares the first state: two metrics whose `tp` coincide after the first batch (top-1
+            # and top-2 accuracy with few hits, say) are merged and one of them silently reports the other's
+            # numbers from then on.  Deliberate deviation.
             if isinstance(s1, Tensor) and isinstance(s2, Tensor):
-                return s1.shape == s2.shape and allclose(s1, s2)
-            if isinstance(s1, list) and isinstance(s2, list):
-                return all(a.shape == b.shape and allclose(a, b) for a, b in zip(s1, s2))
+                if not (s1.shape == s2.shape and allclose(s1, s2)):
+                    return False
+            elif isinstance(s1, list) and isinstance(s2, list):
+                if len(s1) != len(s2) or not all(a.shape == b.shape and allclose(a, b) for a, b in zip(s1, s2)):
+                    return False
         return True
 
     def _compute_groups_create_state_ref(self, copy: bool = False) -> None:
@@ -248,6 +334,7 @@ class MetricCollection(ModuleDict):
             )
 
         self._groups_checked = False
+        self._shared_plan_cache = "unset"
         if self._enable_compute_groups:
             self._init_compute_groups()
         else:

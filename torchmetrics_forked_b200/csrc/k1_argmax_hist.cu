@@ -54,6 +54,12 @@ __device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& 
   }
   if (h.mode == TMB_MC_CONFMAT) {
     hist_add(h, sh, t * h.C + p);
+  } else if (h.mode == TMB_MC_BOTH) {  // batch confusion matrix followed by the three stat-score histograms
+    const int64_t cc = (int64_t)h.C * h.C;
+    hist_add(h, sh, t * h.C + p);
+    hist_add(h, sh, cc + t);
+    hist_add(h, sh, cc + h.C + p);
+    if (p == t) hist_add(h, sh, cc + 2 * (int64_t)h.C + t);
   } else if (h.mode == TMB_MC_STATS) {
     hist_add(h, sh, t);
     hist_add(h, sh, h.C + p);
@@ -523,6 +529,73 @@ __global__ void __launch_bounds__(1024) k1_stats_finalize(unsigned long long* sc
 // ---- host side --------------------------------------------------------------------------------------
 constexpr int kShBinsMax = 4096;  // privatise in shared memory up to this many bins (16 KB)
 
+// ---- shared update of a MetricCollection -------------------------------------------------------
+// TMB_MC_BOTH fills one scratch [C*C | 3C] per batch; these two kernels hand it out: the batch confusion matrix is
+// added into the confusion-matrix state, the histograms into as many stat-score states as subscribe (per class, or
+// summed for `average="micro"`), and the last consumer clears.
+__global__ void __launch_bounds__(256) k1_add_clear(unsigned long long* __restrict__ scratch, long long* __restrict__ dst,
+                                                    int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned long long v = scratch[i];
+    if (v) {
+      dst[i] += (long long)v;
+      scratch[i] = 0;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(1024) k1_stats_share(unsigned long long* scratch, int C, int micro, int clear,
+                                                       long long* tp, long long* fp, long long* tn, long long* fn) {
+  __shared__ long long red[2][32];
+  __shared__ long long total[2];
+  long long pt = 0, pm = 0;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    pt += (long long)scratch[c];
+    pm += (long long)scratch[2 * C + c];
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    pt += __shfl_xor_sync(kFull, pt, d);
+    pm += __shfl_xor_sync(kFull, pm, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    red[0][threadIdx.x >> 5] = pt;
+    red[1][threadIdx.x >> 5] = pm;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long a = 0, b = 0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
+      a += red[0][w];
+      b += red[1][w];
+    }
+    total[0] = a;
+    total[1] = b;
+  }
+  __syncthreads();
+  const long long n = total[0], m = total[1];
+  if (micro) {
+    if (threadIdx.x == 0) {  // same expressions as the TMB_MC_MICRO finalize
+      tp[0] += m;
+      fp[0] += n - m;
+      fn[0] += n - m;
+      tn[0] += (long long)C * n - 2 * n + m;
+    }
+  } else {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      const long long ht = (long long)scratch[c], hp = (long long)scratch[C + c], mm = (long long)scratch[2 * C + c];
+      tp[c] += mm;
+      fp[c] += hp - mm;
+      fn[c] += ht - mm;
+      tn[c] += n - ht - hp + mm;
+    }
+  }
+  if (clear) {
+    __syncthreads();  // every thread has read what it needs (the totals were taken before the barrier above)
+    for (int c = threadIdx.x; c < 3 * C; c += blockDim.x) scratch[c] = 0;
+  }
+}
+
 static int hist_bins(int mode, int64_t C) {
   if (mode == TMB_MC_CONFMAT) return (int)(C * C);
   if (mode == TMB_MC_STATS) return (int)(3 * C);
@@ -531,12 +604,12 @@ static int hist_bins(int mode, int64_t C) {
 
 static int make_hist(HistArgs& h, int mode, int64_t C, int has_ignore, int64_t ignore, int64_t* out,
                      int32_t* err) {
-  if (mode != TMB_MC_CONFMAT && mode != TMB_MC_STATS && mode != TMB_MC_MICRO) return TMB_E_MODE;
+  if (mode != TMB_MC_CONFMAT && mode != TMB_MC_STATS && mode != TMB_MC_MICRO && mode != TMB_MC_BOTH) return TMB_E_MODE;
   if (C < 1 || C > (1 << 24)) return TMB_E_SHAPE;
   if (!out || !err) return TMB_E_NULL;
   h.mode = mode;
   h.C = (int)C;
-  int64_t bins = mode == TMB_MC_CONFMAT ? C * C : (mode == TMB_MC_STATS ? 3 * C : 0);
+  int64_t bins = mode == TMB_MC_CONFMAT ? C * C : (mode == TMB_MC_STATS ? 3 * C : (mode == TMB_MC_BOTH ? C * C + 3 * C : 0));
   h.sh_bins = (bins > 0 && bins <= kShBinsMax) ? (int)bins : 0;
   h.has_ignore = has_ignore;
   h.ignore = ignore;
@@ -843,6 +916,7 @@ extern "C" int tmb_build_arch(void) { return 100; }
 extern "C" int64_t tmb_mc_scratch_bytes(int64_t num_classes, int mode) {
   if (mode == TMB_MC_STATS) return 3 * num_classes * (int64_t)sizeof(int64_t);
   if (mode == TMB_MC_MICRO) return 2 * (int64_t)sizeof(int64_t);
+  if (mode == TMB_MC_BOTH) return (num_classes * num_classes + 3 * num_classes) * (int64_t)sizeof(int64_t);
   return 0;
 }
 
@@ -868,6 +942,25 @@ extern "C" int tmb_mc_argmax_hist(const void* preds, int preds_dtype, const void
     case TMB_F16: return launch_strided<TMB_F16>(preds, target, target_dtype, n_outer, n_inner, h, st);
     default: return launch_strided<TMB_BF16>(preds, target, target_dtype, n_outer, n_inner, h, st);
   }
+}
+
+extern "C" int tmb_mc_shared_confmat(int64_t* scratch, int64_t num_classes, int64_t* confmat, void* stream) {
+  if (!scratch || !confmat) return TMB_E_NULL;
+  if (num_classes < 1 || num_classes > (1 << 15)) return TMB_E_SHAPE;
+  const int64_t n = num_classes * num_classes;
+  k1_add_clear<<<wave_grid((n + 255) / 256, 4), 256, 0, (cudaStream_t)stream>>>((unsigned long long*)scratch,
+                                                                                (long long*)confmat, n);
+  return launch_status();
+}
+
+extern "C" int tmb_mc_shared_stats(int64_t* scratch, int64_t num_classes, int micro, int clear, int64_t* tp,
+                                   int64_t* fp, int64_t* tn, int64_t* fn, void* stream) {
+  if (!scratch || !tp || !fp || !tn || !fn) return TMB_E_NULL;
+  if (num_classes < 1 || num_classes > (1 << 15)) return TMB_E_SHAPE;
+  unsigned long long* stats = (unsigned long long*)scratch + num_classes * num_classes;
+  k1_stats_share<<<1, 1024, 0, (cudaStream_t)stream>>>(stats, (int)num_classes, micro, clear, (long long*)tp,
+                                                       (long long*)fp, (long long*)tn, (long long*)fn);
+  return launch_status();
 }
 
 extern "C" int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* target, int target_dtype,

@@ -19,7 +19,7 @@ from torchmetrics_forked_b200._exact import (  # noqa: F401
     softmax_normalize,
 )
 
-MC_CONFMAT, MC_STATS, MC_MICRO = nat.MC_CONFMAT, nat.MC_STATS, nat.MC_MICRO
+MC_CONFMAT, MC_STATS, MC_MICRO, MC_BOTH = nat.MC_CONFMAT, nat.MC_STATS, nat.MC_MICRO, nat.MC_BOTH
 
 
 def _ignore_args(ignore_index: Optional[int]):
@@ -73,6 +73,32 @@ def mc_argmax_hist(
             nat.ptr(out), nat.ptr(err), nat.stream_ptr(preds.device),
         )  # fmt: skip
     nat.check(rc, "tmb_mc_argmax_hist")
+
+
+def mc_shared_confmat(scratch: Tensor, num_classes: int, confmat: Tensor) -> None:
+    """Add the batch confusion matrix held in a ``MC_BOTH`` scratch into the ``[C, C]`` state and zero it."""
+    nat.require_cuda(scratch, "scratch")
+    nat.require_cuda(confmat, "state")
+    with torch.cuda.device(scratch.device):
+        rc = nat.lib().tmb_mc_shared_confmat(
+            nat.ptr(scratch), int(num_classes), nat.ptr(confmat), nat.stream_ptr(scratch.device)
+        )
+    nat.check(rc, "tmb_mc_shared_confmat")
+
+
+def mc_shared_stats(
+    scratch: Tensor, num_classes: int, micro: bool, clear: bool, tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor
+) -> None:
+    """Add the stat scores held in a ``MC_BOTH`` scratch into one metric's ``tp/fp/tn/fn`` (``micro``: summed
+    over classes into 1-element states); ``clear`` zeroes the histograms (last subscriber)."""
+    for t in (scratch, tp, fp, tn, fn):
+        nat.require_cuda(t, "state")
+    with torch.cuda.device(scratch.device):
+        rc = nat.lib().tmb_mc_shared_stats(
+            nat.ptr(scratch), int(num_classes), int(micro), int(clear), nat.ptr(tp), nat.ptr(fp), nat.ptr(tn),
+            nat.ptr(fn), nat.stream_ptr(scratch.device),
+        )  # fmt: skip
+    nat.check(rc, "tmb_mc_shared_stats")
 
 
 TOPK_MAX_CLASSES = 1024  # row width the top-k kernel keeps in registers
