@@ -268,8 +268,21 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     record("k2_multilabel_curve_T200_2^21x100", lambda: m.update(ml_p, ml_t), nl, nl * L * 12, nl * L * 4, 4)
     del ml_p, ml_t, m
     torch.cuda.empty_cache()
-    # row f3: top-5 accuracy at the config-2 row shape (bf16 [2^20, 1000])
+    # row f4: MulticlassAccuracy + MulticlassConfusionMatrix in one MetricCollection at the config-2 row shape: one
+    # pass over the logits feeds both (the bytes counted are ONE read of the batch)
+    from torchmetrics_forked_b200 import MetricCollection
     from torchmetrics_forked_b200.classification import MulticlassAccuracy
+    from torchmetrics_forked_b200.classification import MulticlassConfusionMatrix as _MCM
+
+    r4 = 1 << 20
+    p4, t4 = make_cfg2(r4, device, 55)
+    coll = MetricCollection([MulticlassAccuracy(C2_CLASSES, average="micro", validate_args=False),
+                             _MCM(C2_CLASSES, validate_args=False)]).to(device)
+    coll.update(p4, t4)  # the first update discovers the compute groups; sharing starts with the second
+    record("f4_collection_accuracy+confmat_2^20_rows", lambda: coll.update(p4, t4), r4, r4 * 2008, r4 * 2000, 3)
+    del p4, t4, coll
+    torch.cuda.empty_cache()
+    # row f3: top-5 accuracy at the config-2 row shape (bf16 [2^20, 1000])
 
     r5 = 1 << 20
     p5, t5 = make_cfg2(r5, device, 77)
