@@ -105,6 +105,18 @@ int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* target, int
 int tmb_mc_stats_finalize(int64_t* scratch, int64_t num_classes, int mode, int64_t* tp, int64_t* fp,
                           int64_t* tn, int64_t* fn, void* stream);
 
+/* multidim_average="samplewise" for multiclass stat scores (the other half of SURVEY §8 row f3):
+ *   _multiclass_stat_scores_update with sum_dim = [1]   functional/classification/stat_scores.py:363-393
+ * preds [n_samples, num_classes, n_inner] float scores (argmax fused) or, with preds_is_label, [n_samples, n_inner]
+ * integer labels; target [n_samples, n_inner].  Fills scratch (int64 [n_samples, 3 * num_classes], zero on entry)
+ * with the TMB_MC_STATS histograms of every sample; tmb_mc_stats_finalize_samplewise WRITES tp/fp/tn/fn (int64
+ * [n_samples, num_classes]) from them and re-zeroes the scratch. */
+int tmb_mc_hist_samplewise(const void* preds, int preds_dtype, int preds_is_label, const void* target,
+                           int target_dtype, int64_t n_samples, int64_t num_classes, int64_t n_inner,
+                           int has_ignore, int64_t ignore_index, int64_t* scratch, int32_t* err, void* stream);
+int tmb_mc_stats_finalize_samplewise(int64_t* scratch, int64_t n_samples, int64_t num_classes, int64_t* tp,
+                                     int64_t* fp, int64_t* tn, int64_t* fn, void* stream);
+
 /* One argmax for a whole MetricCollection (collections.py:200-226 calls every compute group's
  * update, so Accuracy + ConfusionMatrix read the logits twice and run argmax twice): tmb_mc_argmax_hist /
  * tmb_mc_label_hist with mode TMB_MC_BOTH fill one scratch, then

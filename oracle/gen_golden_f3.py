@@ -43,6 +43,33 @@ def main() -> None:
     case("multidim_k2", torch.randn(40, 6, 5, 4, generator=g), torch.randint(6, (40, 5, 4), generator=g), 6, 2)
     case("c1000_k5_probs", torch.rand(300, 1000, generator=g), torch.randint(1000, (300,), generator=g), 1000, 5)
     case("k_equals_c", torch.randn(200, 4, generator=g), torch.randint(4, (200,), generator=g), 4, 4)
+    # ---- multidim_average="samplewise" ------------------------------------------------------------------
+    def sw_case(name, task, preds, target, **kw):
+        d = {"preds": preds.numpy(), "target": target.numpy(), "ignore_index": -999 if kw.get("ignore_index") is None else kw["ignore_index"]}
+        for k in ("num_classes", "num_labels"):
+            if k in kw:
+                d[k] = kw[k]
+        avgs = (None,) if task == "binary" else ("micro", "macro", "weighted", "none")
+        for avg in avgs:
+            extra = {} if task == "binary" else {"average": avg}
+            tag = "" if task == "binary" else f"_{avg}"
+            d[f"stat_scores{tag}"] = getattr(rf, f"{task}_stat_scores")(preds, target, multidim_average="samplewise", **kw, **extra).numpy()
+            for fn in ("accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+                d[f"{fn}{tag}"] = getattr(rf, f"{task}_{fn}")(preds, target, multidim_average="samplewise", **kw, **extra).numpy()
+        np.savez_compressed(OUT / f"f3_samplewise_{name}.npz", **d)
+
+    bt = torch.randint(2, (9, 7, 11), generator=g)
+    bt[torch.rand(9, 7, 11, generator=g) < 0.15] = -1
+    sw_case("binary_logits_ignore", "binary", torch.randn(9, 7, 11, generator=g), bt, ignore_index=-1)
+    sw_case("binary_probs", "binary", torch.rand(12, 50, generator=g), torch.randint(2, (12, 50), generator=g))
+    mt = torch.randint(6, (8, 5, 13), generator=g)
+    mt[torch.rand(8, 5, 13, generator=g) < 0.1] = -1
+    sw_case("multiclass_logits_ignore", "multiclass", torch.randn(8, 6, 5, 13, generator=g), mt, num_classes=6, ignore_index=-1)
+    sw_case("multiclass_labels", "multiclass", torch.randint(5, (10, 40), generator=g), torch.randint(5, (10, 40), generator=g), num_classes=5)
+    sw_case("multiclass_ignore_inside", "multiclass", torch.randn(6, 4, 30, generator=g), torch.randint(4, (6, 30), generator=g), num_classes=4, ignore_index=1)
+    lt = torch.randint(2, (7, 4, 20), generator=g)
+    lt[torch.rand(7, 4, 20, generator=g) < 0.1] = -1
+    sw_case("multilabel_logits_ignore", "multilabel", torch.randn(7, 4, 20, generator=g), lt, num_labels=4, ignore_index=-1)
     print("wrote", sorted(p.name for p in OUT.glob("f3_*.npz")))
 
 

@@ -270,6 +270,61 @@ def multilabel_curve_binned(
     return out
 
 
+# ------------------------------------------------------------------------------------------ samplewise stat scores (row f3)
+def _counts(t: Array, p: Array, axes) -> Tuple[Array, Array, Array, Array]:
+    tp = ((t == p) & (t == 1)).sum(axes)
+    fn = ((t != p) & (t == 1)).sum(axes)
+    fp = ((t != p) & (t == 0)).sum(axes)
+    tn = ((t == p) & (t == 0)).sum(axes)
+    return tp.astype(np.int64), fp.astype(np.int64), tn.astype(np.int64), fn.astype(np.int64)
+
+
+def binary_stat_scores_samplewise(preds: Array, target: Array, threshold: float = 0.5,
+                                  ignore_index: Optional[int] = None,
+                                  sigmoid_fn: SigmoidFn = torch_cpu_sigmoid) -> Tuple[Array, Array, Array, Array]:
+    """`_binary_stat_scores_update` with `multidim_average="samplewise"` (stat_scores.py:116-129, sum_dim = 1): `[N]`
+    counts; the sigmoid decision still looks at the whole batch."""
+    preds = np.asarray(preds)
+    p = _threshold_labels(preds, threshold, np.ones(preds.shape, bool), sigmoid_fn).reshape(preds.shape[0], -1)
+    t = np.asarray(target).astype(np.int64).reshape(preds.shape[0], -1)
+    if ignore_index is not None:
+        t = np.where(t == ignore_index, -1, t)
+    return _counts(t, p, 1)
+
+
+def multilabel_stat_scores_samplewise(preds: Array, target: Array, num_labels: int, threshold: float = 0.5,
+                                      ignore_index: Optional[int] = None,
+                                      sigmoid_fn: SigmoidFn = torch_cpu_sigmoid) -> Tuple[Array, Array, Array, Array]:
+    """`_multilabel_stat_scores_update`, samplewise (stat_scores.py:672-679, sum_dim = 2): `[N, L]` counts."""
+    preds = np.asarray(preds)
+    p = _threshold_labels(preds, threshold, np.ones(preds.shape, bool), sigmoid_fn)
+    p = p.reshape(p.shape[0], num_labels, -1)
+    t = np.asarray(target).astype(np.int64).reshape(p.shape[0], num_labels, -1)
+    if ignore_index is not None:
+        t = np.where(t == ignore_index, -1, t)
+    return _counts(t, p, 2)
+
+
+def multiclass_stat_scores_samplewise(preds: Array, target: Array, num_classes: int,
+                                      ignore_index: Optional[int] = None) -> Tuple[Array, Array, Array, Array]:
+    """`_multiclass_stat_scores_update`, samplewise, `top_k = 1` (stat_scores.py:363-393 with sum_dim = [1]): `[N, C]`
+    counts from the one-hot prediction / target; ignored positions leave all four."""
+    preds = np.asarray(preds)
+    target = np.asarray(target).astype(np.int64)
+    labels = argmax_first(preds.astype(np.float32), 1) if preds.ndim == target.ndim + 1 else preds.astype(np.int64)
+    n = target.shape[0]
+    labels, t = labels.reshape(n, -1), target.reshape(n, -1)
+    classes = np.arange(num_classes)[None, None, :]
+    keep = np.ones(t.shape, bool) if ignore_index is None else t != ignore_index
+    hot_t = (t[..., None] == classes) & keep[..., None]
+    hot_p = (labels[..., None] == classes) & keep[..., None]
+    tp = (hot_t & hot_p).sum(1)
+    fn = (hot_t & ~hot_p).sum(1)
+    fp = (~hot_t & hot_p).sum(1)
+    tn = (keep[..., None] & ~hot_t & ~hot_p).sum(1)
+    return tp.astype(np.int64), fp.astype(np.int64), tn.astype(np.int64), fn.astype(np.int64)
+
+
 # ------------------------------------------------------------------------------------------ top-k stat scores (row f3)
 def topk_sets(rows: Array, k: int) -> Array:
     """`select_topk` (utilities/data.py:115-139) as a boolean [M, C] membership matrix: the k largest scores of a row,

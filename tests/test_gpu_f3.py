@@ -82,8 +82,64 @@ def test_topk_argument_handling():
     with pytest.raises(ValueError, match="top_k"):
         F.multiclass_accuracy(t, t, 4, top_k=2)  # label-valued preds cannot be ranked
     with pytest.raises(NotImplementedError):
-        C.MulticlassStatScores(4, multidim_average="samplewise")
+        C.MulticlassStatScores(4, multidim_average="samplewise", top_k=2)  # the combination is not built
     bad = t.clone()
     bad[0] = 9
     with pytest.raises(RuntimeError, match="target"):
         F.multiclass_accuracy(p, bad, 4, top_k=2)
+
+
+# ------------------------------------------------------------------------------------------ samplewise
+def cuda_sigmoid(x: np.ndarray) -> np.ndarray:
+    return torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).cuda().sigmoid().cpu().numpy()
+
+
+@pytest.mark.parametrize("name", golden_names("f3_samplewise_"))
+def test_samplewise_golden(name):
+    """`multidim_average="samplewise"`: per-sample counts bit for bit (logits: against the oracle with the device
+    sigmoid, H5), derived scores within 1e-6, functional and module API (list states over two updates)."""
+    from torchmetrics_forked_b200 import classification as C
+    from torchmetrics_forked_b200 import functional as F
+
+    c = load_golden(name)
+    ign = ignore_of(c)
+    task = name.split("_")[2]
+    preds, target = torch.from_numpy(c["preds"]).cuda(), torch.from_numpy(c["target"]).cuda()
+    logits = "logits" in name and task != "multiclass"  # argmax needs no sigmoid: multiclass is exact on any device
+    kw = {"ignore_index": ign, "multidim_average": "samplewise"}
+    if task == "binary":
+        tp, fp, tn, fn = O.binary_stat_scores_samplewise(c["preds"], c["target"], 0.5, ign, cuda_sigmoid)
+        want = np.stack([tp, fp, tn, fn, tp + fn], 1)
+        got = F.binary_stat_scores(preds, target, **kw)
+        assert np.array_equal(got.cpu().numpy(), want)
+        if not logits:
+            assert np.array_equal(want, c["stat_scores"])
+            for fn_ in ("accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+                np.testing.assert_allclose(getattr(F, f"binary_{fn_}")(preds, target, **kw).cpu().numpy(), c[fn_],
+                                           rtol=1e-6, atol=1e-7)
+        m = C.BinaryStatScores(**kw).cuda()
+        args = {}
+    else:
+        n_key = "num_classes" if task == "multiclass" else "num_labels"
+        n_cls = int(c[n_key])
+        if task == "multiclass":
+            tp, fp, tn, fn = O.multiclass_stat_scores_samplewise(c["preds"], c["target"], n_cls, ign)
+        else:
+            tp, fp, tn, fn = O.multilabel_stat_scores_samplewise(c["preds"], c["target"], n_cls, 0.5, ign, cuda_sigmoid)
+        want = np.stack([tp, fp, tn, fn, tp + fn], -1)
+        got = getattr(F, f"{task}_stat_scores")(preds, target, n_cls, average="none", **kw)
+        assert np.array_equal(got.cpu().numpy(), want)
+        if not logits:
+            assert np.array_equal(want, c["stat_scores_none"])
+            for avg in AVERAGES:
+                for fn_ in ("stat_scores", "accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+                    got = getattr(F, f"{task}_{fn_}")(preds, target, n_cls, average=avg, **kw)
+                    np.testing.assert_allclose(got.cpu().numpy(), c[f"{fn_}_{avg}"], rtol=1e-6, atol=1e-7,
+                                               err_msg=f"{fn_} {avg}")
+        m = getattr(C, f"{task.capitalize()}StatScores")(n_cls, average="none", **kw).cuda()
+    h = preds.shape[0] // 2
+    m.update(preds[:h], target[:h])
+    m.update(preds[h:], target[h:])
+    assert isinstance(m.tp, list) and len(m.tp) == 2
+    if not logits:  # two updates take two sigmoid decisions; with probabilities / argmax they agree with one
+        assert np.array_equal(m.compute().cpu().numpy(), want)

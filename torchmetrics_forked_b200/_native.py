@@ -38,6 +38,14 @@ SIGNATURES = {
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p,
          c_void_p],
     ),
+    "tmb_mc_hist_samplewise": (
+        c_int,
+        [c_void_p, c_int, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_void_p, c_void_p,
+         c_void_p],
+    ),
+    "tmb_mc_stats_finalize_samplewise": (
+        c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    ),
     "tmb_mc_shared_confmat": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
     "tmb_mc_shared_stats": (
         c_int, [c_void_p, c_int64, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]

@@ -19,6 +19,9 @@ from torchmetrics_forked_b200.functional.classification.stat_scores import (
     _multiclass_stat_scores_arg_validation,
     _multiclass_stat_scores_compute,
     _multiclass_stat_scores_tensor_validation,
+    _binary_stat_scores_functional_state,
+    _multiclass_stat_scores_functional_state,
+    _multilabel_stat_scores_functional_state,
     _multiclass_stat_scores_update_,
     _multiclass_stats_mode,
     _multilabel_stat_scores_arg_validation,
@@ -41,9 +44,17 @@ class _AbstractStatScores(Metric):
     fn: Tensor
 
     def _create_state(self, size: int, multidim_average: str = "global") -> None:
-        _require_global(multidim_average)
+        """int64 sum-states, or — ``samplewise`` — list states that collect the per-sample counts of every update
+        (reference :52-70)."""
         for name in ("tp", "fp", "tn", "fn"):
-            self.add_state(name, torch.zeros(size, dtype=torch.long), dist_reduce_fx="sum")
+            if multidim_average == "samplewise":
+                self.add_state(name, [], dist_reduce_fx="cat")
+            else:
+                self.add_state(name, torch.zeros(size, dtype=torch.long), dist_reduce_fx="sum")
+
+    def _append_samplewise(self, counts: Tuple[Tensor, Tensor, Tensor, Tensor]) -> None:
+        for name, value in zip(("tp", "fp", "tn", "fn"), counts):
+            getattr(self, name).append(value)
 
     def _final_state(self) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
         return dim_zero_cat(self.tp), dim_zero_cat(self.fp), dim_zero_cat(self.tn), dim_zero_cat(self.fn)
@@ -86,6 +97,14 @@ class BinaryStatScores(_AbstractStatScores):
         if self.validate_args:
             _binary_stat_scores_tensor_validation(preds, target, self.multidim_average, self.ignore_index)
         dev = preds.device
+        if self.multidim_average == "samplewise":
+            self._append_samplewise(
+                _binary_stat_scores_functional_state(
+                    preds, target, self.threshold, self.ignore_index, self.validate_args, "BinaryStatScores.update",
+                    "samplewise",
+                )
+            )
+            return
         tp, fp, tn, fn = self._states_on(dev)
         scratch = self._scratch_buffer("tb", kernels.thresh_count_scratch_numel(1), dev)
         _binary_stat_scores_update_(
@@ -136,6 +155,14 @@ class MulticlassStatScores(_AbstractStatScores):
                 preds, target, self.num_classes, self.multidim_average, self.ignore_index
             )
         dev = preds.device
+        if self.multidim_average == "samplewise":
+            self._append_samplewise(
+                _multiclass_stat_scores_functional_state(
+                    preds, target, self.num_classes, self.average, self.ignore_index, self.validate_args,
+                    "MulticlassStatScores.update", self.top_k, "samplewise",
+                )
+            )
+            return
         tp, fp, tn, fn = self._states_on(dev)
         mode = _multiclass_stats_mode(self.average, self.top_k)
         scratch = self._scratch_buffer(f"mc{mode}", kernels.mc_scratch_numel(self.num_classes, mode), dev)
@@ -185,6 +212,14 @@ class MultilabelStatScores(_AbstractStatScores):
                 preds, target, self.num_labels, self.multidim_average, self.ignore_index
             )
         dev = preds.device
+        if self.multidim_average == "samplewise":
+            self._append_samplewise(
+                _multilabel_stat_scores_functional_state(
+                    preds, target, self.num_labels, self.threshold, self.ignore_index, self.validate_args,
+                    "MultilabelStatScores.update", "samplewise",
+                )
+            )
+            return
         tp, fp, tn, fn = self._states_on(dev)
         scratch = self._scratch_buffer("tb", kernels.thresh_count_scratch_numel(self.num_labels), dev)
         _multilabel_stat_scores_update_(

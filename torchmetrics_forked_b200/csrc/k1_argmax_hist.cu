@@ -26,6 +26,8 @@ struct HistArgs {
   int64_t ignore;
   unsigned long long* out;
   int* err;
+  int64_t per_sample;  // > 0 (TMB_MC_STATS_SAMPLEWISE): one [3C] histogram block per sample, `per_sample` bins apart
+  int64_t sample_len;  // flattened positions per sample (label-valued preds need it to find their sample)
 };
 
 // per-thread micro counters (mode MICRO) live in registers and are flushed once per CTA
@@ -42,7 +44,7 @@ __device__ __forceinline__ void hist_add(const HistArgs& h, int* sh, int64_t bin
 
 // one classified sample: t = target, p = predicted class
 __device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& mi, int64_t t, int64_t p,
-                                             bool p_is_label) {
+                                             bool p_is_label, int64_t sample = 0) {
   if (h.has_ignore && t == h.ignore) return;
   if (t < 0 || t >= h.C) {
     atomicOr(h.err, TMB_ERR_TARGET_RANGE);
@@ -61,9 +63,10 @@ __device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& 
     hist_add(h, sh, cc + h.C + p);
     if (p == t) hist_add(h, sh, cc + 2 * (int64_t)h.C + t);
   } else if (h.mode == TMB_MC_STATS) {
-    hist_add(h, sh, t);
-    hist_add(h, sh, h.C + p);
-    if (p == t) hist_add(h, sh, 2 * (int64_t)h.C + t);
+    const int64_t base = sample * h.per_sample;  // 0 unless samplewise (then sh_bins == 0: global atomics)
+    hist_add(h, sh, base + t);
+    hist_add(h, sh, base + h.C + p);
+    if (p == t) hist_add(h, sh, base + 2 * (int64_t)h.C + t);
   } else {
     mi.n += 1;
     mi.match += (p == t);
@@ -439,7 +442,7 @@ __global__ void __launch_bounds__(256) k1_strided(const char* __restrict__ preds
 #pragma unroll
       for (int q = 0; q < PPT; ++q) {
         int64_t t = load_label(target, target_dtype, n * S + s0 + q);
-        count_sample(h, sh, mi, t, (idx2[q >> 1] >> (16 * (q & 1))) & 0xffffu, false);
+        count_sample(h, sh, mi, t, (idx2[q >> 1] >> (16 * (q & 1))) & 0xffffu, false, n);
       }
       continue;
     }
@@ -461,7 +464,7 @@ __global__ void __launch_bounds__(256) k1_strided(const char* __restrict__ preds
 #pragma unroll
     for (int q = 0; q < PPT; ++q) {
       int64_t t = load_label(target, target_dtype, n * S + s0 + q);
-      count_sample(h, sh, mi, t, best_index(b[q]), false);
+      count_sample(h, sh, mi, t, best_index(b[q]), false, n);
     }
   }
   hist_epilogue(h, sh, mi);
@@ -477,7 +480,7 @@ __global__ void __launch_bounds__(256) k1_labels(const void* __restrict__ preds,
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     int64_t t = load_label(target, target_dtype, i);
     int64_t p = load_label(preds, preds_dtype, i);
-    count_sample(h, sh, mi, t, p, true);
+    count_sample(h, sh, mi, t, p, true, h.per_sample > 0 ? i / h.sample_len : 0);
   }
   hist_epilogue(h, sh, mi);
 }
@@ -596,6 +599,39 @@ __global__ void __launch_bounds__(1024) k1_stats_share(unsigned long long* scrat
   }
 }
 
+// samplewise (multidim_average="samplewise", stat_scores.py:363-393 with sum_dim = [1]): one block per sample turns
+// its [3C] histograms into rows of the [N, C] outputs and clears them
+__global__ void __launch_bounds__(256) k1_stats_finalize_rows(unsigned long long* scratch, int C, long long* tp,
+                                                              long long* fp, long long* tn, long long* fn) {
+  __shared__ long long red[8];
+  __shared__ long long total;
+  unsigned long long* h = scratch + (int64_t)blockIdx.x * 3 * C;
+  long long part = 0;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) part += (long long)h[c];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(kFull, part, d);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long s = 0;
+    for (int w = 0; w < 8; ++w) s += red[w];
+    total = s;
+  }
+  __syncthreads();
+  const long long n = total;
+  const int64_t row = (int64_t)blockIdx.x * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const long long ht = (long long)h[c], hp = (long long)h[C + c], m = (long long)h[2 * C + c];
+    tp[row + c] = m;
+    fp[row + c] = hp - m;
+    fn[row + c] = ht - m;
+    tn[row + c] = n - ht - hp + m;
+    h[c] = 0;
+    h[C + c] = 0;
+    h[2 * C + c] = 0;
+  }
+}
+
 static int hist_bins(int mode, int64_t C) {
   if (mode == TMB_MC_CONFMAT) return (int)(C * C);
   if (mode == TMB_MC_STATS) return (int)(3 * C);
@@ -615,6 +651,8 @@ static int make_hist(HistArgs& h, int mode, int64_t C, int has_ignore, int64_t i
   h.ignore = ignore;
   h.out = (unsigned long long*)out;
   h.err = err;
+  h.per_sample = 0;
+  h.sample_len = 1;
   (void)hist_bins;
   return 0;
 }
@@ -942,6 +980,43 @@ extern "C" int tmb_mc_argmax_hist(const void* preds, int preds_dtype, const void
     case TMB_F16: return launch_strided<TMB_F16>(preds, target, target_dtype, n_outer, n_inner, h, st);
     default: return launch_strided<TMB_BF16>(preds, target, target_dtype, n_outer, n_inner, h, st);
   }
+}
+
+extern "C" int tmb_mc_hist_samplewise(const void* preds, int preds_dtype, int preds_is_label, const void* target,
+                                      int target_dtype, int64_t n_samples, int64_t num_classes, int64_t n_inner,
+                                      int has_ignore, int64_t ignore_index, int64_t* scratch, int32_t* err,
+                                      void* stream) {
+  if (label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (preds_is_label ? label_bytes(preds_dtype) == 0 : float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (n_samples < 0 || n_inner < 1) return TMB_E_SHAPE;
+  HistArgs h;
+  if (int rc = make_hist(h, TMB_MC_STATS, num_classes, has_ignore, ignore_index, scratch, err)) return rc;
+  h.sh_bins = 0;  // every sample has its own histograms: straight to global memory
+  h.per_sample = 3 * num_classes;
+  h.sample_len = n_inner;
+  if (n_samples == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (preds_is_label) {
+    const int64_t n = n_samples * n_inner;
+    k1_labels<<<wave_grid((n + 1023) / 1024, 8), 256, 0, st>>>(preds, preds_dtype, target, target_dtype, n, h);
+    return launch_status();
+  }
+  switch (preds_dtype) {  // [N, C, S] with S >= 1: the strided kernel (a thread per pixel group) knows its sample
+    case TMB_F32: return launch_strided<TMB_F32>(preds, target, target_dtype, n_samples, n_inner, h, st);
+    case TMB_F16: return launch_strided<TMB_F16>(preds, target, target_dtype, n_samples, n_inner, h, st);
+    default: return launch_strided<TMB_BF16>(preds, target, target_dtype, n_samples, n_inner, h, st);
+  }
+}
+
+extern "C" int tmb_mc_stats_finalize_samplewise(int64_t* scratch, int64_t n_samples, int64_t num_classes,
+                                                int64_t* tp, int64_t* fp, int64_t* tn, int64_t* fn, void* stream) {
+  if (!scratch || !tp || !fp || !tn || !fn) return TMB_E_NULL;
+  if (n_samples < 0 || num_classes < 1 || num_classes > (1 << 24) || n_samples > 0x7fffffff) return TMB_E_SHAPE;
+  if (n_samples == 0) return 0;
+  k1_stats_finalize_rows<<<(unsigned)n_samples, 256, 0, (cudaStream_t)stream>>>(
+      (unsigned long long*)scratch, (int)num_classes, (long long*)tp, (long long*)fp, (long long*)tn, (long long*)fn);
+  return launch_status();
 }
 
 extern "C" int tmb_mc_shared_confmat(int64_t* scratch, int64_t num_classes, int64_t* confmat, void* stream) {

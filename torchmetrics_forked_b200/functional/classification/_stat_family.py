@@ -95,7 +95,8 @@ def functional_family(stem: str, reducer: Reducer) -> Tuple[Callable, Callable, 
             _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
         _require_global(multidim_average)
         tp, fp, tn, fn = _binary_stat_scores_functional_state(
-            preds, target, threshold, ignore_index, validate_args, f"binary_{stem}"
+            preds, target, threshold, ignore_index, validate_args, f"binary_{stem}",
+            multidim_average=multidim_average,
         )
         return reducer(tp, fp, tn, fn, average="binary", multidim_average=multidim_average)
 
@@ -114,7 +115,8 @@ def functional_family(stem: str, reducer: Reducer) -> Tuple[Callable, Callable, 
             _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
         _require_global(multidim_average, top_k)
         tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-            preds, target, num_classes, average, ignore_index, validate_args, f"multiclass_{stem}", top_k
+            preds, target, num_classes, average, ignore_index, validate_args, f"multiclass_{stem}", top_k,
+            multidim_average=multidim_average,
         )
         return reducer(tp, fp, tn, fn, average=average, multidim_average=multidim_average)
 
@@ -133,7 +135,8 @@ def functional_family(stem: str, reducer: Reducer) -> Tuple[Callable, Callable, 
             _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
         _require_global(multidim_average)
         tp, fp, tn, fn = _multilabel_stat_scores_functional_state(
-            preds, target, num_labels, threshold, ignore_index, validate_args, f"multilabel_{stem}"
+            preds, target, num_labels, threshold, ignore_index, validate_args, f"multilabel_{stem}",
+            multidim_average=multidim_average,
         )
         return reducer(tp, fp, tn, fn, average=average, multidim_average=multidim_average, multilabel=True)
 

@@ -61,7 +61,8 @@ def binary_accuracy(
         _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
     _require_global(multidim_average)
     tp, fp, tn, fn = _binary_stat_scores_functional_state(
-        preds, target, threshold, ignore_index, validate_args, "binary_accuracy"
+        preds, target, threshold, ignore_index, validate_args, "binary_accuracy",
+        multidim_average=multidim_average,
     )
     return _accuracy_reduce(tp, fp, tn, fn, average="binary", multidim_average=multidim_average)
 
@@ -82,7 +83,8 @@ def multiclass_accuracy(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_accuracy", top_k
+        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_accuracy", top_k,
+        multidim_average=multidim_average,
     )
     return _accuracy_reduce(tp, fp, tn, fn, average=average, multidim_average=multidim_average)
 
@@ -103,7 +105,8 @@ def multilabel_accuracy(
         _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
     _require_global(multidim_average)
     tp, fp, tn, fn = _multilabel_stat_scores_functional_state(
-        preds, target, num_labels, threshold, ignore_index, validate_args, "multilabel_accuracy"
+        preds, target, num_labels, threshold, ignore_index, validate_args, "multilabel_accuracy",
+        multidim_average=multidim_average,
     )
     return _accuracy_reduce(tp, fp, tn, fn, average=average, multidim_average=multidim_average, multilabel=True)
 

@@ -93,7 +93,8 @@ def binary_fbeta_score(
         _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
     _require_global(multidim_average)
     tp, fp, tn, fn = _binary_stat_scores_functional_state(
-        preds, target, threshold, ignore_index, validate_args, "binary_fbeta_score"
+        preds, target, threshold, ignore_index, validate_args, "binary_fbeta_score",
+        multidim_average=multidim_average,
     )
     return _fbeta_reduce(tp, fp, tn, fn, beta, average="binary", multidim_average=multidim_average)
 
@@ -115,7 +116,8 @@ def multiclass_fbeta_score(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(
-        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_fbeta_score", top_k
+        preds, target, num_classes, average, ignore_index, validate_args, "multiclass_fbeta_score", top_k,
+        multidim_average=multidim_average,
     )
     return _fbeta_reduce(tp, fp, tn, fn, beta, average=average, multidim_average=multidim_average)
 
@@ -137,7 +139,8 @@ def multilabel_fbeta_score(
         _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
     _require_global(multidim_average)
     tp, fp, tn, fn = _multilabel_stat_scores_functional_state(
-        preds, target, num_labels, threshold, ignore_index, validate_args, "multilabel_fbeta_score"
+        preds, target, num_labels, threshold, ignore_index, validate_args, "multilabel_fbeta_score",
+        multidim_average=multidim_average,
     )
     return _fbeta_reduce(tp, fp, tn, fn, beta, average=average, multidim_average=multidim_average, multilabel=True)
 

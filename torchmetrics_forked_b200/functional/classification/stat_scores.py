@@ -38,23 +38,51 @@ def _check_multidim(multidim_average: str) -> None:
 
 
 def _require_global(multidim_average: str, top_k: int = 1) -> None:
-    if multidim_average != "global":
+    """Both halves of row f3 are built, but not their combination."""
+    if multidim_average != "global" and top_k != 1:
         raise NotImplementedError(
-            "The sm_100a update path covers `multidim_average='global'`; the samplewise branch of the reference"
-            " (functional/classification/stat_scores.py:363-393) is not part of it."
+            "`multidim_average='samplewise'` together with `top_k > 1` is not built on the sm_100a update path"
         )
 
 
-def _stack_stats(tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str], micro_sums: bool) -> Tensor:
-    """``[tp, fp, tn, fn, support]`` stacked on the last dim, then averaged over classes / labels."""
+def _samplewise_thresh_stats(
+    preds: Tensor, target: Tensor, rows: int, threshold: float, ignore_index: Optional[int], err: Tensor
+) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Binary / multilabel ``multidim_average="samplewise"`` (reference :116-129, :672-679 with ``sum_dim = 1``):
+    every (sample[, label]) pair is one "label" of the single-threshold kernel — ``rows`` of them, each owning the
+    trailing positions — so one launch returns the four ``[rows]`` count vectors.  The sigmoid test still looks at
+    the whole batch, as the reference's ``_format`` does."""
+    dev = preds.device
+    outs = tuple(torch.zeros(rows, dtype=torch.long, device=dev) for _ in range(4))
+    if preds.numel() == 0:
+        return outs
+    p, t = preds.reshape(1, rows, -1), target.reshape(1, rows, -1)
+    scratch = torch.zeros(kernels.thresh_count_scratch_numel(rows), dtype=torch.long, device=dev)
+    kernels.thresh_count(
+        p, t, num_labels=rows, threshold=threshold, ignore_index=ignore_index, flag_counts_ignored=True,
+        layout=kernels.TC_STATS, scratch=scratch, out=outs, err=err, binary=False,
+    )  # fmt: skip
+    return outs
+
+
+def _stack_stats(
+    tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str], micro_sums: bool,
+    multidim_average: str = "global",
+) -> Tensor:  # fmt: skip
+    """``[tp, fp, tn, fn, support]`` stacked on the last dim, then averaged over classes / labels (dim 0, or dim 1 of
+    the per-sample ``[N, C]`` counts)."""
     res = torch.stack([tp, fp, tn, fn, tp + fn], dim=-1)
+    dim = 0 if multidim_average == "global" else 1
     if average == "micro":
-        return res.sum(0) if (micro_sums or res.ndim > 1) else res
+        return res.sum(dim) if (micro_sums or res.ndim > 1) else res
     if average == "macro":
-        return res.float().mean(0)
+        return res.float().mean(dim)
     if average == "weighted":
         weight = tp + fn
-        return (res * (weight / weight.sum()).reshape(*weight.shape, 1)).sum(0)
+        # multilabel (micro_sums) normalises by the grand total even per sample (reference :704), multiclass by the
+        # sample's own total (:443-445)
+        total = weight.sum() if (multidim_average == "global" or micro_sums) else weight.sum(-1, keepdim=True)
+        return (res * (weight / total).reshape(*weight.shape, 1)).sum(dim)
     if average is None or average == "none":
         return res
     return None  # type: ignore[return-value]
@@ -111,15 +139,10 @@ def binary_stat_scores(
     if validate_args:
         _binary_stat_scores_arg_validation(threshold, multidim_average, ignore_index)
         _binary_stat_scores_tensor_validation(preds, target, multidim_average, ignore_index)
-    _require_global(multidim_average)
-    dev = preds.device
-    tp, fp, tn, fn = (torch.zeros(1, dtype=torch.long, device=dev) for _ in range(4))
-    err = torch.zeros(1, dtype=torch.int32, device=dev)
-    scratch = torch.zeros(kernels.thresh_count_scratch_numel(1), dtype=torch.long, device=dev)
-    _binary_stat_scores_update_(preds, target, threshold, ignore_index, tp, fp, tn, fn, scratch, err)
-    if validate_args:
-        kernels.raise_on_error_word(err, "binary_stat_scores")
-    return _binary_stat_scores_compute(tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze(), multidim_average)
+    tp, fp, tn, fn = _binary_stat_scores_functional_state(
+        preds, target, threshold, ignore_index, validate_args, "binary_stat_scores", multidim_average
+    )
+    return _binary_stat_scores_compute(tp, fp, tn, fn, multidim_average)
 
 
 # ------------------------------------------------------------------------------------------ multiclass
@@ -186,8 +209,8 @@ def _multiclass_stat_scores_update_(
 def _multiclass_stat_scores_compute(
     tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str] = "macro", multidim_average: str = "global"
 ) -> Tensor:
-    """Reference: stat_scores.py:421-448 (global branch)."""
-    return _stack_stats(tp, fp, tn, fn, average, micro_sums=False)
+    """Reference: stat_scores.py:421-448."""
+    return _stack_stats(tp, fp, tn, fn, average, micro_sums=False, multidim_average=multidim_average)
 
 
 def multiclass_stat_scores(
@@ -206,16 +229,25 @@ def multiclass_stat_scores(
         _multiclass_stat_scores_tensor_validation(preds, target, num_classes, multidim_average, ignore_index)
     _require_global(multidim_average, top_k)
     tp, fp, tn, fn = _multiclass_stat_scores_functional_state(preds, target, num_classes, average, ignore_index,
-                                                              validate_args, "multiclass_stat_scores", top_k)
+                                                              validate_args, "multiclass_stat_scores", top_k,
+                                                              multidim_average=multidim_average,
+)
     return _multiclass_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
 def _multiclass_stat_scores_functional_state(
     preds: Tensor, target: Tensor, num_classes: int, average: Optional[str], ignore_index: Optional[int],
-    validate_args: bool, where: str, top_k: int = 1,
+    validate_args: bool, where: str, top_k: int = 1, multidim_average: str = "global",
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:  # fmt: skip
     """Fresh zero states + one fused update; shared by the functional accuracy / f-beta entry points."""
     dev = preds.device
+    if multidim_average == "samplewise":
+        # per-sample, per-class counts [N, C]: the reference's one-hot branch (:363-393) with sum_dim = [1]
+        err = torch.zeros(1, dtype=torch.int32, device=dev)
+        out = kernels.mc_stats_samplewise(preds, target, num_classes, ignore_index, err)
+        if validate_args:
+            kernels.raise_on_error_word(err, where)
+        return out
     mode = _multiclass_stats_mode(average, top_k)
     size = 1 if mode == kernels.MC_MICRO else num_classes
     tp, fp, tn, fn = (torch.zeros(size, dtype=torch.long, device=dev) for _ in range(4))
@@ -279,8 +311,8 @@ def _multilabel_stat_scores_update_(
 def _multilabel_stat_scores_compute(
     tp: Tensor, fp: Tensor, tn: Tensor, fn: Tensor, average: Optional[str] = "macro", multidim_average: str = "global"
 ) -> Tensor:
-    """Reference: stat_scores.py:684-708 (global branch)."""
-    return _stack_stats(tp, fp, tn, fn, average, micro_sums=True)
+    """Reference: stat_scores.py:684-708."""
+    return _stack_stats(tp, fp, tn, fn, average, micro_sums=True, multidim_average=multidim_average)
 
 
 def multilabel_stat_scores(
@@ -299,35 +331,50 @@ def multilabel_stat_scores(
         _multilabel_stat_scores_tensor_validation(preds, target, num_labels, multidim_average, ignore_index)
     _require_global(multidim_average)
     tp, fp, tn, fn = _multilabel_stat_scores_functional_state(preds, target, num_labels, threshold, ignore_index,
-                                                              validate_args, "multilabel_stat_scores")
+                                                              validate_args, "multilabel_stat_scores",
+                                                              multidim_average=multidim_average,
+)
     return _multilabel_stat_scores_compute(tp, fp, tn, fn, average, multidim_average)
 
 
 def _multilabel_stat_scores_functional_state(
     preds: Tensor, target: Tensor, num_labels: int, threshold: float, ignore_index: Optional[int],
-    validate_args: bool, where: str,
+    validate_args: bool, where: str, multidim_average: str = "global",
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:  # fmt: skip
     dev = preds.device
-    tp, fp, tn, fn = (torch.zeros(num_labels, dtype=torch.long, device=dev) for _ in range(4))
-    scratch = torch.zeros(kernels.thresh_count_scratch_numel(num_labels), dtype=torch.long, device=dev)
     err = torch.zeros(1, dtype=torch.int32, device=dev)
-    _multilabel_stat_scores_update_(preds, target, num_labels, threshold, ignore_index, tp, fp, tn, fn, scratch, err)
+    if multidim_average == "samplewise":
+        n = preds.shape[0]
+        out = tuple(
+            x.reshape(n, num_labels)
+            for x in _samplewise_thresh_stats(preds, target, n * num_labels, threshold, ignore_index, err)
+        )
+    else:
+        tp, fp, tn, fn = (torch.zeros(num_labels, dtype=torch.long, device=dev) for _ in range(4))
+        scratch = torch.zeros(kernels.thresh_count_scratch_numel(num_labels), dtype=torch.long, device=dev)
+        _multilabel_stat_scores_update_(preds, target, num_labels, threshold, ignore_index, tp, fp, tn, fn, scratch, err)
+        out = (tp, fp, tn, fn)
     if validate_args:
         kernels.raise_on_error_word(err, where)
-    return tp, fp, tn, fn
+    return out
 
 
 def _binary_stat_scores_functional_state(
-    preds: Tensor, target: Tensor, threshold: float, ignore_index: Optional[int], validate_args: bool, where: str
-) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    preds: Tensor, target: Tensor, threshold: float, ignore_index: Optional[int], validate_args: bool, where: str,
+    multidim_average: str = "global",
+) -> Tuple[Tensor, Tensor, Tensor, Tensor]:  # fmt: skip
     dev = preds.device
-    tp, fp, tn, fn = (torch.zeros(1, dtype=torch.long, device=dev) for _ in range(4))
-    scratch = torch.zeros(kernels.thresh_count_scratch_numel(1), dtype=torch.long, device=dev)
     err = torch.zeros(1, dtype=torch.int32, device=dev)
-    _binary_stat_scores_update_(preds, target, threshold, ignore_index, tp, fp, tn, fn, scratch, err)
+    if multidim_average == "samplewise":
+        out = _samplewise_thresh_stats(preds, target, preds.shape[0], threshold, ignore_index, err)
+    else:
+        tp, fp, tn, fn = (torch.zeros(1, dtype=torch.long, device=dev) for _ in range(4))
+        scratch = torch.zeros(kernels.thresh_count_scratch_numel(1), dtype=torch.long, device=dev)
+        _binary_stat_scores_update_(preds, target, threshold, ignore_index, tp, fp, tn, fn, scratch, err)
+        out = (tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze())
     if validate_args:
         kernels.raise_on_error_word(err, where)
-    return tp.squeeze(), fp.squeeze(), tn.squeeze(), fn.squeeze()
+    return out
 
 
 def stat_scores(

@@ -4,7 +4,7 @@ Each function checks devices / dtypes / contiguity, picks up torch's current str
 point of libtmb200.so.  Nothing here computes anything on the host and nothing falls back to torch ops:
 a CPU tensor or a missing library raises.
 """
-from typing import Optional
+from typing import Optional, Tuple
 
 import torch
 from torch import Tensor
@@ -73,6 +73,47 @@ def mc_argmax_hist(
             nat.ptr(out), nat.ptr(err), nat.stream_ptr(preds.device),
         )  # fmt: skip
     nat.check(rc, "tmb_mc_argmax_hist")
+
+
+def mc_stats_samplewise(
+    preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int], err: Tensor
+) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
+    """Per-sample ``tp/fp/tn/fn`` (int64 ``[N, C]``) of ``preds [N, C, ...]`` float scores (argmax fused) or
+    ``[N, ...]`` integer labels against ``target [N, ...]``: ``multidim_average="samplewise"``."""
+    nat.require_cuda(preds, "preds")
+    nat.require_cuda(target, "target")
+    is_label = not preds.is_floating_point()
+    if is_label:
+        if preds.shape != target.shape:
+            raise ValueError("label-valued `preds` must have the shape of `target`")
+    elif preds.ndim < 2 or preds.shape[1] != num_classes or preds.ndim != target.ndim + 1:
+        raise ValueError("`preds` must have shape (N, C, ...) with C equal to `num_classes`")
+    preds = _as_kernel_input(preds)
+    target = _as_kernel_input(target)
+    n = preds.shape[0]
+    inner = target.numel() // n if n else 1
+    dev = preds.device
+    outs = tuple(torch.empty(n, num_classes, dtype=torch.int64, device=dev) for _ in range(4))
+    if n == 0:
+        return outs
+    if inner == 0:
+        for o in outs:
+            o.zero_()
+        return outs
+    scratch = torch.zeros(n * 3 * num_classes, dtype=torch.int64, device=dev)
+    has_ign, ign = _ignore_args(ignore_index)
+    pcode = nat.label_code(preds, "preds") if is_label else nat.float_code(preds)
+    with torch.cuda.device(dev):
+        rc = nat.lib().tmb_mc_hist_samplewise(
+            nat.ptr(preds), pcode, int(is_label), nat.ptr(target), nat.label_code(target), n, int(num_classes),
+            inner, has_ign, ign, nat.ptr(scratch), nat.ptr(err), nat.stream_ptr(dev),
+        )  # fmt: skip
+        nat.check(rc, "tmb_mc_hist_samplewise")
+        rc = nat.lib().tmb_mc_stats_finalize_samplewise(
+            nat.ptr(scratch), n, int(num_classes), *(nat.ptr(o) for o in outs), nat.stream_ptr(dev)
+        )
+        nat.check(rc, "tmb_mc_stats_finalize_samplewise")
+    return outs
 
 
 def mc_shared_confmat(scratch: Tensor, num_classes: int, confmat: Tensor) -> None:
