@@ -369,6 +369,20 @@ def extras_block(device, steps: int, warmup: int, peak: float):
         ).to(device)
         record(f"cfg1_C{C}_collection", lambda coll=coll, preds=preds, tgt=tgt: coll.update(preds, tgt), 100_000,
                2 * 100_000 * (4 * C + 8), 2 * 100_000 * 4 * C, 3)
+        # the same update captured once in a CUDA graph and replayed: what is left when Python + launch overhead go
+        try:
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                coll.update(preds, tgt)
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                coll.update(preds, tgt)
+            record(f"cfg1_C{C}_collection_cuda_graph", graph.replay, 100_000, 100_000 * (4 * C + 8), 100_000 * 4 * C, 3)
+            del graph
+        except Exception as e:  # noqa: BLE001
+            out[f"cfg1_C{C}_collection_cuda_graph"] = {"error": repr(e)}
     return out
 
 
