@@ -301,6 +301,33 @@ def extras_block(device, steps: int, warmup: int, peak: float):
                rows_mc * (C_mc * 4 + 8), rows_mc * C_mc * 4, 4)
         del mc_p, mc_t, m
         torch.cuda.empty_cache()
+    # row f2, exact mode: MulticlassAUROC(thresholds=None) — update = conditional row softmax (read + write), compute =
+    # sort + scan of all classes
+    try:
+        rows_e, C_e = 1 << 21, 100
+        m = MulticlassAUROC(C_e, thresholds=None, average="macro", validate_args=False).to(device)
+        mc_p = torch.randn(rows_e, C_e, generator=g, device=device)
+        mc_t = torch.randint(C_e, (rows_e,), generator=g, device=device)
+
+        def upd():
+            m.reset()
+            m.update(mc_p, mc_t)
+
+        record(f"f2_multiclass_exact_update_{rows_e}x{C_e}", upd, rows_e, rows_e * (C_e * 8 + 8), rows_e * C_e * 4, 2)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        m.compute()          # warm-up (allocator, first-call set-up)
+        m._computed = None   # drop the cached result so that the timed call really computes
+        e0.record()
+        val = m.compute()
+        e1.record()
+        torch.cuda.synchronize()
+        out[f"f2_multiclass_exact_update_{rows_e}x{C_e}"]["compute_ms"] = e0.elapsed_time(e1)
+        out[f"f2_multiclass_exact_update_{rows_e}x{C_e}"]["auroc"] = float(val)
+        del m, mc_p, mc_t
+    except Exception as e:  # noqa: BLE001
+        out["f2_multiclass_exact"] = {"error": repr(e)}
+    torch.cuda.empty_cache()
     # config 2 rows through StatScores (three C-bin histograms instead of the C x C matrix)
     r2 = 1 << 20
     p2, t2 = make_cfg2(r2, device, 99)

@@ -62,6 +62,17 @@ elif which == "f2":
     m = MulticlassAUROC(C, thresholds=200, validate_args=False).to(dev)
     for _ in range(3):
         m.update(p, t)
+elif which == "f2x":
+    from torchmetrics_forked_b200.classification import MulticlassAUROC
+
+    n, C = 1 << 21, 100
+    p = torch.randn(n, C, generator=g, device=dev)
+    t = torch.randint(C, (n,), generator=g, device=dev)
+    m = MulticlassAUROC(C, thresholds=None, validate_args=False).to(dev)
+    for _ in range(3):
+        m.reset()
+        m.update(p, t)
+    print(float(m.compute()))
 elif which == "f3":
     from torchmetrics_forked_b200.classification import MulticlassAccuracy
 

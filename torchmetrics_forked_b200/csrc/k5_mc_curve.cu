@@ -53,33 +53,52 @@ __global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restri
   if (__any_sync(kFull, found) && lane == 0 && *((volatile unsigned long long*)flag) != gen) atomicMax(flag, gen);
 }
 
-// pass B: out = (flag == gen) ? softmax(x, dim=1) : x
+// pass B: out = (flag == gen) ? softmax(x, dim=1) : x.  A lane takes 8 elements per trip — SLOTS of each of
+// ROWS = 8 / SLOTS rows when a row gives it fewer — so that narrow rows still keep several loads in flight per lane
+// (one 400-byte row per warp and trip left the kernel waiting on DRAM latency at 35 % of the HBM roofline), and the
+// rows of the next trip are requested into L2 while this trip is computed.
 template <int DT, int SLOTS>
 __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ x, void* __restrict__ out,
                                                        int64_t rows, int C, RowMap rm,
                                                        const unsigned long long* __restrict__ flag,
                                                        unsigned long long gen) {
+  constexpr int ROWS = SLOTS < 8 ? 8 / SLOTS : 1;
   const bool soft = *flag == gen;
   const int lane = threadIdx.x & 31;
   const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
   const int rows_per_warp = 32 >> rm.log2W;
+  const int64_t rows_per_trip = (int64_t)rows_per_warp * ROWS;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r0 = warp * rows_per_warp; r0 < rows; r0 += nwarps * rows_per_warp) {  // warp-uniform trip count
-    const int64_t r = r0 + sub;
-    const bool active = r < rows;
-    const int64_t base = r * C;
-    float e[SLOTS];
-#pragma unroll
-    for (int it = 0; it < SLOTS; ++it) {
-      const int c = it * rm.W + j;
-      e[it] = (active && c < C) ? load_elem<DT>(x, base + c) : -INFINITY;
+  for (int64_t r0 = warp * rows_per_trip; r0 < rows; r0 += nwarps * rows_per_trip) {  // warp-uniform trip count
+    {
+      const int64_t rn = r0 + nwarps * rows_per_trip;
+      const int64_t first = rn * C * Elem<DT>::kBytes, end = min(rn + rows_per_trip, rows) * C * Elem<DT>::kBytes;
+      const int64_t mine = (first & ~(int64_t)127) + (int64_t)lane * 128;
+      if (rn < rows && mine < end) prefetch_l2((const char*)x + mine);
     }
-    if (soft) softmax_row_inplace<DT, SLOTS>(e, rm);
+    float e[ROWS][SLOTS];
 #pragma unroll
-    for (int it = 0; it < SLOTS; ++it) {
-      const int c = it * rm.W + j;
-      if (active && c < C) store_elem<DT>(out, base + c, e[it]);
+    for (int q = 0; q < ROWS; ++q) {
+      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
+#pragma unroll
+      for (int it = 0; it < SLOTS; ++it) {
+        const int c = it * rm.W + j;
+        e[q][it] = (r < rows && c < C) ? load_elem<DT>(x, r * C + c) : -INFINITY;
+      }
+    }
+    if (soft) {
+#pragma unroll
+      for (int q = 0; q < ROWS; ++q) softmax_row_inplace<DT, SLOTS>(e[q], rm);
+    }
+#pragma unroll
+    for (int q = 0; q < ROWS; ++q) {
+      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
+#pragma unroll
+      for (int it = 0; it < SLOTS; ++it) {
+        const int c = it * rm.W + j;
+        if (r < rows && c < C) store_elem<DT>(out, r * C + c, e[q][it]);
+      }
     }
   }
 }
@@ -98,8 +117,9 @@ template <int DT>
 static int launch_softmax_rows(const void* x, void* out, int64_t rows, int C, const unsigned long long* flag,
                                unsigned long long gen, cudaStream_t st) {
   const RowMap rm = row_map(C);
-  const int64_t work = (rows * rm.W + 255) / 256;
   TMB_DISPATCH_SLOTS(rm.slots, {
+    constexpr int kRowsPerLane = SLOTS < 8 ? 8 / SLOTS : 1;
+    const int64_t work = (rows * rm.W / kRowsPerLane + 255) / 256 + 1;
     auto k = k5_softmax_rows<DT, SLOTS>;
     k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, out, rows, C, rm, flag, gen);
   })
