@@ -288,7 +288,13 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     p5, t5 = make_cfg2(r5, device, 77)
     m = MulticlassAccuracy(C2_CLASSES, top_k=5, average="micro", validate_args=False).to(device)
     record("f3_top5_accuracy_2^20_rows", lambda: m.update(p5, t5), r5, r5 * 2008, r5 * 2000, 2)
-    del p5, t5, m
+    del p5, m
+    torch.cuda.empty_cache()
+    p5f = torch.randn(r5 // 2, C2_CLASSES, generator=g, device=device)
+    t5f = t5[: r5 // 2].contiguous()
+    m = MulticlassAccuracy(C2_CLASSES, top_k=5, average="micro", validate_args=False).to(device)
+    record("f3_top5_accuracy_fp32_2^19_rows", lambda: m.update(p5f, t5f), r5 // 2, (r5 // 2) * 4008, (r5 // 2) * 4000, 2)
+    del p5f, t5f, t5, m
     torch.cuda.empty_cache()
     # row f2: multiclass binned curves, fused row softmax + binning (MulticlassAUROC(thresholds=200) update)
     from torchmetrics_forked_b200.classification import MulticlassAUROC

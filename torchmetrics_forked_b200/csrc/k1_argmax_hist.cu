@@ -912,12 +912,107 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
   }
 }
 
+// fp32 scores: no spare key bits, so the (value key, class) pair stays split as in k1_rows_topk, but the row arrives
+// as 16-byte vectors (vector v of the row in lane v % 32, 4 scores each) with the next row already in flight.
+// Needs C % 4 == 0 (16-byte aligned rows) and C <= 1024.
+template <int VECS>
+__global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ preds, const void* __restrict__ target,
+                                                      int tdt, int64_t rows, int C, int top_k, int has_ignore,
+                                                      int64_t ignore, unsigned long long* __restrict__ out, int* err) {
+  extern __shared__ int sh_topk[];  // [3 * C]: T | P | M
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int n_vec = C >> 2;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  uint4 raw[VECS];
+  auto fetch = [&](int64_t r) {
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      const int v = lane + 32 * q;
+      raw[q] = v < n_vec ? ldg_stream16((const char*)preds + (r * C + (int64_t)v * 4) * 4) : make_uint4(0, 0, 0, 0);
+    }
+  };
+  int64_t r = warp;
+  if (r < rows) fetch(r);
+  for (; r < rows; r += nwarps) {  // warp-uniform
+    const int64_t t = load_label(target, tdt, r);
+    uint32_t key[VECS * 4];
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      const bool live = lane + 32 * q < n_vec;
+      const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) key[q * 4 + e] = live ? topk_key(__uint_as_float(w[e])) : 0u;
+    }
+    if (r + nwarps < rows) fetch(r + nwarps);
+    if (has_ignore && t == ignore) continue;
+    if (t < 0 || t >= C) {
+      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      continue;
+    }
+    bool hit = false;
+    for (int round = 0; round < top_k; ++round) {
+      uint32_t best = 0;
+      int best_i = 0;
+#pragma unroll
+      for (int i = 0; i < VECS * 4; ++i) {
+        if (key[i] > best) {  // slots ascend with the class index inside a lane: the first maximum is the lowest class
+          best = key[i];
+          best_i = i;
+        }
+      }
+      const uint32_t top = __reduce_max_sync(kFull, best);
+      const uint32_t mine = (uint32_t)((lane + 32 * (best_i >> 2)) * 4 + (best_i & 3));
+      const uint32_t cls = __reduce_min_sync(kFull, best == top ? mine : 0xffffffffu);
+#pragma unroll
+      for (int i = 0; i < VECS * 4; ++i)
+        if ((uint32_t)((lane + 32 * (i >> 2)) * 4 + (i & 3)) == cls) key[i] = 0u;
+      if (lane == 0) atomicAdd(&sh_topk[C + (int)cls], 1);
+      hit |= (int64_t)cls == t;
+    }
+    if (lane == 0) {
+      atomicAdd(&sh_topk[(int)t], 1);
+      if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const int v = sh_topk[i];
+    if (v) atomicAdd(&out[i], (unsigned long long)v);
+  }
+}
+
 template <int DT>
 static int launch_rows_topk(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
                             int has_ignore, int64_t ignore, unsigned long long* out, int* err, cudaStream_t st) {
   const RowMap rm = row_map(C < 32 ? 32 : C);  // always 32 lanes per row here; slots = next_pow2(C) / 32
   const int smem = 3 * C * (int)sizeof(int);
   const int64_t work = (rows * 32 + 255) / 256;
+  if constexpr (DT == TMB_F32) {
+    if (C % 4 == 0 && (((uintptr_t)preds) & 15) == 0) {  // 16-byte aligned rows: vector loads, next row in flight
+      const int vecs = (C / 4 + 31) / 32;  // 16-byte vectors per lane: 1 .. 8
+#define TMB_LAUNCH_TOPK32(V)                                                                                   \
+  {                                                                                                            \
+    auto k = k1_rows_topk32<V>;                                                                                \
+    k<<<resident_grid(k, 256, smem, work), 256, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore,   \
+                                                           ignore, out, err);                                 \
+  }
+      switch (vecs) {
+        case 1: TMB_LAUNCH_TOPK32(1) break;
+        case 2: TMB_LAUNCH_TOPK32(2) break;
+        case 3: TMB_LAUNCH_TOPK32(3) break;
+        case 4: TMB_LAUNCH_TOPK32(4) break;
+        case 5: TMB_LAUNCH_TOPK32(5) break;
+        case 6: TMB_LAUNCH_TOPK32(6) break;
+        case 7: TMB_LAUNCH_TOPK32(7) break;
+        default: TMB_LAUNCH_TOPK32(8) break;
+      }
+#undef TMB_LAUNCH_TOPK32
+      return launch_status();
+    }
+  }
   if constexpr (DT != TMB_F32) {
     if (C % 8 == 0 && (((uintptr_t)preds) & 15) == 0) {  // 16-byte aligned rows: packed keys, vector loads
       const int vecs = (C / 8 + 31) / 32;  // 16-byte vectors per lane: 1 .. 4
