@@ -696,3 +696,34 @@ def test_update_path_is_cuda_graph_capturable():
     for name in ("MulticlassAccuracy", "MulticlassConfusionMatrix", "MulticlassAUROC"):
         for state in eager[name]._defaults:
             assert torch.equal(getattr(eager[name], state), getattr(graphed[name], state)), (name, state)
+
+
+def test_forward_accumulates_in_place_and_returns_batch_values():
+    """SURVEY §8 row f4, `forward()`: batch states are views of one zeroed buffer, the kernels fill them, one fused add
+    folds them into the global tensors IN PLACE.  Batch values equal the functional results, the accumulated state
+    equals update-only accumulation, also through a MetricCollection's forward."""
+    from torchmetrics_forked_b200 import MetricCollection
+    from torchmetrics_forked_b200 import classification as M
+    from torchmetrics_forked_b200 import functional as F
+
+    g = torch.Generator().manual_seed(21)
+    C = 12
+    acc, ref = M.MulticlassAccuracy(C, average="macro").cuda(), M.MulticlassAccuracy(C, average="macro").cuda()
+    curve, curve_ref = M.BinaryAUROC(thresholds=50).cuda(), M.BinaryAUROC(thresholds=50).cuda()
+    coll = MetricCollection([M.MulticlassPrecision(C), M.MulticlassRecall(C), M.MulticlassConfusionMatrix(C)]).cuda()
+    tp_tensor = acc.tp
+    for _ in range(3):
+        p, t = torch.randn(700, C, generator=g).cuda(), torch.randint(C, (700,), generator=g).cuda()
+        assert torch.equal(acc(p, t), F.multiclass_accuracy(p, t, C, average="macro"))
+        ref.update(p, t)
+        bp, bt = torch.randn(900, generator=g).cuda(), torch.randint(2, (900,), generator=g).cuda()
+        assert torch.equal(curve(bp, bt), F.binary_auroc(bp, bt, thresholds=50))
+        curve_ref.update(bp, bt)
+        out = coll(p, t)
+        assert torch.equal(out["MulticlassRecall"], F.multiclass_recall(p, t, C))
+    assert acc.tp is tp_tensor  # same tensor object, accumulated in place
+    for s in ("tp", "fp", "tn", "fn"):
+        assert torch.equal(getattr(acc, s), getattr(ref, s))
+    assert torch.equal(curve.confmat, curve_ref.confmat) and acc._update_count == 3
+    assert torch.equal(acc.compute(), ref.compute())
+    assert torch.equal(coll["MulticlassPrecision"].tp, ref.tp) and torch.equal(coll["MulticlassRecall"].fn, ref.fn)

@@ -116,6 +116,16 @@ def test_forward_both_strategies():
     m._is_synced = True
     with pytest.raises(TorchMetricsUserError, match="The Metric shouldn't be synced when performing"):
         m(torch.tensor(1.0))
+    # all-sum tensor states (full_state_update=False) take the fused path: the global state tensor keeps its
+    # identity (accumulated in place), a failing update leaves it untouched and restored
+    m = DummySum()
+    assert m._all_sum_tensor_states()
+    before = m.x
+    assert m(torch.tensor(2.0)) == 2 and m(torch.tensor(3.0)) == 3
+    assert m.x is before and m.x == 5 and m.update_count == 2
+    with pytest.raises(TypeError):
+        m("not a number")
+    assert m.x is before and m.x == 5 and m.update_count == 2
 
 
 def test_constants_and_iteration_and_hash():

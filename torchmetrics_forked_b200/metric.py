@@ -322,8 +322,49 @@ class Metric(Module, ABC):
             self._update_count = seen
         return batch_val
 
+    def _forward_sum_states(self, *args: Any, **kwargs: Any) -> Any:
+        """``forward`` for metrics whose states are all sum-reduced tensors of one dtype (every K1 / K2 metric): the
+        other half of SURVEY §8 row f4.  The reference resets (one fill per state), updates, computes and then adds
+        global and batch state into NEW tensors (one add per state, metric.py:352-390).  Here the batch states are
+        views of ONE zero-filled buffer, the kernels accumulate into them, and one fused ``_foreach_add_`` folds them
+        into the global tensors in place — which therefore keep their identity (compute groups stay linked)."""
+        names = list(self._defaults)
+        glob = [getattr(self, n) for n in names]
+        flat = torch.zeros(sum(g.numel() for g in glob), dtype=glob[0].dtype, device=glob[0].device)
+        batch, at = [], 0
+        for g in glob:
+            batch.append(flat[at : at + g.numel()].view(g.shape))
+            at += g.numel()
+        seen, done = self._update_count, False
+        try:
+            for n, b in zip(names, batch):
+                setattr(self, n, b)
+            with self._batch_mode():
+                self._computed = None
+                self.update(*args, **kwargs)
+                batch_val = self.compute()
+                with torch.no_grad():
+                    torch._foreach_add_(glob, batch)
+            done = True
+        finally:  # a failing update leaves the global state and the counter as they were
+            for n, g in zip(names, glob):
+                setattr(self, n, g)
+            self._update_count = seen + 1 if done else seen
+        return batch_val
+
+    def _all_sum_tensor_states(self) -> bool:
+        states = [getattr(self, n) for n in self._defaults]
+        return (
+            len(states) > 0
+            and all(isinstance(s, Tensor) for s in states)
+            and all(self._reductions[n] == dim_zero_sum for n in self._defaults)
+            and len({(s.dtype, s.device) for s in states}) == 1
+        )
+
     def _forward_reduce_state_update(self, *args: Any, **kwargs: Any) -> Any:
         """Fast strategy (``full_state_update=False``): batch state from scratch, then merge into the global one."""
+        if self._all_sum_tensor_states():
+            return self._forward_sum_states(*args, **kwargs)
         global_state = {name: getattr(self, name) for name in self._defaults}
         seen = self._update_count
         self.reset()
