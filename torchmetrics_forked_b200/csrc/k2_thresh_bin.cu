@@ -803,9 +803,7 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   int trip = 0;
   auto count = [&](int c, bool hot, int k) {
     const int pair = (micro ? 0 : c) * 2 + (hot ? 1 : 0);
-    if (low_k == 0) {
-      atomicAdd(&hist[pair * kbins + k], 1u);  // the whole histogram is in shared memory
-    } else if (k < low_k) {
+    if (k < low_k) {  // always, when the whole histogram is in shared memory (low_k == kbins)
       atomicAdd(&hist[pair * low_k + k], 1u);
     } else {
       atomicAdd(&gh[pair * kbins + k], 1ULL);
@@ -888,7 +886,7 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
     const uint32_t v = hist[i];
     if (v) {
-      const int64_t dst = low_k == 0 ? (int64_t)i : (int64_t)(i / low_k) * kbins + (i % low_k);
+      const int64_t dst = (int64_t)(i / low_k) * kbins + (i % low_k);  // == i when low_k == kbins
       atomicAdd(&gh[dst], (unsigned long long)v);
     }
   }
@@ -1275,7 +1273,7 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
   int sh_bins, low_k;
   if (pairs * kbins <= room) {
     sh_bins = (int)(pairs * kbins);
-    low_k = 0;
+    low_k = (int)kbins;  // every bin is a "low" bin
   } else {
     low_k = (int)(room / pairs);  // 0 for an absurd class count: everything goes to global memory
     if (low_k > kbins) low_k = (int)kbins;
