@@ -845,8 +845,7 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
       stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
       if (stop) break;
     } else {
-#pragma unroll
-      for (int q = 0; q < ROWS; ++q) softmax_row_inplace<PDT, SLOTS>(e[q], rm);
+      softmax_rows_inplace<PDT, SLOTS, ROWS>(e, rm);
     }
 #pragma unroll
     for (int gi = 0; gi < kGroups; ++gi) {

@@ -87,10 +87,7 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
         e[q][it] = (r < rows && c < C) ? load_elem<DT>(x, r * C + c) : -INFINITY;
       }
     }
-    if (soft) {
-#pragma unroll
-      for (int q = 0; q < ROWS; ++q) softmax_row_inplace<DT, SLOTS>(e[q], rm);
-    }
+    if (soft) softmax_rows_inplace<DT, SLOTS, ROWS>(e, rm);
 #pragma unroll
     for (int q = 0; q < ROWS; ++q) {
       const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
