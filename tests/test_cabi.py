@@ -62,6 +62,21 @@ def test_argument_errors_need_no_gpu(lib):
     assert lib.tmb_thresh_bin_update(None, 0, 0, None, 9, 1, 1, 1, None, 1, 0, 0, 0, 0, None, 0, None, None) == -1
     assert lib.tmb_thresh_bin_finalize(None, 0, 1, 1, None, 0, None, None, None, None, None) == -3
     assert lib.tmb_bincount(None, 9, 1, 1, None, None, None) == -1
+    # rows f2 / f3 / f4: documented limits and dtype checks come first too
+    E_DTYPE, E_SHAPE, E_NULL, E_LIMIT = -1, -2, -3, -6
+    assert lib.tmb_softmax_rows(None, 0, 4, 1025, None, None, 1, None) == E_LIMIT
+    assert lib.tmb_softmax_rows(None, 9, 4, 10, None, None, 1, None) == E_DTYPE
+    assert lib.tmb_softmax_rows(None, 0, 4, 10, None, None, 0, None) == E_SHAPE  # generation counters start at 1
+    assert lib.tmb_rows_outside_flag(None, 0, 4, 10, None, 0, 0, 0, None, 1, None) == E_NULL
+    assert lib.tmb_mc_curve_update(None, 0, None, 0, 4, 1025, None, 5, 0, 0, 0, None, 0, None, None) == E_LIMIT
+    assert lib.tmb_mc_curve_update(None, 0, None, 0, 4, 1, None, 5, 0, 0, 0, None, 0, None, None) == E_SHAPE
+    assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, 1025, 5, 0, 0, None, None, None) == E_LIMIT
+    assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, 10, 11, 0, 0, None, None, None) == E_SHAPE  # top_k > classes
+    assert lib.tmb_mc_hist_samplewise(None, 9, 0, None, 0, 4, 10, 3, 0, 0, None, None, None) == E_DTYPE
+    assert lib.tmb_mc_shared_confmat(None, 10, None, None) == E_NULL
+    assert lib.tmb_mc_shared_stats(None, 10, 0, 1, None, None, None, None, None) == E_NULL
+    assert lib.tmb_mc_scratch_bytes(10, 3) == (100 + 30) * 8  # TMB_MC_BOTH: batch confusion matrix + 3 histograms
+    assert lib.tmb_clf_curves_chunked(None, 1, 0, 0, 5, 2, 0, 0, 1, 0, None, 0, None, None, None, None, None, None) == E_NULL
 
 
 def test_no_cpu_fallback():
