@@ -173,7 +173,7 @@ __global__ void __launch_bounds__(256) k3_normalize_vec(const void* __restrict__
                                                         int64_t n_vec, const unsigned long long* flag,
                                                         unsigned long long gen) {
   constexpr int E = VecIO<DT>::kElems;
-  constexpr int U = 4;
+  constexpr int U = 8;
   const bool sig = *flag == gen;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_vec; b += stride * U) {
@@ -1033,7 +1033,7 @@ static int run_normalize(const void* x, void* out, int64_t n, const void* target
   // pass B: copy or sigmoid
   if (n_vec > 0) {
     auto k = k3_normalize_vec<DT>;
-    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 4 - 1) / (256 * 4)), 256, 0, st>>>(x, out, n_vec, flag, gen);
+    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 8 - 1) / (256 * 8)), 256, 0, st>>>(x, out, n_vec, flag, gen);
     if (int rc = launch_status()) return rc;
   }
   if (n_tail > 0) {
