@@ -29,7 +29,7 @@ def sigmoid_normalize(preds: Tensor, target: Optional[Tensor], ignore_index: Opt
     if has_ign:
         nat.require_cuda(target, "target")
         target = _as_kernel_input(target)
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         rc = nat.lib().tmb_sigmoid_normalize(
             nat.ptr(preds), nat.float_code(preds), preds.numel(),
             nat.ptr(target) if has_ign else 0, nat.label_code(target) if has_ign else 0, has_ign,
@@ -67,7 +67,7 @@ def softmax_normalize(
         target = _as_kernel_input(target.reshape(-1))
         if target.numel() != rows:
             raise ValueError("`target` must hold one class index per row of `preds`")
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         rc = nat.lib().tmb_rows_outside_flag(
             nat.ptr(preds), nat.float_code(preds), rows, num_classes, nat.ptr(target) if has_ign else 0,
             nat.label_code(target) if has_ign else 0, has_ign, int(ignore_index) if has_ign else 0, nat.ptr(flag), 1,
@@ -105,7 +105,7 @@ def compact_not_ignored(preds: Tensor, target: Tensor, ignore_index: int) -> Tup
         return out_p, out_t
     count = torch.zeros(1, dtype=torch.int64, device=dev)
     scratch = torch.empty(int(nat.lib().tmb_compact_scratch_bytes(n)), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         rc = nat.lib().tmb_compact_not_ignored(
             nat.ptr(preds), preds.element_size(), nat.ptr(target), nat.label_code(target), n, int(ignore_index),
             nat.ptr(out_p), nat.ptr(out_t), nat.ptr(count), nat.ptr(scratch), scratch.numel(), nat.stream_ptr(dev),
@@ -190,7 +190,7 @@ def _run_curves(
             nat.ptr(scratch), scratch.numel(), nat.ptr(fps), nat.ptr(tps), nat.ptr(thr), nat.ptr(counts),
             nat.ptr(err), nat.stream_ptr(dev),
         )  # fmt: skip
-        with torch.cuda.device(dev):
+        with nat.on_device(dev):
             if len(ps) == 1 and not class_targets:
                 rc = nat.lib().tmb_clf_curves(
                     nat.ptr(ps[0]), nat.float_code(ps[0]), nat.ptr(ts[0]), nat.label_code(ts[0]), *head, *tail
@@ -250,7 +250,7 @@ def clf_curve_scores(
     has_ign = int(ignore_index is not None)
     nbytes = int(nat.lib().tmb_clf_curve_scratch_bytes(n, num_labels))
     scratch = torch.empty(max(nbytes, 1), dtype=torch.uint8, device=dev)
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         rc = nat.lib().tmb_clf_curve_scores_chunked(
             nat.ptr(table), len(ps), nat.float_code(ps[0]), nat.label_code(ts[0]), n, num_labels, has_ign,
             int(ignore_index) if has_ign else 0, int(pos_label), int(class_targets), int(want_ap), nat.ptr(scratch),

@@ -173,9 +173,34 @@ def label_code(t: Tensor, name: str = "target") -> int:
         ) from None
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def stream_ptr(device: torch.device) -> int:
     """cudaStream_t of torch's current stream on `device`, as an integer."""
+    if _raw_stream is not None and device.index is not None:
+        return _raw_stream(device.index)  # one C call; the Stream object route costs ~3 us per launch
     return torch.cuda.current_stream(device).cuda_stream
+
+
+class _NoGuard:
+    def __enter__(self) -> None:
+        return None
+
+    def __exit__(self, *exc: object) -> bool:
+        return False
+
+
+_NO_GUARD = _NoGuard()
+
+
+def on_device(device: torch.device):
+    """Context that makes `device` current for the launches inside it.  Small updates are launch / Python bound
+    (tens of microseconds), and `torch.cuda.device(...)` alone costs several of them: when the device is current
+    already — the usual case — nothing is switched."""
+    if device.index is None or torch.cuda.current_device() == device.index:
+        return _NO_GUARD
+    return torch.cuda.device(device)
 
 
 def ptr(t: Optional[Tensor]) -> int:

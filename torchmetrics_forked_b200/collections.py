@@ -30,6 +30,28 @@ def _find_duplicate_keys(results: Dict[str, Any]) -> bool:
     return False
 
 
+_SHARED_FNS: List[Any] = []
+
+
+def _shared_update_functions() -> List[Any]:
+    """The kernels module and the three helpers of the shared update, imported once (the classification package
+    imports this module, so the import cannot sit at the top; a function-level import on every update costs
+    microseconds of a launch-bound call)."""
+    if not _SHARED_FNS:
+        from torchmetrics_forked_b200 import kernels
+        from torchmetrics_forked_b200.functional.classification.confusion_matrix import (
+            _multiclass_confusion_matrix_tensor_validation,
+            _multiclass_hist_update_,
+        )
+        from torchmetrics_forked_b200.functional.classification.stat_scores import (
+            _multiclass_stat_scores_tensor_validation,
+        )
+
+        _SHARED_FNS.extend([kernels, _multiclass_confusion_matrix_tensor_validation, _multiclass_hist_update_,
+                            _multiclass_stat_scores_tensor_validation])
+    return _SHARED_FNS
+
+
 class MetricCollection(ModuleDict):
     """Chain metrics that share a call pattern.
 
@@ -141,14 +163,8 @@ class MetricCollection(ModuleDict):
         preds, target = args
         if not (isinstance(preds, Tensor) and isinstance(target, Tensor) and preds.is_cuda and target.is_cuda):
             return []
-        from torchmetrics_forked_b200 import kernels
-        from torchmetrics_forked_b200.functional.classification.confusion_matrix import (
-            _multiclass_confusion_matrix_tensor_validation,
-            _multiclass_hist_update_,
-        )
-        from torchmetrics_forked_b200.functional.classification.stat_scores import (
-            _multiclass_stat_scores_tensor_validation,
-        )
+        kernels, _multiclass_confusion_matrix_tensor_validation, _multiclass_hist_update_, \
+            _multiclass_stat_scores_tensor_validation = _shared_update_functions()
 
         cm = getattr(self, plan[0])
         subs = [getattr(self, n) for n in plan[1]]
@@ -163,8 +179,8 @@ class MetricCollection(ModuleDict):
             if m.validate_args:
                 _multiclass_stat_scores_tensor_validation(preds, target, C, m.multidim_average, m.ignore_index)
         for m in (cm, *subs):  # what Metric._wrap_update does around an update
-            m._computed = None
-            m._update_count += 1
+            m.__dict__["_computed"] = None
+            m.__dict__["_update_count"] += 1
         with torch.no_grad():
             scratch = cm._scratch_buffer("both", kernels.mc_scratch_numel(C, kernels.MC_BOTH), dev)
             err = cm._error_word(dev)

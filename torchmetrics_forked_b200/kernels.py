@@ -66,7 +66,7 @@ def mc_argmax_hist(
     if n_inner == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
-    with torch.cuda.device(preds.device):
+    with nat.on_device(preds.device):
         rc = nat.lib().tmb_mc_argmax_hist(
             nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target),
             n_outer, int(num_classes), n_inner, has_ign, ign, int(mode),
@@ -103,7 +103,7 @@ def mc_stats_samplewise(
     scratch = torch.zeros(n * 3 * num_classes, dtype=torch.int64, device=dev)
     has_ign, ign = _ignore_args(ignore_index)
     pcode = nat.label_code(preds, "preds") if is_label else nat.float_code(preds)
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         rc = nat.lib().tmb_mc_hist_samplewise(
             nat.ptr(preds), pcode, int(is_label), nat.ptr(target), nat.label_code(target), n, int(num_classes),
             inner, has_ign, ign, nat.ptr(scratch), nat.ptr(err), nat.stream_ptr(dev),
@@ -120,7 +120,7 @@ def mc_shared_confmat(scratch: Tensor, num_classes: int, confmat: Tensor) -> Non
     """Add the batch confusion matrix held in a ``MC_BOTH`` scratch into the ``[C, C]`` state and zero it."""
     nat.require_cuda(scratch, "scratch")
     nat.require_cuda(confmat, "state")
-    with torch.cuda.device(scratch.device):
+    with nat.on_device(scratch.device):
         rc = nat.lib().tmb_mc_shared_confmat(
             nat.ptr(scratch), int(num_classes), nat.ptr(confmat), nat.stream_ptr(scratch.device)
         )
@@ -134,7 +134,7 @@ def mc_shared_stats(
     over classes into 1-element states); ``clear`` zeroes the histograms (last subscriber)."""
     for t in (scratch, tp, fp, tn, fn):
         nat.require_cuda(t, "state")
-    with torch.cuda.device(scratch.device):
+    with nat.on_device(scratch.device):
         rc = nat.lib().tmb_mc_shared_stats(
             nat.ptr(scratch), int(num_classes), int(micro), int(clear), nat.ptr(tp), nat.ptr(fp), nat.ptr(tn),
             nat.ptr(fn), nat.stream_ptr(scratch.device),
@@ -166,7 +166,7 @@ def mc_topk_hist(
     if preds.shape[0] == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
-    with torch.cuda.device(preds.device):
+    with nat.on_device(preds.device):
         rc = nat.lib().tmb_mc_topk_hist(
             nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target), preds.shape[0],
             int(num_classes), int(top_k), has_ign, ign, nat.ptr(out), nat.ptr(err), nat.stream_ptr(preds.device),
@@ -192,7 +192,7 @@ def mc_label_hist(
     if preds.numel() != target.numel():
         raise ValueError("`preds` and `target` must have the same number of elements")
     has_ign, ign = _ignore_args(ignore_index)
-    with torch.cuda.device(preds.device):
+    with nat.on_device(preds.device):
         rc = nat.lib().tmb_mc_label_hist(
             nat.ptr(preds), nat.label_code(preds, "preds"), nat.ptr(target), nat.label_code(target),
             preds.numel(), int(num_classes), has_ign, ign, int(mode),
@@ -207,7 +207,7 @@ def mc_stats_finalize(scratch: Tensor, num_classes: int, mode: int, tp: Tensor, 
         nat.require_cuda(t, name)
         if t.dtype != torch.int64 or not t.is_contiguous():
             raise ValueError(f"`{name}` must be a contiguous int64 tensor")
-    with torch.cuda.device(scratch.device):
+    with nat.on_device(scratch.device):
         rc = nat.lib().tmb_mc_stats_finalize(
             nat.ptr(scratch), int(num_classes), int(mode), nat.ptr(tp), nat.ptr(fp), nat.ptr(tn), nat.ptr(fn),
             nat.stream_ptr(scratch.device),
@@ -290,7 +290,7 @@ def thresh_bin_update(
     is_label = not preds.is_floating_point()
     pcode = nat.label_code(preds, "preds") if is_label else nat.float_code(preds)
     has_ign, ign = _ignore_args(ignore_index)
-    with torch.cuda.device(preds.device):
+    with nat.on_device(preds.device):
         rc = nat.lib().tmb_thresh_bin_update(
             nat.ptr(preds), pcode, int(is_label), nat.ptr(target), nat.label_code(target),
             n_outer, n_labels, n_inner, nat.ptr(thresholds), thresholds.numel(), int(cmp_gt),
@@ -327,7 +327,7 @@ def mc_curve_update(
     if preds.numel() == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
-    with torch.cuda.device(preds.device):
+    with nat.on_device(preds.device):
         rc = nat.lib().tmb_mc_curve_update(
             nat.ptr(preds), nat.float_code(preds), nat.ptr(target), nat.label_code(target), preds.shape[0],
             preds.shape[1], nat.ptr(thresholds), thresholds.numel(), has_ign, ign, int(micro), nat.ptr(scratch),
@@ -345,7 +345,7 @@ def thresh_bin_finalize(
         nat.require_cuda(t, "state")
         if t.dtype != torch.int64 or not t.is_contiguous():
             raise ValueError("metric states updated by the kernels must be contiguous int64 tensors")
-    with torch.cuda.device(scratch.device):
+    with nat.on_device(scratch.device):
         rc = nat.lib().tmb_thresh_bin_finalize(
             nat.ptr(scratch), scratch.numel(), int(num_labels), int(num_thresholds), nat.ptr(perm), int(layout),
             nat.ptr(outs[0]), nat.ptr(outs[1]), nat.ptr(outs[2]), nat.ptr(outs[3]), nat.stream_ptr(scratch.device),
@@ -398,7 +398,7 @@ def bincount(x: Tensor, minlength: int) -> Tensor:
     x = _as_kernel_input(x.reshape(-1))
     code = nat.label_code(x, "x")
     dev = x.device
-    with torch.cuda.device(dev):
+    with nat.on_device(dev):
         top = torch.empty(1, dtype=torch.int64, device=dev)
         nat.check(nat.lib().tmb_label_max(nat.ptr(x), code, x.numel(), nat.ptr(top), nat.stream_ptr(dev)), "tmb_label_max")
         biggest = int(top.item()) if x.numel() else -1  # the output size depends on the data, like torch.bincount
