@@ -56,15 +56,37 @@ def recorded_traffic(kernel: str):
 
 
 class ClockSampler:
-    """`nvidia-smi` clocks / throttle reasons sampled every 100 ms while the timed region runs."""
+    """SM clock / throttle reasons sampled WHILE the timed region runs: NVML in a thread every ~5 ms (the default
+    timed region is only tens of milliseconds long, which an `nvidia-smi -lms` child process mostly misses), with
+    `nvidia-smi` as the fall-back when NVML cannot be loaded."""
 
     FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
               "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.thread = index, [], None, None
+        self.nvml, self.handle, self.stop = None, None, threading.Event()
+        self.sm, self.mx, self.reason_bits = [], [], 0
 
     def __enter__(self):
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            phys = self.index
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            if visible:  # NVML numbers the physical devices
+                ids = [v.strip() for v in visible.split(",") if v.strip()]
+                if self.index < len(ids) and ids[self.index].isdigit():
+                    phys = int(ids[self.index])
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.nvml = pynvml
+            self.mx.append(float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)))
+            self.thread = threading.Thread(target=self._poll_nvml, daemon=True)
+            self.thread.start()
+            return self
+        except Exception:  # noqa: BLE001
+            self.nvml = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
@@ -75,11 +97,26 @@ class ClockSampler:
             self.proc = None
         return self
 
+    def _poll_nvml(self):
+        n = self.nvml
+        while not self.stop.is_set():
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+                self.reason_bits |= int(n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle))
+            except Exception:  # noqa: BLE001
+                break
+            self.stop.wait(0.005)
+
     def _pump(self):
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
     def __exit__(self, *exc):
+        if self.nvml is not None:
+            self.stop.set()
+            if self.thread is not None:
+                self.thread.join(timeout=1)
+            return
         if self.proc is not None:
             time.sleep(0.15)
             self.proc.terminate()
@@ -89,12 +126,22 @@ class ClockSampler:
                 self.proc.kill()
 
     def summary(self):
+        if self.nvml is not None:
+            n = self.nvml
+            flags = {"hw_slowdown": n.nvmlClocksThrottleReasonHwSlowdown,
+                     "hw_thermal_slowdown": n.nvmlClocksThrottleReasonHwThermalSlowdown,
+                     "sw_thermal_slowdown": n.nvmlClocksThrottleReasonSwThermalSlowdown,
+                     "sw_power_cap": n.nvmlClocksThrottleReasonSwPowerCap}
+            reasons = sorted(k for k, bit in flags.items() if self.reason_bits & bit)
+            return {"sm_mhz": statistics.median(self.sm) if self.sm else None,
+                    "sm_max_mhz": max(self.mx) if self.mx else None, "reasons": reasons, "samples": len(self.sm),
+                    "source": "nvml"}
         sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "", 1).isdigit()]
         mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "", 1).isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower() == "active"})
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "source": "nvidia-smi"}
 
 
 def dist_setup(n_gpus: int):
