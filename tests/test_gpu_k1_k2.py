@@ -635,7 +635,7 @@ def test_collection_shares_one_argmax(case):
         if step == 0:
             continue
         plan = coll._shared_plan_cache
-        assert plan is not None and plan[0] == "cm" and sorted(plan[1]) == (["acc", "f1"] if case != "labels" else ["acc", "f1"])
+        assert plan is not None and plan[0] == "cm" and sorted(plan[1]) == ["acc", "f1"]
     # "rec" (average none) shares f1's [C] states, "iou" shares cm's, "top2" is its own group (top_k = 2)
     for k in names:
         a, b = coll[k], alone[k]
@@ -727,3 +727,30 @@ def test_forward_accumulates_in_place_and_returns_batch_values():
     assert torch.equal(curve.confmat, curve_ref.confmat) and acc._update_count == 3
     assert torch.equal(acc.compute(), ref.compute())
     assert torch.equal(coll["MulticlassPrecision"].tp, ref.tp) and torch.equal(coll["MulticlassRecall"].fn, ref.fn)
+
+
+def test_collection_shares_one_argmax_without_confusion_matrix():
+    """Stat-score heads that only differ in their averaging (micro keeps [1] states, macro [C]) share one pass too."""
+    from torchmetrics_forked_b200 import MetricCollection
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(78)
+    C = 9
+
+    def make():
+        return {"acc": M.MulticlassAccuracy(C, average="micro"), "f1": M.MulticlassF1Score(C, average="macro"),
+                "prec": M.MulticlassPrecision(C, average="weighted"), "spec": M.MulticlassSpecificity(C, average="micro")}
+
+    coll, alone = MetricCollection(make()).cuda(), {k: m.cuda() for k, m in make().items()}
+    for _ in range(3):
+        p, t = torch.randn(777, C, generator=g).cuda(), torch.randint(C, (777,), generator=g).cuda()
+        coll.update(p, t)
+        for m in alone.values():
+            m.update(p, t)
+    plan = coll._shared_plan_cache
+    assert plan is not None and plan[0] is None and sorted(plan[1]) == ["acc", "f1"]  # heads of the two groups
+    out = coll.compute()
+    for k, m in alone.items():
+        for state in m._defaults:
+            assert torch.equal(getattr(coll[k], state), getattr(m, state)), (k, state)
+        assert torch.equal(out[k], m.compute()) and coll[k]._update_count == 3

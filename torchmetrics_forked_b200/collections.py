@@ -124,7 +124,7 @@ class MetricCollection(ModuleDict):
             self._compute_groups_create_state_ref()
 
     # ------------------------------------------------------------------ one argmax per collection
-    def _shared_argmax_plan(self) -> Optional[Tuple[str, List[str]]]:
+    def _shared_argmax_plan(self) -> Optional[Tuple[Optional[str], List[str]]]:
         """``(confusion-matrix head, [stat-score heads])`` that can be fed by ONE pass over the logits.
 
         The reference updates every compute group separately (collections.py:200-226), so e.g. ``Accuracy`` +
@@ -151,6 +151,20 @@ class MetricCollection(ModuleDict):
             ]  # fmt: skip
             if subs:
                 return name, subs
+        # no confusion-matrix head: stat-score heads that differ only in their averaging (Accuracy "micro" keeps
+        # [1] states, F1 "macro" [C] states — two groups, two argmax passes in the reference) still share one pass
+        stats = [
+            n for n in heads
+            if isinstance(getattr(self, n), MulticlassStatScores)
+            and getattr(self, n).top_k == 1 and getattr(self, n).multidim_average == "global"
+            and getattr(self, n).num_classes <= 2048
+        ]  # fmt: skip
+        for first in stats:
+            a = getattr(self, first)
+            same = [n for n in stats if getattr(self, n).num_classes == a.num_classes
+                    and getattr(self, n).ignore_index == a.ignore_index]
+            if len(same) >= 2:
+                return None, same
         return None
 
     def _shared_argmax_update(self, args: Tuple[Any, ...], kwargs: Dict[str, Any]) -> List[str]:
@@ -166,33 +180,38 @@ class MetricCollection(ModuleDict):
         kernels, _multiclass_confusion_matrix_tensor_validation, _multiclass_hist_update_, \
             _multiclass_stat_scores_tensor_validation = _shared_update_functions()
 
-        cm = getattr(self, plan[0])
+        cm = getattr(self, plan[0]) if plan[0] is not None else None
         subs = [getattr(self, n) for n in plan[1]]
-        if any(m.compute_on_cpu or m.dist_sync_on_step for m in (cm, *subs)):
+        members = ([cm] if cm is not None else []) + subs
+        owner = members[0]  # holds the scratch and the error word of the shared launch
+        if any(m.compute_on_cpu or m.dist_sync_on_step for m in members):
             return []
-        dev, C = preds.device, cm.num_classes
-        if cm.confmat.device != dev or any(m.tp.device != dev for m in subs):
+        dev, C = preds.device, owner.num_classes
+        if (cm is not None and cm.confmat.device != dev) or any(m.tp.device != dev for m in subs):
             return []  # let the individual updates raise their usual device error
-        if cm.validate_args:
+        if cm is not None and cm.validate_args:
             _multiclass_confusion_matrix_tensor_validation(preds, target, C, cm.ignore_index)
         for m in subs:
             if m.validate_args:
                 _multiclass_stat_scores_tensor_validation(preds, target, C, m.multidim_average, m.ignore_index)
-        for m in (cm, *subs):  # what Metric._wrap_update does around an update
+        for m in members:  # what Metric._wrap_update does around an update
             m.__dict__["_computed"] = None
             m.__dict__["_update_count"] += 1
         with torch.no_grad():
-            scratch = cm._scratch_buffer("both", kernels.mc_scratch_numel(C, kernels.MC_BOTH), dev)
-            err = cm._error_word(dev)
-            _multiclass_hist_update_(preds, target, C, cm.ignore_index, kernels.MC_BOTH, scratch, err)
-            kernels.mc_shared_confmat(scratch, C, cm.confmat)
+            scratch = owner._scratch_buffer("both", kernels.mc_scratch_numel(C, kernels.MC_BOTH), dev)
+            err = owner._error_word(dev)
+            if cm is not None:
+                _multiclass_hist_update_(preds, target, C, owner.ignore_index, kernels.MC_BOTH, scratch, err)
+                kernels.mc_shared_confmat(scratch, C, cm.confmat)
+            else:  # the three histograms only, at the place the shared finalize expects them
+                _multiclass_hist_update_(preds, target, C, owner.ignore_index, kernels.MC_STATS, scratch[C * C :], err)
             for i, m in enumerate(subs):
                 kernels.mc_shared_stats(
                     scratch, C, m.average == "micro", i == len(subs) - 1, m.tp, m.fp, m.tn, m.fn
                 )
-        if cm.validate_args or any(m.validate_args for m in subs):
-            cm._raise_on_data_errors()
-        return [plan[0], *plan[1]]
+        if any(m.validate_args for m in members):
+            owner._raise_on_data_errors()
+        return [m for m in plan[1]] + ([plan[0]] if plan[0] is not None else [])
 
     # ------------------------------------------------------------------ compute groups
     def _merge_compute_groups(self) -> None:
