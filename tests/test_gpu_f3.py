@@ -143,3 +143,16 @@ def test_samplewise_golden(name):
     assert isinstance(m.tp, list) and len(m.tp) == 2
     if not logits:  # two updates take two sigmoid decisions; with probabilities / argmax they agree with one
         assert np.array_equal(m.compute().cpu().numpy(), want)
+
+
+def test_samplewise_many_samples_go_through_in_slices():
+    """More samples than one 256 MB scratch holds ([3C] int64 per sample): the wrapper slices the batch."""
+    from torchmetrics_forked_b200 import functional as F
+
+    g = torch.Generator().manual_seed(3)
+    C, n = 1000, 12_000  # 11184 samples per slice at C = 1000
+    preds, target = torch.randint(C, (n, 6), generator=g), torch.randint(C, (n, 6), generator=g)
+    got = F.multiclass_stat_scores(preds.cuda(), target.cuda(), C, average="micro", multidim_average="samplewise")
+    tp = (preds == target).sum(1)
+    want = torch.stack([tp, 6 - tp, 6 * C - 12 + tp, 6 - tp, torch.full_like(tp, 6)], 1)
+    assert torch.equal(got.cpu(), want)

@@ -100,19 +100,24 @@ def mc_stats_samplewise(
         for o in outs:
             o.zero_()
         return outs
-    scratch = torch.zeros(n * 3 * num_classes, dtype=torch.int64, device=dev)
+    # one [3C] histogram block per sample: the scratch is capped at 256 MB and the samples go through in slices
+    step = max(1, (1 << 25) // (3 * num_classes))
+    scratch = torch.zeros(min(n, step) * 3 * num_classes, dtype=torch.int64, device=dev)
     has_ign, ign = _ignore_args(ignore_index)
     pcode = nat.label_code(preds, "preds") if is_label else nat.float_code(preds)
     with nat.on_device(dev):
-        rc = nat.lib().tmb_mc_hist_samplewise(
-            nat.ptr(preds), pcode, int(is_label), nat.ptr(target), nat.label_code(target), n, int(num_classes),
-            inner, has_ign, ign, nat.ptr(scratch), nat.ptr(err), nat.stream_ptr(dev),
-        )  # fmt: skip
-        nat.check(rc, "tmb_mc_hist_samplewise")
-        rc = nat.lib().tmb_mc_stats_finalize_samplewise(
-            nat.ptr(scratch), n, int(num_classes), *(nat.ptr(o) for o in outs), nat.stream_ptr(dev)
-        )
-        nat.check(rc, "tmb_mc_stats_finalize_samplewise")
+        for s0 in range(0, n, step):
+            p, t = preds[s0 : s0 + step], target[s0 : s0 + step]  # leading-dimension slices stay contiguous
+            rc = nat.lib().tmb_mc_hist_samplewise(
+                nat.ptr(p), pcode, int(is_label), nat.ptr(t), nat.label_code(target), p.shape[0], int(num_classes),
+                inner, has_ign, ign, nat.ptr(scratch), nat.ptr(err), nat.stream_ptr(dev),
+            )  # fmt: skip
+            nat.check(rc, "tmb_mc_hist_samplewise")
+            rc = nat.lib().tmb_mc_stats_finalize_samplewise(
+                nat.ptr(scratch), p.shape[0], int(num_classes), *(nat.ptr(o[s0 : s0 + step]) for o in outs),
+                nat.stream_ptr(dev),
+            )
+            nat.check(rc, "tmb_mc_stats_finalize_samplewise")
     return outs
 
 
