@@ -357,6 +357,18 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     # row f2, exact mode: MulticlassAUROC(thresholds=None) — update = conditional row softmax (read + write), compute =
     # sort + scan of all classes
     try:
+        for rows_s, C_s in ((1 << 24, 10),):  # narrow rows: one thread per row
+            ms_ = MulticlassAUROC(C_s, thresholds=None, average="macro", validate_args=False).to(device)
+            sp = torch.randn(rows_s, C_s, generator=g, device=device)
+            st_ = torch.randint(C_s, (rows_s,), generator=g, device=device)
+
+            def upd_s():
+                ms_.reset()
+                ms_.update(sp, st_)
+
+            record(f"f2_multiclass_exact_update_{rows_s}x{C_s}", upd_s, rows_s, rows_s * (C_s * 8 + 8), rows_s * C_s * 4, 2)
+            del ms_, sp, st_
+            torch.cuda.empty_cache()
         rows_e, C_e = 1 << 21, 100
         m = MulticlassAUROC(C_e, thresholds=None, average="macro", validate_args=False).to(device)
         mc_p = torch.randn(rows_e, C_e, generator=g, device=device)

@@ -891,6 +891,118 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   }
 }
 
+// ---- multiclass binned curves, C <= 32: one THREAD per row ------------------------------------------------------
+// For up to 32 classes torch's softmax layout gives every lane one element (W = next_pow2(C) lanes per row), so its
+// arithmetic is: max over the row, e_c = expf(x_c - max), and the xor-butterfly sum — which is the balanced tree
+// "s[i] += s[i + W/2], s[i] += s[i + W/4], ..." over the W values (zeros past C; float addition is commutative, so
+// every lane of the butterfly ends with this very tree).  A single thread holding the row reproduces that bit for
+// bit with W - 1 adds and no shuffles; the sub-warp version spends ~8 shuffle steps per row on one element per
+// lane.  Rows come through shared memory (coalesced loads, odd row stride: conflict-free reads).
+constexpr int kSmallRows = 256;  // rows per CTA tile = threads per CTA
+
+template <int PDT, bool SOFT, int W>
+__global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows, int C, int micro, int sh_bins,
+                                                          int low_k) {
+  extern __shared__ uint32_t sh_u32[];
+  if (!pass_enabled(a, SOFT)) return;
+  float* sh_pad = (float*)sh_u32;
+  const int pad_words = (a.T + 2 + 31) / 32 * 32;
+  const int kbins = a.T + 1;
+  uint32_t* hist = sh_u32 + pad_words;
+  const int hist_words = (sh_bins + 31) / 32 * 32;
+  float* stage = (float*)(hist + hist_words);  // [kSmallRows][stride]
+  const int stride = C | 1;
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
+  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
+  const bool on_grid = bn.grid_eps < 0.01f;
+  unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
+  const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;  // e / C for e * C < 2^32
+  bool bad_target = false;
+  int stop = 0;
+  constexpr int kGroups = (W + kPer - 1) / kPer;
+  for (int64_t tile0 = (int64_t)blockIdx.x * kSmallRows; tile0 < rows && !stop; tile0 += (int64_t)gridDim.x * kSmallRows) {
+    const int n_rows = (int)min((int64_t)kSmallRows, rows - tile0);
+    const int total = n_rows * C;
+    __syncthreads();  // the previous tile's rows have been read
+    for (int e = threadIdx.x; e < total; e += kSmallRows) {
+      const int r = C > 1 ? (int)__umulhi((uint32_t)e, magic) : e;
+      stage[r * stride + (e - r * C)] = load_elem<PDT>(a.preds, tile0 * C + e);
+    }
+    __syncthreads();
+    const int r = threadIdx.x;
+    const bool active = r < n_rows;
+    const int64_t t = active ? load_label(a.target, a.tdt, tile0 + r) : 0;
+    const bool counted = active && !(a.has_ignore && t == a.ignore);
+    if (counted && (t < 0 || t >= C)) bad_target = true;
+    float e[W];
+#pragma unroll
+    for (int c = 0; c < W; ++c) e[c] = 0.0f;
+    if (counted) {
+#pragma unroll
+      for (int c = 0; c < W; ++c) {
+        if (c >= C) break;  // CTA-uniform
+        e[c] = stage[r * stride + c];
+      }
+    }
+    if (!SOFT) {
+      bool mine = false;
+      if (counted) {
+#pragma unroll
+        for (int c = 0; c < W; ++c) {
+          if (c >= C) break;
+          mine |= !(e[c] >= 0.0f && e[c] <= 1.0f);
+        }
+      }
+      if (mine) raise_flag(a);
+      stop = __syncthreads_or(mine || (threadIdx.x == 0 && flag_up(a)));
+      if (stop) break;
+    } else if (counted) {
+      softmax_row_thread<PDT, W>(e, C);
+    }
+#pragma unroll
+    for (int gi = 0; gi < kGroups; ++gi) {
+      if (gi * kPer >= C) break;  // CTA-uniform
+      Decoded d;
+      d.bad = 0;
+      d.outside = 0;
+#pragma unroll
+      for (int i = 0; i < kPer; ++i) {
+        const int c = gi * kPer + i;
+        const bool valid = c < W && counted && c < C;
+        d.x[i] = valid ? e[c < W ? c : 0] : 0.5f;
+        d.inc[i] = valid ? 1u : 0u;
+        d.toff[i] = 0u;
+      }
+      int g[kPer];
+      if (on_grid)
+        batch_bins<PDT, false, true>(bn, d, g);
+      else
+        batch_bins<PDT, false, false>(bn, d, g);
+#pragma unroll
+      for (int i = 0; i < kPer; ++i) {
+        const int c = gi * kPer + i;
+        if (d.inc[i]) {
+          const int pair = (micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0);
+          if (g[i] < low_k)
+            atomicAdd(&hist[pair * low_k + g[i]], 1u);
+          else
+            atomicAdd(&gh[pair * kbins + g[i]], 1ULL);
+        }
+      }
+    }
+  }
+  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_RANGE);
+  __syncthreads();
+  if (!SOFT && (stop || flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
+  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
+    const uint32_t v = hist[i];
+    if (v) {
+      const int64_t dst = (int64_t)(i / low_k) * kbins + (i % low_k);
+      atomicAdd(&gh[dst], (unsigned long long)v);
+    }
+  }
+}
+
 // ---- K1b fast path: ONE threshold, [N, L] row-major (binary = L 1) ---------------------------------------------
 // Stat scores / confusion matrices / accuracy / F1 / Jaccard of binary and multilabel tasks compare against a
 // single threshold, so a sample only needs "above or not" — four counters per label.  The grid-stride is a
@@ -1281,6 +1393,36 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
   }
   const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
   int rc = 0;
+  if (C <= 32) {  // one thread per row (see k2_mc_small)
+    const int hist_words = (sh_bins + 31) / 32 * 32;
+    const int small_smem = (int)pad_bytes + hist_words * 4 + kSmallRows * (C | 1) * 4;
+    if (small_smem <= dev_info().max_smem_optin - 1024) {
+      const int64_t work = (rows + kSmallRows - 1) / kSmallRows;
+#define TMB_LAUNCH_SMALL(W_)                                                                    \
+  {                                                                                             \
+    auto ka = k2_mc_small<PDT, false, W_>;                                                      \
+    auto kb = k2_mc_small<PDT, true, W_>;                                                       \
+    cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
+    cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
+    const int grid = resident_grid(kb, kSmallRows, small_smem, work);                           \
+    ka<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, sh_bins, low_k);                \
+    rc = launch_status();                                                                       \
+    if (rc == 0) {                                                                              \
+      kb<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, sh_bins, low_k);              \
+      rc = launch_status();                                                                     \
+    }                                                                                           \
+  }
+      switch (rm.W) {
+        case 2: TMB_LAUNCH_SMALL(2) break;
+        case 4: TMB_LAUNCH_SMALL(4) break;
+        case 8: TMB_LAUNCH_SMALL(8) break;
+        case 16: TMB_LAUNCH_SMALL(16) break;
+        default: TMB_LAUNCH_SMALL(32) break;
+      }
+#undef TMB_LAUNCH_SMALL
+      return rc;
+    }
+  }
   TMB_DISPATCH_SLOTS(rm.slots, {
     auto ka = k2_mc_rows<PDT, false, SLOTS>;
     auto kb = k2_mc_rows<PDT, true, SLOTS>;

@@ -100,6 +100,53 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
   }
 }
 
+// C <= 32: one thread per row (softmax_row_thread), rows staged through shared memory in both directions so that
+// global loads and stores stay coalesced.
+constexpr int kSoftmaxSmallRows = 256;
+
+template <int DT, int W>
+__global__ void __launch_bounds__(kSoftmaxSmallRows) k5_softmax_small(const void* __restrict__ x, void* __restrict__ out,
+                                                                      int64_t rows, int C,
+                                                                      const unsigned long long* __restrict__ flag,
+                                                                      unsigned long long gen) {
+  extern __shared__ float stage[];  // [kSoftmaxSmallRows][C | 1]
+  const bool soft = *flag == gen;
+  const int stride = C | 1;
+  const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;
+  for (int64_t tile0 = (int64_t)blockIdx.x * kSoftmaxSmallRows; tile0 < rows;
+       tile0 += (int64_t)gridDim.x * kSoftmaxSmallRows) {
+    const int n_rows = (int)min((int64_t)kSoftmaxSmallRows, rows - tile0);
+    const int total = n_rows * C;
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += kSoftmaxSmallRows) {
+      const int r = C > 1 ? (int)__umulhi((uint32_t)i, magic) : i;
+      stage[r * stride + (i - r * C)] = load_elem<DT>(x, tile0 * C + i);
+    }
+    __syncthreads();
+    if (soft && (int)threadIdx.x < n_rows) {
+      float e[W];
+#pragma unroll
+      for (int c = 0; c < W; ++c) e[c] = 0.0f;
+#pragma unroll
+      for (int c = 0; c < W; ++c) {
+        if (c >= C) break;
+        e[c] = stage[threadIdx.x * stride + c];
+      }
+      softmax_row_thread<DT, W>(e, C);
+#pragma unroll
+      for (int c = 0; c < W; ++c) {
+        if (c >= C) break;
+        stage[threadIdx.x * stride + c] = e[c];
+      }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < total; i += kSoftmaxSmallRows) {
+      const int r = C > 1 ? (int)__umulhi((uint32_t)i, magic) : i;
+      store_elem<DT>(out, tile0 * C + i, stage[r * stride + (i - r * C)]);
+    }
+  }
+}
+
 template <int DT>
 static int launch_rows_flag(const void* x, int64_t rows, int C, const void* target, int tdt, int has_ignore,
                             int64_t ignore, unsigned long long* flag, unsigned long long gen, cudaStream_t st) {
@@ -114,6 +161,24 @@ template <int DT>
 static int launch_softmax_rows(const void* x, void* out, int64_t rows, int C, const unsigned long long* flag,
                                unsigned long long gen, cudaStream_t st) {
   const RowMap rm = row_map(C);
+  if (C <= 32 && C >= 2) {
+    const int smem = kSoftmaxSmallRows * (C | 1) * 4;
+    const int64_t work = (rows + kSoftmaxSmallRows - 1) / kSoftmaxSmallRows;
+#define TMB_LAUNCH_SM_SMALL(W_)                                                                        \
+  {                                                                                                    \
+    auto k = k5_softmax_small<DT, W_>;                                                                 \
+    k<<<resident_grid(k, kSoftmaxSmallRows, smem, work), kSoftmaxSmallRows, smem, st>>>(x, out, rows, C, flag, gen); \
+  }
+    switch (rm.W) {
+      case 2: TMB_LAUNCH_SM_SMALL(2) break;
+      case 4: TMB_LAUNCH_SM_SMALL(4) break;
+      case 8: TMB_LAUNCH_SM_SMALL(8) break;
+      case 16: TMB_LAUNCH_SM_SMALL(16) break;
+      default: TMB_LAUNCH_SM_SMALL(32) break;
+    }
+#undef TMB_LAUNCH_SM_SMALL
+    return launch_status();
+  }
   TMB_DISPATCH_SLOTS(rm.slots, {
     constexpr int kRowsPerLane = SLOTS < 8 ? 8 / SLOTS : 1;
     const int64_t work = (rows * rm.W / kRowsPerLane + 255) / 256 + 1;
