@@ -83,4 +83,14 @@ elif which == "f3":
     for _ in range(3):
         m.update(p, t)
 torch.cuda.synchronize()
+if which in ("f2", "f2x", "f3") and "TIME" in __import__("os").environ:  # quick timing while iterating (not a bench value)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(20):
+        if which == "f2x":
+            m.reset()
+        m.update(p, t)
+    b.record()
+    torch.cuda.synchronize()
+    print(which, sys.argv[2:], "ms/update", a.elapsed_time(b) / 20)
 print("done", which)

@@ -794,44 +794,60 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   const bool on_grid = bn.grid_eps < 0.01f;
   unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
   const int lane = threadIdx.x & 31;
-  const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
-  const int rows_per_warp = 32 >> rm.log2W;
-  const int64_t rows_per_trip = (int64_t)rows_per_warp * ROWS;
+  // more than one slot per lane means the row takes the whole warp: W is a compile-time 32 there, which turns the
+  // slot offsets into immediates of the load instructions
+  const int W = SLOTS > 1 ? 32 : rm.W, log2W = SLOTS > 1 ? 5 : rm.log2W;
+  const int sub = lane >> log2W, j = lane & (W - 1);
+  const int rows_per_warp = 32 >> log2W;
+  const int rows_per_trip = rows_per_warp * ROWS;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   bool stop = false, bad_target = false;
   int trip = 0;
+  // Addresses: one 64-bit pointer per trip (advanced by a constant), everything a lane adds to it is a 32-bit,
+  // loop-invariant offset.  (With `r * C + c` spelled out per element the compiler carried a dozen 64-bit induction
+  // variables: a third of the kernel's instructions were address arithmetic.)
+  const int trip_elems = rows_per_trip * C;  // <= 8 rows of <= 1024 classes
+  const char* tp = (const char*)a.preds + warp * trip_elems * Elem<PDT>::kBytes;
+  const int64_t tp_step = nwarps * trip_elems * Elem<PDT>::kBytes;
+  const char* const preds_end = (const char*)a.preds + rows * C * Elem<PDT>::kBytes;
+  const bool labels64 = a.tdt == TMB_I64;
+  // shared-memory counters of one class: [2][low_k] and one word of padding — an odd stride, so that the 32 lanes of
+  // a warp (32 consecutive classes, and for softmax scores mostly the same one or two bins) hit 32 different banks;
+  // with the even stride 2 * low_k the atomics of a warp took 3 (C = 100) to 8 (C = 1000) passes
+  const int class_words = 2 * low_k + 1;
+  const int class_stride = micro ? 0 : class_words;
   auto count = [&](int c, bool hot, int k) {
-    const int pair = (micro ? 0 : c) * 2 + (hot ? 1 : 0);
     if (k < low_k) {  // always, when the whole histogram is in shared memory (low_k == kbins)
-      atomicAdd(&hist[pair * low_k + k], 1u);
+      atomicAdd(&hist[c * class_stride + (hot ? low_k : 0) + k], 1u);
     } else {
-      atomicAdd(&gh[pair * kbins + k], 1ULL);
+      atomicAdd(&gh[((micro ? 0 : c) * 2 + (hot ? 1 : 0)) * kbins + k], 1ULL);
     }
   };
-  for (int64_t r0 = warp * rows_per_trip; r0 < rows && !stop; r0 += nwarps * rows_per_trip, ++trip) {  // warp-uniform
+  for (int64_t r0 = warp * rows_per_trip; r0 < rows && !stop; r0 += nwarps * rows_per_trip, tp += tp_step, ++trip) {
     {  // the rows of this warp's NEXT trip are one contiguous region of at most 4 KB: one L2 prefetch per 128-byte
        // line, so that the register loads of that trip wait for L2, not for DRAM (half of all stall samples)
-      const int64_t rn = r0 + nwarps * rows_per_trip;
-      const int64_t first = rn * C * Elem<PDT>::kBytes, end = min(rn + rows_per_trip, rows) * C * Elem<PDT>::kBytes;
-      const int64_t mine = (first & ~(int64_t)127) + (int64_t)lane * 128;
-      if (rn < rows && mine < end) prefetch_l2((const char*)a.preds + mine);
+      const char* nx = tp + tp_step;
+      const char* mine = (const char*)((uintptr_t)nx & ~(uintptr_t)127) + lane * 128;
+      if (mine < nx + trip_elems * Elem<PDT>::kBytes && mine < preds_end) prefetch_l2(mine);
     }
+    const int left = (int)min((int64_t)rows_per_trip, rows - r0);  // rows of this trip that exist
     float e[ROWS][SLOTS];
-    int64_t t[ROWS];
+    int t[ROWS];
     bool counted[ROWS];
 #pragma unroll
     for (int q = 0; q < ROWS; ++q) {
-      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
-      const bool active = r < rows;
-      t[q] = active ? load_label(a.target, a.tdt, r) : 0;
-      counted[q] = active && !(a.has_ignore && t[q] == a.ignore);
-      if (counted[q] && (t[q] < 0 || t[q] >= C)) bad_target = true;
-      const int64_t base = r * C;
+      const int row = q * rows_per_warp + sub;  // within the trip
+      const bool active = row < left;
+      int64_t label = 0;
+      if (active) label = labels64 ? __ldg((const long long*)a.target + (r0 + row)) : load_label(a.target, a.tdt, r0 + row);
+      counted[q] = active && !(a.has_ignore && label == a.ignore);
+      if (counted[q] && (label < 0 || label >= C)) bad_target = true;
+      t[q] = (int)label;  // out-of-range labels raise the error bit; what they count as does not matter
 #pragma unroll
       for (int it = 0; it < SLOTS; ++it) {
-        const int c = it * rm.W + j;
-        e[q][it] = (counted[q] && c < C) ? load_elem<PDT>(a.preds, base + c) : -INFINITY;
+        const int c = it * W + j;
+        e[q][it] = (counted[q] && c < C) ? load_elem<PDT>(tp, row * C + c) : -INFINITY;
       }
     }
     if (!SOFT) {
@@ -840,25 +856,26 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
       for (int q = 0; q < ROWS; ++q)
 #pragma unroll
         for (int it = 0; it < SLOTS; ++it)
-          if (counted[q] && it * rm.W + j < C) mine |= !(e[q][it] >= 0.0f && e[q][it] <= 1.0f);
+          if (counted[q] && it * W + j < C) mine |= !(e[q][it] >= 0.0f && e[q][it] <= 1.0f);
       if (mine) raise_flag(a);
       stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
       if (stop) break;
     } else {
       softmax_rows_inplace<PDT, SLOTS, ROWS>(e, rm);
     }
-#pragma unroll
-    for (int gi = 0; gi < kGroups; ++gi) {
+    // One batch of kPer elements through the binning code.  Element i is (row i / SLOTS, slot i % SLOTS) when a
+    // lane holds several rows (SLOTS < kPer), else slot slot0 + i of the one row, found in register e[0][i].
+    auto bin_group = [&](int slot0) {
       Decoded d;
       d.bad = 0;
       d.outside = 0;
-      // element i of the batch: (row q, slot it) — ROWS > 1 means SLOTS < kPer and one group
 #pragma unroll
       for (int i = 0; i < kPer; ++i) {
         const int q = ROWS > 1 ? i / SLOTS : 0;
-        const int it = ROWS > 1 ? i % SLOTS : gi * kPer + i;
-        const bool valid = it < SLOTS && counted[q] && it * rm.W + j < C;
-        d.x[i] = valid ? e[q][it < SLOTS ? it : 0] : 0.5f;
+        const int reg = ROWS > 1 ? i % SLOTS : (i < SLOTS ? i : 0);
+        const int it = ROWS > 1 ? reg : slot0 + i;
+        const bool valid = i < ROWS * SLOTS && counted[q] && it * W + j < C;
+        d.x[i] = valid ? e[q][reg] : 0.5f;
         d.inc[i] = valid ? 1u : 0u;
         d.toff[i] = 0u;
       }
@@ -870,11 +887,23 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
 #pragma unroll
       for (int i = 0; i < kPer; ++i) {
         const int q = ROWS > 1 ? i / SLOTS : 0;
-        const int it = ROWS > 1 ? i % SLOTS : gi * kPer + i;
-        if (it < SLOTS && d.inc[i]) {
-          const int c = it * rm.W + j;
-          count(c, c == (int)t[q], g[i]);
+        const int it = ROWS > 1 ? i % SLOTS : slot0 + i;
+        if (d.inc[i]) {
+          const int c = it * W + j;
+          count(c, c == t[q], g[i]);
         }
+      }
+    };
+    if constexpr (kGroups == 1) {
+      bin_group(0);
+    } else {
+      // wide rows: a rolled loop over the groups, the row shifted down by one group after each (the unrolled form
+      // was 5400 instructions, 86 KB of code, and a quarter of the stall samples were instruction fetches)
+#pragma unroll 1
+      for (int gi = 0; gi < kGroups; ++gi) {
+        bin_group(gi * kPer);
+#pragma unroll
+        for (int i = 0; i + kPer < SLOTS; ++i) e[0][i] = e[0][i + kPer];
       }
     }
   }
@@ -884,9 +913,10 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   if (dead || (!SOFT && flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
     const uint32_t v = hist[i];
-    if (v) {
-      const int64_t dst = (int64_t)(i / low_k) * kbins + (i % low_k);  // == i when low_k == kbins
-      atomicAdd(&gh[dst], (unsigned long long)v);
+    if (v) {  // never the padding word
+      const int cls = i / class_words, rem = i - cls * class_words;
+      const int hot = rem >= low_k ? 1 : 0;
+      atomicAdd(&gh[(int64_t)(cls * 2 + hot) * kbins + (rem - hot * low_k)], (unsigned long long)v);
     }
   }
 }
@@ -1381,20 +1411,16 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
   const int64_t pad_bytes = (int64_t)(a.T + 2 + 31) / 32 * 32 * 4;
   const int64_t pairs = (int64_t)a.L * 2, kbins = a.T + 1;
   const int64_t room = ((int64_t)dev_info().max_smem_optin - 1024 - pad_bytes) / 4;  // 32-bit counters that fit
-  int sh_bins, low_k;
-  if (pairs * kbins <= room) {
-    sh_bins = (int)(pairs * kbins);
-    low_k = (int)kbins;  // every bin is a "low" bin
-  } else {
-    low_k = (int)(room / pairs);  // 0 for an absurd class count: everything goes to global memory
-    if (low_k > kbins) low_k = (int)kbins;
-    sh_bins = (int)(pairs * low_k);
-    if (low_k == 0) low_k = -1;  // "nothing in shared memory": k < low_k never holds
-  }
+  // k2_mc_rows keeps 2 * low_k + 1 words per class (see class_words there), k2_mc_small 2 * low_k
+  int low_k = (int)((room / a.L - 1) / 2);  // <= 0 for an absurd class count: everything goes to global memory
+  if (low_k > kbins) low_k = (int)kbins;    // every bin is a "low" bin
+  if (low_k <= 0) low_k = -1;               // "nothing in shared memory": k < low_k never holds
+  const int sh_bins = low_k > 0 ? (int)((int64_t)a.L * (2 * low_k + 1)) : 0;
   const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
   int rc = 0;
-  if (C <= 32) {  // one thread per row (see k2_mc_small)
-    const int hist_words = (sh_bins + 31) / 32 * 32;
+  if (C <= 32 && low_k > 0) {  // one thread per row (see k2_mc_small)
+    const int small_bins = (int)(pairs * low_k);
+    const int hist_words = (small_bins + 31) / 32 * 32;
     const int small_smem = (int)pad_bytes + hist_words * 4 + kSmallRows * (C | 1) * 4;
     if (small_smem <= dev_info().max_smem_optin - 1024) {
       const int64_t work = (rows + kSmallRows - 1) / kSmallRows;
@@ -1405,10 +1431,10 @@ static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaS
     cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
     cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
     const int grid = resident_grid(kb, kSmallRows, small_smem, work);                           \
-    ka<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, sh_bins, low_k);                \
+    ka<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, small_bins, low_k);                \
     rc = launch_status();                                                                       \
     if (rc == 0) {                                                                              \
-      kb<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, sh_bins, low_k);              \
+      kb<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, small_bins, low_k);              \
       rc = launch_status();                                                                     \
     }                                                                                           \
   }
