@@ -802,7 +802,8 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   const int rows_per_trip = rows_per_warp * ROWS;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  bool stop = false, bad_target = false;
+  bool stop = false;
+  unsigned bad_target = 0;
   int trip = 0;
   // Addresses: one 64-bit pointer per trip (advanced by a constant), everything a lane adds to it is a 32-bit,
   // loop-invariant offset.  (With `r * C + c` spelled out per element the compiler carried a dozen 64-bit induction
@@ -832,23 +833,30 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
       if (mine < nx + trip_elems * Elem<PDT>::kBytes && mine < preds_end) prefetch_l2(mine);
     }
     const int left = (int)min((int64_t)rows_per_trip, rows - r0);  // rows of this trip that exist
+    // Scores and labels are requested together and the labels are first looked at after the softmax: a row whose
+    // loads waited for `target != ignore_index` paid two memory latencies back to back (13 % of the stall samples).
+    // Ignored rows are normalised like the others and dropped when the batch is counted.
     float e[ROWS][SLOTS];
-    int t[ROWS];
-    bool counted[ROWS];
+    int64_t label[ROWS];
 #pragma unroll
     for (int q = 0; q < ROWS; ++q) {
       const int row = q * rows_per_warp + sub;  // within the trip
       const bool active = row < left;
-      int64_t label = 0;
-      if (active) label = labels64 ? __ldg((const long long*)a.target + (r0 + row)) : load_label(a.target, a.tdt, r0 + row);
-      counted[q] = active && !(a.has_ignore && label == a.ignore);
-      if (counted[q] && (label < 0 || label >= C)) bad_target = true;
-      t[q] = (int)label;  // out-of-range labels raise the error bit; what they count as does not matter
+      label[q] = a.ignore;
+      if (active) label[q] = labels64 ? __ldg((const long long*)a.target + (r0 + row)) : load_label(a.target, a.tdt, r0 + row);
+      const char* lp = tp + (row * C + j) * Elem<PDT>::kBytes;  // slot offsets become immediates of the loads
 #pragma unroll
-      for (int it = 0; it < SLOTS; ++it) {
-        const int c = it * W + j;
-        e[q][it] = (counted[q] && c < C) ? load_elem<PDT>(tp, row * C + c) : -INFINITY;
-      }
+      for (int it = 0; it < SLOTS; ++it) e[q][it] = (active && it * W + j < C) ? load_elem<PDT>(lp, it * W) : -INFINITY;
+    }
+    if (SOFT) softmax_rows_inplace<PDT, SLOTS, ROWS>(e, rm);
+    int t[ROWS];
+    bool counted[ROWS];
+#pragma unroll
+    for (int q = 0; q < ROWS; ++q) {
+      const bool ignored = (q * rows_per_warp + sub >= left) | ((a.has_ignore != 0) & (label[q] == a.ignore));
+      counted[q] = !ignored;
+      bad_target |= (unsigned)(!ignored & ((uint64_t)label[q] >= (uint64_t)C));  // label < 0 or >= C
+      t[q] = (int)label[q];  // out-of-range labels raise the error bit; what they count as does not matter
     }
     if (!SOFT) {
       bool mine = false;
@@ -860,8 +868,6 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
       if (mine) raise_flag(a);
       stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
       if (stop) break;
-    } else {
-      softmax_rows_inplace<PDT, SLOTS, ROWS>(e, rm);
     }
     // One batch of kPer elements through the binning code.  Element i is (row i / SLOTS, slot i % SLOTS) when a
     // lane holds several rows (SLOTS < kPer), else slot slot0 + i of the one row, found in register e[0][i].

@@ -65,37 +65,41 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
   constexpr int ROWS = SLOTS < 8 ? 8 / SLOTS : 1;
   const bool soft = *flag == gen;
   const int lane = threadIdx.x & 31;
-  const int sub = lane >> rm.log2W, j = lane & (rm.W - 1);
-  const int rows_per_warp = 32 >> rm.log2W;
-  const int64_t rows_per_trip = (int64_t)rows_per_warp * ROWS;
+  const int W = SLOTS > 1 ? 32 : rm.W, log2W = SLOTS > 1 ? 5 : rm.log2W;  // several slots: the row takes the warp
+  const int sub = lane >> log2W, j = lane & (W - 1);
+  const int rows_per_warp = 32 >> log2W;
+  const int rows_per_trip = rows_per_warp * ROWS;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r0 = warp * rows_per_trip; r0 < rows; r0 += nwarps * rows_per_trip) {  // warp-uniform trip count
+  // one 64-bit pointer pair per trip; what a lane adds is a 32-bit loop-invariant offset (see k2_mc_rows)
+  const int trip_elems = rows_per_trip * C;
+  const int64_t first = warp * trip_elems * Elem<DT>::kBytes, step = nwarps * trip_elems * Elem<DT>::kBytes;
+  const char* tp = (const char*)x + first;
+  char* op = (char*)out + first;
+  const char* const x_end = (const char*)x + rows * C * Elem<DT>::kBytes;
+  for (int64_t r0 = warp * rows_per_trip; r0 < rows; r0 += nwarps * rows_per_trip, tp += step, op += step) {
     {
-      const int64_t rn = r0 + nwarps * rows_per_trip;
-      const int64_t first = rn * C * Elem<DT>::kBytes, end = min(rn + rows_per_trip, rows) * C * Elem<DT>::kBytes;
-      const int64_t mine = (first & ~(int64_t)127) + (int64_t)lane * 128;
-      if (rn < rows && mine < end) prefetch_l2((const char*)x + mine);
+      const char* nx = tp + step;
+      const char* mine = (const char*)((uintptr_t)nx & ~(uintptr_t)127) + lane * 128;
+      if (mine < nx + trip_elems * Elem<DT>::kBytes && mine < x_end) prefetch_l2(mine);
     }
+    const int left = (int)min((int64_t)rows_per_trip, rows - r0);
     float e[ROWS][SLOTS];
 #pragma unroll
     for (int q = 0; q < ROWS; ++q) {
-      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
+      const int row = q * rows_per_warp + sub;
+      const char* lp = tp + (row * C + j) * Elem<DT>::kBytes;  // slot offsets become immediates of the loads
 #pragma unroll
-      for (int it = 0; it < SLOTS; ++it) {
-        const int c = it * rm.W + j;
-        e[q][it] = (r < rows && c < C) ? load_elem<DT>(x, r * C + c) : -INFINITY;
-      }
+      for (int it = 0; it < SLOTS; ++it) e[q][it] = (row < left && it * W + j < C) ? load_elem<DT>(lp, it * W) : -INFINITY;
     }
     if (soft) softmax_rows_inplace<DT, SLOTS, ROWS>(e, rm);
 #pragma unroll
     for (int q = 0; q < ROWS; ++q) {
-      const int64_t r = r0 + (int64_t)q * rows_per_warp + sub;
+      const int row = q * rows_per_warp + sub;
+      char* sp = op + (row * C + j) * Elem<DT>::kBytes;
 #pragma unroll
-      for (int it = 0; it < SLOTS; ++it) {
-        const int c = it * rm.W + j;
-        if (r < rows && c < C) store_elem<DT>(out, r * C + c, e[q][it]);
-      }
+      for (int it = 0; it < SLOTS; ++it)
+        if (row < left && it * W + j < C) store_elem<DT>(sp, it * W, e[q][it]);
     }
   }
 }
