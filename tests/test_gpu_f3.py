@@ -57,6 +57,9 @@ def test_topk_ties_and_special_values_follow_torch_topk(C, k, dtype):
     preds[3, :] = 0.0
     if C > 1:
         preds[3, 1] = -0.0
+    preds[4, C // 2] = -float("nan")  # sign bit set
+    preds[5, :] = float("inf")
+    preds[5, 0] = float("nan")
     target = torch.randint(C, (n,), generator=g)
     target[::11] = -1
     dp, dt = preds.cuda(), target.cuda()

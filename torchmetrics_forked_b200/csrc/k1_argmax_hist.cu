@@ -870,16 +870,36 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
   if (r < rows) fetch(r);
   for (; r < rows; r += nwarps) {  // warp-uniform
     const int64_t t = load_label(target, tdt, r);
-    uint32_t key[VECS * 8];
+    // Keys, four instructions each: the score moves to the high half (it is there already for the odd elements),
+    // torch's order-preserving map is "flip everything if negative, else the sign" on the whole word, and one LOP3
+    // puts 0xffff - class into the low half.  NaN (-> 0xffff) needs a compare per element; instead one test per
+    // 32-bit word looks for an all-ones exponent (inf or NaN) in either half, and a lane that saw one redoes its
+    // keys with the exact rule.
+    constexpr uint32_t kExp2 = DT == TMB_BF16 ? 0x7f807f80u : 0x7c007c00u;  // exponent field of both halves
+    constexpr uint32_t kCarry2 = DT == TMB_BF16 ? 0x00800080u : 0x04000400u;  // + lowest exponent bit: carry into bit 15
+    uint32_t key[VECS * 8], group[VECS], special = 0;
 #pragma unroll
     for (int q = 0; q < VECS; ++q) {
       const int v = lane + 32 * q;
       const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
 #pragma unroll
+      for (int h = 0; h < 4; ++h) special |= ((w[h] & kExp2) + kCarry2) & 0x80008000u;
+#pragma unroll
       for (int e = 0; e < 8; ++e) {
-        const uint32_t bits = (e & 1) ? (w[e >> 1] >> 16) : (w[e >> 1] & 0xffffu);
-        const uint32_t idx = (uint32_t)v * 8u + e;
-        key[q * 8 + e] = v < n_vec ? (topk_key16<DT>(bits) << 16) | (0xffffu - idx) : 0u;
+        uint32_t k = (e & 1) ? (w[e >> 1] & 0xffff0000u) : (w[e >> 1] << 16);
+        k ^= (uint32_t)((int32_t)k >> 31) | 0x80000000u;
+        key[q * 8 + e] = (k & 0xffff0000u) | (0xffffu - ((uint32_t)v * 8u + e));
+      }
+    }
+    if (special) {
+#pragma unroll
+      for (int q = 0; q < VECS; ++q) {
+        const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const uint32_t bits = (e & 1) ? (w[e >> 1] >> 16) : (w[e >> 1] & 0xffffu);
+          key[q * 8 + e] = (topk_key16<DT>(bits) << 16) | (key[q * 8 + e] & 0xffffu);
+        }
       }
     }
     if (r + nwarps < rows) fetch(r + nwarps);  // the next row travels while this one is ranked
@@ -888,15 +908,38 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
       if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
       continue;
     }
+    // A lane keeps the maximum of each of its vectors (8 keys) and the maximum of those.  Keys are unique, so a round
+    // is one REDUX.MAX, and only the lane that owned the winner has anything to update: it clears the key in the one
+    // vector whose maximum it was and redoes that maximum (8 of its 32 keys; clearing and re-scanning all of them in
+    // every lane was 80 instructions a round, two fifths of the kernel).  Vectors past the row end never win.
+    auto group_max = [&](int q) {
+      uint32_t m = 0;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) m = max(m, key[q * 8 + e]);
+      return m;
+    };
+    uint32_t best = 0;
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      group[q] = lane + 32 * q < n_vec ? group_max(q) : 0u;
+      best = max(best, group[q]);
+    }
     bool hit = false;
     for (int round = 0; round < top_k; ++round) {
-      uint32_t best = 0;
-#pragma unroll
-      for (int i = 0; i < VECS * 8; ++i) best = max(best, key[i]);
       const uint32_t top = __reduce_max_sync(kFull, best);
       const int cls = (int)(0xffffu - (top & 0xffffu));
+      if (best == top && round + 1 < top_k) {  // the owner
+        best = 0;
 #pragma unroll
-      for (int i = 0; i < VECS * 8; ++i) key[i] = key[i] == top ? 0u : key[i];  // keys are unique: only the owner's
+        for (int q = 0; q < VECS; ++q) {
+          if (group[q] == top) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) key[q * 8 + e] = key[q * 8 + e] == top ? 0u : key[q * 8 + e];
+            group[q] = group_max(q);
+          }
+          best = max(best, group[q]);
+        }
+      }
       if (lane == 0) atomicAdd(&sh_topk[C + cls], 1);
       hit |= (int64_t)cls == t;
     }
