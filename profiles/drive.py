@@ -13,7 +13,7 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
 
 which = sys.argv[1] if len(sys.argv) > 1 else "k1"
-reps = int(sys.argv[2]) if len(sys.argv) > 2 and which != "f2" else 4
+reps = int(sys.argv[2]) if len(sys.argv) > 2 and which in ("k1", "k2", "k5") else 4
 dev = torch.device("cuda")
 g = torch.Generator(device=dev).manual_seed(0)
 
@@ -79,6 +79,9 @@ elif which == "f3":
     rows = 1 << 20
     t = torch.randint(1000, (rows,), generator=g, device=dev)
     p = torch.randn(rows, 1000, generator=g, device=dev).bfloat16()
+    if len(sys.argv) > 2 and sys.argv[2] == "fp32":
+        p = p.float()[: rows // 2]
+        t = t[: rows // 2]
     m = MulticlassAccuracy(1000, top_k=5, average="micro", validate_args=False).to(dev)
     for _ in range(3):
         m.update(p, t)

@@ -981,13 +981,26 @@ __global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ p
   if (r < rows) fetch(r);
   for (; r < rows; r += nwarps) {  // warp-uniform
     const int64_t t = load_label(target, tdt, r);
-    uint32_t key[VECS * 4];
+    // keys: "flip everything if negative, else the sign" is two instructions; NaN (-> all ones) is looked for once per
+    // lane (an all-ones exponent, i.e. inf or NaN, in any of its scores) and fixed up in the rare lane that has one
+    uint32_t key[VECS * 4], group[VECS];
+    bool special = false;
 #pragma unroll
     for (int q = 0; q < VECS; ++q) {
-      const bool live = lane + 32 * q < n_vec;
       const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) key[q * 4 + e] = live ? topk_key(__uint_as_float(w[e])) : 0u;
+      for (int e = 0; e < 4; ++e) {
+        special |= (w[e] & 0x7f800000u) == 0x7f800000u;
+        key[q * 4 + e] = w[e] ^ ((uint32_t)((int32_t)w[e] >> 31) | 0x80000000u);
+      }
+    }
+    if (special) {
+#pragma unroll
+      for (int q = 0; q < VECS; ++q) {
+        const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) key[q * 4 + e] = topk_key(__uint_as_float(w[e]));
+      }
     }
     if (r + nwarps < rows) fetch(r + nwarps);
     if (has_ignore && t == ignore) continue;
@@ -995,23 +1008,42 @@ __global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ p
       if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
       continue;
     }
+    // Per-vector maxima as in k1_rows_topk16.  Equal scores are possible here: the lanes holding the warp maximum
+    // name the lowest class they hold it for (vectors and elements ascend with the class inside a lane), REDUX.MIN
+    // picks the lowest of those, and the lane that named it clears that one key and redoes that one vector.
+    auto group_max = [&](int q) { return max(max(key[q * 4], key[q * 4 + 1]), max(key[q * 4 + 2], key[q * 4 + 3])); };
+    uint32_t best = 0;
+#pragma unroll
+    for (int q = 0; q < VECS; ++q) {
+      group[q] = lane + 32 * q < n_vec ? group_max(q) : 0u;  // 0: padding, below every real key
+      best = max(best, group[q]);
+    }
     bool hit = false;
     for (int round = 0; round < top_k; ++round) {
-      uint32_t best = 0;
-      int best_i = 0;
+      const uint32_t top = __reduce_max_sync(kFull, best);
+      uint32_t mine = 0xffffffffu;
+      if (best == top) {
 #pragma unroll
-      for (int i = 0; i < VECS * 4; ++i) {
-        if (key[i] > best) {  // slots ascend with the class index inside a lane: the first maximum is the lowest class
-          best = key[i];
-          best_i = i;
+        for (int q = VECS - 1; q >= 0; --q) {
+          if (group[q] == top) {
+            const int e = key[q * 4] == top ? 0 : (key[q * 4 + 1] == top ? 1 : (key[q * 4 + 2] == top ? 2 : 3));
+            mine = (uint32_t)((lane + 32 * q) * 4 + e);
+          }
         }
       }
-      const uint32_t top = __reduce_max_sync(kFull, best);
-      const uint32_t mine = (uint32_t)((lane + 32 * (best_i >> 2)) * 4 + (best_i & 3));
-      const uint32_t cls = __reduce_min_sync(kFull, best == top ? mine : 0xffffffffu);
+      const uint32_t cls = __reduce_min_sync(kFull, mine);
+      if (mine == cls && round + 1 < top_k) {  // the owner
+        best = 0;
 #pragma unroll
-      for (int i = 0; i < VECS * 4; ++i)
-        if ((uint32_t)((lane + 32 * (i >> 2)) * 4 + (i & 3)) == cls) key[i] = 0u;
+        for (int q = 0; q < VECS; ++q) {
+          if ((uint32_t)(lane + 32 * q) == (cls >> 2)) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) key[q * 4 + e] = (uint32_t)e == (cls & 3u) ? 0u : key[q * 4 + e];
+            group[q] = group_max(q);
+          }
+          best = max(best, group[q]);
+        }
+      }
       if (lane == 0) atomicAdd(&sh_topk[C + (int)cls], 1);
       hit |= (int64_t)cls == t;
     }

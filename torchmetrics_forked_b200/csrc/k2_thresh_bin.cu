@@ -953,6 +953,7 @@ __global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows
   const bool on_grid = bn.grid_eps < 0.01f;
   unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
   const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;  // e / C for e * C < 2^32
+  const int class_stride = micro ? 0 : 2 * low_k;  // [C][2][low_k] counters in shared memory
   bool bad_target = false;
   int stop = 0;
   constexpr int kGroups = (W + kPer - 1) / kPer;
@@ -970,6 +971,7 @@ __global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows
     const int64_t t = active ? load_label(a.target, a.tdt, tile0 + r) : 0;
     const bool counted = active && !(a.has_ignore && t == a.ignore);
     if (counted && (t < 0 || t >= C)) bad_target = true;
+    const int tc = (int)t;
     float e[W];
 #pragma unroll
     for (int c = 0; c < W; ++c) e[c] = 0.0f;
@@ -1018,11 +1020,11 @@ __global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows
       for (int i = 0; i < kPer; ++i) {
         const int c = gi * kPer + i;
         if (d.inc[i]) {
-          const int pair = (micro ? 0 : c) * 2 + (c == (int)t ? 1 : 0);
+          const bool hot = c == tc;
           if (g[i] < low_k)
-            atomicAdd(&hist[pair * low_k + g[i]], 1u);
+            atomicAdd(&hist[c * class_stride + (hot ? low_k : 0) + g[i]], 1u);
           else
-            atomicAdd(&gh[pair * kbins + g[i]], 1ULL);
+            atomicAdd(&gh[((micro ? 0 : c) * 2 + (hot ? 1 : 0)) * kbins + g[i]], 1ULL);
         }
       }
     }
