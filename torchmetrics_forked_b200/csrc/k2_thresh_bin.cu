@@ -23,417 +23,9 @@
 // works on 8 samples stage by stage so their dependency chains interleave, and 16 warps per SM (bytes, not
 // 16-bit pairs, made that fit) cover the rest.  Loads: one register batch ahead plus L2 prefetches four
 // batches ahead.
-#include "common.cuh"
-#include "softmax_rows.cuh"
+#include "k2_binning.cuh"
 
 namespace tmb {
-
-constexpr int kHdr = 8;  // scratch[0] = "saw a value outside [0,1]" flag, [1..7] reserved
-
-struct TbArgs {
-  const void* preds;
-  const void* target;
-  const float* thr;
-  unsigned long long* scratch;
-  int* err;
-  int64_t n_total;  // n_outer * L * S
-  int64_t S;
-  int64_t ignore;
-  int L;
-  int T;
-  int pdt;  // float code, or label code when preds_is_label
-  int tdt;
-  int preds_is_label;
-  int cmp_gt;
-  int has_ignore;
-  int flag_counts_ignored;
-};
-
-__device__ __forceinline__ unsigned long long* hist_base(const TbArgs& a, int variant) {
-  return a.scratch + kHdr + (int64_t)variant * a.L * 2 * (a.T + 1);
-}
-
-// torch's CUDA sigmoid for fp32 opmath: 1 / (1 + exp(-x)), IEEE division, full-precision expf
-// (aten/src/ATen/native/cuda/UnarySpecialOpsKernel.cu; the reference calls it at
-// precision_recall_curve.py:184).  Narrow dtypes round the result back, like the reference tensor would.
-template <int DT>
-__device__ __forceinline__ float sigmoid_as(float x) {
-  float y = 1.0f / (1.0f + expf(-x));
-  if constexpr (DT == TMB_BF16) y = __bfloat162float(__float2bfloat16_rn(y));
-  if constexpr (DT == TMB_F16) y = __half2float(__float2half_rn(y));
-  return y;
-}
-
-// Number of thresholds j with thr[j] <= q (GE mode) or thr[j] < q (GT mode); thr ascending; NaN -> 0.
-// `pad` is the threshold array with sentinels: pad[0] = -inf, pad[1 + j] = thr[j], pad[T + 1] = +inf, so
-// "k is the right bin" reads  pad[k] <= q  and not  pad[k + 1] <= q  without any index special-casing.
-struct Binner {
-  const float* pad;  // shared or global, T + 2 entries
-  int T;
-  float lo, scale;  // guess = (q - lo) * scale
-  // u(q) = fmaf(q, scale, 1 - lo*scale) maps threshold j to (nearly) the integer j + 1.  grid_eps is the largest
-  // distance of any u(thr[j]) from j + 1: because u() is monotone in q, a sample whose u lies further than grid_eps
-  // from every integer is on a known side of every threshold — no compare against the buffer needed.  A small
-  // grid_eps means the thresholds are (numerically) evenly spaced, e.g. torch.linspace.
-  float grid_eps;
-  bool gt;
-  __device__ __forceinline__ bool below(float t, float q) const { return gt ? (t < q) : (t <= q); }
-  __device__ __forceinline__ int guess(float q) const {
-    float gf = (q - lo) * scale;
-    gf = fminf(fmaxf(gf, -1.0f), (float)T);  // NaN -> -1
-    int g = (int)gf + 1;
-    return g > T ? T : g;
-  }
-  __device__ __forceinline__ bool verified(int g, float q) const {
-    return (below(pad[g], q) && !below(pad[g + 1], q)) || (q != q && g == 0);
-  }
-  __device__ __forceinline__ int bisect(float q) const {  // cold path: guess was off
-    int lo_i = 0, hi_i = T;
-    while (lo_i < hi_i) {
-      int mid = (lo_i + hi_i) >> 1;
-      if (below(pad[mid + 1], q)) lo_i = mid + 1; else hi_i = mid;
-    }
-    return lo_i;
-  }
-  __device__ __forceinline__ int bin(float q) const {
-    int g = guess(q);
-    return verified(g, q) ? g : bisect(q);
-  }
-};
-
-// `sh_pad` must hold T + 2 floats when T + 2 <= sh_cap; otherwise the padded copy in the scratch tail is
-// not available and the caller passes a global padded array instead.
-__device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_pad, int sh_cap, const float* global_pad) {
-  Binner b;
-  b.T = a.T;
-  b.gt = a.cmp_gt != 0;
-  if (a.T + 2 <= sh_cap) {
-    for (int i = threadIdx.x; i < a.T + 2; i += blockDim.x)
-      sh_pad[i] = (i == 0) ? -INFINITY : (i == a.T + 1 ? INFINITY : a.thr[i - 1]);
-    __syncthreads();
-    b.pad = sh_pad;
-  } else {
-    b.pad = global_pad;
-  }
-  float lo = a.thr[0], hi = a.thr[a.T - 1];
-  float span = hi - lo;
-  b.lo = lo;
-  b.scale = (span > 0.0f && a.T > 1) ? (float)(a.T - 1) / span : 0.0f;
-  // how far the thresholds are from the evenly spaced grid, in bins (CTA-wide maximum)
-  __shared__ unsigned grid_eps_bits;
-  if (threadIdx.x == 0) grid_eps_bits = 0u;
-  __syncthreads();
-  const float bias = 1.0f - lo * b.scale;
-  float worst = 0.0f;
-  for (int j = threadIdx.x; j < a.T; j += blockDim.x) {
-    float d = fabsf(fmaf(a.thr[j], b.scale, bias) - (float)(j + 1));
-    worst = (d == d) ? fmaxf(worst, d) : INFINITY;
-  }
-  atomicMax(&grid_eps_bits, __float_as_uint(worst));  // non-negative floats order like their bit patterns
-  __syncthreads();
-  b.grid_eps = (b.scale > 0.0f) ? __uint_as_float(grid_eps_bits) : INFINITY;
-  return b;
-}
-
-__device__ __forceinline__ bool flag_up(const TbArgs& a) {
-  return *((volatile unsigned long long*)a.scratch) != 0ULL;
-}
-__device__ __forceinline__ void raise_flag(const TbArgs& a) { *((volatile unsigned long long*)a.scratch) = 1ULL; }
-
-// CTA-uniform decision whether this pass has anything to do (the flag may flip while pass A runs, so
-// one thread samples it for everybody).
-__device__ __forceinline__ bool pass_enabled(const TbArgs& a, bool sig_pass) {
-  __shared__ int go;
-  if (threadIdx.x == 0) go = sig_pass ? flag_up(a) : !flag_up(a);
-  __syncthreads();
-  return go != 0;
-}
-
-// ---- binary fast path: lane-private packed histograms ------------------------------------------------
-// Targets are decoded from their raw 32-bit halves (no 64-bit arithmetic in the hot loop): four
-// consecutive targets starting at element i (i % 4 == 0, base pointer 16-byte aligned).
-template <int TDT>
-__device__ __forceinline__ void load_targets4(const void* base, int64_t i, uint32_t lo[4], uint32_t hi[4]) {
-  if constexpr (TDT == TMB_I64) {
-    uint4 a = ldg_stream16((const char*)base + i * 8);
-    uint4 b = ldg_stream16((const char*)base + i * 8 + 16);
-    lo[0] = a.x; hi[0] = a.y; lo[1] = a.z; hi[1] = a.w;
-    lo[2] = b.x; hi[2] = b.y; lo[3] = b.z; hi[3] = b.w;
-  } else if constexpr (TDT == TMB_I32) {
-    uint4 a = ldg_stream16((const char*)base + i * 4);
-    lo[0] = a.x; lo[1] = a.y; lo[2] = a.z; lo[3] = a.w;
-#pragma unroll
-    for (int e = 0; e < 4; ++e) hi[e] = (uint32_t)((int)lo[e] >> 31);
-  } else {
-    uint32_t w = ldg_stream4((const char*)base + i);
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      uint32_t b = (w >> (8 * e)) & 0xffu;
-      if (TDT == TMB_I8) {
-        lo[e] = (uint32_t)(int)(signed char)b;
-        hi[e] = (uint32_t)((int)lo[e] >> 31);
-      } else {
-        lo[e] = b;
-        hi[e] = 0u;
-      }
-    }
-  }
-}
-
-template <int PDT>
-__device__ __forceinline__ void load_preds4(const void* base, int64_t i, float x[4]) {
-  if constexpr (PDT == TMB_F32) {
-    uint4 a = ldg_stream16((const char*)base + i * 4);
-    x[0] = __uint_as_float(a.x); x[1] = __uint_as_float(a.y);
-    x[2] = __uint_as_float(a.z); x[3] = __uint_as_float(a.w);
-  } else {
-    uint2 a = ldg_stream8((const char*)base + i * 2);
-    x[0] = Elem<PDT>::get(a.x, 0); x[1] = Elem<PDT>::get(a.x, 1);
-    x[2] = Elem<PDT>::get(a.y, 0); x[3] = Elem<PDT>::get(a.y, 1);
-  }
-}
-
-// Lane-private counters, one BYTE per (bin, target class, lane): byte (k*2 + t)*32 + lane of the warp's block.
-// Four neighbouring lanes share a 32-bit word and therefore a bank, but they touch different bytes of it, which
-// the shared-memory pipe merges like any sub-word access: no conflicts, no atomics.  Bytes instead of 16-bit
-// pairs halve the footprint — (T+1)*64 B per warp, 16 warps per SM at T = 200 instead of 8 — and occupancy is
-// what this kernel is short of (with 2 warps per scheduler every dependent instruction pair left issue slots
-// empty: "stall_wait" was the top stall reason at 49 % issue utilisation).  A byte overflows after 255 hits, so
-// each warp folds its block into the CTA-wide 32-bit histogram every kFoldEvery batches: one lane per row,
-// 32 bytes summed with eight dp4a, about 1 extra instruction per sample.
-struct LaneHist {
-  uint8_t* col;        // this warp's [(T+1)*2][32] bytes, already offset by the lane
-  uint8_t* warp_base;  // the same block without the lane offset (16-byte aligned)
-  uint32_t* cta_hist;  // [2*(T+1)] words shared by the CTA, row r = k*2 + t
-  int lane;
-  int batches;         // batches binned since the last fold
-};
-
-constexpr int kBatch = 2;         // vectors of 4 samples per thread per iteration
-constexpr int kPer = kBatch * 4;  // samples per thread per iteration
-constexpr int kFoldEvery = 255 / kPer;  // a lane adds at most kPer to one byte per batch
-
-__device__ __forceinline__ void lane_fold(const TbArgs& a, LaneHist& h) {
-  __syncwarp();
-  const int rows = 2 * (a.T + 1);
-  for (int r = h.lane; r < rows; r += 32) {
-    uint4* row = reinterpret_cast<uint4*>(h.warp_base + r * 32);
-    const uint4 lo = row[0], hi = row[1];
-    row[0] = make_uint4(0u, 0u, 0u, 0u);
-    row[1] = make_uint4(0u, 0u, 0u, 0u);
-    unsigned s = 0;
-    s = __dp4a(lo.x, 0x01010101u, s); s = __dp4a(lo.y, 0x01010101u, s);
-    s = __dp4a(lo.z, 0x01010101u, s); s = __dp4a(lo.w, 0x01010101u, s);
-    s = __dp4a(hi.x, 0x01010101u, s); s = __dp4a(hi.y, 0x01010101u, s);
-    s = __dp4a(hi.z, 0x01010101u, s); s = __dp4a(hi.w, 0x01010101u, s);
-    if (s) atomicAdd(&h.cta_hist[r], s);
-  }
-  h.batches = 0;
-  __syncwarp();
-}
-
-struct Batch {  // what the loads deliver
-  float x[kPer];
-  uint32_t lo[kPer], hi[kPer];
-};
-
-struct Decoded {  // what is left of a batch once its registers have been released to the next loads
-  float x[kPer];
-  uint32_t inc[kPer];   // 1 = counted, 0 = not
-  uint32_t toff[kPer];  // byte offset of the target class inside a bin: t * 32
-  unsigned bad;         // non-zero: a target that is neither 0, 1 nor ignored
-  unsigned outside;     // non-zero: a value outside [0,1] that takes part in the sigmoid test (pass A)
-};
-
-// Filtered exact binning of sigmoid(x) (fp32 only).  The bin only changes when q crosses a threshold, so the
-// exact value of q is needed only near one.  A 4-instruction approximation qa = 1/(1 + 2^(-x*log2e))
-// (FMUL, MUFU.EX2, FADD, MUFU.RCP) comes with a rigorous bound on its distance from q, the value torch's
-// kernel (full-precision expf + IEEE divide) returns:
-//   2^(..) vs e^-x : ex2.approx is good to 2 ulp and the rounding of x*log2e costs |x*log2e| * 2^-24 in the
-//                    exponent, i.e. at most (2 + 1.173|x|) ulp in e  (the bound CUDA documents for __expf)
-//   1 + e          : 0.5 ulp;   approximate reciprocal: 1 ulp
-//   q itself       : torch's expression is within 3 ulp of the true value
-// so |qa - q| <= (6.5 + 1.173|x|) ulp * q.  The margin used is twice that, rel(x) = 1.6e-6 + 2.9e-7|x|, plus
-// 1e-30 absolute for the flushed-to-zero ends (|x| > 87, where both expressions saturate at 0 / 1).  If the
-// approximate score clears every threshold by more than the margin the bin is certain; otherwise (about 0.2 %
-// of the samples at T = 200) the sample is re-done with the exact expression.  The result is bit-identical to
-// binning torch's sigmoid at a third of the instructions.
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
-// Cold path.  Arguments by value so that the caller's Binner stays in registers (a by-reference call put it in
-// local memory and the reloads showed up as long-scoreboard stalls): exact score, then guess / verify / bisect
-// against the threshold buffer.
-template <int PDT, bool SIG>
-__device__ __noinline__ int exact_bin(const float* pad, int T, float lo, float scale, bool gt, float x) {
-  Binner b;
-  b.pad = pad;
-  b.T = T;
-  b.lo = lo;
-  b.scale = scale;
-  b.gt = gt;
-  b.grid_eps = 0.0f;
-  if (SIG && PDT == TMB_F32) {
-    // The grid test loses its resolution right at the first / last threshold, where saturated sigmoids pile up
-    // (q ~ 1e-9 is certainly above a threshold of 0, yet u(q) rounds onto the integer).  Before paying for the
-    // exact expression, bracket the score: the bin is monotone in q, so if q - margin and q + margin fall into
-    // the same bin of the real threshold buffer, that is the bin.
-    const float q = rcp_approx(1.0f + ex2_approx(x * -1.4426950408889634f));
-    const float margin = fmaf(q, fmaf(fabsf(x), 2.9e-7f, 1.6e-6f), 1e-30f);
-    if (margin < 1.0f) {  // false for NaN / infinite inputs: those go straight to the exact expression
-      const int k_low = b.bin(q - margin), k_high = b.bin(q + margin);
-      if (k_low == k_high) return k_low;
-    }
-  }
-  return b.bin(SIG ? sigmoid_as<PDT>(x) : x);
-}
-
-// First touch of a freshly loaded batch: everything that depends on the targets, and a copy of the scores.
-// After this the load registers are dead, so the NEXT batch can be requested into them right away; the wait
-// that precedes this function therefore only ever covers loads that are really needed now.  (With two register
-// buffers the wait for batch i also waited for the just-issued loads of batch i+1 whenever both shared one of
-// the six scoreboard slots — 21 % of the kernel's stall samples sat on that one instruction.)
-template <bool SIG, bool FULL, bool IGN>
-__device__ __forceinline__ void decode_batch(const TbArgs& a, const Batch& s, unsigned live, Decoded& d) {
-  const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
-  d.bad = 0;
-  d.outside = 0;
-#pragma unroll
-  for (int i = 0; i < kPer; ++i) {
-    const unsigned is_live = FULL ? 1u : ((live >> i) & 1u);
-    const unsigned kept = IGN ? (unsigned)!((s.lo[i] == ign_lo) & (s.hi[i] == ign_hi)) : 1u;
-    const unsigned not01 = s.hi[i] | (s.lo[i] >> 1);  // zero exactly for targets 0 and 1
-    const unsigned counted = is_live & kept & (unsigned)(not01 == 0u);
-    d.bad |= (is_live & kept) ? not01 : 0u;
-    if (!SIG) {
-      const unsigned outside = (unsigned)!(s.x[i] >= 0.0f && s.x[i] <= 1.0f);
-      d.outside |= is_live & outside & (kept | (unsigned)(a.flag_counts_ignored != 0));
-    }
-    d.inc[i] = counted;
-    d.toff[i] = (s.lo[i] & 1u) * 32u;
-    d.x[i] = s.x[i];
-  }
-}
-
-// Bins of kPer decoded samples.  Written stage by stage over all kPer samples (not sample by sample) so that the
-// dependency chains of different samples interleave.  GRID = thresholds on a (numerically) even grid: certainty
-// comes from arithmetic alone; otherwise the two neighbouring thresholds of the guess are fetched and compared.
-template <int PDT, bool SIG, bool GRID>
-__device__ __forceinline__ void batch_bins(const Binner& bn, const Decoded& d, int (&g)[kPer]) {
-  constexpr bool kFiltered = SIG && PDT == TMB_F32;
-  float q[kPer], lowq[kPer], highq[kPer], slack[kPer];
-  const float bias = 1.0f - bn.lo * bn.scale;
-  const float top = (float)bn.T;
-
-  // stage 1: the score each sample is binned by
-  if (kFiltered) {
-    float e[kPer];
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) e[i] = ex2_approx(d.x[i] * -1.4426950408889634f);
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) q[i] = rcp_approx(1.0f + e[i]);
-    if (GRID) {
-      // uncertainty of u(q) in bins: the score margin scaled, the grid's own unevenness, 2 ulp of u.  The margin
-      // rel(x) * q + 1e-30 is bounded with q <= 1, which makes the slack ONE fma of |x| (constants folded per
-      // kernel) instead of three dependent ones; the bound is looser only where q is small, i.e. below the first
-      // thresholds, and the fraction of samples sent to the exact path stays ~0.2 %.
-      const float c1 = 2.9e-7f * bn.scale;
-      const float c0 = fmaf(1.6e-6f, bn.scale, bn.grid_eps + top * 2.4e-7f + 1e-30f * bn.scale);
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) slack[i] = fmaf(fabsf(d.x[i]), c1, c0);
-    } else {
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const float rel = fmaf(fabsf(d.x[i]), 2.9e-7f, 1.6e-6f);
-        const float margin = fmaf(q[i], rel, 1e-30f);
-        lowq[i] = q[i] - margin;
-        highq[i] = q[i] + margin;
-      }
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) q[i] = SIG ? sigmoid_as<PDT>(d.x[i]) : d.x[i];
-  }
-  // stage 2: guessed bin
-  float below[kPer], above[kPer], off_centre[kPer];
-  if (GRID) {
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) {
-      // below the first / above the last threshold (and NaN) clamp to the middle of the end bins: certain
-      const float u = fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.5f), top + 0.5f);
-      const float fl = floorf(u);
-      g[i] = (int)fl;
-      off_centre[i] = fabsf((u - fl) - 0.5f);  // 0 in the middle of a bin, 0.5 on a threshold
-    }
-  } else {
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) g[i] = (int)fminf(fmaxf(fmaf(q[i], bn.scale, bias), 0.0f), top);  // NaN -> 0
-#pragma unroll
-    for (int i = 0; i < kPer; ++i) {
-      below[i] = bn.pad[g[i]];
-      above[i] = bn.pad[g[i] + 1];
-    }
-  }
-  // stage 3: is the guess certain?
-  unsigned recheck = 0;
-#pragma unroll
-  for (int i = 0; i < kPer; ++i) {
-    unsigned sure;
-    if (GRID) {
-      // exact scores only carry the grid's unevenness; approximate ones add their own margin (see stage 1)
-      const float allowed = kFiltered ? slack[i] : bn.grid_eps;
-      sure = (unsigned)(off_centre[i] + allowed < 0.5f);
-    } else if (kFiltered) {
-      // certain for `>=` thresholds and for `>` thresholds alike: q lies strictly between the neighbours
-      sure = (unsigned)((below[i] < lowq[i]) & (highq[i] < above[i]));
-    } else {
-      const unsigned lo_ok = bn.gt ? (unsigned)(below[i] < q[i]) : (unsigned)(below[i] <= q[i]);
-      const unsigned hi_ok = bn.gt ? (unsigned)!(above[i] < q[i]) : (unsigned)!(above[i] <= q[i]);
-      sure = (lo_ok & hi_ok) | (unsigned)((q[i] != q[i]) & (g[i] == 0));
-    }
-    recheck |= (sure ^ 1u) << i;
-  }
-  // cold path: too close to a threshold for the approximation, or a guess that missed
-  if (recheck) {
-#pragma unroll
-    for (int i = 0; i < kPer; ++i)
-      if ((recheck >> i) & 1u) g[i] = exact_bin<PDT, SIG>(bn.pad, bn.T, bn.lo, bn.scale, bn.gt, d.x[i]);
-  }
-}
-
-template <int PDT, bool SIG, bool GRID>
-__device__ __forceinline__ void bin_batch(const Binner& bn, LaneHist& h, const Decoded& d) {
-  int g[kPer];
-  batch_bins<PDT, SIG, GRID>(bn, d, g);
-  // stage 4: the read-modify-writes on this lane's own bytes.  Done four at a time: the four loads are issued
-  // together, a sample whose counter repeats an earlier one of the group takes that one's updated value instead
-  // of its own (stale) load, and the stores go out in order so the last writer holds the complete count.  This
-  // cuts the LDS->IADD->STS dependency chain from kPer links to kPer/4.
-#pragma unroll
-  for (int i = 0; i < kPer; i += 4) {
-    const uint32_t o0 = g[i] * 64 + d.toff[i], o1 = g[i + 1] * 64 + d.toff[i + 1];
-    const uint32_t o2 = g[i + 2] * 64 + d.toff[i + 2], o3 = g[i + 3] * 64 + d.toff[i + 3];
-    const uint32_t v0 = h.col[o0], v1 = h.col[o1], v2 = h.col[o2], v3 = h.col[o3];
-    const uint32_t u0 = v0 + d.inc[i];
-    const uint32_t u1 = (o1 == o0 ? u0 : v1) + d.inc[i + 1];
-    const uint32_t u2 = (o2 == o1 ? u1 : (o2 == o0 ? u0 : v2)) + d.inc[i + 2];
-    const uint32_t u3 = (o3 == o2 ? u2 : (o3 == o1 ? u1 : (o3 == o0 ? u0 : v3))) + d.inc[i + 3];
-    h.col[o0] = (uint8_t)u0;
-    h.col[o1] = (uint8_t)u1;
-    h.col[o2] = (uint8_t)u2;
-    h.col[o3] = (uint8_t)u3;
-  }
-  h.batches += 1;
-}
-
 template <int PDT, int TDT, bool SIG>
 __global__ void __launch_bounds__(512, 1) k2_binary_lanes(TbArgs a, int warps_per_cta) {
   extern __shared__ uint32_t sh_u32[];
@@ -764,283 +356,6 @@ __global__ void __launch_bounds__(512, 1) k2_multi(TbArgs a) {
   }
 }
 
-// ---- multiclass binned curves: row softmax fused into the binning ------------------------------
-// _multiclass_precision_recall_curve_format/_update (precision_recall_curve.py:423-527): softmax over the classes
-// if any kept value is outside [0,1], then every (row, class) element is binned against the thresholds with the
-// one-hot target `class == target[row]`.  The reference materialises the probabilities and an N x C x T
-// comparison (or loops T times over N x C); here a sub-warp keeps a row in registers in the lane layout of
-// torch's persistent softmax (softmax_rows.cuh: bit-identical probabilities), bins its elements and adds them to
-// the CTA-wide [C][2][T+1] histogram in shared memory — the logits are read once, nothing is written but counts.
-// `micro` folds all classes into label 0 (the reference flattens preds and one-hot targets into one binary task).
-// Histograms that do not fit one SM go to global memory with one atomic per element.
-// A lane takes kPer elements per trip through the binning code: SLOTS elements of each of ROWS = kPer / SLOTS rows
-// when a row gives it fewer than kPer (C <= 128), so narrow rows (C = 10: one element per lane and row) still fill
-// the batch and keep ROWS loads in flight.  When the [C][2][T+1] histogram does not fit one SM (C = 1000, T = 200
-// is 1.6 MB) only the lowest `low_k` bins of every (class, target) pair live in shared memory — softmax mass of a
-// wide row sits near 0 — and the rest goes to global memory with one atomic per element.
-template <int PDT, bool SOFT, int SLOTS>
-__global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
-    k2_mc_rows(TbArgs a, RowMap rm, int64_t rows, int C, int micro, int sh_bins, int low_k) {
-  constexpr int ROWS = SLOTS < kPer ? kPer / SLOTS : 1;
-  constexpr int kGroups = (SLOTS + kPer - 1) / kPer;
-  extern __shared__ uint32_t sh_u32[];
-  if (!pass_enabled(a, SOFT)) return;
-  float* sh_pad = (float*)sh_u32;
-  const int pad_words = (a.T + 2 + 31) / 32 * 32;
-  const int kbins = a.T + 1;
-  uint32_t* hist = sh_u32 + pad_words;
-  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
-  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
-  const bool on_grid = bn.grid_eps < 0.01f;
-  unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
-  const int lane = threadIdx.x & 31;
-  // more than one slot per lane means the row takes the whole warp: W is a compile-time 32 there, which turns the
-  // slot offsets into immediates of the load instructions
-  const int W = SLOTS > 1 ? 32 : rm.W, log2W = SLOTS > 1 ? 5 : rm.log2W;
-  const int sub = lane >> log2W, j = lane & (W - 1);
-  const int rows_per_warp = 32 >> log2W;
-  const int rows_per_trip = rows_per_warp * ROWS;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  bool stop = false;
-  unsigned bad_target = 0;
-  int trip = 0;
-  // Addresses: one 64-bit pointer per trip (advanced by a constant), everything a lane adds to it is a 32-bit,
-  // loop-invariant offset.  (With `r * C + c` spelled out per element the compiler carried a dozen 64-bit induction
-  // variables: a third of the kernel's instructions were address arithmetic.)
-  const int trip_elems = rows_per_trip * C;  // <= 8 rows of <= 1024 classes
-  const char* tp = (const char*)a.preds + warp * trip_elems * Elem<PDT>::kBytes;
-  const int64_t tp_step = nwarps * trip_elems * Elem<PDT>::kBytes;
-  const char* const preds_end = (const char*)a.preds + rows * C * Elem<PDT>::kBytes;
-  const bool labels64 = a.tdt == TMB_I64;
-  // shared-memory counters of one class: [2][low_k] and one word of padding — an odd stride, so that the 32 lanes of
-  // a warp (32 consecutive classes, and for softmax scores mostly the same one or two bins) hit 32 different banks;
-  // with the even stride 2 * low_k the atomics of a warp took 3 (C = 100) to 8 (C = 1000) passes
-  const int class_words = 2 * low_k + 1;
-  const int class_stride = micro ? 0 : class_words;
-  auto count = [&](int c, bool hot, int k) {
-    if (k < low_k) {  // always, when the whole histogram is in shared memory (low_k == kbins)
-      atomicAdd(&hist[c * class_stride + (hot ? low_k : 0) + k], 1u);
-    } else {
-      atomicAdd(&gh[((micro ? 0 : c) * 2 + (hot ? 1 : 0)) * kbins + k], 1ULL);
-    }
-  };
-  for (int64_t r0 = warp * rows_per_trip; r0 < rows && !stop; r0 += nwarps * rows_per_trip, tp += tp_step, ++trip) {
-    {  // the rows of this warp's NEXT trip are one contiguous region of at most 4 KB: one L2 prefetch per 128-byte
-       // line, so that the register loads of that trip wait for L2, not for DRAM (half of all stall samples)
-      const char* nx = tp + tp_step;
-      const char* mine = (const char*)((uintptr_t)nx & ~(uintptr_t)127) + lane * 128;
-      if (mine < nx + trip_elems * Elem<PDT>::kBytes && mine < preds_end) prefetch_l2(mine);
-    }
-    const int left = (int)min((int64_t)rows_per_trip, rows - r0);  // rows of this trip that exist
-    // Scores and labels are requested together and the labels are first looked at after the softmax: a row whose
-    // loads waited for `target != ignore_index` paid two memory latencies back to back (13 % of the stall samples).
-    // Ignored rows are normalised like the others and dropped when the batch is counted.
-    float e[ROWS][SLOTS];
-    int64_t label[ROWS];
-#pragma unroll
-    for (int q = 0; q < ROWS; ++q) {
-      const int row = q * rows_per_warp + sub;  // within the trip
-      const bool active = row < left;
-      label[q] = a.ignore;
-      if (active) label[q] = labels64 ? __ldg((const long long*)a.target + (r0 + row)) : load_label(a.target, a.tdt, r0 + row);
-      const char* lp = tp + (row * C + j) * Elem<PDT>::kBytes;  // slot offsets become immediates of the loads
-#pragma unroll
-      for (int it = 0; it < SLOTS; ++it) e[q][it] = (active && it * W + j < C) ? load_elem<PDT>(lp, it * W) : -INFINITY;
-    }
-    if (SOFT) softmax_rows_inplace<PDT, SLOTS, ROWS>(e, rm);
-    int t[ROWS];
-    bool counted[ROWS];
-#pragma unroll
-    for (int q = 0; q < ROWS; ++q) {
-      const bool ignored = (q * rows_per_warp + sub >= left) | ((a.has_ignore != 0) & (label[q] == a.ignore));
-      counted[q] = !ignored;
-      bad_target |= (unsigned)(!ignored & ((uint64_t)label[q] >= (uint64_t)C));  // label < 0 or >= C
-      t[q] = (int)label[q];  // out-of-range labels raise the error bit; what they count as does not matter
-    }
-    if (!SOFT) {
-      bool mine = false;
-#pragma unroll
-      for (int q = 0; q < ROWS; ++q)
-#pragma unroll
-        for (int it = 0; it < SLOTS; ++it)
-          if (counted[q] && it * W + j < C) mine |= !(e[q][it] >= 0.0f && e[q][it] <= 1.0f);
-      if (mine) raise_flag(a);
-      stop = __any_sync(kFull, mine || ((trip & 7) == 7 && flag_up(a)));
-      if (stop) break;
-    }
-    // One batch of kPer elements through the binning code.  Element i is (row i / SLOTS, slot i % SLOTS) when a
-    // lane holds several rows (SLOTS < kPer), else slot slot0 + i of the one row, found in register e[0][i].
-    auto bin_group = [&](int slot0) {
-      Decoded d;
-      d.bad = 0;
-      d.outside = 0;
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const int q = ROWS > 1 ? i / SLOTS : 0;
-        const int reg = ROWS > 1 ? i % SLOTS : (i < SLOTS ? i : 0);
-        const int it = ROWS > 1 ? reg : slot0 + i;
-        const bool valid = i < ROWS * SLOTS && counted[q] && it * W + j < C;
-        d.x[i] = valid ? e[q][reg] : 0.5f;
-        d.inc[i] = valid ? 1u : 0u;
-        d.toff[i] = 0u;
-      }
-      int g[kPer];
-      if (on_grid)
-        batch_bins<PDT, false, true>(bn, d, g);
-      else
-        batch_bins<PDT, false, false>(bn, d, g);
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const int q = ROWS > 1 ? i / SLOTS : 0;
-        const int it = ROWS > 1 ? i % SLOTS : slot0 + i;
-        if (d.inc[i]) {
-          const int c = it * W + j;
-          count(c, c == t[q], g[i]);
-        }
-      }
-    };
-    if constexpr (kGroups == 1) {
-      bin_group(0);
-    } else {
-      // wide rows: a rolled loop over the groups, the row shifted down by one group after each (the unrolled form
-      // was 5400 instructions, 86 KB of code, and a quarter of the stall samples were instruction fetches)
-#pragma unroll 1
-      for (int gi = 0; gi < kGroups; ++gi) {
-        bin_group(gi * kPer);
-#pragma unroll
-        for (int i = 0; i + kPer < SLOTS; ++i) e[0][i] = e[0][i + kPer];
-      }
-    }
-  }
-  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_RANGE);
-  const bool dead = !SOFT && __syncthreads_or(stop);
-  if (SOFT) __syncthreads();
-  if (dead || (!SOFT && flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
-  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
-    const uint32_t v = hist[i];
-    if (v) {  // never the padding word
-      const int cls = i / class_words, rem = i - cls * class_words;
-      const int hot = rem >= low_k ? 1 : 0;
-      atomicAdd(&gh[(int64_t)(cls * 2 + hot) * kbins + (rem - hot * low_k)], (unsigned long long)v);
-    }
-  }
-}
-
-// ---- multiclass binned curves, C <= 32: one THREAD per row ------------------------------------------------------
-// For up to 32 classes torch's softmax layout gives every lane one element (W = next_pow2(C) lanes per row), so its
-// arithmetic is: max over the row, e_c = expf(x_c - max), and the xor-butterfly sum — which is the balanced tree
-// "s[i] += s[i + W/2], s[i] += s[i + W/4], ..." over the W values (zeros past C; float addition is commutative, so
-// every lane of the butterfly ends with this very tree).  A single thread holding the row reproduces that bit for
-// bit with W - 1 adds and no shuffles; the sub-warp version spends ~8 shuffle steps per row on one element per
-// lane.  Rows come through shared memory (coalesced loads, odd row stride: conflict-free reads).
-constexpr int kSmallRows = 256;  // rows per CTA tile = threads per CTA
-
-template <int PDT, bool SOFT, int W>
-__global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows, int C, int micro, int sh_bins,
-                                                          int low_k) {
-  extern __shared__ uint32_t sh_u32[];
-  if (!pass_enabled(a, SOFT)) return;
-  float* sh_pad = (float*)sh_u32;
-  const int pad_words = (a.T + 2 + 31) / 32 * 32;
-  const int kbins = a.T + 1;
-  uint32_t* hist = sh_u32 + pad_words;
-  const int hist_words = (sh_bins + 31) / 32 * 32;
-  float* stage = (float*)(hist + hist_words);  // [kSmallRows][stride]
-  const int stride = C | 1;
-  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
-  Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
-  const bool on_grid = bn.grid_eps < 0.01f;
-  unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
-  const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;  // e / C for e * C < 2^32
-  const int class_stride = micro ? 0 : 2 * low_k;  // [C][2][low_k] counters in shared memory
-  bool bad_target = false;
-  int stop = 0;
-  constexpr int kGroups = (W + kPer - 1) / kPer;
-  for (int64_t tile0 = (int64_t)blockIdx.x * kSmallRows; tile0 < rows && !stop; tile0 += (int64_t)gridDim.x * kSmallRows) {
-    const int n_rows = (int)min((int64_t)kSmallRows, rows - tile0);
-    const int total = n_rows * C;
-    __syncthreads();  // the previous tile's rows have been read
-    for (int e = threadIdx.x; e < total; e += kSmallRows) {
-      const int r = C > 1 ? (int)__umulhi((uint32_t)e, magic) : e;
-      stage[r * stride + (e - r * C)] = load_elem<PDT>(a.preds, tile0 * C + e);
-    }
-    __syncthreads();
-    const int r = threadIdx.x;
-    const bool active = r < n_rows;
-    const int64_t t = active ? load_label(a.target, a.tdt, tile0 + r) : 0;
-    const bool counted = active && !(a.has_ignore && t == a.ignore);
-    if (counted && (t < 0 || t >= C)) bad_target = true;
-    const int tc = (int)t;
-    float e[W];
-#pragma unroll
-    for (int c = 0; c < W; ++c) e[c] = 0.0f;
-    if (counted) {
-#pragma unroll
-      for (int c = 0; c < W; ++c) {
-        if (c >= C) break;  // CTA-uniform
-        e[c] = stage[r * stride + c];
-      }
-    }
-    if (!SOFT) {
-      bool mine = false;
-      if (counted) {
-#pragma unroll
-        for (int c = 0; c < W; ++c) {
-          if (c >= C) break;
-          mine |= !(e[c] >= 0.0f && e[c] <= 1.0f);
-        }
-      }
-      if (mine) raise_flag(a);
-      stop = __syncthreads_or(mine || (threadIdx.x == 0 && flag_up(a)));
-      if (stop) break;
-    } else if (counted) {
-      softmax_row_thread<PDT, W>(e, C);
-    }
-#pragma unroll
-    for (int gi = 0; gi < kGroups; ++gi) {
-      if (gi * kPer >= C) break;  // CTA-uniform
-      Decoded d;
-      d.bad = 0;
-      d.outside = 0;
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const int c = gi * kPer + i;
-        const bool valid = c < W && counted && c < C;
-        d.x[i] = valid ? e[c < W ? c : 0] : 0.5f;
-        d.inc[i] = valid ? 1u : 0u;
-        d.toff[i] = 0u;
-      }
-      int g[kPer];
-      if (on_grid)
-        batch_bins<PDT, false, true>(bn, d, g);
-      else
-        batch_bins<PDT, false, false>(bn, d, g);
-#pragma unroll
-      for (int i = 0; i < kPer; ++i) {
-        const int c = gi * kPer + i;
-        if (d.inc[i]) {
-          const bool hot = c == tc;
-          if (g[i] < low_k)
-            atomicAdd(&hist[c * class_stride + (hot ? low_k : 0) + g[i]], 1u);
-          else
-            atomicAdd(&gh[((micro ? 0 : c) * 2 + (hot ? 1 : 0)) * kbins + g[i]], 1ULL);
-        }
-      }
-    }
-  }
-  if (bad_target) atomicOr(a.err, TMB_ERR_TARGET_RANGE);
-  __syncthreads();
-  if (!SOFT && (stop || flag_up(a))) return;  // finalize discards the raw histogram once the flag is up
-  for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) {
-    const uint32_t v = hist[i];
-    if (v) {
-      const int64_t dst = (int64_t)(i / low_k) * kbins + (i % low_k);
-      atomicAdd(&gh[dst], (unsigned long long)v);
-    }
-  }
-}
-
 // ---- K1b fast path: ONE threshold, [N, L] row-major (binary = L 1) ---------------------------------------------
 // Stat scores / confusion matrices / accuracy / F1 / Jaccard of binary and multilabel tasks compare against a
 // single threshold, so a sample only needs "above or not" — four counters per label.  The grid-stride is a
@@ -1357,10 +672,6 @@ __global__ void __launch_bounds__(256) k_label_max(const void* __restrict__ x, i
 __global__ void k_set_i64(long long* p, long long v) { *p = v; }
 
 // ---- host ------------------------------------------------------------------------------------------------
-// scratch layout (int64 elements): [0, kHdr) header | 2 histogram variants | padded thresholds (as floats)
-static int64_t hist_elems(int64_t L, int64_t T) { return 2 * L * 2 * (T + 1); }
-static int64_t pad_elems(int64_t T) { return (T + 2 + 1) / 2; }
-static int64_t scratch_elems_for(int64_t L, int64_t T) { return kHdr + hist_elems(L, T) + pad_elems(T); }
 
 template <int PDT, int TDT>
 static int launch_binary_lanes(const TbArgs& a, int warps, int smem, cudaStream_t st) {
@@ -1411,69 +722,6 @@ static int launch_multi_p(const TbArgs& a, int smem, cudaStream_t st) {
     case TMB_U8: return launch_multi_pt<PDT, TMB_U8>(a, smem, st);
     default: return launch_multi_pt<PDT, TMB_I8>(a, smem, st);
   }
-}
-
-template <int PDT>
-static int launch_mc_rows(const TbArgs& a, int64_t rows, int C, int micro, cudaStream_t st) {
-  const RowMap rm = row_map(C);
-  const int64_t pad_bytes = (int64_t)(a.T + 2 + 31) / 32 * 32 * 4;
-  const int64_t pairs = (int64_t)a.L * 2, kbins = a.T + 1;
-  const int64_t room = ((int64_t)dev_info().max_smem_optin - 1024 - pad_bytes) / 4;  // 32-bit counters that fit
-  // k2_mc_rows keeps 2 * low_k + 1 words per class (see class_words there), k2_mc_small 2 * low_k
-  int low_k = (int)((room / a.L - 1) / 2);  // <= 0 for an absurd class count: everything goes to global memory
-  if (low_k > kbins) low_k = (int)kbins;    // every bin is a "low" bin
-  if (low_k <= 0) low_k = -1;               // "nothing in shared memory": k < low_k never holds
-  const int sh_bins = low_k > 0 ? (int)((int64_t)a.L * (2 * low_k + 1)) : 0;
-  const int smem = (int)(pad_bytes + (int64_t)sh_bins * 4);
-  int rc = 0;
-  if (C <= 32 && low_k > 0) {  // one thread per row (see k2_mc_small)
-    const int small_bins = (int)(pairs * low_k);
-    const int hist_words = (small_bins + 31) / 32 * 32;
-    const int small_smem = (int)pad_bytes + hist_words * 4 + kSmallRows * (C | 1) * 4;
-    if (small_smem <= dev_info().max_smem_optin - 1024) {
-      const int64_t work = (rows + kSmallRows - 1) / kSmallRows;
-#define TMB_LAUNCH_SMALL(W_)                                                                    \
-  {                                                                                             \
-    auto ka = k2_mc_small<PDT, false, W_>;                                                      \
-    auto kb = k2_mc_small<PDT, true, W_>;                                                       \
-    cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
-    cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, small_smem);          \
-    const int grid = resident_grid(kb, kSmallRows, small_smem, work);                           \
-    ka<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, small_bins, low_k);                \
-    rc = launch_status();                                                                       \
-    if (rc == 0) {                                                                              \
-      kb<<<grid, kSmallRows, small_smem, st>>>(a, rows, C, micro, small_bins, low_k);              \
-      rc = launch_status();                                                                     \
-    }                                                                                           \
-  }
-      switch (rm.W) {
-        case 2: TMB_LAUNCH_SMALL(2) break;
-        case 4: TMB_LAUNCH_SMALL(4) break;
-        case 8: TMB_LAUNCH_SMALL(8) break;
-        case 16: TMB_LAUNCH_SMALL(16) break;
-        default: TMB_LAUNCH_SMALL(32) break;
-      }
-#undef TMB_LAUNCH_SMALL
-      return rc;
-    }
-  }
-  TMB_DISPATCH_SLOTS(rm.slots, {
-    auto ka = k2_mc_rows<PDT, false, SLOTS>;
-    auto kb = k2_mc_rows<PDT, true, SLOTS>;
-    cudaFuncSetAttribute(ka, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    cudaFuncSetAttribute(kb, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    const int block = SLOTS <= 8 ? 1024 : 512;
-    constexpr int kRowsPerLane = SLOTS < kPer ? kPer / SLOTS : 1;
-    const int64_t work = (rows * rm.W / kRowsPerLane + block - 1) / block + 1;
-    const int grid = resident_grid(kb, block, smem, work);
-    ka<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins, low_k);
-    rc = launch_status();
-    if (rc == 0) {
-      kb<<<grid, block, smem, st>>>(a, rm, rows, C, micro, sh_bins, low_k);
-      rc = launch_status();
-    }
-  })
-  return rc;
 }
 
 template <int PDT, int TDT>
@@ -1631,44 +879,6 @@ extern "C" int tmb_thresh_bin_update(const void* preds, int preds_dtype, int pre
     case TMB_F32: return launch_generic<TMB_F32>(a, st);
     case TMB_F16: return launch_generic<TMB_F16>(a, st);
     default: return launch_generic<TMB_BF16>(a, st);
-  }
-}
-
-extern "C" int tmb_mc_curve_update(const void* preds, int preds_dtype, const void* target, int target_dtype,
-                                   int64_t n_rows, int64_t num_classes, const float* thr, int64_t num_thresholds,
-                                   int has_ignore, int64_t ignore_index, int micro, int64_t* scratch,
-                                   int64_t scratch_elems, int32_t* err, void* stream) {
-  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
-  if (n_rows < 0 || num_classes < 2) return TMB_E_SHAPE;
-  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;
-  if (num_thresholds < 1 || num_thresholds > (1 << 26)) return TMB_E_SHAPE;
-  if (!scratch || !err || !thr) return TMB_E_NULL;
-  const int64_t labels = micro ? 1 : num_classes;
-  if (scratch_elems < scratch_elems_for(labels, num_thresholds)) return TMB_E_SCRATCH;
-  if (n_rows == 0) return 0;
-  if (!preds || !target) return TMB_E_NULL;
-  cudaStream_t st = (cudaStream_t)stream;
-  TbArgs a;
-  a.preds = preds;
-  a.target = target;
-  a.thr = thr;
-  a.scratch = (unsigned long long*)scratch;
-  a.err = err;
-  a.n_total = n_rows * num_classes;
-  a.S = 1;
-  a.ignore = ignore_index;
-  a.L = (int)labels;
-  a.T = (int)num_thresholds;
-  a.pdt = preds_dtype;
-  a.tdt = target_dtype;
-  a.preds_is_label = 0;
-  a.cmp_gt = 0;
-  a.has_ignore = has_ignore;
-  a.flag_counts_ignored = 0;
-  switch (preds_dtype) {
-    case TMB_F32: return launch_mc_rows<TMB_F32>(a, n_rows, (int)num_classes, micro, st);
-    case TMB_F16: return launch_mc_rows<TMB_F16>(a, n_rows, (int)num_classes, micro, st);
-    default: return launch_mc_rows<TMB_BF16>(a, n_rows, (int)num_classes, micro, st);
   }
 }
 
