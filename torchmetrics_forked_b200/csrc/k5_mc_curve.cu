@@ -108,45 +108,41 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
 // global loads and stores stay coalesced.
 constexpr int kSoftmaxSmallRows = 256;
 
-template <int DT, int W>
+template <int DT, int CX>
 __global__ void __launch_bounds__(kSoftmaxSmallRows) k5_softmax_small(const void* __restrict__ x, void* __restrict__ out,
-                                                                      int64_t rows, int C,
+                                                                      int64_t rows,
                                                                       const unsigned long long* __restrict__ flag,
                                                                       unsigned long long gen) {
+  constexpr int C = CX;  // compile-time class count: the per-class loops carry no bounds checks
+  constexpr int W = CX <= 2 ? 2 : (CX <= 4 ? 4 : (CX <= 8 ? 8 : (CX <= 16 ? 16 : 32)));  // torch's lanes per row
   extern __shared__ float stage[];  // [kSoftmaxSmallRows][C | 1]
   const bool soft = *flag == gen;
-  const int stride = C | 1;
-  const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;
+  constexpr int stride = C | 1;
+  constexpr uint32_t magic = (uint32_t)(0x100000000ull / (unsigned)C) + 1u;  // i / C for i * C < 2^32
   for (int64_t tile0 = (int64_t)blockIdx.x * kSoftmaxSmallRows; tile0 < rows;
        tile0 += (int64_t)gridDim.x * kSoftmaxSmallRows) {
     const int n_rows = (int)min((int64_t)kSoftmaxSmallRows, rows - tile0);
     const int total = n_rows * C;
+    const char* src = (const char*)x + tile0 * C * Elem<DT>::kBytes;
+    char* dst = (char*)out + tile0 * C * Elem<DT>::kBytes;
     __syncthreads();
     for (int i = threadIdx.x; i < total; i += kSoftmaxSmallRows) {
-      const int r = C > 1 ? (int)__umulhi((uint32_t)i, magic) : i;
-      stage[r * stride + (i - r * C)] = load_elem<DT>(x, tile0 * C + i);
+      const int r = (int)__umulhi((uint32_t)i, magic);
+      stage[r * stride + (i - r * C)] = load_elem<DT>(src, i);
     }
     __syncthreads();
     if (soft && (int)threadIdx.x < n_rows) {
       float e[W];
 #pragma unroll
-      for (int c = 0; c < W; ++c) e[c] = 0.0f;
-#pragma unroll
-      for (int c = 0; c < W; ++c) {
-        if (c >= C) break;
-        e[c] = stage[threadIdx.x * stride + c];
-      }
+      for (int c = 0; c < W; ++c) e[c] = c < C ? stage[threadIdx.x * stride + (c < C ? c : 0)] : 0.0f;
       softmax_row_thread<DT, W>(e, C);
 #pragma unroll
-      for (int c = 0; c < W; ++c) {
-        if (c >= C) break;
-        stage[threadIdx.x * stride + c] = e[c];
-      }
+      for (int c = 0; c < C; ++c) stage[threadIdx.x * stride + c] = e[c];
     }
     __syncthreads();
     for (int i = threadIdx.x; i < total; i += kSoftmaxSmallRows) {
-      const int r = C > 1 ? (int)__umulhi((uint32_t)i, magic) : i;
-      store_elem<DT>(out, tile0 * C + i, stage[r * stride + (i - r * C)]);
+      const int r = (int)__umulhi((uint32_t)i, magic);
+      store_elem<DT>(dst, i, stage[r * stride + (i - r * C)]);
     }
   }
 }
@@ -168,19 +164,19 @@ static int launch_softmax_rows(const void* x, void* out, int64_t rows, int C, co
   if (C <= 32 && C >= 2) {
     const int smem = kSoftmaxSmallRows * (C | 1) * 4;
     const int64_t work = (rows + kSoftmaxSmallRows - 1) / kSoftmaxSmallRows;
-#define TMB_LAUNCH_SM_SMALL(W_)                                                                        \
-  {                                                                                                    \
-    auto k = k5_softmax_small<DT, W_>;                                                                 \
-    k<<<resident_grid(k, kSoftmaxSmallRows, smem, work), kSoftmaxSmallRows, smem, st>>>(x, out, rows, C, flag, gen); \
-  }
-    switch (rm.W) {
-      case 2: TMB_LAUNCH_SM_SMALL(2) break;
-      case 4: TMB_LAUNCH_SM_SMALL(4) break;
-      case 8: TMB_LAUNCH_SM_SMALL(8) break;
-      case 16: TMB_LAUNCH_SM_SMALL(16) break;
-      default: TMB_LAUNCH_SM_SMALL(32) break;
+    switch (C) {
+#define TMB_SM_CASE(N)                                                                                       \
+  case N: {                                                                                                  \
+    auto k = k5_softmax_small<DT, N>;                                                                        \
+    k<<<resident_grid(k, kSoftmaxSmallRows, smem, work), kSoftmaxSmallRows, smem, st>>>(x, out, rows, flag, gen); \
+  } break;
+      TMB_SM_CASE(2) TMB_SM_CASE(3) TMB_SM_CASE(4) TMB_SM_CASE(5) TMB_SM_CASE(6) TMB_SM_CASE(7) TMB_SM_CASE(8)
+      TMB_SM_CASE(9) TMB_SM_CASE(10) TMB_SM_CASE(11) TMB_SM_CASE(12) TMB_SM_CASE(13) TMB_SM_CASE(14) TMB_SM_CASE(15)
+      TMB_SM_CASE(16) TMB_SM_CASE(17) TMB_SM_CASE(18) TMB_SM_CASE(19) TMB_SM_CASE(20) TMB_SM_CASE(21) TMB_SM_CASE(22)
+      TMB_SM_CASE(23) TMB_SM_CASE(24) TMB_SM_CASE(25) TMB_SM_CASE(26) TMB_SM_CASE(27) TMB_SM_CASE(28) TMB_SM_CASE(29)
+      TMB_SM_CASE(30) TMB_SM_CASE(31) TMB_SM_CASE(32)
+#undef TMB_SM_CASE
     }
-#undef TMB_LAUNCH_SM_SMALL
     return launch_status();
   }
   TMB_DISPATCH_SLOTS(rm.slots, {
