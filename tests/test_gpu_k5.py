@@ -25,6 +25,24 @@ def test_softmax_rows_bits_equal_torch(dtype):
         assert torch.equal(got, x.softmax(1)), (C, dtype)
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_softmax_rows_wide_dynamic_range(dtype):
+    """Logits spread over +-150: the exp values run through the whole range from 1 down to denormals and zero, i.e.
+    through both branches of the shared-divisor division (three FFMAs above 2^-80, the full IEEE division below)."""
+    from torchmetrics_forked_b200 import kernels
+
+    g = torch.Generator(device="cuda").manual_seed(11)
+    for C in (2, 3, 10, 31, 33, 100, 257, 1000):
+        x = (torch.randn(20011, C, generator=g, device="cuda") * 35).to(dtype)
+        x[::7] *= 0.02  # rows with close scores in between
+        got = kernels.softmax_normalize(x)
+        want = x.softmax(1)
+        assert torch.equal(got, want), (C, dtype, int((got != want).sum()))
+        if dtype == torch.float32:
+            tiny = (want > 0) & (want < 2.0 ** -80)
+            assert C == 2 or bool(tiny.any())  # the slow branch was really taken
+
+
 def test_softmax_normalize_decision_and_special_rows():
     from torchmetrics_forked_b200 import kernels
 
