@@ -58,6 +58,8 @@ elif which == "f2":
 
     n, C = (1 << 21, 100) if len(sys.argv) < 4 else (int(sys.argv[2]), int(sys.argv[3]))
     p = torch.randn(n, C, generator=g, device=dev)
+    if __import__("os").environ.get("DT") == "bf16":
+        p = p.bfloat16()
     t = torch.randint(C, (n,), generator=g, device=dev)
     m = MulticlassAUROC(C, thresholds=200, validate_args=False).to(dev)
     for _ in range(3):
