@@ -373,11 +373,12 @@ __device__ __forceinline__ void batch_bins(const Binner& bn, const Decoded& d, i
       // certain for `>=` thresholds and for `>` thresholds alike: q lies strictly between the neighbours
       sure = (unsigned)((below[i] < lowq[i]) & (highq[i] < above[i]));
     } else {
-      const unsigned lo_ok = bn.gt ? (unsigned)(below[i] < q[i]) : (unsigned)(below[i] <= q[i]);
-      const unsigned hi_ok = bn.gt ? (unsigned)!(above[i] < q[i]) : (unsigned)!(above[i] <= q[i]);
-      sure = (lo_ok & hi_ok) | (unsigned)((q[i] != q[i]) & (g[i] == 0));
+      // `x < q` or `x <= q` by the run-time mode, as predicate logic (two compares and a select per side otherwise)
+      const bool lo_ok = (below[i] < q[i]) | (!bn.gt & (below[i] == q[i]));
+      const bool hi_bad = (above[i] < q[i]) | (!bn.gt & (above[i] == q[i]));
+      sure = (unsigned)((lo_ok & !hi_bad) | ((q[i] != q[i]) & (g[i] == 0)));
     }
-    recheck |= (sure ^ 1u) << i;
+    if (!sure) recheck |= 1u << i;
   }
   // A guess that missed, exact scores, thresholds off the even grid (e.g. a linspace rounded to bf16, which 16-bit
   // scores then hit exactly): the right bin is almost always the neighbour on the side the failed compare points to.

@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(SLOTS <= 8 ? 1024 : 512, 1)
   uint32_t* hist = sh_u32 + pad_words;
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
   Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
+  bn.gt = false;  // tmb_mc_curve_update only knows `>=`: a compile-time constant for the compares below
   const bool on_grid = bn.grid_eps < 0.01f;
   unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
   const int lane = threadIdx.x & 31;

@@ -30,6 +30,7 @@ __global__ void __launch_bounds__(kSmallRows) k2_mc_small(TbArgs a, int64_t rows
   const int stride = C | 1;
   for (int i = threadIdx.x; i < sh_bins; i += blockDim.x) hist[i] = 0;
   Binner bn = make_binner(a, sh_pad, 1 << 30, nullptr);  // contains __syncthreads
+  bn.gt = false;  // tmb_mc_curve_update only knows `>=`: a compile-time constant for the compares below
   const bool on_grid = bn.grid_eps < 0.01f;
   unsigned long long* gh = hist_base(a, SOFT ? 1 : 0);
   const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;  // e / C for e * C < 2^32
