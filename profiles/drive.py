@@ -69,6 +69,8 @@ elif which == "f2x":
 
     n, C = (1 << 21, 100) if len(sys.argv) < 4 else (int(sys.argv[2]), int(sys.argv[3]))
     p = torch.randn(n, C, generator=g, device=dev)
+    if __import__("os").environ.get("DT") == "bf16":
+        p = p.bfloat16()
     t = torch.randint(C, (n,), generator=g, device=dev)
     m = MulticlassAUROC(C, thresholds=None, validate_args=False).to(dev)
     for _ in range(3):
