@@ -81,13 +81,14 @@ elif which == "f2x":
 elif which == "f3":
     from torchmetrics_forked_b200.classification import MulticlassAccuracy
 
-    rows = 1 << 20
-    t = torch.randint(1000, (rows,), generator=g, device=dev)
-    p = torch.randn(rows, 1000, generator=g, device=dev).bfloat16()
+    C = int(sys.argv[3]) if len(sys.argv) > 3 else 1000
+    rows = (1 << 30) // C // 1024 * 1024
+    t = torch.randint(C, (rows,), generator=g, device=dev)
+    p = torch.randn(rows, C, generator=g, device=dev).bfloat16()
     if len(sys.argv) > 2 and sys.argv[2] == "fp32":
         p = p.float()[: rows // 2]
         t = t[: rows // 2]
-    m = MulticlassAccuracy(1000, top_k=5, average="micro", validate_args=False).to(dev)
+    m = MulticlassAccuracy(C, top_k=5, average="micro", validate_args=False).to(dev)
     for _ in range(3):
         m.update(p, t)
 torch.cuda.synchronize()

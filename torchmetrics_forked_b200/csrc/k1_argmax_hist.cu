@@ -1059,9 +1059,131 @@ __global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ p
   }
 }
 
+// Up to 128 classes: one THREAD per row.  A warp per row pays ~300 instructions of fixed cost per row (k REDUX rounds,
+// atomics, loop) however short the row is — at C = 10 that was 32 ms for 2^30 scores.  Here a CTA stages a tile of rows
+// into shared memory as keys (coalesced loads, odd row stride: conflict-free reads), and every thread runs the k
+// selection passes over its own row: pass j takes the largest key below the one pass j - 1 took, so nothing is marked.
+// 16-bit scores: unique keys `value key << 16 | 0xfffe - class`; fp32 scores: the value key alone, equal keys are
+// taken in class order (`key == previous && class > previous class` stays eligible).
+template <int DT>
+__global__ void __launch_bounds__(256) k1_rows_topk_thread(const void* __restrict__ preds,
+                                                           const void* __restrict__ target, int tdt, int64_t rows,
+                                                           int C, int top_k, int has_ignore, int64_t ignore,
+                                                           unsigned long long* __restrict__ out, int* err) {
+  extern __shared__ int sh_topk[];  // [3 * C] T | P | M, then the key tile [blockDim.x][C | 1]
+  uint32_t* keys = (uint32_t*)(sh_topk + (3 * C + 31) / 32 * 32);
+  const int stride = C | 1, tile_rows = blockDim.x;
+  const uint32_t magic = C > 1 ? (uint32_t)(0x100000000ull / (unsigned)C) + 1u : 0u;  // i / C for i * C < 2^32
+  const bool vec_ok = (((uintptr_t)preds) & 15) == 0;  // tiles are 128 or 256 rows: every tile then starts 16-byte aligned
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
+  for (int64_t tile0 = (int64_t)blockIdx.x * tile_rows; tile0 < rows; tile0 += (int64_t)gridDim.x * tile_rows) {
+    const int n_rows = (int)min((int64_t)tile_rows, rows - tile0);
+    const int total = n_rows * C;
+    const char* src = (const char*)preds + tile0 * C * Elem<DT>::kBytes;
+    __syncthreads();  // the previous tile has been ranked (and, first time round, the counters are zero)
+    // staging: 16-byte vectors, four per thread in flight (with one 2-byte load per trip the CTA waited a DRAM
+    // latency per element: 7.6 ms at C = 100); what is left of a ragged last tile, or everything when the tensor is
+    // not 16-byte aligned, goes element by element
+    constexpr int kPerVec = 16 / Elem<DT>::kBytes;
+    const int n_vec = vec_ok ? total / kPerVec : 0;
+    auto put = [&](int i, uint32_t bits) {  // element i of the tile; bits: fp32 pattern or the 16-bit pattern
+      const int r = C > 1 ? (int)__umulhi((uint32_t)i, magic) : i;
+      const int c = i - r * C;
+      uint32_t key;
+      if constexpr (DT == TMB_F32) {
+        key = topk_key(__uint_as_float(bits));
+      } else {
+        key = (topk_key16<DT>(bits) << 16) | (0xfffeu - (uint32_t)c);
+      }
+      keys[r * stride + c] = key;
+    };
+    for (int v0 = threadIdx.x; v0 < n_vec; v0 += 4 * blockDim.x) {
+      uint4 w[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int v = v0 + u * blockDim.x;
+        w[u] = v < n_vec ? ldg_stream16(src + (int64_t)v * 16) : make_uint4(0, 0, 0, 0);
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int v = v0 + u * blockDim.x;
+        if (v < n_vec) {
+          const uint32_t x[4] = {w[u].x, w[u].y, w[u].z, w[u].w};
+#pragma unroll
+          for (int e = 0; e < kPerVec; ++e) {
+            if constexpr (DT == TMB_F32) {
+              put(v * kPerVec + e, x[e]);
+            } else {
+              put(v * kPerVec + e, (e & 1) ? (x[e >> 1] >> 16) : (x[e >> 1] & 0xffffu));
+            }
+          }
+        }
+      }
+    }
+    for (int i = n_vec * kPerVec + threadIdx.x; i < total; i += blockDim.x) {
+      if constexpr (DT == TMB_F32) {
+        put(i, ldg_stream4(src + (int64_t)i * 4));
+      } else {
+        put(i, ldg_stream2(src + (int64_t)i * 2));
+      }
+    }
+    __syncthreads();
+    if ((int)threadIdx.x >= n_rows) continue;
+    const int64_t t = load_label(target, tdt, tile0 + threadIdx.x);
+    if (has_ignore && t == ignore) continue;
+    if (t < 0 || t >= C) {
+      atomicOr(err, TMB_ERR_TARGET_RANGE);
+      continue;
+    }
+    const uint32_t* row = keys + threadIdx.x * stride;
+    bool hit = false;
+    uint32_t prev = 0xffffffffu;  // 16-bit keys end in 0xfffe - class: all below this
+    int prev_c = -1;
+    for (int round = 0; round < top_k; ++round) {
+      uint32_t best = 0;  // below every key
+      int best_c = 0;
+#pragma unroll 4
+      for (int c = 0; c < C; ++c) {
+        const uint32_t k = row[c];
+        if constexpr (DT == TMB_F32) {
+          const bool eligible = (k < prev) | ((k == prev) & (c > prev_c));
+          if (eligible & (k > best)) {  // strictly greater: the lowest class of equal scores
+            best = k;
+            best_c = c;
+          }
+        } else {
+          if ((k < prev) & (k > best)) best = k;
+        }
+      }
+      prev = best;
+      if constexpr (DT == TMB_F32) prev_c = best_c;
+      const int cls = DT == TMB_F32 ? best_c : (int)(0xfffeu - (best & 0xffffu));
+      atomicAdd(&sh_topk[C + cls], 1);
+      hit |= (int64_t)cls == t;
+    }
+    atomicAdd(&sh_topk[(int)t], 1);
+    if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+    const int v = sh_topk[i];
+    if (v) atomicAdd(&out[i], (unsigned long long)v);
+  }
+}
+
 template <int DT>
 static int launch_rows_topk(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
                             int has_ignore, int64_t ignore, unsigned long long* out, int* err, cudaStream_t st) {
+  if (C <= 128) {  // one thread per row
+    const int tile_rows = C <= 64 ? 256 : 128;
+    const int smem = ((3 * C + 31) / 32 * 32 + tile_rows * (C | 1)) * (int)sizeof(int);
+    auto k = k1_rows_topk_thread<DT>;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    const int64_t work = (rows + tile_rows - 1) / tile_rows;
+    k<<<resident_grid(k, tile_rows, smem, work), tile_rows, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore,
+                                                                       ignore, out, err);
+    return launch_status();
+  }
   const RowMap rm = row_map(C < 32 ? 32 : C);  // always 32 lanes per row here; slots = next_pow2(C) / 32
   const int smem = 3 * C * (int)sizeof(int);
   const int64_t work = (rows * 32 + 255) / 256;
