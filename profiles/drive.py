@@ -78,6 +78,19 @@ elif which == "f2x":
         m.update(p, t)
     if n * C <= 1 << 28:
         print(float(m.compute()))
+elif which == "k1c":  # argmax + histogram at other class counts: python profiles/drive.py k1c bf16|fp32 C
+    from torchmetrics_forked_b200.classification import MulticlassAccuracy
+
+    C = int(sys.argv[3])
+    rows = (1 << 30) // C // 1024 * 1024
+    t = torch.randint(C, (rows,), generator=g, device=dev)
+    p = torch.randn(rows, C, generator=g, device=dev).bfloat16()
+    if sys.argv[2] == "fp32":
+        p = p.float()[: rows // 2]
+        t = t[: rows // 2]
+    m = MulticlassAccuracy(C, average="macro", validate_args=False).to(dev)
+    for _ in range(3):
+        m.update(p, t)
 elif which == "f3":
     from torchmetrics_forked_b200.classification import MulticlassAccuracy
 
@@ -92,7 +105,7 @@ elif which == "f3":
     for _ in range(3):
         m.update(p, t)
 torch.cuda.synchronize()
-if which in ("f2", "f2x", "f3") and "TIME" in __import__("os").environ:  # quick timing while iterating (not a bench value)
+if which in ("f2", "f2x", "f3", "k1c") and "TIME" in __import__("os").environ:  # quick timing while iterating (not a bench value)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(20):

@@ -150,6 +150,14 @@ def test_multiclass_golden(name, F):
         (3000, 37, torch.bfloat16),  # 74-byte rows: 2-byte granularity
         (1500, 333, torch.float16),
         (257, 4099, torch.bfloat16),  # rows longer than one register tile
+        # 17 .. 64 vectors per row: several rows per warp (k1_rows_sub), 8 or 16 lanes per row, ragged row counts
+        (3001, 136, torch.bfloat16),
+        (3001, 100, torch.float32),
+        (2999, 256, torch.bfloat16),
+        (1777, 200, torch.float32),
+        (4001, 72, torch.float32),
+        (2003, 132, torch.float16),
+        (999, 512, torch.bfloat16),
     ],
 )
 @pytest.mark.parametrize("tdtype", [torch.int64, torch.uint8, torch.int32])

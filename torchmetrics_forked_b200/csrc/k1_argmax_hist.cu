@@ -665,6 +665,71 @@ static int vec_bytes(const void* p, int64_t pitch_bytes, int elem_bytes) {
   return v;
 }
 
+// ---- rows_sub: several rows per warp -----------------------------------------------------------------------
+// Rows of 17 .. 64 vectors (e.g. C = 136 bf16, C = 100 fp32) left half of a warp idle in the kernels above and paid
+// the per-row costs (label load, 5-step merge, atomics, loop) once per 272 .. 1024 bytes: 2 - 6 times the HBM time.
+// Here 2^k lanes (the smallest power of two with 4 vectors per lane covering the row) hold a row, a warp takes
+// 32 >> k rows per trip, and the merge runs over the k butterfly steps that stay inside a group.
+template <int DT, int VB>
+__global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ preds, const void* __restrict__ target,
+                                                   int target_dtype, int64_t n_rows, HistArgs h, int log2_lanes) {
+  extern __shared__ int sh[];
+  constexpr int ES = Elem<DT>::kBytes;
+  constexpr int EPV = VB / ES;
+  constexpr int U = 4;
+  hist_prologue(h, sh);
+  Micro mi{0, 0};
+  const int lane = threadIdx.x & 31;
+  const int lanes = 1 << log2_lanes, sub = lane >> log2_lanes, j = lane & (lanes - 1);
+  const int rows_per_warp = 32 >> log2_lanes;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int64_t row_bytes = (int64_t)h.C * ES;
+  const int nvec = (int)(row_bytes / VB);  // <= lanes * U, checked by the launcher
+
+  Vec<VB> cur[U], nxt[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) cur[u] = Vec<VB>{}, nxt[u] = Vec<VB>{};
+  int64_t t_cur = 0, t_nxt = 0;
+  auto issue = [&](int64_t row, Vec<VB>(&r)[U], int64_t& t) {
+    if (row < n_rows) {
+      const char* rp = preds + row * row_bytes;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int vi = u * lanes + j;
+        if (vi < nvec) r[u].load(rp + (int64_t)vi * VB);
+      }
+      t = load_label(target, target_dtype, row);
+    }
+  };
+  int64_t row0 = warp * rows_per_warp;  // warp-uniform
+  if (row0 < n_rows) issue(row0 + sub, cur, t_cur);
+  for (; row0 < n_rows; row0 += nwarps * rows_per_warp) {
+    const int64_t next = row0 + nwarps * rows_per_warp;
+    if (next < n_rows) issue(next + sub, nxt, t_nxt);
+    Best b = best_init();
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int vi = u * lanes + j;
+      if (vi < nvec) {
+#pragma unroll
+        for (int e = 0; e < EPV; ++e) best_step(b, vec_elem<DT, VB>(cur[u], e), vi * EPV + e);
+      }
+    }
+    for (int d = lanes >> 1; d > 0; d >>= 1) {  // xor offsets below `lanes` stay inside the group
+      Best o;
+      o.v = __shfl_xor_sync(kFull, b.v, d);
+      o.i = __shfl_xor_sync(kFull, b.i, d);
+      b = best_merge(b, o);
+    }
+    if (j == 0 && row0 + sub < n_rows) count_sample(h, sh, mi, t_cur, best_index(b), false);
+#pragma unroll
+    for (int u = 0; u < U; ++u) cur[u] = nxt[u];
+    t_cur = t_nxt;
+  }
+  hist_epilogue(h, sh, mi);
+}
+
 template <int DT>
 static int launch_rows(const void* preds, const void* target, int tdt, int64_t n_rows, const HistArgs& h,
                        cudaStream_t st) {
@@ -703,6 +768,32 @@ static int launch_rows(const void* preds, const void* target, int tdt, int64_t n
   const int64_t ctas = (n_rows + 7) / 8;
   const char* p = (const char*)preds;
   const bool one_tile = row_bytes / vb <= 128;  // the row fits U = 4 vectors per lane: pipelined kernel
+  if (row_bytes / vb <= 64) {  // at most half a warp's worth of vectors: several rows per warp (k1_rows_sub)
+    const int per_lane4 = (int)((row_bytes / vb + 3) / 4);
+    int log2_lanes = 0;
+    while ((1 << log2_lanes) < per_lane4) ++log2_lanes;  // 1 .. 4
+    const int64_t sub_ctas = (n_rows + 8 * (32 >> log2_lanes) - 1) / (8 * (32 >> log2_lanes));
+#define TMB_LAUNCH_SUB(VB_)                                                                                   \
+  {                                                                                                           \
+    auto k = k1_rows_sub<DT, VB_>;                                                                            \
+    k<<<resident_grid(k, block, hist_smem, sub_ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h,      \
+                                                                               log2_lanes);                   \
+  }
+    switch (vb) {
+      case 16: TMB_LAUNCH_SUB(16) break;
+      case 8: TMB_LAUNCH_SUB(8) break;
+      case 4: TMB_LAUNCH_SUB(4) break;
+      default:
+        if constexpr (ES == 2) {
+          TMB_LAUNCH_SUB(2)
+          break;
+        } else {
+          return TMB_E_SHAPE;
+        }
+    }
+#undef TMB_LAUNCH_SUB
+    return launch_status();
+  }
 #define TMB_LAUNCH_ROWS(VB_)                                                                              \
   if (one_tile) {                                                                                         \
     auto k = k1_rows_pipe<DT, VB_>;                                                                       \
