@@ -665,14 +665,58 @@ static int vec_bytes(const void* p, int64_t pitch_bytes, int elem_bytes) {
   return v;
 }
 
+// row_argmax_packed16 for a row held by LANES lanes (vector v of the row in lane v % LANES of the group): the same
+// two phases, the reductions as butterflies over the xor offsets below LANES (they stay inside the group)
+template <int DT, int U, int LANES>
+__device__ __forceinline__ int row_argmax_packed16_group(const Vec<16> (&r)[U], int nvec, int j) {
+  using P = Packed<DT>;
+  uint32_t m2 = P::kNegInf2;
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (u * LANES + j < nvec) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) m2 = P::max_nan(m2, r[u].w[q]);
+    }
+  }
+  float lo = Elem<DT>::get(m2, 0), hi = Elem<DT>::get(m2, 1);
+  unsigned row_nan = (unsigned)((lo != lo) || (hi != hi));
+  float m = fmaxf(lo, hi);  // NaN-free when it matters: rows with a NaN take the other branch below
+#pragma unroll
+  for (int d = LANES / 2; d > 0; d >>= 1) {
+    m = fmaxf(m, __shfl_xor_sync(kFull, m, d));
+    row_nan |= __shfl_xor_sync(kFull, row_nan, d);
+  }
+  const uint32_t M2 = P::splat(m);
+  int mine = 0x7fffffff;
+#pragma unroll
+  for (int u = U - 1; u >= 0; --u) {
+    const int vi = u * LANES + j;
+    if (vi < nvec) {
+      uint32_t k[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) k[q] = row_nan ? P::nan_mask(r[u].w[q]) : P::eq_mask(r[u].w[q], M2);
+      if (k[0] | k[1] | k[2] | k[3]) {
+        int pos = 0;
+#pragma unroll
+        for (int q = 3; q >= 0; --q)
+          if (k[q]) pos = 2 * q + ((k[q] & 0xffffu) ? 0 : 1);
+        mine = vi * 8 + pos;  // u descends, so the lowest vector index wins
+      }
+    }
+  }
+#pragma unroll
+  for (int d = LANES / 2; d > 0; d >>= 1) mine = min(mine, __shfl_xor_sync(kFull, mine, d));
+  return mine;
+}
+
 // ---- rows_sub: several rows per warp -----------------------------------------------------------------------
 // Rows of 17 .. 64 vectors (e.g. C = 136 bf16, C = 100 fp32) left half of a warp idle in the kernels above and paid
 // the per-row costs (label load, 5-step merge, atomics, loop) once per 272 .. 1024 bytes: 2 - 6 times the HBM time.
 // Here 2^k lanes (the smallest power of two with 4 vectors per lane covering the row) hold a row, a warp takes
 // 32 >> k rows per trip, and the merge runs over the k butterfly steps that stay inside a group.
-template <int DT, int VB>
+template <int DT, int VB, int LANES>
 __global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ preds, const void* __restrict__ target,
-                                                   int target_dtype, int64_t n_rows, HistArgs h, int log2_lanes) {
+                                                   int target_dtype, int64_t n_rows, HistArgs h) {
   extern __shared__ int sh[];
   constexpr int ES = Elem<DT>::kBytes;
   constexpr int EPV = VB / ES;
@@ -680,8 +724,8 @@ __global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ pred
   hist_prologue(h, sh);
   Micro mi{0, 0};
   const int lane = threadIdx.x & 31;
-  const int lanes = 1 << log2_lanes, sub = lane >> log2_lanes, j = lane & (lanes - 1);
-  const int rows_per_warp = 32 >> log2_lanes;
+  constexpr int lanes = LANES, rows_per_warp = 32 / LANES;  // 8 or 16 lanes per row
+  const int sub = lane / LANES, j = lane % LANES;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
   const int64_t row_bytes = (int64_t)h.C * ES;
@@ -707,22 +751,30 @@ __global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ pred
   for (; row0 < n_rows; row0 += nwarps * rows_per_warp) {
     const int64_t next = row0 + nwarps * rows_per_warp;
     if (next < n_rows) issue(next + sub, nxt, t_nxt);
-    Best b = best_init();
+    int p;
+    if constexpr (ES == 2 && VB == 16) {
+      p = row_argmax_packed16_group<DT, U, LANES>(cur, nvec, j);
+      if (p == 0x7fffffff) p = 0;  // rows past the end (never counted)
+    } else {
+      Best b = best_init();
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int vi = u * lanes + j;
-      if (vi < nvec) {
+      for (int u = 0; u < U; ++u) {
+        const int vi = u * lanes + j;
+        if (vi < nvec) {
 #pragma unroll
-        for (int e = 0; e < EPV; ++e) best_step(b, vec_elem<DT, VB>(cur[u], e), vi * EPV + e);
+          for (int e = 0; e < EPV; ++e) best_step(b, vec_elem<DT, VB>(cur[u], e), vi * EPV + e);
+        }
       }
+#pragma unroll
+      for (int d = LANES / 2; d > 0; d >>= 1) {  // xor offsets below LANES stay inside the group
+        Best o;
+        o.v = __shfl_xor_sync(kFull, b.v, d);
+        o.i = __shfl_xor_sync(kFull, b.i, d);
+        b = best_merge(b, o);
+      }
+      p = best_index(b);
     }
-    for (int d = lanes >> 1; d > 0; d >>= 1) {  // xor offsets below `lanes` stay inside the group
-      Best o;
-      o.v = __shfl_xor_sync(kFull, b.v, d);
-      o.i = __shfl_xor_sync(kFull, b.i, d);
-      b = best_merge(b, o);
-    }
-    if (j == 0 && row0 + sub < n_rows) count_sample(h, sh, mi, t_cur, best_index(b), false);
+    if (j == 0 && row0 + sub < n_rows) count_sample(h, sh, mi, t_cur, p, false);
 #pragma unroll
     for (int u = 0; u < U; ++u) cur[u] = nxt[u];
     t_cur = t_nxt;
@@ -770,14 +822,15 @@ static int launch_rows(const void* preds, const void* target, int tdt, int64_t n
   const bool one_tile = row_bytes / vb <= 128;  // the row fits U = 4 vectors per lane: pipelined kernel
   if (row_bytes / vb <= 64) {  // at most half a warp's worth of vectors: several rows per warp (k1_rows_sub)
     const int per_lane4 = (int)((row_bytes / vb + 3) / 4);
-    int log2_lanes = 0;
-    while ((1 << log2_lanes) < per_lane4) ++log2_lanes;  // 1 .. 4
-    const int64_t sub_ctas = (n_rows + 8 * (32 >> log2_lanes) - 1) / (8 * (32 >> log2_lanes));
-#define TMB_LAUNCH_SUB(VB_)                                                                                   \
-  {                                                                                                           \
-    auto k = k1_rows_sub<DT, VB_>;                                                                            \
-    k<<<resident_grid(k, block, hist_smem, sub_ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h,      \
-                                                                               log2_lanes);                   \
+    const int lanes = per_lane4 <= 8 ? 8 : 16;  // rows of 17 .. 64 vectors: 5 .. 16 lanes' worth
+    const int64_t sub_ctas = (n_rows + 8 * (32 / lanes) - 1) / (8 * (32 / lanes));
+#define TMB_LAUNCH_SUB(VB_)                                                                                     \
+  if (lanes == 8) {                                                                                             \
+    auto k = k1_rows_sub<DT, VB_, 8>;                                                                           \
+    k<<<resident_grid(k, block, hist_smem, sub_ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h);       \
+  } else {                                                                                                      \
+    auto k = k1_rows_sub<DT, VB_, 16>;                                                                          \
+    k<<<resident_grid(k, block, hist_smem, sub_ctas), block, hist_smem, st>>>(p, target, tdt, n_rows, h);       \
   }
     switch (vb) {
       case 16: TMB_LAUNCH_SUB(16) break;
