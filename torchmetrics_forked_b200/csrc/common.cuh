@@ -171,17 +171,19 @@ __device__ __forceinline__ Best best_init() { return Best{-INFINITY, 0x7fffffff}
 // scan step, candidates visited in increasing index order inside one thread
 __device__ __forceinline__ void best_step(Best& b, float v, int i) {
   // v replaces b when it is strictly greater, or when it is the first NaN
-  bool take = (v > b.v) || ((v != v) && (b.v == b.v));
-  if (take) {
-    b.v = v;
-    b.i = i;
-  }
+  // (bitwise operators and selects: with `||` / `&&` and an `if` the compiler emitted a branch per element)
+  const bool take = (v > b.v) | ((v != v) & (b.v == b.v));
+  b.v = take ? v : b.v;
+  b.i = take ? i : b.i;
 }
 // merge of two partial results that cover disjoint index sets
 __device__ __forceinline__ Best best_merge(Best a, Best o) {
-  bool an = a.v != a.v, on = o.v != o.v;
-  bool take = on ? (!an || o.i < a.i) : (!an && (o.v > a.v || (o.v == a.v && o.i < a.i)));
-  return take ? o : a;
+  const bool an = a.v != a.v, on = o.v != o.v, lower = o.i < a.i;
+  const bool take = on ? (!an | lower) : (!an & ((o.v > a.v) | ((o.v == a.v) & lower)));
+  Best r;
+  r.v = take ? o.v : a.v;
+  r.i = take ? o.i : a.i;
+  return r;
 }
 __device__ __forceinline__ Best best_warp(Best b) {
 #pragma unroll
