@@ -158,6 +158,13 @@ def test_multiclass_golden(name, F):
         (4001, 72, torch.float32),
         (2003, 132, torch.float16),
         (999, 512, torch.bfloat16),
+        # rows of a multiple of four words in the thread-per-row kernel: padded shared-memory tile
+        (5003, 64, torch.float32),  # 64 x 64 confusion matrix = the largest privatised histogram, next to the tile
+        (5003, 128, torch.bfloat16),
+        (7001, 32, torch.float32),
+        (7001, 8, torch.bfloat16),
+        (7001, 4, torch.float32),
+        (4099, 16, torch.float16),
     ],
 )
 @pytest.mark.parametrize("tdtype", [torch.int64, torch.uint8, torch.int32])
