@@ -255,7 +255,7 @@ def run_reference_arm(args):
         "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------ extras (other configs)
@@ -565,14 +565,34 @@ def run_ours(args):
             except Exception as e:  # noqa: BLE001
                 line["extras"] = {"error": repr(e)}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         import torch.distributed as dist
 
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line) -> None:
+    """The one JSON line, on the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    # stdout carries the JSON line and nothing else: native libraries write there too (NCCL prints its version
+    # line to stdout when NCCL_DEBUG is set, as it is on the GPU boxes), so file descriptor 1 is pointed at stderr
+    # for the run and the line goes to a duplicate of the original
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
