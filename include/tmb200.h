@@ -187,7 +187,11 @@ int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, int64_t num
  * ADDS the result into `confmat` (int64 [num_thresholds, 2, 2]).  The caller still passes inputs, thresholds,
  * state and error word; the histogram scratch is a static __device__ array inside the library (about 36 KB on
  * every GPU that loads it, kept until the process exits).  The call itself allocates and frees nothing.
- *   Limit: num_thresholds <= 1024; more returns TMB_E_LIMIT and launches nothing.
+ *   Thresholds: `thr` is a device array of float32 in ASCENDING order (as for tmb_thresh_bin_update; an unsorted
+ *     user list has to be sorted by the caller, who then permutes the rows of `confmat` back).
+ *   Limit: num_thresholds <= 1024; more returns TMB_E_LIMIT and launches nothing.  All argument checks (dtype
+ *     codes, sizes, NULL pointers) run before anything is enqueued: a negative return leaves the array untouched.
+ *   Threads: the per-device address cache is an atomic pointer, so host threads may make the first call together.
  *   Set-up: the first call on each device looks up the array's device address (cudaGetSymbolAddress) with that
  *     device current.  Make that first call outside any stream capture.
  *   Sharing: every call on a device uses the same array, and the array keeps the previous call's contents.
@@ -316,6 +320,10 @@ int tmb_compact_not_ignored(const void* preds, int preds_elem_bytes, const void*
  * TMB_ERR_PREDS_RANGE.  Replaces torch.bincount inside _bincount (utilities/data.py:169-199). */
 int tmb_bincount(const void* x, int x_dtype, int64_t n, int64_t length, int64_t* out, int32_t* err,
                  void* stream);
+/* float32 sum of x[0..n) in index order, one rounding per addition -> *out.  Replaces Python's `sum(tk * pk)` over a
+ * device tensor in _matthews_corrcoef_reduce (functional/classification/matthews_corrcoef.py:59-61): the covariances
+ * subtract numbers of size N^2, so the order of the additions decides bits that the cancellation magnifies. */
+int tmb_sum_sequential_f32(const float* x, int64_t n, float* out, void* stream);
 /* Largest value of x (int64 result, INT64_MIN for n == 0) -> *out_max, used to size a bincount. */
 int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out_max, void* stream);
 

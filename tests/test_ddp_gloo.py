@@ -175,9 +175,55 @@ def check_noncontiguous_and_multidim_gather(rank: int) -> None:
     assert torch.equal(gather_all_tensors(torch.tensor(float(rank)))[1], torch.tensor(1.0))
 
 
+def check_data_errors_raise_on_every_rank_after_the_collective(rank: int) -> None:
+    """A kernel-recorded data error on ONE rank: its bits ride in the packed sync, `compute()` raises on BOTH ranks
+    (nobody is left waiting in the all-reduce), the local state is restored, and `reset()` clears the word."""
+    from torchmetrics_forked_b200 import Metric
+
+    class SumOnly(Metric):
+        def __init__(self):
+            super().__init__()
+            self.add_state("tp", torch.zeros(4, dtype=torch.long), dist_reduce_fx="sum")
+
+        def update(self, tp):
+            self.tp += tp
+
+        def compute(self):
+            return self.tp.sum()
+
+    class CatOnly(Metric):
+        def __init__(self):
+            super().__init__()
+            self.add_state("preds", [], dist_reduce_fx="cat")
+
+        def update(self, preds):
+            self.preds.append(preds)
+
+        def compute(self):
+            return torch.cat(self.preds).sum() if isinstance(self.preds, list) else self.preds.sum()
+
+    for m, arg in ((SumOnly(), torch.arange(4)), (CatOnly(), torch.ones(2 + rank, 3)), (_metric_classes()(), None)):
+        if arg is None:
+            m.update(**_states_for(rank))
+        else:
+            m.update(arg)
+        if rank == 1:  # what a kernel does when it meets a label outside [0, num_classes)
+            m._err_word = torch.tensor([1], dtype=torch.int32)
+        with pytest.raises(RuntimeError, match="Invalid values detected.*outside"):
+            m.compute()
+        assert not m._is_synced
+        m.reset()
+        if arg is None:
+            m.update(**_states_for(rank))
+        else:
+            m.update(arg)
+        m.compute()  # clean epoch after the reset: nothing left to report
+
+
 @pytest.mark.parametrize(
     "fn",
     [
+        "check_data_errors_raise_on_every_rank_after_the_collective",
         "check_packed_sync_matches_oracle",
         "check_matches_generic_gather",
         "check_empty_and_one_sided_lists",

@@ -744,6 +744,48 @@ def test_forward_accumulates_in_place_and_returns_batch_values():
     assert torch.equal(coll["MulticlassPrecision"].tp, ref.tp) and torch.equal(coll["MulticlassRecall"].fn, ref.fn)
 
 
+def test_forward_on_grouped_collection_matches_standalone_metrics():
+    """update -> forward and reset -> forward on a collection whose compute groups are formed (Precision + Recall share
+    tp/fp/tn/fn, ConfusionMatrix + Jaccard share confmat): every state takes each batch exactly once."""
+    from torchmetrics_forked_b200 import MetricCollection
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(33)
+    C = 7
+
+    def make():
+        return [M.MulticlassPrecision(C), M.MulticlassRecall(C), M.MulticlassConfusionMatrix(C),
+                M.MulticlassJaccardIndex(C)]
+
+    coll = MetricCollection(make()).cuda()
+    alone = [m.cuda() for m in make()]
+    batches = [(torch.randn(500, C, generator=g).cuda(), torch.randint(C, (500,), generator=g).cuda()) for _ in range(5)]
+
+    def check():
+        out = coll.compute()
+        for m in alone:
+            assert torch.equal(out[type(m).__name__], m.compute()), type(m).__name__
+        assert torch.equal(coll["MulticlassRecall"].tp, alone[1].tp)
+        assert torch.equal(coll["MulticlassJaccardIndex"].confmat, alone[3].confmat)
+
+    coll.update(*batches[0])
+    [m.update(*batches[0]) for m in alone]
+    assert len(coll.compute_groups) == 2
+    batch_vals = coll(*batches[1])          # update -> forward
+    for m in alone:
+        assert torch.equal(batch_vals[type(m).__name__], m(*batches[1]))
+    check()
+    coll.update(*batches[2])                # forward -> update links the members again
+    [m.update(*batches[2]) for m in alone]
+    check()
+    coll.reset()
+    [m.reset() for m in alone]
+    for b in batches[3:]:                   # reset -> forward, forward
+        coll(*b)
+        [m(*b) for m in alone]
+    check()
+
+
 def test_collection_shares_one_argmax_without_confusion_matrix():
     """Stat-score heads that only differ in their averaging (micro keeps [1] states, macro [C]) share one pass too."""
     from torchmetrics_forked_b200 import MetricCollection

@@ -484,3 +484,29 @@ def test_fused_scores_float32_rounding_path_beyond_2p24():
     small = kernels.clf_curve_scores(P[:100_000], T[:100_000], None, 1, want_ap=False)
     torch.testing.assert_close(small[:, 0], _emit_then_reduce(P[:100_000].contiguous(), T[:100_000].contiguous(), None)[:, 0],
                                rtol=0, atol=0)
+
+
+def test_compute_on_cpu_exact_mode_brings_the_buffers_back():
+    """`compute_on_cpu=True` moves the list states to host memory after every update (reference metric.py:172-173);
+    `compute()` of the exact-mode metrics must still work (the buffers return to the metric's device for the sort)
+    and give the values of an ordinary metric."""
+    from torchmetrics_forked_b200 import classification as M
+
+    g = torch.Generator().manual_seed(91)
+    pairs = [
+        (M.MultilabelAUROC(4, thresholds=None, compute_on_cpu=True), M.MultilabelAUROC(4, thresholds=None), (300, 4)),
+        (M.BinaryAveragePrecision(thresholds=None, compute_on_cpu=True), M.BinaryAveragePrecision(thresholds=None), (500,)),
+        (M.BinaryROC(thresholds=None, compute_on_cpu=True), M.BinaryROC(thresholds=None), (400,)),
+    ]
+    for parked, plain, shape in pairs:
+        parked, plain = parked.cuda(), plain.cuda()
+        for _ in range(3):
+            p, t = torch.randn(*shape, generator=g).cuda(), torch.randint(2, shape, generator=g).cuda()
+            parked.update(p, t)
+            plain.update(p, t)
+        assert all(not c.is_cuda for c in parked.preds) and all(not c.is_cuda for c in parked.target)
+        a, b = parked.compute(), plain.compute()
+        if isinstance(a, tuple):
+            assert all(torch.equal(x, y) for x, y in zip(a, b))
+        else:
+            assert torch.equal(a, b)

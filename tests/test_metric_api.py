@@ -286,6 +286,40 @@ def test_compute_groups_discovery_and_copy_on_access():
     assert deepcopy(coll).compute_groups == coll.compute_groups
 
 
+def test_forward_on_a_grouped_collection_counts_each_batch_once():
+    """Members of a compute group alias one state tensor and `forward` accumulates in place: the batch must land
+    once per metric, not once per member (update -> forward, reset -> forward, forward -> update)."""
+
+    class A(DummySum):
+        pass
+
+    class B(DummySum):
+        def compute(self):
+            return self.x * 2
+
+    x = torch.tensor(6.0)
+    coll = MetricCollection([A(), B()])
+    coll.update(x)
+    assert coll.compute_groups == {0: ["A", "B"]}
+    batch = coll(x)
+    assert batch["A"] == 6 and batch["B"] == 12
+    out = coll.compute()
+    assert out["A"] == 12 and out["B"] == 24
+    coll.update(x)  # links the members again; the head alone is updated
+    out = coll.compute()
+    assert out["A"] == 18 and out["B"] == 36
+    assert coll["A"].update_count == coll["B"].update_count == 3
+    coll.reset()
+    coll(x)
+    coll(x)
+    out = coll.compute()
+    assert out["A"] == 12 and out["B"] == 24
+    alone_a, alone_b = A(), B()
+    for m in (alone_a, alone_b):
+        m(x), m(x)
+    assert out["A"] == alone_a.compute() and out["B"] == alone_b.compute()
+
+
 def test_task_wrappers_and_arg_validation():
     from torchmetrics_forked_b200.classification import (
         AUROC, Accuracy, BinaryAccuracy, BinaryAUROC, ConfusionMatrix, F1Score, JaccardIndex,

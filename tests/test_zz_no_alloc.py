@@ -7,7 +7,8 @@ inputs, thresholds, the int64 state and the error word; the histogram scratch is
 library.
 
 The test drives the entry point through the C ABI exactly as such a host would (ctypes, raw pointers) and
-checks it, twice in a row, against the ordinary entry points fed with caller-allocated scratch.  The two calls
+checks it, twice in a row, against the ordinary entry points fed with caller-allocated scratch and against the
+CPU oracle (`oracle/hotpath.binary_curve_binned`, fed the device's own sigmoid as every logit parity test is).  The two calls
 are chosen so that stale contents of the shared array would show: the first batch holds logits (it raises the
 "apply sigmoid" flag and fills the sigmoid histogram), the second holds probabilities (flag must be down again,
 raw histogram must start empty).  Integer states must be identical.
@@ -17,8 +18,11 @@ other test.  It passes on its own in a fresh process as well as after the rest o
 """
 import ctypes
 
+import numpy as np
 import pytest
 import torch
+
+import hotpath as O
 
 pytestmark = pytest.mark.gpu
 
@@ -63,16 +67,29 @@ def test_noalloc_matches_ordinary_entry_point_twice(T):
     def allocations():  # number of allocation events torch's caching allocator has served so far
         return torch.cuda.memory_stats().get("allocation.all.allocated", 0)
 
+    def device_free_bytes():  # cudaMemGetInfo: sees a cudaMalloc made by ANY runtime in the process, also the
+        return torch.cuda.mem_get_info()[0]  # library's statically linked one, which torch's counters cannot
+
+    sig = lambda x: torch.from_numpy(x).cuda().sigmoid().cpu().numpy()  # noqa: E731
+    oracle = np.zeros((T, 2, 2), dtype=np.int64)
+    lib.tmb_binary_curve_update_noalloc(_p(probs), 0, _p(target), 0, n, _p(thr), T, 1, -1, _p(got), _p(err), st)
+    torch.cuda.synchronize()  # set-up call (address look-up, module load) before the memory readings
+    got.zero_()
     for batch in (logits, probs):  # two calls in a row on the same shared array
-        before = allocations()
+        torch.cuda.synchronize()
+        before, free_before = allocations(), device_free_bytes()
         rc = lib.tmb_binary_curve_update_noalloc(_p(batch), 0, _p(target), 0, n, _p(thr), T, 1, -1, _p(got), _p(err), st)
-        after = allocations()
+        torch.cuda.synchronize()
+        after, free_after = allocations(), device_free_bytes()
         assert rc == 0
         assert after == before, "the entry point must not allocate through torch either"
-        torch.cuda.synchronize()
+        assert free_after >= free_before, "device-wide free memory shrank: something called cudaMalloc"
         _reference_state(lib, batch, target, thr, -1, want)
         assert int(err.item()) == 0
         assert torch.equal(got, want)  # exact: integer counts, same kernels, same sigmoid
+        oracle += O.binary_curve_binned(batch.cpu().numpy(), target.cpu().numpy(), thr.cpu().numpy(), ignore_index=-1,
+                                        sigmoid_fn=sig)
+        assert np.array_equal(got.cpu().numpy(), oracle), "differs from the CPU oracle"
     assert int(got[0].sum()) == 2 * int((target != -1).sum())  # every counted sample landed once per call
 
 
@@ -92,3 +109,22 @@ def test_noalloc_rejects_more_thresholds_than_the_array_holds():
     assert int(state.sum()) == 0
     with pytest.raises(ValueError, match="limit"):
         nat.check(rc, "tmb_binary_curve_update_noalloc")
+
+
+def test_noalloc_argument_errors_enqueue_nothing():
+    """Bad dtype codes, a negative size or NULL inputs come back as negative codes before any kernel is launched."""
+    from torchmetrics_forked_b200 import _native as nat
+
+    lib = nat.lib()
+    thr = torch.linspace(0, 1, 8).cuda()
+    x, t = torch.rand(16).cuda(), torch.zeros(16, dtype=torch.int64).cuda()
+    state = torch.zeros(8, 2, 2, dtype=torch.int64, device="cuda")
+    err = torch.zeros(1, dtype=torch.int32, device="cuda")
+    call = lib.tmb_binary_curve_update_noalloc
+    assert call(_p(x), 9, _p(t), 0, 16, _p(thr), 8, 0, 0, _p(state), _p(err), None) == -1   # preds dtype
+    assert call(_p(x), 0, _p(t), 9, 16, _p(thr), 8, 0, 0, _p(state), _p(err), None) == -1   # target dtype
+    assert call(_p(x), 0, _p(t), 0, -1, _p(thr), 8, 0, 0, _p(state), _p(err), None) == -2   # n < 0
+    assert call(None, 0, _p(t), 0, 16, _p(thr), 8, 0, 0, _p(state), _p(err), None) == -3    # NULL preds, n > 0
+    assert call(_p(x), 0, _p(t), 0, 16, _p(thr), 8, 0, 0, None, _p(err), None) == -3        # NULL state
+    torch.cuda.synchronize()
+    assert int(state.sum()) == 0 and int(err.item()) == 0

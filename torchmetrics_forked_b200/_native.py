@@ -111,6 +111,7 @@ SIGNATURES = {
     ),
     "tmb_bincount": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_label_max": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p]),
+    "tmb_sum_sequential_f32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
 }
 
 _lib: Optional[ctypes.CDLL] = None

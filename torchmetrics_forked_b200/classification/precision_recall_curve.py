@@ -69,10 +69,16 @@ class _CurveStateMixin:
 
     def _curve_state(self) -> Union[Tensor, Tuple[Tensor, Tensor]]:
         if self.thresholds is None:
-            if isinstance(self.preds, list) and len(self.preds) > 1:
+            preds, target = self.preds, self.target
+            if self.compute_on_cpu and self.device.type == "cuda":
+                # `compute_on_cpu=True` parks the per-update buffers in host memory after every update
+                # (metric.py:172-173); the sort runs on the metric's device, so they come back for `compute()`
+                preds = [p.to(self.device) for p in preds] if isinstance(preds, list) else preds.to(self.device)
+                target = [t.to(self.device) for t in target] if isinstance(target, list) else target.to(self.device)
+            if isinstance(preds, list) and len(preds) > 1:
                 # the per-update buffers go to the kernels as they are (chunk table): no concatenated copy
-                return list(self.preds), list(self.target)
-            return dim_zero_cat(self.preds), dim_zero_cat(self.target)
+                return list(preds), list(target)
+            return dim_zero_cat(preds), dim_zero_cat(target)
         return self.confmat
 
 

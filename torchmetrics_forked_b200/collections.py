@@ -103,9 +103,8 @@ class MetricCollection(ModuleDict):
                 for name in members[1:]:
                     getattr(self, name)._computed = None
             if self._state_is_copy:
-                # states were handed out as copies in between: link them again
+                # states were handed out as copies in between (or `forward` un-linked them): link them again
                 self._compute_groups_create_state_ref()
-                self._state_is_copy = False
         else:
             for m in self.values(copy_state=False):
                 m.update(*args, **m._filter_kwargs(**kwargs))
@@ -118,7 +117,7 @@ class MetricCollection(ModuleDict):
         return self._compute_and_reduce("compute")
 
     def reset(self) -> None:
-        for m in self.values(copy_state=False):
+        for m in self._modules.values():
             m.reset()
         if self._enable_compute_groups and self._groups_checked:
             self._compute_groups_create_state_ref()
@@ -256,18 +255,24 @@ class MetricCollection(ModuleDict):
         return True
 
     def _compute_groups_create_state_ref(self, copy: bool = False) -> None:
-        """Point every group member at the head's state objects (or at deep copies when ``copy``)."""
-        if not self._state_is_copy:
-            for members in self._groups.values():
-                head = getattr(self, members[0])
-                for name in members[1:]:
-                    follower = getattr(self, name)
-                    for state in head._defaults:
-                        value = getattr(head, state)
-                        setattr(follower, state, deepcopy(value) if copy else value)
-                    follower._update_count = deepcopy(head._update_count) if copy else head._update_count
-                    # data errors recorded by the head's kernels must also surface through the followers
-                    follower._err_word = head._err_word
+        """Point every group member at the head's state objects, or (``copy``) hand every follower deep copies.
+
+        Linking always happens on ``copy=False``; copies are made once and the flag then stays up until the next
+        link.  (The reference skips the link while the flag is up and clears it, collections.py:289-307, so the link
+        comes one call late; the states it ends up with are the same.)
+        """
+        if copy and self._state_is_copy:
+            return
+        for members in self._groups.values():
+            head = getattr(self, members[0])
+            for name in members[1:]:
+                follower = getattr(self, name)
+                for state in head._defaults:
+                    value = getattr(head, state)
+                    setattr(follower, state, deepcopy(value) if copy else value)
+                follower._update_count = head._update_count
+                # data errors recorded by the head's kernels must also surface through the followers
+                follower._err_word = head._err_word
         self._state_is_copy = copy
 
     @property
@@ -293,11 +298,21 @@ class MetricCollection(ModuleDict):
         if method_name not in ("compute", "forward"):
             raise ValueError(f"method_name should be either 'compute' or 'forward', but got {method_name}")
         raw: Dict[str, Any] = {}
-        for k, m in self.items(keep_base=True, copy_state=False):
+        if method_name == "forward" and self._groups_checked:
+            # Members of a compute group alias ONE set of state tensors, and `forward` folds the batch into the
+            # global state in place (`Metric._forward_sum_states`): run on linked members the shared tensors would
+            # take the batch once per member.  Give every member its own copy first; each then accumulates the batch
+            # itself (what the reference's `_reduce_states` ends up with, metric.py:392-421) and the next `update`
+            # links them to the head again.
+            self._compute_groups_create_state_ref(copy=True)
+            members = self._modules.items()
+        else:
+            members = self.items(keep_base=True, copy_state=False)
+        for k, m in members:
             raw[k] = m.compute() if method_name == "compute" else m(*args, **m._filter_kwargs(**kwargs))
         duplicates = _find_duplicate_keys(raw)
         flat: Dict[str, Any] = {}
-        for k, m in self.items(keep_base=True, copy_state=False):
+        for k, m in self._modules.items():
             res = raw[k]
             if not isinstance(res, dict):
                 flat[k] = res

@@ -23,6 +23,8 @@
 // works on 8 samples stage by stage so their dependency chains interleave, and 16 warps per SM (bytes, not
 // 16-bit pairs, made that fit) cover the rest.  Loads: one register batch ahead plus L2 prefetches four
 // batches ahead.
+#include <atomic>
+
 #include "k2_binning.cuh"
 
 namespace tmb {
@@ -671,6 +673,22 @@ __global__ void __launch_bounds__(256) k_label_max(const void* __restrict__ x, i
 
 __global__ void k_set_i64(long long* p, long long v) { *p = v; }
 
+// float32 sum of x[0..n) in index order, one rounding per addition (what Python's `sum(tensor)` does): the CTA stages
+// tiles in shared memory, thread 0 adds them left to right.  For the handful of class-length vectors of MCC.
+__global__ void __launch_bounds__(256) k_sum_sequential_f32(const float* __restrict__ x, int64_t n, float* out) {
+  __shared__ float tile[2048];
+  float acc = 0.0f;
+  for (int64_t base = 0; base < n; base += 2048) {
+    const int m = (int)(n - base < 2048 ? n - base : 2048);
+    for (int i = threadIdx.x; i < m; i += 256) tile[i] = x[base + i];
+    __syncthreads();
+    if (threadIdx.x == 0)
+      for (int i = 0; i < m; ++i) acc = __fadd_rn(acc, tile[i]);
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *out = acc;
+}
+
 // ---- host ------------------------------------------------------------------------------------------------
 
 template <int PDT, int TDT>
@@ -926,6 +944,13 @@ extern "C" int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out
   return launch_status();
 }
 
+extern "C" int tmb_sum_sequential_f32(const float* x, int64_t n, float* out, void* stream) {
+  if (n < 0) return TMB_E_SHAPE;
+  if (!out || (n > 0 && !x)) return TMB_E_NULL;
+  k_sum_sequential_f32<<<1, 256, 0, (cudaStream_t)stream>>>(x, n, out);
+  return launch_status();
+}
+
 // ---- binned binary curve update for callers that cannot allocate device memory -------------------------------
 //
 // Everything above takes its histogram scratch from the caller.  Some callers have nowhere to get it from:
@@ -945,21 +970,23 @@ static __device__ __align__(256) unsigned long long g_noalloc_scratch[kNoAllocSc
 // `g_noalloc_scratch` in HOST code is only a handle for the runtime, not a device address; the address a
 // kernel can use has to be asked for, once per device, while that device is current.
 static int noalloc_scratch_address(unsigned long long** out) {
-  static unsigned long long* address[64] = {};
-  static bool known[64] = {};
+  // one slot per device; two host threads making the first call together both look the address up and store the
+  // same value, so a plain atomic pointer is all the synchronisation this needs
+  static std::atomic<unsigned long long*> address[64];
   int dev = -1;
   cudaError_t e = cudaGetDevice(&dev);
   if (e != cudaSuccess) return (int)e;
   if (dev < 0 || dev >= 64) return TMB_E_LIMIT;
-  if (!known[dev]) {
+  unsigned long long* a = address[dev].load(std::memory_order_acquire);
+  if (a == nullptr) {
     void* p = nullptr;
     e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
     if (e != cudaSuccess) return (int)e;
     if (p == nullptr) return (int)cudaErrorInvalidSymbol;
-    address[dev] = (unsigned long long*)p;
-    known[dev] = true;
+    a = (unsigned long long*)p;
+    address[dev].store(a, std::memory_order_release);
   }
-  *out = address[dev];
+  *out = a;
   return 0;
 }
 
@@ -967,9 +994,13 @@ extern "C" int tmb_binary_curve_update_noalloc(const void* preds, int preds_dtyp
                                                int target_dtype, int64_t n, const float* thr,
                                                int64_t num_thresholds, int has_ignore, int64_t ignore_index,
                                                int64_t* confmat, int32_t* err, void* stream) {
-  if (num_thresholds < 1) return TMB_E_SHAPE;
+  // every argument check of the calls below comes first: a negative return means that nothing at all was enqueued
+  // (not even the clear of the shared array)
+  if (label_bytes(target_dtype) == 0 || float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (n < 0 || num_thresholds < 1) return TMB_E_SHAPE;
   if (num_thresholds > kNoAllocMaxThresholds) return TMB_E_LIMIT;  // the static array is sized for 1024
   if (!confmat || !err || !thr) return TMB_E_NULL;
+  if (n > 0 && (!preds || !target)) return TMB_E_NULL;
   if (scratch_elems_for(1, num_thresholds) > kNoAllocScratchElems) return TMB_E_LIMIT;
   unsigned long long* scratch = nullptr;
   if (int rc = noalloc_scratch_address(&scratch)) return rc;

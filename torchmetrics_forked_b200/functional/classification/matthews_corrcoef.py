@@ -3,7 +3,6 @@
 """
 from typing import Optional
 
-import numpy as np
 import torch
 from torch import Tensor
 from typing_extensions import Literal
@@ -25,10 +24,18 @@ from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 def _left_to_right_sum(x: Tensor) -> Tensor:
     """float32 sum in index order.  The reference adds these products with Python's ``sum`` (one float32 add per
     class, left to right); the covariances below subtract numbers of size N^2 from each other, so the order of
-    the additions decides low-order bits that the cancellation then magnifies.  ``np.cumsum`` is sequential."""
-    seq = np.cumsum(x.detach().to("cpu", torch.float32).numpy(), dtype=np.float32)
-    last = seq[-1] if seq.size else np.float32(0)
-    return torch.tensor(last, dtype=torch.float32, device=x.device)
+    the additions decides low-order bits that the cancellation then magnifies.  On the device a one-CTA kernel adds
+    in index order (``tmb_sum_sequential_f32``); the state never leaves the GPU."""
+    from torchmetrics_forked_b200 import _native as nat
+
+    x = x.detach().to(torch.float32).contiguous()
+    if not x.is_cuda:  # a state that was moved to the host: the reference's own expression (sequential by nature)
+        return sum(x, torch.zeros((), dtype=torch.float32))
+    out = torch.empty((), dtype=torch.float32, device=x.device)
+    with nat.on_device(x.device):
+        rc = nat.lib().tmb_sum_sequential_f32(nat.ptr(x), x.numel(), nat.ptr(out), nat.stream_ptr(x.device))
+    nat.check(rc, "tmb_sum_sequential_f32")
+    return out
 
 
 def _matthews_corrcoef_reduce(confmat: Tensor) -> Tensor:

@@ -186,13 +186,22 @@ class Metric(Module, ABC):
                 )
             if self._computed is not None:
                 return self._computed
-            # natural sync point: surface data errors the kernels recorded while validate_args was off
-            self._raise_on_data_errors()
+            # natural sync point: surface data errors the kernels recorded while validate_args was off.  The batch
+            # value inside `forward` is not such a point (its `.item()` would put a host sync into every step): the
+            # epoch-level `compute()` reports.  When the states are about to be synchronised the error bits travel
+            # with them and every rank raises AFTER the collective — a rank that raised before it would leave the
+            # others waiting in the all-reduce.
+            in_forward = self.__dict__.get("_in_batch", False)
+            travels = not in_forward and self._errors_travel_with_sync()
+            if not in_forward and not travels:
+                self._raise_on_data_errors()
             with self.sync_context(
                 dist_sync_fn=self.dist_sync_fn,
                 should_sync=self._to_sync,
                 should_unsync=self._should_unsync,
             ):
+                if travels:
+                    self._raise_on_data_errors(merged=self.__dict__.pop("_err_merged", None))
                 value = _squeeze_if_scalar(compute(*args, **kwargs))
             if self.compute_with_cache:
                 self._computed = value
@@ -224,15 +233,50 @@ class Metric(Module, ABC):
             self._scratch[full_key] = buf
         return buf
 
-    def _raise_on_data_errors(self) -> None:
-        """Read the device error word (one 4-byte copy) and raise ``RuntimeError`` if a kernel set it."""
-        if self._err_word is None:
+    def _raise_on_data_errors(self, merged: Optional[Tensor] = None) -> None:
+        """Read the device error word (one 4-byte copy) and raise ``RuntimeError`` if a kernel set it.  ``merged``:
+        the error bits of all ranks as they came back from the state sync (OR-ed with this rank's)."""
+        if self._err_word is None and merged is None:
             return
-        bits = int(self._err_word.item())
+        bits = int(self._err_word.item()) if self._err_word is not None else 0
+        if merged is not None:
+            bits |= int(merged.item())
         if bits:
-            self._err_word.zero_()
+            if self._err_word is not None:
+                self._err_word.zero_()
+            if self._is_synced:
+                self.unsync()
             reasons = "; ".join(text for bit, text in _DATA_ERROR_TEXT.items() if bits & bit)
             raise RuntimeError(f"Invalid values detected while updating {self.__class__.__name__}: {reasons}.")
+
+    _ERR_BITS = 4  # number of distinct data-error bits (_DATA_ERROR_TEXT)
+
+    def _errors_travel_with_sync(self) -> bool:
+        """True when this ``compute()`` will run the packed state sync and that sync has room for the error bits:
+        an int64 "sum" tensor state (the bits ride in the packed all-reduce) or a "cat" list state (they ride in its
+        size exchange).  Decided from the state declarations alone, so every rank decides alike."""
+        if not (self._to_sync and not self._is_synced and self.dist_sync_fn is None):
+            return False
+        if not (callable(self.distributed_available_fn) and self.distributed_available_fn()):
+            return False
+        return self._error_carrier() is not None
+
+    def _error_carrier(self) -> Optional[str]:
+        for n, fn in self._reductions.items():
+            v = getattr(self, n)
+            if fn == dim_zero_sum and isinstance(v, Tensor) and v.dtype == torch.int64:
+                return "sum"
+        for n, fn in self._reductions.items():
+            if fn == dim_zero_cat and isinstance(getattr(self, n), list):
+                return "cat"
+        return None
+
+    def _error_bits_vector(self, device: torch.device) -> Tensor:
+        """int64[_ERR_BITS]: one 0/1 entry per error bit of this rank (summed / maxed over ranks by the sync)."""
+        shifts = torch.arange(self._ERR_BITS, device=device)
+        if self._err_word is None or self._err_word.device != device:
+            return torch.zeros(self._ERR_BITS, dtype=torch.int64, device=device)
+        return (self._err_word.to(torch.int64) >> shifts) & 1
 
     # ------------------------------------------------------------------ state registry
     @property
@@ -299,9 +343,11 @@ class Metric(Module, ABC):
         self._should_unsync = False
         self.compute_on_cpu = False
         self._enable_grad = True
+        self.__dict__["_in_batch"] = True
         try:
             yield
         finally:
+            self.__dict__["_in_batch"] = False
             self._is_synced = False
             self._should_unsync = True
             self._to_sync = self.sync_on_compute
@@ -317,13 +363,20 @@ class Metric(Module, ABC):
         seen = self._update_count
         with self._batch_mode():
             saved = {name: getattr(self, name) for name in self._defaults}
-            self.reset()
+            self._reset_keeping_errors()
             self.update(*args, **kwargs)
             batch_val = self.compute()
             for name, val in saved.items():
                 setattr(self, name, val)
             self._update_count = seen
         return batch_val
+
+    def _reset_keeping_errors(self) -> None:
+        self.__dict__["_in_forward_reset"] = True
+        try:
+            self.reset()
+        finally:
+            self.__dict__["_in_forward_reset"] = False
 
     def _forward_sum_states(self, *args: Any, **kwargs: Any) -> Any:
         """``forward`` for metrics whose states are all sum-reduced tensors of one dtype (every K1 / K2 metric): the
@@ -370,7 +423,7 @@ class Metric(Module, ABC):
             return self._forward_sum_states(*args, **kwargs)
         global_state = {name: getattr(self, name) for name in self._defaults}
         seen = self._update_count
-        self.reset()
+        self._reset_keeping_errors()
         with self._batch_mode():
             self.update(*args, **kwargs)
             batch_val = self.compute()
@@ -452,15 +505,29 @@ class Metric(Module, ABC):
         ]
         rest = [n for n in self._reductions if n not in sum_names and n not in cat_names]
 
+        carrier = self._error_carrier()
         if sum_names:
-            reduced = packed_all_reduce_sum([getattr(self, n) for n in sum_names], group)
+            tensors = [getattr(self, n) for n in sum_names]
+            if carrier == "sum":  # the error bits of this rank ride in the same all-reduce
+                dev = next(t.device for t in tensors if t.dtype == torch.int64)
+                tensors.append(self._error_bits_vector(dev))
+            reduced = packed_all_reduce_sum(tensors, group)
+            if carrier == "sum":
+                counts = reduced.pop()
+                self.__dict__["_err_merged"] = ((counts > 0).to(torch.int64) << torch.arange(
+                    self._ERR_BITS, device=counts.device)).sum()
             for n, t in zip(sum_names, reduced):
                 setattr(self, n, t)
-        for n in cat_names:
+        for i, n in enumerate(cat_names):
             parts = getattr(self, n)
             local = dim_zero_cat(parts) if parts else None
             device = local.device if local is not None else self._device
-            merged = all_gather_cat(local, device, group)
+            if carrier == "cat" and i == 0:  # the error word rides in the size exchange of the first list state
+                word = int(self._err_word.item()) if self._err_word is not None else 0
+                merged, err_or = all_gather_cat(local, device, group, extra_word=word)
+                self.__dict__["_err_merged"] = torch.tensor(err_or)
+            else:
+                merged = all_gather_cat(local, device, group)
             setattr(self, n, [] if merged is None else merged)
         if rest:
             keep = self._reductions
@@ -541,6 +608,10 @@ class Metric(Module, ABC):
                 setattr(self, name, [])
         self._cache = None
         self._is_synced = False
+        # data errors recorded for samples that are no longer in the state must not surface after a reset (the
+        # resets `forward` does around a batch keep them: those samples are still in the global state)
+        if self._err_word is not None and not self.__dict__.get("_in_forward_reset", False):
+            self._err_word.zero_()
 
     def clone(self) -> "Metric":
         return deepcopy(self)

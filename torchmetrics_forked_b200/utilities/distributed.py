@@ -73,15 +73,26 @@ _DTYPES = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.in
 _MAX_TRAIL = 6
 
 
-def all_gather_cat(local: Optional[Tensor], device: torch.device, group: Optional[Any] = None) -> Optional[Tensor]:
+def all_gather_cat(
+    local: Optional[Tensor], device: torch.device, group: Optional[Any] = None, extra_word: Optional[int] = None
+):
     """Rank-ordered concatenation along dim 0 of every rank's ``local`` (``None`` = this rank has no rows).
 
     One small all-gather exchanges (rows, trailing shape, dtype); one all-gather moves the data. Returns
     ``None`` when no rank has rows.  Trailing shapes must agree between the ranks that have data.
+    ``extra_word``: a small integer that rides in the size exchange; the call then returns ``(result, OR of every
+    rank's word)`` (the metric's data-error bits travel this way).
     """
+    if extra_word is None:
+        return _all_gather_cat(local, device, group, 0)[0]
+    return _all_gather_cat(local, device, group, int(extra_word))
+
+
+def _all_gather_cat(local: Optional[Tensor], device: torch.device, group: Optional[Any], word: int):
     group = _world(group)
     world = dist.get_world_size(group)
-    meta = torch.zeros(3 + _MAX_TRAIL, dtype=torch.int64)
+    meta = torch.zeros(4 + _MAX_TRAIL, dtype=torch.int64)
+    meta[3 + _MAX_TRAIL] = word
     if local is not None:
         if local.ndim == 0:
             local = local.unsqueeze(0)
@@ -100,9 +111,13 @@ def all_gather_cat(local: Optional[Tensor], device: torch.device, group: Optiona
     metas = torch.empty(world * meta.numel(), dtype=torch.int64, device=device)
     dist.all_gather_into_tensor(metas, meta, group=group)
     metas_cpu = metas.view(world, -1).cpu()
+    word_or = 0
+    for r in range(world):
+        word_or |= int(metas_cpu[r, 3 + _MAX_TRAIL])
+    metas_cpu = metas_cpu[:, : 3 + _MAX_TRAIL]
     owners = [r for r in range(world) if int(metas_cpu[r, 1]) >= 0]
     if not owners:
-        return None
+        return None, word_or
     ref = metas_cpu[owners[0]]
     for r in owners[1:]:
         if not torch.equal(metas_cpu[r, 1:], ref[1:]):
@@ -124,6 +139,6 @@ def all_gather_cat(local: Optional[Tensor], device: torch.device, group: Optiona
     if dtype == torch.bool:
         recv = recv.view(torch.bool)
     if all(r == most for r in rows):
-        return recv
+        return recv, word_or
     recv = recv.view(world, most, *trail)
-    return torch.cat([recv[r, : rows[r]] for r in range(world)], dim=0)
+    return torch.cat([recv[r, : rows[r]] for r in range(world)], dim=0), word_or
