@@ -2,15 +2,19 @@
 """bench.py — throughput of the classification-metric update path on B200 (driver contract).
 
     python bench.py --gpus N --steps K --warmup W            # our CUDA path (one JSON line on stdout)
-    python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (op-for-op port)
-    torchrun ... bench.py --gpus N ...                        # N > 1: one rank per GPU, NCCL
+    python bench.py --impl reference --steps K --warmup W    # the reference's own CPU path (oracle/_ref), all host threads
+    torchrun ... bench.py --gpus N ...                        # N > 1: one rank per GPU, NCCL; adds the sync parity
+                                                              # prologue and the strong-scaling block
 
 Headline workload (BASELINE.json configs[1]): `MulticlassConfusionMatrix(1000)`, one `update` = bf16 logits
 [2^22, 1000] + int64 targets per GPU (8.42 GB, far larger than the 126 MB L2, so no flush is needed),
 samples independent -> sharded by sample, weak scaling, one `compute()` (packed all-reduce sync) closes the
 timed region.  `value` = samples/s over all GPUs with inputs resident in HBM; `e2e` = the same through the
 public Metric API from pinned host buffers (H2D inside the timed region, accuracy read back every step).
-`extras` carries the other BASELINE configs (3, 5, 1) measured the same way on rank 0 at N = 1.
+`extras` carries the other BASELINE configs (1, 3, 4, 5) measured the same way on rank 0 at N = 1, each beside the
+UNMODIFIED reference run on the same GPU (`ref_cuda_ms`, torch's stock CUDA kernels; `oracle/_ref`).  At N > 1 the run
+starts with an untimed parity prologue of the state sync (`sync_parity`) and `extras.strong` holds the strong-scaling
+measurement of configs 2, 3 and 4 (the global batch BASELINE.json names, sharded over the N ranks, sync included).
 """
 import argparse
 import json
@@ -211,29 +215,71 @@ def timed_loop(fn, steps: int, warmup: int, world: int, device, tail=None):
     return max_over_ranks(total, world, device), sum(per_step) / len(per_step)
 
 
-# ------------------------------------------------------------------------------------------ CPU arms
-def cpu_confmat_rate(rows: int, steps: int, warmup: int, budget_s: float = 25.0):
-    """The reference's CPU update path (op-for-op ATen port) on a bounded sample of config 2."""
-    import torch_cpu as ref_port
+# ------------------------------------------------------------------------------------------ reference arms
+def host_threads() -> int:
+    """Give torch's intra-op pool every host core this process may use.  `torch.distributed.run` exports
+    OMP_NUM_THREADS=1 to its workers, which would leave the CPU arm on ONE thread."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(n, 1))
+    return torch.get_num_threads()
 
+
+_REF = {"tried": False, "module": None}
+
+
+def reference_module():
+    """The unmodified reference package from `oracle/_ref` (staged by oracle/build_ref.py), or None."""
+    if not _REF["tried"]:
+        _REF["tried"] = True
+        try:
+            import ref_loader
+
+            _REF["module"] = ref_loader.load_staged_reference()
+        except Exception as e:  # noqa: BLE001
+            print(f"reference package not importable: {e!r}", file=sys.stderr)
+    return _REF["module"]
+
+
+def cpu_confmat_rate(rows: int, steps: int, warmup: int, budget_s: float = 25.0):
+    """The reference's CPU update path on a bounded sample of config 2: the unmodified
+    `MulticlassConfusionMatrix(1000).update` when `oracle/_ref` is present (kind "reference"), else the op-for-op
+    ATen port of it (kind "port")."""
+    cores = host_threads()
     g = torch.Generator().manual_seed(1234)
     target = torch.randint(C2_CLASSES, (rows,), generator=g)
     preds = torch.randn(rows, C2_CLASSES, generator=g)
     hot = torch.rand(rows, generator=g) < 0.7
     preds[hot, target[hot]] += 4
     preds = preds.bfloat16()
-    state = torch.zeros(C2_CLASSES, C2_CLASSES, dtype=torch.long)
+    ref = reference_module()
+    if ref is not None:
+        metric = ref.classification.MulticlassConfusionMatrix(C2_CLASSES, validate_args=False)
+        kind = "reference"
+
+        def step():
+            metric.update(preds, target)
+    else:
+        import torch_cpu as ref_port
+
+        state = torch.zeros(C2_CLASSES, C2_CLASSES, dtype=torch.long)
+        kind = "port"
+
+        def step():
+            state.add_(ref_port.multiclass_confusion_matrix_update(preds, target, C2_CLASSES, validate_args=False))
     for _ in range(warmup):
-        state += ref_port.multiclass_confusion_matrix_update(preds, target, C2_CLASSES, validate_args=False)
+        step()
     t0 = time.perf_counter()
     done = 0
     for _ in range(steps):
-        state += ref_port.multiclass_confusion_matrix_update(preds, target, C2_CLASSES, validate_args=False)
+        step()
         done += 1
         if time.perf_counter() - t0 > budget_s:
             break
     dt = time.perf_counter() - t0
-    return rows * done / dt, dt / done * 1e3, done
+    return rows * done / dt, dt / done * 1e3, done, kind, cores
 
 
 def run_reference_arm(args):
@@ -241,21 +287,56 @@ def run_reference_arm(args):
     if rank != 0:
         return
     rows = args.cpu_rows
-    rate, ms, done = cpu_confmat_rate(rows, args.steps, max(args.warmup, 1), budget_s=120.0)
-    cores = torch.get_num_threads()
+    rate, ms, done, kind, cores = cpu_confmat_rate(rows, args.steps, max(args.warmup, 1), budget_s=120.0)
+    print(f"reference arm: kind={kind}, {cores} host threads (OMP_NUM_THREADS was "
+          f"{os.environ.get('OMP_NUM_THREADS')!r}), {ms:.2f} ms per {rows} rows", file=sys.stderr)
+    what = ("the unmodified reference (oracle/_ref: torchmetrics 1.3.0dev, MulticlassConfusionMatrix.update)"
+            if kind == "reference" else "op-for-op torch-CPU port of the reference (oracle/torch_cpu.py; oracle/_ref absent)")
     sample = f"{done} updates of bf16 logits [{rows},1000] + int64 targets (config 2 rows, bounded sample)"
     line = {
         "impl": "reference", "metric": METRIC, "value": rate, "unit": "samples/s", "n_gpus": args.gpus,
         "steps": done, "warmup": max(args.warmup, 1), "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": "cfg2: MulticlassConfusionMatrix(1000).update, validate_args=False", "rows_per_step": rows,
-                   "classes": C2_CLASSES, "note": "reference algorithm on host cores: op-for-op torch-CPU port "
-                   "(oracle/torch_cpu.py); the pure-Python reference itself cannot travel to the GPU box"},
-        "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": cores, "kind": "port", "sample": sample},
+                   "classes": C2_CLASSES, "note": f"reference algorithm on host cores: {what}", "host_threads": cores},
+        "cpu_baseline": {"value": rate, "unit": "samples/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": rate, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     emit(line)
+
+
+def time_on_device(fn, reps: int, warmup: int = 1) -> float:
+    """Mean CUDA-event milliseconds of `fn` over `reps` calls after `warmup` calls."""
+    for _ in range(warmup):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def ref_cuda_update_ms(make_metric, inputs, reps: int = 3):
+    """The unmodified reference metric on the SAME device and inputs: ms per `update`, validate_args False / True.
+    Returns {} when `oracle/_ref` is absent.  `make_metric(ref_module, validate_args)` builds the reference object."""
+    ref = reference_module()
+    if ref is None:
+        return {}
+    out = {}
+    for key, validate in (("ref_cuda_ms", False), ("ref_cuda_ms_validate_args", True)):
+        try:
+            m = make_metric(ref, validate).to(inputs[0].device)
+            out[key] = time_on_device(lambda m=m: m.update(*inputs), reps)
+            del m
+        except Exception as e:  # noqa: BLE001
+            out[key] = None
+            out[key + "_error"] = repr(e)[:200]
+        torch.cuda.empty_cache()
+    return out
 
 
 # ------------------------------------------------------------------------------------------ extras (other configs)
@@ -272,13 +353,17 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     out = {}
     g = torch.Generator(device=device).manual_seed(4321)
 
-    def record(name, fn, samples, algo_bytes, preds_bytes, launches):
+    def record(name, fn, samples, algo_bytes, preds_bytes, launches, ref=None):
         _, ms = timed_loop(fn, steps, warmup, 1, device)
         out[name] = {
             "ms_per_update": ms, "samples_per_s": samples / ms * 1e3, "preds_gbs": preds_bytes / ms / 1e6,
             "algo_gbs": algo_bytes / ms / 1e6, "roofline_frac": algo_bytes / ms / 1e6 / peak,
             "launches_per_update": launches,
         }
+        if ref is not None:  # the unmodified reference on the same GPU and the same tensors (torch's stock kernels)
+            out[name].update(ref_cuda_update_ms(*ref))
+            if out[name].get("ref_cuda_ms"):
+                out[name]["speedup_vs_ref_cuda"] = out[name]["ref_cuda_ms"] / ms
 
     # config 3: BinaryPrecisionRecallCurve(thresholds=200), 2^28 fp32 logits
     n3 = 1 << 28
@@ -286,7 +371,9 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     for tdt, tag, tb in ((torch.int64, "cfg3_int64_targets", 8), (torch.uint8, "cfg3_uint8_targets", 1)):
         tgt = torch.randint(2, (n3,), generator=g, device=device).to(tdt)
         m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(device)
-        record(tag, lambda m=m, tgt=tgt: m.update(logits, tgt), n3, n3 * (4 + tb), n3 * 4, 4)
+        ref3 = (lambda R, v: R.classification.BinaryPrecisionRecallCurve(thresholds=200, validate_args=v),
+                (logits, tgt), 2) if tdt == torch.int64 else None
+        record(tag, lambda m=m, tgt=tgt: m.update(logits, tgt), n3, n3 * (4 + tb), n3 * 4, 4, ref=ref3)
         del tgt, m
     probs = torch.rand(n3, generator=g, device=device)
     tgt = torch.randint(2, (n3,), generator=g, device=device)
@@ -407,7 +494,8 @@ def extras_block(device, steps: int, warmup: int, peak: float):
         tgt = torch.randint(150, (16, 512, 512), generator=g, device=device)
         m = MulticlassJaccardIndex(150, validate_args=False).to(device)
         px = 16 * 512 * 512
-        record(tag, lambda m=m, preds=preds, tgt=tgt: m.update(preds, tgt), px, px * (150 * eb + 8), px * 150 * eb, 1)
+        record(tag, lambda m=m, preds=preds, tgt=tgt: m.update(preds, tgt), px, px * (150 * eb + 8), px * 150 * eb, 1,
+               ref=(lambda R, v: R.classification.MulticlassJaccardIndex(150, validate_args=v), (preds, tgt)))
         del preds, tgt, m
     torch.cuda.empty_cache()
 
@@ -451,6 +539,37 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     except Exception as e:  # noqa: BLE001
         out["cfg4_multilabel_auroc_exact"] = {"error": repr(e)}
         torch.cuda.empty_cache()
+    # the unmodified reference on the same GPU for config 4: 8 updates (sigmoid + append) and the exact compute()
+    # (dim_zero_cat, then a Python loop of 100 x (argsort, gathers, cumsum))
+    ref = reference_module()
+    if ref is not None and "error" not in out.get("cfg4_multilabel_auroc_exact", {"error": 1}):
+        try:
+            n4, L4, upd = 1 << 21, 100, 8
+            g4 = torch.Generator(device=device).manual_seed(4321)
+            rm = ref.classification.MultilabelAUROC(L4, thresholds=None, validate_args=False).to(device)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            batches = [(torch.randn(n4, L4, generator=g4, device=device),
+                        torch.randint(2, (n4, L4), generator=g4, device=device)) for _ in range(upd)]
+            rm.update(*batches[0])
+            rm.reset()
+            torch.cuda.synchronize()
+            ev[0].record()
+            for p, t in batches:
+                rm.update(p, t)
+            ev[1].record()
+            del batches
+            rv = rm.compute()
+            ev[2].record()
+            torch.cuda.synchronize()
+            o4 = out["cfg4_multilabel_auroc_exact"]
+            o4["ref_cuda_update_ms"] = ev[0].elapsed_time(ev[1]) / upd
+            o4["ref_cuda_compute_ms"] = ev[1].elapsed_time(ev[2])
+            o4["ref_cuda_auroc"] = float(rv)
+            o4["compute_speedup_vs_ref_cuda"] = o4["ref_cuda_compute_ms"] / o4["compute_ms"]
+            del rm, rv
+        except Exception as e:  # noqa: BLE001
+            out["cfg4_multilabel_auroc_exact"]["ref_cuda_error"] = repr(e)[:200]
+        torch.cuda.empty_cache()
 
     # config 1: MetricCollection([MulticlassAccuracy, MulticlassConfusionMatrix]), 100 000 fp32 probs (latency bound)
     for C in (5, 10):
@@ -460,7 +579,10 @@ def extras_block(device, steps: int, warmup: int, peak: float):
             [MulticlassAccuracy(C, average="micro", validate_args=False), MulticlassConfusionMatrix(C, validate_args=False)]
         ).to(device)
         record(f"cfg1_C{C}_collection", lambda coll=coll, preds=preds, tgt=tgt: coll.update(preds, tgt), 100_000,
-               2 * 100_000 * (4 * C + 8), 2 * 100_000 * 4 * C, 3)
+               2 * 100_000 * (4 * C + 8), 2 * 100_000 * 4 * C, 3,
+               ref=(lambda R, v, C=C: R.MetricCollection([R.classification.MulticlassAccuracy(C, average="micro", validate_args=v),
+                                                          R.classification.MulticlassConfusionMatrix(C, validate_args=v)]),
+                    (preds, tgt), 10))
         # the same update captured once in a CUDA graph and replayed: what is left when Python + launch overhead go
         try:
             side = torch.cuda.Stream()
@@ -478,6 +600,201 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     return out
 
 
+# ------------------------------------------------------------------------------------------ N > 1: sync parity + strong scaling
+def _rank_auroc_f64(scores, y):
+    """AUROC of one label as the float64 rank statistic (ties share their average rank) — independent of K3."""
+    s = scores.double()
+    _, inv, cnt = torch.unique(s, return_inverse=True, return_counts=True)
+    rank = (torch.cumsum(cnt, 0) - cnt + (cnt + 1) / 2.0)[inv]
+    n_pos = int((y == 1).sum())
+    u = rank[y == 1].sum() - n_pos * (n_pos + 1) / 2
+    return float(u / (n_pos * (s.numel() - n_pos)))
+
+
+def sync_parity_prologue(rank: int, world: int, device) -> dict:
+    """Untimed proof that the packed state sync (K4) returns what the reference's `_sync_dist` would
+    (reference metric.py:423-453, utilities/distributed.py:97-147, tests/unittests/bases/test_ddp.py:33-76).
+
+    Every rank updates from its own seeded shard (uneven row counts), then EVERY rank regenerates all shards and
+    checks, bit for bit: (sum path) `MulticlassConfusionMatrix(1000).compute()` and the four `MulticlassStatScores`
+    states against `argmax` + `bincount` of all shards; (cat path) `MultilabelAUROC(thresholds=None)` — inside
+    `sync_context()` the gathered `preds` / `target` against the rank-ordered concatenation, one rank without any
+    rows taking part, and the AUROC against a float64 rank statistic (1e-6).  `compute()` must leave the local
+    state as it was.  Raises on any difference (the run then exits non-zero)."""
+    import torch.distributed as dist
+
+    from torchmetrics_forked_b200.classification import (
+        MulticlassConfusionMatrix,
+        MulticlassStatScores,
+        MultilabelAUROC,
+    )
+
+    C = C2_CLASSES
+    rows_of = lambda r: (1 << 14) + 640 * r  # noqa: E731  (uneven shards)
+    shard = lambda r: make_cfg2(rows_of(r), device, 9000 + r)  # noqa: E731
+    checks = {}
+
+    # ---- sum path: one packed all-reduce per metric
+    preds, target = shard(rank)
+    cm = MulticlassConfusionMatrix(C, validate_args=False).to(device)
+    ss = MulticlassStatScores(C, average=None, validate_args=False).to(device)
+    cm.update(preds, target)
+    ss.update(preds, target)
+    local = cm.confmat.clone()
+    got_cm = cm.compute()
+    got_ss = ss.compute()  # [C, 5]: tp, fp, tn, fn, support
+    want = torch.zeros(C, C, dtype=torch.int64, device=device)
+    for r in range(world):
+        p, t = shard(r)
+        want += torch.bincount(t * C + p.argmax(1), minlength=C * C).reshape(C, C)
+    tp = want.diag()
+    fp, fn = want.sum(0) - tp, want.sum(1) - tp
+    tn = want.sum() - (tp + fp + fn)
+    checks["sum_confmat_bit_exact"] = bool(torch.equal(got_cm, want))
+    checks["sum_stat_scores_bit_exact"] = bool(torch.equal(got_ss, torch.stack([tp, fp, tn, fn, tp + fn], dim=1)))
+    checks["sum_unsync_restores_local"] = bool(torch.equal(cm.confmat, local))
+    del preds, target, want
+
+    # ---- cat path: uneven shards, two updates per rank, the last rank of a second metric has no rows at all
+    L = 6
+
+    def ml_shard(r):
+        g = torch.Generator(device=device).manual_seed(7000 + r)
+        n1, n2 = 3000 + 517 * r, 1000 + 3 * r
+        return [(torch.randn(n, L, generator=g, device=device), torch.randint(2, (n, L), generator=g, device=device))
+                for n in (n1, n2)]
+
+    au = MultilabelAUROC(L, thresholds=None, average="none", validate_args=False).to(device)
+    part = MultilabelAUROC(L, thresholds=None, average="none", validate_args=False).to(device)
+    for p, t in ml_shard(rank):
+        au.update(p, t)
+        if rank != world - 1:
+            part.update(p, t)
+    every = [ml_shard(r) for r in range(world)]
+    all_p = torch.cat([p.sigmoid() for sh in every for p, _ in sh])
+    all_t = torch.cat([t for sh in every for _, t in sh])
+    some_p = torch.cat([p.sigmoid() for sh in every[:-1] for p, _ in sh])
+    with au.sync_context():
+        checks["cat_preds_rank_ordered_bit_exact"] = bool(torch.equal(au.preds, all_p))
+        checks["cat_target_rank_ordered"] = bool(torch.equal(au.target.to(torch.int64), all_t))
+    checks["cat_unsync_restores_list"] = isinstance(au.preds, list) and len(au.preds) == 2
+    with part.sync_context():
+        checks["cat_rank_without_rows"] = bool(torch.equal(part.preds, some_p))
+    got = au.compute()
+    worst = max(abs(float(got[l]) - _rank_auroc_f64(all_p[:, l], all_t[:, l])) for l in range(L))
+    checks["cat_auroc_within_1e-6"] = worst < 1e-6
+    checks["cat_auroc_max_abs_diff"] = worst
+
+    ok = torch.tensor([int(all(v for k, v in checks.items() if isinstance(v, bool)))], device=device)
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+    checks["all_ranks"] = bool(ok.item())
+    if not checks["all_ranks"]:
+        raise AssertionError(f"rank {rank}: state-sync parity failed: {checks}")
+    return checks
+
+
+def _instrument_sync(metric):
+    """CUDA events around every `_sync_dist` of `metric` (the collectives + pack / unpack of one state sync)."""
+    spans, orig = [], metric._sync_dist
+
+    def timed(*a, **k):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        orig(*a, **k)
+        e1.record()
+        spans.append((e0, e1))
+
+    metric.__dict__["_sync_dist"] = timed
+    return spans
+
+
+def _epoch_ms(metric, batches, world, device, synced: bool, reps: int = 3):
+    """ms of one epoch = update over `batches` + one compute(), max over ranks; sync ms inside it (0 if local)."""
+    spans = _instrument_sync(metric) if synced else []
+    best, best_sync, value = None, 0.0, None
+    for i in range(reps + 1):  # first epoch = warm-up (allocator, communicator)
+        metric.reset()
+        del spans[:]
+        barrier(world)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        for b in batches:
+            metric.update(*b)
+        e1.record()
+        value = metric.compute()
+        e2.record()
+        barrier(world)
+        total = max_over_ranks(e0.elapsed_time(e2), world, device)
+        upd = max_over_ranks(e0.elapsed_time(e1), world, device)
+        sync = max_over_ranks(sum(a.elapsed_time(b) for a, b in spans), world, device) if spans else 0.0
+        if i > 0 and (best is None or total < best[0]):
+            best, best_sync = (total, upd), sync
+    return {"epoch_ms": best[0], "update_ms_total": best[1], "compute_ms": best[0] - best[1], "sync_ms": best_sync}, value
+
+
+def strong_block(rank: int, world: int, device, steps: int) -> dict:
+    """Strong scaling of BASELINE.json's configs 2, 3, 4: the named global batch sharded by sample over the N ranks,
+    one `compute()` (state sync included) per epoch.  Beside each, the same epoch on ONE GPU (every rank runs the
+    whole problem locally with `sync_on_compute=False`; max over ranks) — `efficiency` = t_1 / (N * t_N)."""
+    from torchmetrics_forked_b200.classification import (
+        BinaryPrecisionRecallCurve,
+        MulticlassConfusionMatrix,
+        MultilabelAUROC,
+    )
+
+    out = {}
+    k = max(3, min(steps, 10))
+
+    def both(name, make_metric, full_batches, shard_batches, units):
+        one, v1 = _epoch_ms(make_metric(False).to(device), full_batches, world, device, synced=False)
+        many, vn = _epoch_ms(make_metric(True).to(device), shard_batches, world, device, synced=True)
+        out[name] = {"n_gpus": world, "units_per_epoch_global": units,
+                     "one_gpu": one, "sharded": many, "efficiency": one["epoch_ms"] / (world * many["epoch_ms"]),
+                     "speedup": one["epoch_ms"] / many["epoch_ms"],
+                     "units_per_s_sharded": units / many["epoch_ms"] * 1e3}
+        return v1, vn
+
+    # config 2: [2^22, 1000] bf16 per update over all ranks -> 2^22 / N rows per rank; 8 MB packed all-reduce
+    rows = C2_ROWS
+    preds, target = make_cfg2(rows, device, 1234)  # every rank holds the same global batch; rank r takes slice r
+    lo, hi = rank * (rows // world), (rank + 1) * (rows // world)
+    full = [(preds, target)] * k
+    mine = [(preds[lo:hi], target[lo:hi])] * k
+    v1, vn = both("cfg2_confmat_2^22_rows_per_update",
+                  lambda sync: MulticlassConfusionMatrix(C2_CLASSES, validate_args=False, sync_on_compute=sync),
+                  full, mine, rows * k)
+    out["cfg2_confmat_2^22_rows_per_update"]["sharded_equals_one_gpu"] = bool(torch.equal(v1, vn))
+    del preds, target, full, mine, v1, vn
+    torch.cuda.empty_cache()
+
+    # config 3: 2^28 fp32 logits per update -> 2^28 / N per rank; 6.4 kB all-reduce
+    n3 = 1 << 28
+    g = torch.Generator(device=device).manual_seed(4321)
+    logits = torch.randn(n3, generator=g, device=device) * 3
+    tgt = torch.randint(2, (n3,), generator=g, device=device)
+    lo, hi = rank * (n3 // world), (rank + 1) * (n3 // world)
+    v1, vn = both("cfg3_binary_curve_T200_2^28_per_update",
+                  lambda sync: BinaryPrecisionRecallCurve(thresholds=200, validate_args=False, sync_on_compute=sync),
+                  [(logits, tgt)] * k, [(logits[lo:hi], tgt[lo:hi])] * k, n3 * k)
+    out["cfg3_binary_curve_T200_2^28_per_update"]["sharded_equals_one_gpu"] = bool(
+        all(torch.equal(a, b) for a, b in zip(v1, vn)))
+    del logits, tgt, v1, vn
+    torch.cuda.empty_cache()
+
+    # config 4: MultilabelAUROC exact, 2^24 samples x 100 labels in 8 updates -> 2^21 / N rows per rank and update
+    n4, L4, upd = 1 << 21, 100, 8
+    batches = [(torch.randn(n4, L4, generator=g, device=device), torch.randint(2, (n4, L4), generator=g, device=device))
+               for _ in range(upd)]
+    lo, hi = rank * (n4 // world), (rank + 1) * (n4 // world)
+    v1, vn = both("cfg4_multilabel_auroc_exact_2^24x100",
+                  lambda sync: MultilabelAUROC(L4, thresholds=None, validate_args=False, sync_on_compute=sync),
+                  batches, [(p[lo:hi], t[lo:hi]) for p, t in batches], n4 * upd * L4)
+    out["cfg4_multilabel_auroc_exact_2^24x100"]["auroc_abs_diff_sharded_vs_one_gpu"] = abs(float(v1) - float(vn))
+    del batches
+    torch.cuda.empty_cache()
+    return out
+
+
 # ------------------------------------------------------------------------------------------ our arm
 def run_ours(args):
     rank, world, local = dist_setup(args.gpus)
@@ -485,6 +802,7 @@ def run_ours(args):
     from torchmetrics_forked_b200.classification import MulticlassConfusionMatrix
 
     rows = args.rows
+    parity = sync_parity_prologue(rank, world, device) if world > 1 else None
     preds, target = make_cfg2(rows, device, 1234 + rank)
     metric = MulticlassConfusionMatrix(C2_CLASSES, validate_args=False).to(device)
     peak, peak_src = measured_peak_gbs()
@@ -513,6 +831,12 @@ def run_ours(args):
     seen = int(result["confmat"].sum().item())
     expect = rows * world * (args.steps + args.warmup + 1)
     assert seen == expect, f"confusion matrix holds {seen} samples, expected {expect}"
+
+    # the unmodified reference on the same GPU and tensors (rank 0 of a 1-GPU run; torch's stock argmax + bincount)
+    ref_cuda = {}
+    if rank == 0 and world == 1 and not args.no_extras:
+        ref_cuda = ref_cuda_update_ms(
+            lambda R, v: R.classification.MulticlassConfusionMatrix(C2_CLASSES, validate_args=v), (preds, target))
 
     # end to end through the public API from pinned host memory
     metric.reset()
@@ -552,18 +876,31 @@ def run_ours(args):
         "clocks": clk,
     }
     del h_preds, h_target
+    torch.cuda.empty_cache()
+    if parity is not None:
+        line["sync_parity"] = parity["all_ranks"]
+        line["sync_parity_checks"] = parity
+    if world > 1 and not args.no_extras:
+        try:
+            strong = strong_block(rank, world, device, args.steps)
+        except Exception as e:  # noqa: BLE001
+            strong = {"error": repr(e)}
+        line["extras"] = {"strong": strong}
     if rank == 0 and world == 1:
-        rate, ms, done = cpu_confmat_rate(args.cpu_rows, 1000, 1, budget_s=args.cpu_budget)
+        rate, ms, done, kind, cores = cpu_confmat_rate(args.cpu_rows, 1000, 1, budget_s=args.cpu_budget)
+        what = "the unmodified reference, oracle/_ref" if kind == "reference" else "op-for-op torch-CPU port of the reference"
         line["cpu_baseline"] = {
-            "value": rate, "unit": "samples/s", "cores": torch.get_num_threads(), "kind": "port",
-            "sample": f"{done} updates of bf16 logits [{args.cpu_rows},1000] (op-for-op torch-CPU port of the reference, "
-                      f"{ms:.1f} ms each)",
+            "value": rate, "unit": "samples/s", "cores": cores, "kind": kind,
+            "sample": f"{done} updates of bf16 logits [{args.cpu_rows},1000] ({what}, {ms:.1f} ms each)",
         }
         if not args.no_extras:
             try:
                 line["extras"] = extras_block(device, max(3, min(args.steps, 10)), max(args.warmup, 3), peak)
             except Exception as e:  # noqa: BLE001
                 line["extras"] = {"error": repr(e)}
+            line["extras"]["cfg2_confmat_2^22_rows"] = dict(
+                ms_per_update=kernel_ms, roofline_frac=achieved / peak, **ref_cuda,
+                **({"speedup_vs_ref_cuda": ref_cuda["ref_cuda_ms"] / kernel_ms} if ref_cuda.get("ref_cuda_ms") else {}))
     if rank == 0:
         emit(line)
     if world > 1:
