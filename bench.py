@@ -790,6 +790,9 @@ def strong_block(rank: int, world: int, device, steps: int) -> dict:
                   lambda sync: MultilabelAUROC(L4, thresholds=None, validate_args=False, sync_on_compute=sync),
                   batches, [(p[lo:hi], t[lo:hi]) for p, t in batches], n4 * upd * L4)
     out["cfg4_multilabel_auroc_exact_2^24x100"]["auroc_abs_diff_sharded_vs_one_gpu"] = abs(float(v1) - float(vn))
+    from torchmetrics_forked_b200 import _sharded
+
+    out["cfg4_multilabel_auroc_exact_2^24x100"]["compute_path"] = dict(_sharded.LAST, rows=None)
     del batches
     torch.cuda.empty_cache()
     return out

@@ -296,6 +296,35 @@ int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t num_chunks,
                                  int64_t pos_label, int class_targets, int want_ap, void* scratch,
                                  int64_t scratch_bytes, double* scores, int32_t* err, void* stream);
 
+/* ---- label-sharded exact compute over several GPUs (K4 for "cat" states) -----------------------------------
+ *
+ * Replaces, for the scalar exact-mode metrics (AUROC / AveragePrecision with thresholds=None), the reference's
+ *   Metric._sync_dist                     metric.py:423-453   (pre-concatenate the list states, all_gather each)
+ *   gather_all_tensors                    utilities/distributed.py:97-147
+ * followed by every rank sorting every label
+ *   _multilabel_roc_compute / _binary_clf_curve   functional/classification/roc.py:345-355, precision_recall_curve.py:28-80
+ * The labels are dealt out in blocks of `labels_per_rank` (rank r owns [r * labels_per_rank, ...)).
+ *
+ * tmb_clf_pack_keys_sharded: rank s turns its local chunks (same chunk table as tmb_clf_curves_chunked) into sort keys
+ * and stores the keys of label l directly into the OWNER's key buffer, rows [row_offset, row_offset + n_local) of that
+ * label's n_total-row segment: peer_keys[r] / peer_nvalid[r] (device arrays of `world` addresses) are rank r's key
+ * buffer ([labels_per_rank, n_total] uint32) and its n_valid array (uint64 [labels_per_rank], zeroed by its owner
+ * before any rank packs) as mapped into THIS process (peer / symmetric memory; ordinary stores and atomics over
+ * NVLink).  The caller separates the calls of different ranks from the owner's use of the buffer with barriers.
+ *
+ * tmb_clf_sorted_scores: sort `num_labels` segments of `n` packed keys in place and reduce them to the same
+ * [num_labels, 4] float64 rows as tmb_clf_curve_scores_chunked.  all_rows_valid != 0: no entry was ignored, n_valid is
+ * filled with n here.  Scratch: tmb_clf_sorted_scores_scratch_bytes(n, num_labels).
+ */
+int tmb_clf_pack_keys_sharded(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype, int target_dtype,
+                              int64_t n_local, int64_t num_labels, int has_ignore, int64_t ignore_index,
+                              int64_t pos_label, int class_targets, const uint64_t* peer_keys,
+                              const uint64_t* peer_nvalid, int64_t world, int64_t labels_per_rank, int64_t n_total,
+                              int64_t row_offset, int32_t* err, void* stream);
+int64_t tmb_clf_sorted_scores_scratch_bytes(int64_t n, int64_t num_labels);
+int tmb_clf_sorted_scores(uint32_t* keys, uint64_t* n_valid, int64_t n, int64_t num_labels, int all_rows_valid,
+                          int want_ap, void* scratch, int64_t scratch_bytes, double* scores, void* stream);
+
 /* Area reductions over the curves tmb_clf_curves emitted (same fps / tps buffers, label stride n, counts[l] points
  * each), replacing the per-label torch chains of
  *   _binary_roc_compute + _auc_compute_without_check   functional/classification/roc.py:53-78, utilities/compute.py:88-96

@@ -102,6 +102,61 @@ def _worker(rank: int, port: int, out_dir: str) -> None:
         top3.update(mine["mc_preds"], mine["mc_target"])
         tp, fp, tn, fn = O.multiclass_stat_scores_topk(cat("mc_preds"), cat("mc_target"), 50, 3)
         assert abs(float(top3.compute()) - tp.sum() / (tp.sum() + fn.sum())) < 1e-6
+        # ---- label-sharded exact compute (_sharded.py): every variant against the same metric computed on ONE rank
+        # from all rows (no process group involved: sync_on_compute=False), and across the exchange flavours
+        import os as _os
+
+        from torchmetrics_forked_b200.classification import (
+            BinaryAUROC,
+            BinaryAveragePrecision,
+            MultilabelAveragePrecision,
+        )
+
+        def ml(r):
+            g = torch.Generator().manual_seed(900 + r)
+            n = 5000 + 777 * r
+            p = torch.randn(n, 5, generator=g)
+            p[:, 2] = (p[:, 2] * 4).round() / 4  # ties
+            t = torch.randint(2, (n, 5), generator=g)
+            t[torch.rand(n, 5, generator=g) < 0.1] = -1
+            return p, t
+
+        def variants():
+            yield "ml_auroc", lambda **k: MultilabelAUROC(5, thresholds=None, average="none", ignore_index=-1, **k), ml
+            yield "ml_ap", lambda **k: MultilabelAveragePrecision(5, thresholds=None, average="macro", ignore_index=-1, **k), ml
+            yield "bin_auroc", lambda **k: BinaryAUROC(thresholds=None, **k), lambda r: (ml(r)[0][:, 0], (ml(r)[1][:, 0] > 0).long())
+            yield "bin_ap", lambda **k: BinaryAveragePrecision(thresholds=None, **k), lambda r: (ml(r)[0][:, 1], (ml(r)[1][:, 1] > 0).long())
+            yield "mc_auroc", lambda **k: MulticlassAUROC(50, thresholds=None, average="macro", **k), lambda r: (
+                probs(_shard(r)), _shard(r)["mc_target"][:4000])
+
+        for flavour in ("symm", "nccl", "gather"):
+            _os.environ["TMB_EXACT_EXCHANGE"] = "nccl" if flavour == "nccl" else "symm"
+            _os.environ["TMB_EXACT_SHARDED"] = "0" if flavour == "gather" else "1"
+            for name, make, data in variants():
+                m, alone = make().to(dev), make(sync_on_compute=False).to(dev)
+                p, t = data(rank)
+                half = p.shape[0] // 2
+                m.update(p[:half].to(dev), t[:half].to(dev))      # two chunks per rank
+                m.update(p[half:].to(dev), t[half:].to(dev))
+                for r in range(WORLD):
+                    pr, tr = data(r)
+                    alone.update(pr.to(dev), tr.to(dev))
+                got, want = m.compute(), alone.compute()
+                torch.testing.assert_close(got, want, rtol=1e-6, atol=1e-7), (flavour, name)
+                assert isinstance(m.preds, list) and len(m.preds) == 2, "compute() must leave the local state"
+            # a rank without any rows takes part in the exchange
+            m = MultilabelAUROC(5, thresholds=None, average="none", ignore_index=-1).to(dev)
+            alone = MultilabelAUROC(5, thresholds=None, average="none", ignore_index=-1, sync_on_compute=False).to(dev)
+            if rank == 0:
+                m.update(*[x.to(dev) for x in ml(0)])
+            alone.update(*[x.to(dev) for x in ml(0)])
+            import warnings
+
+            with warnings.catch_warnings():
+                warnings.simplefilter("ignore")
+                torch.testing.assert_close(m.compute(), alone.compute(), rtol=1e-6, atol=1e-7)
+        _os.environ.pop("TMB_EXACT_EXCHANGE", None)
+        _os.environ.pop("TMB_EXACT_SHARDED", None)
         Path(out_dir, f"ok{rank}").write_text("ok")
     finally:
         dist.destroy_process_group()

@@ -128,7 +128,11 @@ def as_columns(x: Chunks) -> Chunks:
     """1-d (binary) scores / targets, or a list of such chunks, as ``[n, 1]`` column(s)."""
     if isinstance(x, Tensor):
         return x.reshape(-1, 1)
-    return [c.reshape(-1, 1) for c in x]
+    cols = [c.reshape(-1, 1) for c in x]
+    info = getattr(x, "shard_info", None)
+    if info is not None:  # keep the label-sharded marker (see _sharded.ShardedChunks)
+        return type(x)(cols, info)
+    return cols
 
 
 def _chunk_lists(preds: Chunks, target: Chunks, class_targets: bool = False) -> Tuple[List[Tensor], List[Tensor]]:
@@ -240,7 +244,20 @@ def clf_curve_scores(
     precision_b``; column 2 / 3: total negatives / positives.  ``AUROC = c0 / (c2 * c3)``, ``AP = c1 / c3``.
     ``preds`` / ``target`` as in :func:`clf_curves`; ``want_ap=False`` leaves column 1 at zero (AUROC does not need
     its float64 division per curve point).  Nothing is read back to the host here.
+
+    When ``preds`` carries a ``shard_info`` (the metric's ``compute()`` under a process group, see
+    :mod:`torchmetrics_forked_b200._sharded`) the chunks are this rank's LOCAL rows and the result covers the rows of
+    all ranks: the labels are dealt out to the ranks, each sorts its share.
     """
+    info = getattr(preds, "shard_info", None)
+    if info is not None:
+        from torchmetrics_forked_b200 import _sharded
+
+        if len(preds) > 0:
+            ps, ts = _chunk_lists(list(preds), list(target), class_targets)
+        else:
+            ps, ts = [], []
+        return _sharded.sharded_curve_scores(ps, ts, info, ignore_index, pos_label, want_ap, class_targets)
     ps, ts = _chunk_lists(preds, target, class_targets)
     num_labels = ps[0].shape[1]
     dev = ps[0].device

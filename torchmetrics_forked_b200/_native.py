@@ -102,6 +102,15 @@ SIGNATURES = {
         [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_int, c_void_p,
          c_int64, c_void_p, c_void_p, c_void_p],
     ),
+    "tmb_clf_pack_keys_sharded": (
+        c_int,
+        [c_void_p, c_int64, c_int, c_int, c_int64, c_int64, c_int, c_int64, c_int64, c_int, c_void_p, c_void_p, c_int64,
+         c_int64, c_int64, c_int64, c_void_p, c_void_p],
+    ),
+    "tmb_clf_sorted_scores_scratch_bytes": (c_int64, [c_int64, c_int64]),
+    "tmb_clf_sorted_scores": (
+        c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]
+    ),
     "tmb_curve_reduce": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_compact_scratch_bytes": (c_int64, [c_int64]),
     "tmb_compact_not_ignored": (

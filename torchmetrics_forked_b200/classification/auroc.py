@@ -23,6 +23,7 @@ from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
 
 class BinaryAUROC(BinaryPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False
@@ -47,6 +48,7 @@ class BinaryAUROC(BinaryPrecisionRecallCurve):
 
 
 class MulticlassAUROC(MulticlassPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False
@@ -76,6 +78,7 @@ class MulticlassAUROC(MulticlassPrecisionRecallCurve):
 
 
 class MultilabelAUROC(MultilabelPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False

@@ -23,6 +23,7 @@ from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
 
 class BinaryAveragePrecision(BinaryPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False
@@ -34,6 +35,7 @@ class BinaryAveragePrecision(BinaryPrecisionRecallCurve):
 
 
 class MulticlassAveragePrecision(MulticlassPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False
@@ -63,6 +65,7 @@ class MulticlassAveragePrecision(MulticlassPrecisionRecallCurve):
 
 
 class MultilabelAveragePrecision(MultilabelPrecisionRecallCurve):
+    _sharded_scores = True  # compute() is a reduction of kernels.clf_curve_scores: label-sharded under a process group
     is_differentiable: bool = False
     higher_is_better: bool = True
     full_state_update: bool = False

@@ -67,7 +67,54 @@ class _CurveStateMixin:
             )
         return thr, self._thr_perm
 
+    # ---- label-sharded compute of the scalar exact-mode metrics (AUROC / AveragePrecision) under a process group ----
+    _sharded_scores: bool = False  # subclasses whose compute() is a reduction of kernels.clf_curve_scores set this
+
+    def _label_sharded_ok(self, dist_sync_fn: Any) -> bool:
+        """Decided from the metric's configuration alone, so that every rank decides alike."""
+        from torchmetrics_forked_b200 import _sharded
+
+        if not (self._sharded_scores and self.thresholds is None and dist_sync_fn is None and _sharded.enabled()):
+            return False
+        if not self.__dict__.get("_in_compute_sync", False) or self.compute_on_cpu or self.device.type != "cuda":
+            return False
+        if getattr(self, "max_fpr", None) not in (None, 1, 1.0) or getattr(self, "average", None) == "micro":
+            return False
+        group = self.process_group
+        try:
+            return torch.distributed.get_backend(group) == "nccl"
+        except Exception:  # noqa: BLE001
+            return False
+
+    def _sync_dist(self, dist_sync_fn: Any = None, process_group: Any = None) -> None:
+        """``compute()`` of an exact-mode AUROC / AP does not gather the scores of all ranks onto every rank
+        (reference metric.py:423-453): the states stay local and the sort is dealt out by label
+        (:mod:`torchmetrics_forked_b200._sharded`).  Only the row counts and the data-error bits are exchanged here.
+        An explicit ``sync()`` (and every other metric) takes the packed path of the base class."""
+        if not self._label_sharded_ok(dist_sync_fn):
+            return super()._sync_dist(dist_sync_fn, process_group)
+        from torchmetrics_forked_b200 import _sharded
+
+        group = process_group or self.process_group
+        n_local = sum(int(p.shape[0]) for p in self.preds) if isinstance(self.preds, list) else int(self.preds.shape[0])
+        word = int(self._err_word.item()) if self._err_word is not None else 0
+        rows, err_or = _sharded.exchange_rows_and_errors(n_local, word, self.device, group)
+        self.__dict__["_err_merged"] = torch.tensor(err_or)
+        labels = getattr(self, "num_labels", None) or getattr(self, "num_classes", None) or 1
+        self.__dict__["_shard_info"] = _sharded.ShardInfo(group, rows, int(labels), self.device)
+
+    def unsync(self, should_unsync: bool = True) -> None:
+        self.__dict__.pop("_shard_info", None)
+        return super().unsync(should_unsync)
+
     def _curve_state(self) -> Union[Tensor, Tuple[Tensor, Tensor]]:
+        info = self.__dict__.get("_shard_info")
+        if info is not None and self.thresholds is None:
+            from torchmetrics_forked_b200 import _sharded
+
+            preds = self.preds if isinstance(self.preds, list) else [self.preds]
+            target = self.target if isinstance(self.target, list) else [self.target]
+            return _sharded.ShardedChunks(preds, info), _sharded.ShardedChunks(target, info)
         if self.thresholds is None:
             preds, target = self.preds, self.target
             if self.compute_on_cpu and self.device.type == "cuda":

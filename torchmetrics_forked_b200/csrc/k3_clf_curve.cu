@@ -213,6 +213,21 @@ struct PackSrc {
   int class_targets;       // 1: targets hold ONE class index per row ([rows_c]); label l is positive where it equals l
 };
 
+// Where the keys of label `lab`, rows n0 ... go.  Local form: keys[lab * N + row].  Label-sharded form (state sync of
+// the exact curves over several GPUs, K4): the labels are dealt out in blocks of `labels_per_rank` to the ranks and
+// every rank's pack kernel stores the keys of a label straight into the OWNER's buffer — plain 512-byte runs of
+// st.global over NVLink peer mappings, no staging copy and no separate all-to-all — at the rows
+// [row_offset, row_offset + n_local) of that label's n_total-row segment.  Ignored-entry counts go to the owner's
+// n_valid with remote atomics.  (TMA is not involved: these are ordinary stores; nothing here multicasts.)
+struct PackDst {
+  uint32_t* keys;                         // local form
+  unsigned long long* n_valid;
+  const unsigned long long* peer_keys;    // device array [world]: address of rank r's key buffer (nullptr = local form)
+  const unsigned long long* peer_nvalid;  // device array [world]: address of rank r's n_valid
+  int labels_per_rank;
+  int64_t n_total, row_offset;
+};
+
 constexpr int kPackRows = 128;    // rows per CTA: every label leaves as one 512-byte run of keys
 constexpr int kPackLabels = 128;  // labels per CTA
 constexpr int kPackThreads = 256;
@@ -230,8 +245,7 @@ __host__ __device__ constexpr int pack_stride(int labels) {
 // straddle sectors).  Element e of the region -> (row, label) by a multiply-high with ceil(2^32 / lt).
 template <int DT>
 __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, int64_t N, int L, int has_ignore,
-                                                        int64_t ignore, int64_t pos_label, uint32_t* __restrict__ keys,
-                                                        unsigned long long* n_valid, int* err) {
+                                                        int64_t ignore, int64_t pos_label, PackDst dst, int* err) {
   extern __shared__ uint32_t tile[];  // [lt][stride]
   __shared__ int sh_chunk;
   __shared__ int cnt[kPackLabels];
@@ -318,7 +332,14 @@ __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, in
     uint32_t key = kSentinel;
     if (in_range) {
       key = tile[col * stride + r];
-      keys[(int64_t)(l0 + col) * N + n0 + r] = key;
+      const int lab = l0 + col;
+      if (dst.peer_keys == nullptr) {
+        dst.keys[(int64_t)lab * N + n0 + r] = key;
+      } else {  // the owner's buffer (a warp stays inside one label, so `owner` is warp-uniform)
+        const int owner = lab / dst.labels_per_rank;
+        uint32_t* base = reinterpret_cast<uint32_t*>(dst.peer_keys[owner]);
+        base[(int64_t)(lab - owner * dst.labels_per_rank) * dst.n_total + dst.row_offset + n0 + r] = key;
+      }
     }
     if (has_ignore) {
       const unsigned b = __ballot_sync(kFull, in_range && key_valid(key));
@@ -327,10 +348,17 @@ __global__ void __launch_bounds__(kPackThreads) k3_pack(PackSrc src, int tdt, in
   }
   if (has_ignore) {
     __syncthreads();
-    if (threadIdx.x < lt && cnt[threadIdx.x])
-      atomicAdd(&n_valid[l0 + threadIdx.x], (unsigned long long)cnt[threadIdx.x]);
-  } else if (blockIdx.x == 0 && threadIdx.x < lt) {
-    n_valid[l0 + threadIdx.x] = (unsigned long long)N;  // nothing is ignored: every label counts all N rows
+    if (threadIdx.x < lt && cnt[threadIdx.x]) {
+      const int lab = l0 + threadIdx.x;
+      unsigned long long* nv = dst.n_valid + lab;
+      if (dst.peer_nvalid != nullptr) {
+        const int owner = lab / dst.labels_per_rank;
+        nv = reinterpret_cast<unsigned long long*>(dst.peer_nvalid[owner]) + (lab - owner * dst.labels_per_rank);
+      }
+      atomicAdd(nv, (unsigned long long)cnt[threadIdx.x]);
+    }
+  } else if (dst.peer_keys == nullptr && blockIdx.x == 0 && threadIdx.x < lt) {
+    dst.n_valid[l0 + threadIdx.x] = (unsigned long long)N;  // nothing is ignored: every label counts all N rows
   }
 }
 
@@ -1093,7 +1121,7 @@ static CurveBufs curve_bufs(const CurvePlan& p, void* scratch) {
 
 template <int DT>
 static int launch_pack(const PackSrc& src, int tdt, int64_t n, int L, int has_ignore, int64_t ignore,
-                       int64_t pos_label, const CurveBufs& b, int32_t* err, cudaStream_t st) {
+                       int64_t pos_label, const PackDst& dst, int32_t* err, cudaStream_t st) {
   const int lt_full = L < kPackLabels ? L : kPackLabels;
   const int lt_last = L % kPackLabels ? L % kPackLabels : lt_full;
   int words = lt_full * pack_stride(lt_full);
@@ -1101,8 +1129,38 @@ static int launch_pack(const PackSrc& src, int tdt, int64_t n, int L, int has_ig
   auto k = k3_pack<DT>;
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kPackLabels * pack_stride(kPackLabels) * 4);
   dim3 grid((unsigned)((n + kPackRows - 1) / kPackRows), (unsigned)((L + kPackLabels - 1) / kPackLabels));
-  k<<<grid, kPackThreads, words * 4, st>>>(src, tdt, n, L, has_ignore, ignore, pos_label, b.keys_a, b.n_valid, err);
+  k<<<grid, kPackThreads, words * 4, st>>>(src, tdt, n, L, has_ignore, ignore, pos_label, dst, err);
   return launch_status();
+}
+
+static int pack_keys(const PackSrc& src, int preds_dtype, int target_dtype, int64_t n, int L, int has_ignore,
+                     int64_t ignore, int64_t pos_label, const PackDst& dst, int32_t* err, cudaStream_t st) {
+  switch (preds_dtype) {
+    case TMB_F32: return launch_pack<TMB_F32>(src, target_dtype, n, L, has_ignore, ignore, pos_label, dst, err, st);
+    case TMB_F16: return launch_pack<TMB_F16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, dst, err, st);
+    default: return launch_pack<TMB_BF16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, dst, err, st);
+  }
+}
+
+// 4 LSD passes over [L, n] label-major keys; the sorted keys end up back in keys_a
+static int sort_keys(uint32_t* keys_a, uint32_t* keys_b, uint32_t* cnt, int64_t n, int L, int nb, cudaStream_t st) {
+  uint32_t* src_keys = keys_a;
+  uint32_t* dst_keys = keys_b;
+  cudaFuncSetAttribute(k3_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
+  for (int pass = 0; pass < 4; ++pass) {
+    const int shift = 8 * pass;
+    dim3 grid((unsigned)nb, (unsigned)L);
+    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src_keys, n, shift, cnt, nb);
+    if (int rc = launch_status()) return rc;
+    k3_scan_u32<<<L, 1024, 0, st>>>(cnt, (int64_t)256 * nb, nullptr);
+    if (int rc = launch_status()) return rc;
+    k3_sort_scatter<<<grid, kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, shift, cnt, nb);
+    if (int rc = launch_status()) return rc;
+    uint32_t* tmp = src_keys;
+    src_keys = dst_keys;
+    dst_keys = tmp;
+  }
+  return 0;  // an even number of passes: the result is back in keys_a
 }
 
 // pack + 4 sort passes; the sorted keys end up in b.keys_a
@@ -1110,30 +1168,9 @@ static int pack_and_sort(const PackSrc& src, int preds_dtype, int target_dtype, 
                          int64_t ignore, int64_t pos_label, const CurvePlan& p, const CurveBufs& b, int32_t* err,
                          cudaStream_t st) {
   cudaMemsetAsync(b.n_valid, 0, (size_t)L * 8, st);
-  int rc;
-  switch (preds_dtype) {
-    case TMB_F32: rc = launch_pack<TMB_F32>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
-    case TMB_F16: rc = launch_pack<TMB_F16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
-    default: rc = launch_pack<TMB_BF16>(src, target_dtype, n, L, has_ignore, ignore, pos_label, b, err, st); break;
-  }
-  if (rc) return rc;
-  uint32_t* src_keys = b.keys_a;
-  uint32_t* dst_keys = b.keys_b;
-  cudaFuncSetAttribute(k3_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
-  for (int pass = 0; pass < 4; ++pass) {
-    const int shift = 8 * pass;
-    dim3 grid((unsigned)p.nb, (unsigned)L);
-    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src_keys, n, shift, b.cnt, p.nb);
-    if ((rc = launch_status())) return rc;
-    k3_scan_u32<<<L, 1024, 0, st>>>(b.cnt, (int64_t)256 * p.nb, nullptr);
-    if ((rc = launch_status())) return rc;
-    k3_sort_scatter<<<grid, kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, shift, b.cnt, p.nb);
-    if ((rc = launch_status())) return rc;
-    uint32_t* tmp = src_keys;
-    src_keys = dst_keys;
-    dst_keys = tmp;
-  }
-  return 0;  // an even number of passes: the result is back in keys_a
+  const PackDst dst{b.keys_a, b.n_valid, nullptr, nullptr, L, n, 0};
+  if (int rc = pack_keys(src, preds_dtype, target_dtype, n, L, has_ignore, ignore, pos_label, dst, err, st)) return rc;
+  return sort_keys(b.keys_a, b.keys_b, b.cnt, n, L, p.nb, st);
 }
 
 static int curve_tile_sums(int64_t n, int L, const CurvePlan& p, const CurveBufs& b, long long* counts,
@@ -1175,6 +1212,23 @@ static int curves_impl(const PackSrc& src, int preds_dtype, int target_dtype, in
   cudaFuncSetAttribute(k3_curve_emit, cudaFuncAttributeMaxDynamicSharedMemorySize, kEmitSmem);
   k3_curve_emit<<<grid, kCurveThreads, kEmitSmem, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.bnd_part, p.ntile, fps,
                                                        tps, thresholds);
+  return launch_status();
+}
+
+__global__ void k3_fill_u64(unsigned long long* p, unsigned long long v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// tile partial sums -> scan -> area reductions straight from the sorted keys (b.keys_a, b.n_valid)
+static int scores_from_sorted(int64_t n, int L, const CurvePlan& p, const CurveBufs& b, int want_ap, double* scores,
+                              cudaStream_t st) {
+  if (int rc = curve_tile_sums(n, L, p, b, nullptr, st)) return rc;
+  dim3 grid((unsigned)p.ntile, (unsigned)L);
+  const bool exact = n < ((int64_t)1 << 24), ap = want_ap != 0;
+  auto k = exact ? (ap ? k3_curve_scores<true, true> : k3_curve_scores<true, false>)
+                 : (ap ? k3_curve_scores<false, true> : k3_curve_scores<false, false>);
+  k<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.tile_last, p.ntile, scores);
   return launch_status();
 }
 
@@ -1227,13 +1281,62 @@ extern "C" int tmb_clf_curve_scores_chunked(const int64_t* chunk_table, int64_t 
   const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks, class_targets ? 1 : 0};
   if (int rc = pack_and_sort(src, preds_dtype, target_dtype, n, L, has_ignore, ignore_index, pos_label, p, b, err, st))
     return rc;
-  if (int rc = curve_tile_sums(n, L, p, b, nullptr, st)) return rc;
-  dim3 grid((unsigned)p.ntile, (unsigned)L);
-  const bool exact = n < ((int64_t)1 << 24), ap = want_ap != 0;
-  auto k = exact ? (ap ? k3_curve_scores<true, true> : k3_curve_scores<true, false>)
-                 : (ap ? k3_curve_scores<false, true> : k3_curve_scores<false, false>);
-  k<<<grid, kCurveThreads, 0, st>>>(b.keys_a, n, b.n_valid, b.pos_part, b.tile_last, p.ntile, scores);
-  return launch_status();
+  return scores_from_sorted(n, L, p, b, want_ap, scores, st);
+}
+
+// ---- label-sharded exact compute over several GPUs (K4 for cat states) ------------------------
+// Rank s packs ITS rows of every label straight into the key buffer of the label's owner (tmb_clf_pack_keys_sharded,
+// remote stores over NVLink); after a barrier every rank sorts and reduces only the labels it owns
+// (tmb_clf_sorted_scores) — 1/world of the sort instead of all of it on every rank.
+extern "C" int tmb_clf_pack_keys_sharded(const int64_t* chunk_table, int64_t num_chunks, int preds_dtype,
+                                         int target_dtype, int64_t n_local, int64_t num_labels, int has_ignore,
+                                         int64_t ignore_index, int64_t pos_label, int class_targets,
+                                         const uint64_t* peer_keys, const uint64_t* peer_nvalid, int64_t world,
+                                         int64_t labels_per_rank, int64_t n_total, int64_t row_offset, int32_t* err,
+                                         void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_local < 0 || num_labels < 1 || num_labels > 65535 || world < 1 || labels_per_rank < 1) return TMB_E_SHAPE;
+  if (labels_per_rank * world < num_labels || row_offset < 0 || row_offset + n_local > n_total) return TMB_E_SHAPE;
+  if (n_total >= ((int64_t)1 << 31)) return TMB_E_LIMIT;
+  if (!peer_keys || !peer_nvalid || !err) return TMB_E_NULL;
+  if (n_local == 0) return 0;
+  if (!chunk_table_ok(chunk_table, num_chunks)) return chunk_table ? TMB_E_SHAPE : TMB_E_NULL;
+  const PackSrc src{nullptr, nullptr, (const long long*)chunk_table, (int)num_chunks, class_targets ? 1 : 0};
+  const PackDst dst{nullptr, nullptr, (const unsigned long long*)peer_keys, (const unsigned long long*)peer_nvalid,
+                    (int)labels_per_rank, n_total, row_offset};
+  return pack_keys(src, preds_dtype, target_dtype, n_local, (int)num_labels, has_ignore, ignore_index, pos_label, dst,
+                   err, (cudaStream_t)stream);
+}
+
+extern "C" int64_t tmb_clf_sorted_scores_scratch_bytes(int64_t n, int64_t num_labels) {
+  if (n < 1 || num_labels < 1) return 0;
+  const CurvePlan p = curve_plan(n, num_labels);
+  return p.total - p.off_keys_b;  // everything but the first key buffer, which the caller owns
+}
+
+extern "C" int tmb_clf_sorted_scores(uint32_t* keys, uint64_t* n_valid, int64_t n, int64_t num_labels,
+                                     int all_rows_valid, int want_ap, void* scratch, int64_t scratch_bytes,
+                                     double* scores, void* stream) {
+  if (n < 0 || num_labels < 1 || num_labels > 65535) return TMB_E_SHAPE;
+  if (n >= ((int64_t)1 << 31)) return TMB_E_LIMIT;
+  if (!scores) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(scores, 0, num_labels * 4 * sizeof(double), st);
+  if (int rc = launch_status()) return rc;
+  if (n == 0) return 0;
+  if (!keys || !n_valid || !scratch) return TMB_E_NULL;
+  const CurvePlan p = curve_plan(n, num_labels);
+  if (scratch_bytes < p.total - p.off_keys_b) return TMB_E_SCRATCH;
+  CurveBufs b = curve_bufs(p, (char*)scratch - p.off_keys_b);  // offsets of the plan are relative to keys_a
+  b.keys_a = keys;
+  b.n_valid = (unsigned long long*)n_valid;
+  const int L = (int)num_labels;
+  if (all_rows_valid) {
+    k3_fill_u64<<<(L + 255) / 256, 256, 0, st>>>(b.n_valid, (unsigned long long)n, L);
+    if (int rc = launch_status()) return rc;
+  }
+  if (int rc = sort_keys(b.keys_a, b.keys_b, b.cnt, n, L, p.nb, st)) return rc;
+  return scores_from_sorted(n, L, p, b, want_ap, scores, st);
 }
 
 extern "C" int tmb_curve_reduce(const float* fps, const float* tps, int64_t n, int64_t num_labels,

@@ -64,6 +64,19 @@ _DATA_ERROR_TEXT = {
 }
 
 
+class _entered:
+    """``with`` over a context manager whose ``__enter__`` has already run."""
+
+    def __init__(self, ctx: Any) -> None:
+        self.ctx = ctx
+
+    def __enter__(self) -> Any:
+        return self.ctx
+
+    def __exit__(self, *exc: Any) -> Any:
+        return self.ctx.__exit__(*exc)
+
+
 def jit_distributed_available() -> bool:
     """True when a default process group exists."""
     return torch.distributed.is_available() and torch.distributed.is_initialized()
@@ -195,11 +208,15 @@ class Metric(Module, ABC):
             travels = not in_forward and self._errors_travel_with_sync()
             if not in_forward and not travels:
                 self._raise_on_data_errors()
-            with self.sync_context(
-                dist_sync_fn=self.dist_sync_fn,
-                should_sync=self._to_sync,
-                should_unsync=self._should_unsync,
-            ):
+            self.__dict__["_in_compute_sync"] = True  # lets a subclass tell compute()'s sync from an explicit sync()
+            try:
+                ctx = self.sync_context(
+                    dist_sync_fn=self.dist_sync_fn, should_sync=self._to_sync, should_unsync=self._should_unsync
+                )
+                ctx.__enter__()
+            finally:
+                self.__dict__["_in_compute_sync"] = False
+            with _entered(ctx):
                 if travels:
                     self._raise_on_data_errors(merged=self.__dict__.pop("_err_merged", None))
                 value = _squeeze_if_scalar(compute(*args, **kwargs))
