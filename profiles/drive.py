@@ -104,6 +104,37 @@ elif which == "f3":
     m = MulticlassAccuracy(C, top_k=5, average="micro", validate_args=False).to(dev)
     for _ in range(3):
         m.update(p, t)
+elif which == "evid":  # round 2 evidence set: the kernels of rows a1-a12 that had no --set full capture yet
+    from torchmetrics_forked_b200.classification import (
+        BinaryAccuracy,
+        MulticlassJaccardIndex,
+        MultilabelAUROC,
+        MultilabelPrecisionRecallCurve,
+        MultilabelStatScores,
+    )
+
+    t5 = torch.randint(150, (16, 512, 512), generator=g, device=dev)
+    for dt in (torch.float32, torch.bfloat16):  # k1_strided<f32>, k1_strided<bf16> (config 5)
+        p5 = torch.randn(16, 150, 512, 512, generator=g, device=dev).to(dt)
+        m = MulticlassJaccardIndex(150, validate_args=False).to(dev)
+        for _ in range(2):
+            m.update(p5, t5)
+        del p5, m
+    n = 1 << 28  # k2_single, binary (K1b): BinaryAccuracy on config 3's logits
+    p = torch.randn(n, generator=g, device=dev) * 3
+    t = torch.randint(2, (n,), generator=g, device=dev)
+    m = BinaryAccuracy(validate_args=False).to(dev)
+    for _ in range(2):
+        m.update(p, t)
+    del p, t, m
+    nl, L = 1 << 21, 100  # k2_single multilabel, k2_multi, k3_normalize_vec on [2^21, 100]
+    pl = torch.randn(nl, L, generator=g, device=dev)
+    tl = torch.randint(2, (nl, L), generator=g, device=dev)
+    for m in (MultilabelStatScores(L, validate_args=False), MultilabelPrecisionRecallCurve(L, thresholds=200, validate_args=False),
+              MultilabelAUROC(L, thresholds=None, validate_args=False)):
+        m = m.to(dev)
+        for _ in range(2):
+            m.update(pl, tl)
 torch.cuda.synchronize()
 if which in ("f2", "f2x", "f3", "k1c") and "TIME" in __import__("os").environ:  # quick timing while iterating (not a bench value)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
