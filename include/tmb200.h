@@ -208,7 +208,8 @@ int tmb_binary_curve_update_noalloc(const void* preds, int preds_dtype, const vo
  *   _binary_precision_recall_curve_format      functional/classification/precision_recall_curve.py:176-186
  *   _multilabel_precision_recall_curve_format  same file :752-757
  * out[i] = sigmoid(preds[i]) if ANY element taking part in the test lies outside [0,1] (NaN included),
- * else out[i] = preds[i]; same dtype as preds.  With `target` non-NULL and has_ignore, elements whose target
+ * else out[i] = preds[i]; same dtype as preds.  One read of the data either way: the testing pass copies as it goes
+ * and stops at the first outside value, the sigmoid pass runs only if there was one.  With `target` non-NULL and has_ignore, elements whose target
  * equals ignore_index take no part in the test.  `flag` is one caller-owned int64 that must start at 0 and
  * `generation` a strictly increasing positive call counter for that flag (it replaces clearing the flag).
  */
@@ -226,13 +227,20 @@ int tmb_sigmoid_normalize(const void* preds, int preds_dtype, int64_t n, const v
  * tmb_rows_outside_flag: preds [n_rows, num_classes] row-major; raises *flag to `generation` if any element of a
  *   row whose target (one integer per row; NULL = every row counts) differs from ignore_index lies outside [0,1]
  *   or is NaN.  Any num_classes.
- * tmb_softmax_rows: out = softmax(preds, dim=1) if *flag == generation, else a copy; same dtype as preds.  The
- *   result is bit-identical to torch.softmax on the device for num_classes <= 1024 (its persistent warp kernel's
- *   lane layout, reduction order, expf and IEEE division are reproduced); wider rows return TMB_E_LIMIT and the
- *   caller keeps torch's own kernel for them.
+ * tmb_softmax_rows: out = softmax(preds, dim=1) if *flag == generation; otherwise `out` is left as it is (pass B of
+ *   tmb_softmax_normalize: pass A has already copied the rows).  Same dtype as preds.  The result is bit-identical to
+ *   torch.softmax on the device for num_classes <= 1024 (its persistent warp kernel's lane layout, reduction order,
+ *   expf and IEEE division are reproduced); wider rows return TMB_E_LIMIT and the caller keeps torch's own kernel.
+ * tmb_softmax_normalize: the whole conditional normalisation with ONE read of the data: pass A copies preds to out
+ *   while it tests the rows that count and stops at the first value outside [0,1] (for logits: after the first
+ *   wave of CTAs); pass B (tmb_softmax_rows) overwrites out with the softmax only if pass A raised the flag.
+ *   num_classes <= 1024.  `flag` / `generation` as for tmb_sigmoid_normalize.
  */
 int tmb_rows_outside_flag(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes,
                           const void* target, int target_dtype, int has_ignore, int64_t ignore_index,
+                          int64_t* flag, int64_t generation, void* stream);
+int tmb_softmax_normalize(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes,
+                          const void* target, int target_dtype, int has_ignore, int64_t ignore_index, void* out,
                           int64_t* flag, int64_t generation, void* stream);
 int tmb_softmax_rows(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes, void* out,
                      const int64_t* flag, int64_t generation, void* stream);

@@ -31,12 +31,21 @@ if which == "k1":
 elif which == "k2":
     from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve
 
-    n = 1 << 28
+    n = 1 << int(__import__("os").environ.get("LOG2N", "28"))
     p = torch.randn(n, generator=g, device=dev) * 3
     t = torch.randint(2, (n,), generator=g, device=dev)
     m = BinaryPrecisionRecallCurve(thresholds=200, validate_args=False).to(dev)
     for _ in range(reps):
         m.update(p, t)
+    if "TIME" in __import__("os").environ:
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(20):
+            m.update(p, t)
+        b.record()
+        torch.cuda.synchronize()
+        print("k2 log2n", __import__("os").environ.get("LOG2N", "28"), "ms/update", a.elapsed_time(b) / 20)
 elif which == "k5":
     from torchmetrics_forked_b200.classification import MulticlassJaccardIndex
 
@@ -135,6 +144,28 @@ elif which == "evid":  # round 2 evidence set: the kernels of rows a1-a12 that h
         m = m.to(dev)
         for _ in range(2):
             m.update(pl, tl)
+elif which == "evid2":  # exact-mode update kernels: k3_normalize_vec ([2^21,100] sigmoid), k5_softmax_rows / _small
+    from torchmetrics_forked_b200.classification import MulticlassAUROC, MultilabelAUROC
+
+    nl, L = 1 << 21, 100
+    pl = torch.randn(nl, L, generator=g, device=dev)
+    tl = torch.randint(2, (nl, L), generator=g, device=dev)
+    m = MultilabelAUROC(L, thresholds=None, validate_args=False).to(dev)
+    for _ in range(2):
+        m.reset()
+        m.update(pl, tl)
+    tc = torch.randint(L, (nl,), generator=g, device=dev)
+    m = MulticlassAUROC(L, thresholds=None, validate_args=False).to(dev)
+    for _ in range(2):
+        m.reset()
+        m.update(pl, tc)
+    del pl, tl, m
+    ps = torch.randn(1 << 24, 10, generator=g, device=dev)
+    ts = torch.randint(10, (1 << 24,), generator=g, device=dev)
+    m = MulticlassAUROC(10, thresholds=None, validate_args=False).to(dev)
+    for _ in range(2):
+        m.reset()
+        m.update(ps, ts)
 torch.cuda.synchronize()
 if which in ("f2", "f2x", "f3", "k1c") and "TIME" in __import__("os").environ:  # quick timing while iterating (not a bench value)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)

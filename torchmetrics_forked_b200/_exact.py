@@ -67,22 +67,22 @@ def softmax_normalize(
         target = _as_kernel_input(target.reshape(-1))
         if target.numel() != rows:
             raise ValueError("`target` must hold one class index per row of `preds`")
+    t_ptr, t_code, ign = (nat.ptr(target), nat.label_code(target), int(ignore_index)) if has_ign else (0, 0, 0)
     with nat.on_device(dev):
-        rc = nat.lib().tmb_rows_outside_flag(
-            nat.ptr(preds), nat.float_code(preds), rows, num_classes, nat.ptr(target) if has_ign else 0,
-            nat.label_code(target) if has_ign else 0, has_ign, int(ignore_index) if has_ign else 0, nat.ptr(flag), 1,
-            nat.stream_ptr(dev),
-        )  # fmt: skip
-        nat.check(rc, "tmb_rows_outside_flag")
         if num_classes > SOFTMAX_MAX_CLASSES:
+            rc = nat.lib().tmb_rows_outside_flag(
+                nat.ptr(preds), nat.float_code(preds), rows, num_classes, t_ptr, t_code, has_ign, ign, nat.ptr(flag), 1,
+                nat.stream_ptr(dev),
+            )
+            nat.check(rc, "tmb_rows_outside_flag")
             # torch uses a different (block-reduction) kernel for wide rows; keep its bits by keeping its kernel
             return torch.where(flag.bool(), preds.softmax(1), preds)
         out = torch.empty_like(preds)
-        rc = nat.lib().tmb_softmax_rows(
-            nat.ptr(preds), nat.float_code(preds), rows, num_classes, nat.ptr(out), nat.ptr(flag), 1,
-            nat.stream_ptr(dev),
+        rc = nat.lib().tmb_softmax_normalize(
+            nat.ptr(preds), nat.float_code(preds), rows, num_classes, t_ptr, t_code, has_ign, ign, nat.ptr(out),
+            nat.ptr(flag), 1, nat.stream_ptr(dev),
         )
-        nat.check(rc, "tmb_softmax_rows")
+        nat.check(rc, "tmb_softmax_normalize")
     return out
 
 

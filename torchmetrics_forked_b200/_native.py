@@ -81,6 +81,10 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int, c_int64, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_int64, c_void_p],
     ),
+    "tmb_softmax_normalize": (
+        c_int,
+        [c_void_p, c_int, c_int64, c_int64, c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p, c_int64, c_void_p],
+    ),
     "tmb_softmax_rows": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_int64, c_void_p]),
     "tmb_mc_curve_update": (
         c_int,

@@ -113,16 +113,44 @@ __device__ __forceinline__ Binner make_binner(const TbArgs& a, float* sh_pad, in
   return b;
 }
 
-__device__ __forceinline__ bool flag_up(const TbArgs& a) {
-  return *((volatile unsigned long long*)a.scratch) != 0ULL;
+// The "saw a value outside [0,1]" flag lives in scratch[0].  It is read and written with device-scope relaxed
+// accesses, and a CTA touches it as rarely as it can: `volatile` accesses compile to system-scope ones
+// (LDG/STG.STRONG.SYS), and when every warp of the grid stored to and then loaded from that one word — which is what
+// logits make pass A do: each warp finds an outside value in its first batch — the word's L2 slice serialised ~5000
+// system-scope requests and pass A took 65-90 us instead of ~10 (ncu: 69 % of its stall samples on the compare after
+// that load).  Now a CTA stores at most once (tb_cta_flag remembers), and once it has raised or seen the flag it
+// never loads it again.
+__shared__ int tb_cta_flag;  // this CTA has raised the global flag or seen it up; reset by pass_enabled()
+
+__device__ __forceinline__ unsigned long long ld_flag_word(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
 }
-__device__ __forceinline__ void raise_flag(const TbArgs& a) { *((volatile unsigned long long*)a.scratch) = 1ULL; }
+__device__ __forceinline__ void st_flag_word(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ bool flag_up(const TbArgs& a) {
+  if (*((volatile int*)&tb_cta_flag)) return true;
+  const bool up = ld_flag_word(a.scratch) != 0ULL;
+  if (up) *((volatile int*)&tb_cta_flag) = 1;
+  return up;
+}
+// may be called from divergent code by any subset of a warp
+__device__ __forceinline__ void raise_flag(const TbArgs& a) {
+  const unsigned m = __activemask();
+  if ((threadIdx.x & 31) == (unsigned)(__ffs(m) - 1) && atomicExch(&tb_cta_flag, 1) == 0) st_flag_word(a.scratch, 1ULL);
+}
 
 // CTA-uniform decision whether this pass has anything to do (the flag may flip while pass A runs, so
 // one thread samples it for everybody).
 __device__ __forceinline__ bool pass_enabled(const TbArgs& a, bool sig_pass) {
   __shared__ int go;
-  if (threadIdx.x == 0) go = sig_pass ? flag_up(a) : !flag_up(a);
+  if (threadIdx.x == 0) {
+    const bool up = ld_flag_word(a.scratch) != 0ULL;
+    tb_cta_flag = up ? 1 : 0;
+    go = sig_pass ? up : !up;
+  }
   __syncthreads();
   return go != 0;
 }

@@ -25,6 +25,19 @@ namespace tmb {
 
 constexpr uint32_t kSentinel = 0xffffffffu;  // key of an ignored entry: sorts last
 
+// the generation flag of the conditional normalisation, read with a device-scope relaxed load (a `volatile` read is a
+// system-scope one; thousands of warps polling one word that way queue up at its L2 slice)
+__device__ __forceinline__ unsigned long long ld_gen(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+// end of a testing pass: ONE atomicMax per CTA that found something, none once the flag is known to be up (with
+// logits every thread finds an outside value at once)
+__device__ __forceinline__ void publish_found(bool found, unsigned long long* flag, unsigned long long gen) {
+  if (__syncthreads_or(found) && threadIdx.x == 0 && ld_gen(flag) != gen) atomicMax(flag, gen);
+}
+
 // ---- sort keys --------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t make_key(float v, bool positive, bool& negative_score) {
   uint32_t u = __float_as_uint(v);
@@ -41,33 +54,42 @@ __device__ __forceinline__ uint32_t key_positive(uint32_t key) { return (~key - 
 __device__ __forceinline__ float key_score(uint32_t key) { return __uint_as_float((~key - 1u) >> 1); }
 
 // ---- conditional sigmoid (exact-mode update) ----------------------------------------------------------------
-// pass A: atomicMax(flag, gen) as soon as a value outside [0,1] (or NaN) is seen among the elements that take
-// part in the test; pass B: out = (flag == gen) ? sigmoid(x) : x.  `gen` grows with every call, so the flag
-// never needs clearing.
+// pass A: copy x to out while looking for a value outside [0,1] (or NaN) among the elements that take part in the
+// test; atomicMax(flag, gen) at the first one, after which every CTA stops (what it has copied so far is overwritten
+// by pass B).  pass B: out = sigmoid(x) if flag == gen, else nothing — the copy pass A made stands.  Either way the
+// data is read ONCE and written once: probabilities cost pass A alone, logits pass A's first wave plus pass B.
+// `gen` grows with every call, so the flag never needs clearing.
 template <int DT>
-__global__ void __launch_bounds__(256) k3_outside_flag(const void* __restrict__ x, int64_t n,
+__device__ __forceinline__ void store_raw(void* out, int64_t i, float v) {
+  if constexpr (DT == TMB_F32) {
+    ((float*)out)[i] = v;
+  } else if constexpr (DT == TMB_BF16) {
+    ((__nv_bfloat16*)out)[i] = __float2bfloat16_rn(v);  // exact: v came from a bf16
+  } else {
+    ((__half*)out)[i] = __float2half_rn(v);
+  }
+}
+
+template <int DT>
+__global__ void __launch_bounds__(256) k3_outside_flag(const void* __restrict__ x, void* __restrict__ out, int64_t n,
                                                        const void* __restrict__ target, int tdt, int has_ignore,
                                                        int64_t ignore, unsigned long long* flag,
                                                        unsigned long long gen) {
   __shared__ int go;
-  if (threadIdx.x == 0) go = *((volatile unsigned long long*)flag) != gen;
+  if (threadIdx.x == 0) go = ld_gen(flag) != gen;
   __syncthreads();
   if (!go) return;
   bool found = false;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     float v = load_elem<DT>(x, i);
+    store_raw<DT>(out, i, v);
     bool outside = !(v >= 0.0f && v <= 1.0f);
     if (outside && target != nullptr && has_ignore) outside = load_label(target, tdt, i) != ignore;
     found |= outside;
     if (__any_sync(__activemask(), found)) break;  // somebody in the warp found one: the answer is known
-    if ((i & 0xfffff) < (int64_t)gridDim.x * blockDim.x && *((volatile unsigned long long*)flag) == gen) break;
+    if ((i & 0xfffff) < (int64_t)gridDim.x * blockDim.x && ld_gen(flag) == gen) break;
   }
-  // one atomic per warp, and none once the flag is known to be up: with logits EVERY thread finds an outside
-  // value at once, and 300 k atomics on one address took longer than the whole sigmoid pass
-  const unsigned voters = __activemask();
-  const bool warp_found = __any_sync(voters, found);
-  if (warp_found && (threadIdx.x & 31) == (__ffs(voters) - 1) && *((volatile unsigned long long*)flag) != gen)
-    atomicMax(flag, gen);
+  publish_found(found, flag, gen);
 }
 
 template <int DT>
@@ -81,10 +103,9 @@ __device__ __forceinline__ float sigmoid_round(float x) {
 template <int DT>
 __global__ void __launch_bounds__(256) k3_normalize(const void* __restrict__ x, void* __restrict__ out, int64_t n,
                                                     const unsigned long long* flag, unsigned long long gen) {
-  const bool sig = *flag == gen;
+  if (*flag != gen) return;  // all values were inside [0,1]: pass A's copy is the result
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    float v = load_elem<DT>(x, i);
-    if (sig) v = sigmoid_round<DT>(v);
+    float v = sigmoid_round<DT>(load_elem<DT>(x, i));
     if constexpr (DT == TMB_F32) {
       ((float*)out)[i] = v;
     } else if constexpr (DT == TMB_BF16) {
@@ -129,17 +150,19 @@ struct VecIO {
 };
 
 template <int DT>
-__global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restrict__ x, int64_t n_vec,
-                                                           unsigned long long* flag, unsigned long long gen) {
+__global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restrict__ x, void* __restrict__ out,
+                                                           int64_t n_vec, unsigned long long* flag,
+                                                           unsigned long long gen) {
   constexpr int E = VecIO<DT>::kElems;
-  constexpr int U = 4;
+  constexpr int U = 8;
   __shared__ int go;
-  if (threadIdx.x == 0) go = *((volatile unsigned long long*)flag) != gen;
+  if (threadIdx.x == 0) go = ld_gen(flag) != gen;
   __syncthreads();
   if (!go) return;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   const int lane = threadIdx.x & 31;
   bool found = false;
+  int trip = 0;
   // the loop variable is warp-uniform so that the vote below is reached by the whole warp
   for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x - lane; b < n_vec; b += stride * U) {
     float v[U][E];
@@ -154,18 +177,16 @@ __global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restric
       }
     }
 #pragma unroll
-    for (int u = 0; u < U; ++u)
+    for (int u = 0; u < U; ++u) {
+      const int64_t i = b + lane + (int64_t)u * stride;
+      if (i < n_vec) VecIO<DT>::store(out, i, v[u]);
 #pragma unroll
       for (int e = 0; e < E; ++e) found |= !(v[u][e] >= 0.0f && v[u][e] <= 1.0f);
+    }
     if (__any_sync(kFull, found)) break;
-    if (*((volatile unsigned long long*)flag) == gen) break;  // another CTA already settled it
+    if ((++trip & 15) == 0 && ld_gen(flag) == gen) break;  // another CTA already settled it (polled now and then)
   }
-  // one atomic per warp, and none once the flag is known to be up: with logits EVERY thread finds an outside
-  // value at once, and 300 k atomics on one address took longer than the whole sigmoid pass
-  const unsigned voters = __activemask();
-  const bool warp_found = __any_sync(voters, found);
-  if (warp_found && (threadIdx.x & 31) == (__ffs(voters) - 1) && *((volatile unsigned long long*)flag) != gen)
-    atomicMax(flag, gen);
+  publish_found(found, flag, gen);
 }
 
 template <int DT>
@@ -174,7 +195,8 @@ __global__ void __launch_bounds__(256) k3_normalize_vec(const void* __restrict__
                                                         unsigned long long gen) {
   constexpr int E = VecIO<DT>::kElems;
   constexpr int U = 8;
-  const bool sig = *flag == gen;
+  if (*flag != gen) return;  // all values were inside [0,1]: pass A's copy is the result
+  const bool sig = true;
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
   for (int64_t b = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; b < n_vec; b += stride * U) {
     float v[U][E];
@@ -1048,17 +1070,19 @@ static int run_normalize(const void* x, void* out, int64_t n, const void* target
   // pass A: is any tested element outside [0,1]?
   if (test_all && n_vec > 0) {
     auto k = k3_outside_flag_vec<DT>;
-    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 4 - 1) / (256 * 4)), 256, 0, st>>>(x, n_vec, flag, gen);
+    k<<<resident_grid(k, 256, 0, (n_vec + 256 * 8 - 1) / (256 * 8)), 256, 0, st>>>(x, out, n_vec, flag, gen);
     if (int rc = launch_status()) return rc;
     if (n_tail > 0) {
-      k3_outside_flag<DT><<<1, 256, 0, st>>>(x_tail, n_tail, t_tail, tdt, has_ignore, ignore, flag, gen);
+      k3_outside_flag<DT><<<1, 256, 0, st>>>(x_tail, out_tail, n_tail, t_tail, tdt, has_ignore, ignore, flag, gen);
       if (int rc = launch_status()) return rc;
     }
   } else {
-    k3_outside_flag<DT><<<wave_grid((n + 255) / 256, 8), 256, 0, st>>>(x, n, target, tdt, has_ignore, ignore, flag, gen);
+    k3_outside_flag<DT><<<wave_grid((n + 255) / 256, 8), 256, 0, st>>>(x, out, n, target, tdt, has_ignore, ignore, flag,
+                                                                       gen);
     if (int rc = launch_status()) return rc;
+    // the scalar pass covered everything, including what the vector pass B will overwrite if the flag is up
   }
-  // pass B: copy or sigmoid
+  // pass B: sigmoid, only when pass A raised the flag
   if (n_vec > 0) {
     auto k = k3_normalize_vec<DT>;
     k<<<resident_grid(k, 256, 0, (n_vec + 256 * 8 - 1) / (256 * 8)), 256, 0, st>>>(x, out, n_vec, flag, gen);

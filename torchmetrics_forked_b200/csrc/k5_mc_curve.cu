@@ -19,15 +19,24 @@
 
 namespace tmb {
 
+__device__ __forceinline__ unsigned long long ld_gen(const unsigned long long* p) {  // device-scope relaxed load
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // pass A: atomicMax(flag, gen) as soon as a value outside [0,1] (NaN included) shows up in a row that is not
 // ignored.  Same flag protocol as k3_outside_flag.
+// With `out` non-null the rows are copied while they are tested (ignored rows too): for inputs that already are
+// probabilities this one pass is the whole normalisation (pass B returns at once), so the data is read once.
 template <int DT>
-__global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restrict__ x, int64_t rows, int C, RowMap rm,
+__global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restrict__ x, void* __restrict__ out,
+                                                            int64_t rows, int C, RowMap rm,
                                                             const void* __restrict__ target, int tdt,
                                                             int has_ignore, int64_t ignore, unsigned long long* flag,
                                                             unsigned long long gen) {
   __shared__ int go;
-  if (threadIdx.x == 0) go = *((volatile unsigned long long*)flag) != gen;
+  if (threadIdx.x == 0) go = ld_gen(flag) != gen;
   __syncthreads();
   if (!go) return;
   const int lane = threadIdx.x & 31;
@@ -40,17 +49,19 @@ __global__ void __launch_bounds__(256) k5_rows_outside_flag(const void* __restri
   for (int64_t r0 = warp * rows_per_warp; r0 < rows; r0 += nwarps * rows_per_warp, ++trip) {  // warp-uniform
     const int64_t r = r0 + sub;
     bool counted = r < rows;
+    const bool in_range = counted;
     if (counted && has_ignore && target != nullptr) counted = load_label(target, tdt, r) != ignore;
-    if (counted) {
+    if (counted || (in_range && out != nullptr)) {
       for (int c = j; c < C; c += rm.W) {
         const float v = load_elem<DT>(x, r * C + c);
-        found |= !(v >= 0.0f && v <= 1.0f);
+        if (out != nullptr) store_elem<DT>(out, r * C + c, v);
+        found |= counted & !(v >= 0.0f && v <= 1.0f);
       }
     }
     if (__any_sync(kFull, found)) break;
-    if ((trip & 63) == 63 && *((volatile unsigned long long*)flag) == gen) break;
+    if ((trip & 63) == 63 && ld_gen(flag) == gen) break;
   }
-  if (__any_sync(kFull, found) && lane == 0 && *((volatile unsigned long long*)flag) != gen) atomicMax(flag, gen);
+  if (__syncthreads_or(found) && threadIdx.x == 0 && ld_gen(flag) != gen) atomicMax(flag, gen);  // once per CTA
 }
 
 // pass B: out = (flag == gen) ? softmax(x, dim=1) : x.  A lane takes 8 elements per trip — SLOTS of each of
@@ -63,7 +74,8 @@ __global__ void __launch_bounds__(256) k5_softmax_rows(const void* __restrict__ 
                                                        const unsigned long long* __restrict__ flag,
                                                        unsigned long long gen) {
   constexpr int ROWS = SLOTS < 8 ? 8 / SLOTS : 1;
-  const bool soft = *flag == gen;
+  if (*flag != gen) return;  // nothing outside [0,1]: the copy made by pass A is the result
+  const bool soft = true;
   const int lane = threadIdx.x & 31;
   const int W = SLOTS > 1 ? 32 : rm.W, log2W = SLOTS > 1 ? 5 : rm.log2W;  // several slots: the row takes the warp
   const int sub = lane >> log2W, j = lane & (W - 1);
@@ -116,7 +128,8 @@ __global__ void __launch_bounds__(kSoftmaxSmallRows) k5_softmax_small(const void
   constexpr int C = CX;  // compile-time class count: the per-class loops carry no bounds checks
   constexpr int W = CX <= 2 ? 2 : (CX <= 4 ? 4 : (CX <= 8 ? 8 : (CX <= 16 ? 16 : 32)));  // torch's lanes per row
   extern __shared__ float stage[];  // [kSoftmaxSmallRows][C | 1]
-  const bool soft = *flag == gen;
+  if (*flag != gen) return;  // nothing outside [0,1]: the copy made by pass A is the result
+  const bool soft = true;
   constexpr int stride = C | 1;
   constexpr uint32_t magic = (uint32_t)(0x100000000ull / (unsigned)C) + 1u;  // i / C for i * C < 2^32
   for (int64_t tile0 = (int64_t)blockIdx.x * kSoftmaxSmallRows; tile0 < rows;
@@ -148,12 +161,12 @@ __global__ void __launch_bounds__(kSoftmaxSmallRows) k5_softmax_small(const void
 }
 
 template <int DT>
-static int launch_rows_flag(const void* x, int64_t rows, int C, const void* target, int tdt, int has_ignore,
+static int launch_rows_flag(const void* x, void* out, int64_t rows, int C, const void* target, int tdt, int has_ignore,
                             int64_t ignore, unsigned long long* flag, unsigned long long gen, cudaStream_t st) {
   const RowMap rm = row_map(C < kSoftmaxMaxClasses ? C : kSoftmaxMaxClasses);  // wider rows: 32 lanes stride over C
   auto k = k5_rows_outside_flag<DT>;
   const int64_t work = (rows * rm.W + 255) / 256;
-  k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, rows, C, rm, target, tdt, has_ignore, ignore, flag, gen);
+  k<<<resident_grid(k, 256, 0, work), 256, 0, st>>>(x, out, rows, C, rm, target, tdt, has_ignore, ignore, flag, gen);
   return launch_status();
 }
 
@@ -206,9 +219,37 @@ extern "C" int tmb_rows_outside_flag(const void* preds, int preds_dtype, int64_t
   const unsigned long long gen = (unsigned long long)generation;
   const int C = (int)num_classes;
   switch (preds_dtype) {
-    case TMB_F32: return launch_rows_flag<TMB_F32>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
-    case TMB_F16: return launch_rows_flag<TMB_F16>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
-    default: return launch_rows_flag<TMB_BF16>(preds, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+    case TMB_F32: return launch_rows_flag<TMB_F32>(preds, nullptr, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+    case TMB_F16: return launch_rows_flag<TMB_F16>(preds, nullptr, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+    default: return launch_rows_flag<TMB_BF16>(preds, nullptr, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st);
+  }
+}
+
+extern "C" int tmb_softmax_normalize(const void* preds, int preds_dtype, int64_t n_rows, int64_t num_classes,
+                                     const void* target, int target_dtype, int has_ignore, int64_t ignore_index,
+                                     void* out, int64_t* flag, int64_t generation, void* stream) {
+  if (float_bytes(preds_dtype) == 0) return TMB_E_DTYPE;
+  if (target != nullptr && label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_rows < 0 || num_classes < 1 || generation < 1) return TMB_E_SHAPE;
+  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;
+  if (!flag) return TMB_E_NULL;
+  if (n_rows == 0) return 0;
+  if (!preds || !out) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* f = (unsigned long long*)flag;
+  const unsigned long long gen = (unsigned long long)generation;
+  const int C = (int)num_classes;
+  int rc;
+  switch (preds_dtype) {  // pass A: copy + test, ends at the first value outside [0,1]
+    case TMB_F32: rc = launch_rows_flag<TMB_F32>(preds, out, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st); break;
+    case TMB_F16: rc = launch_rows_flag<TMB_F16>(preds, out, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st); break;
+    default: rc = launch_rows_flag<TMB_BF16>(preds, out, n_rows, C, target, target_dtype, has_ignore, ignore_index, f, gen, st); break;
+  }
+  if (rc) return rc;
+  switch (preds_dtype) {  // pass B: softmax, only when pass A raised the flag
+    case TMB_F32: return launch_softmax_rows<TMB_F32>(preds, out, n_rows, C, f, gen, st);
+    case TMB_F16: return launch_softmax_rows<TMB_F16>(preds, out, n_rows, C, f, gen, st);
+    default: return launch_softmax_rows<TMB_BF16>(preds, out, n_rows, C, f, gen, st);
   }
 }
 
