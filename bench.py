@@ -480,6 +480,25 @@ def extras_block(device, steps: int, warmup: int, peak: float):
     except Exception as e:  # noqa: BLE001
         out["f2_multiclass_exact"] = {"error": repr(e)}
     torch.cuda.empty_cache()
+    # config 2's kernel under atomic contention: the state is updated with one RED.64 per row, so what matters is how
+    # many rows hit the same cell.  (a) a collapsed model: every row lands in ONE cell; (b) all mass on the diagonal of
+    # 10 classes.  Beside them the bench data (70 % of the rows spread over the 1000 diagonal cells).
+    r7 = 1 << 20
+    p7, t7 = make_cfg2(r7, device, 31)
+    m = _MCM(C2_CLASSES, validate_args=False).to(device)
+    record("cfg2_contention_bench_data_2^20_rows", lambda: m.update(p7, t7), r7, r7 * 2008, r7 * 2000, 1)
+    p7[:, 7] = 30.0
+    t7.fill_(7)
+    record("cfg2_contention_all_rows_one_cell", lambda: m.update(p7, t7), r7, r7 * 2008, r7 * 2000, 1)
+    t7 = torch.randint(10, (r7,), generator=g, device=device)
+    p7.copy_(torch.randn(r7, C2_CLASSES, generator=g, device=device).bfloat16())
+    p7[torch.arange(r7, device=device), t7] += 12
+    record("cfg2_contention_diagonal_of_10_classes", lambda: m.update(p7, t7), r7, r7 * 2008, r7 * 2000, 1)
+    base_ms = out["cfg2_contention_bench_data_2^20_rows"]["ms_per_update"]
+    for k in ("cfg2_contention_all_rows_one_cell", "cfg2_contention_diagonal_of_10_classes"):
+        out[k]["vs_bench_data"] = out[k]["ms_per_update"] / base_ms
+    del p7, t7, m
+    torch.cuda.empty_cache()
     # config 2 rows through StatScores (three C-bin histograms instead of the C x C matrix)
     r2 = 1 << 20
     p2, t2 = make_cfg2(r2, device, 99)
@@ -527,7 +546,18 @@ def extras_block(device, steps: int, warmup: int, peak: float):
         upd_ms = ev[0].elapsed_time(ev[upd]) / upd
         cmp_ms = ev[upd].elapsed_time(ev[upd + 1])
         ls = n4 * upd * L4
+        pr = torch.rand(n4, L4, generator=g, device=device)  # inputs that already are probabilities: one copy pass
+        tr = torch.randint(2, (n4, L4), generator=g, device=device)
+        mp = MultilabelAUROC(L4, thresholds=None, validate_args=False).to(device)
+
+        def upd_probs():
+            mp.reset()
+            mp.update(pr, tr)
+
+        _, probs_ms = timed_loop(upd_probs, 5, 2, 1, device)
+        del pr, tr, mp
         out["cfg4_multilabel_auroc_exact"] = {
+            "update_probs_input_ms": probs_ms, "update_probs_input_roofline_frac": n4 * L4 * 8 / probs_ms / 1e6 / peak,
             "update_ms": upd_ms, "update_algo_gbs": n4 * L4 * 8 / upd_ms / 1e6,
             "update_roofline_frac": n4 * L4 * 8 / upd_ms / 1e6 / peak,
             "compute_ms": cmp_ms, "compute_label_samples_per_s": ls / cmp_ms * 1e3,

@@ -90,8 +90,8 @@ int tmb_mc_label_hist(const void* preds, int preds_dtype, const void* target, in
 /* tmb_mc_topk_hist: the top_k > 1 branch of
  *   _multiclass_stat_scores_update      functional/classification/stat_scores.py:363-393
  *   select_topk (torch.topk + scatter)  utilities/data.py:115-139
- * preds [n_rows, num_classes] row-major float scores (2 <= num_classes <= 1024, else TMB_E_LIMIT), target one
- * integer per row.  Adds into `scratch` (int64 [3 * num_classes], the TMB_MC_STATS layout: rows per target class |
+ * preds [n_rows, num_classes] row-major float scores (num_classes >= 2; up to 1024 classes a warp keeps the row
+ * in registers, wider rows are walked once per selection round), target one integer per row.  Adds into `scratch` (int64 [3 * num_classes], the TMB_MC_STATS layout: rows per target class |
  * rows with the class among the top_k scores | rows whose target is among its top_k); follow with
  * tmb_mc_stats_finalize(mode TMB_MC_STATS).  Ties at the k-th score go to the lower class index, NaN ranks highest
  * (torch.topk's CUDA order).  Rows with target == ignore_index are dropped. */
@@ -116,6 +116,15 @@ int tmb_mc_hist_samplewise(const void* preds, int preds_dtype, int preds_is_labe
                            int has_ignore, int64_t ignore_index, int64_t* scratch, int32_t* err, void* stream);
 int tmb_mc_stats_finalize_samplewise(int64_t* scratch, int64_t n_samples, int64_t num_classes, int64_t* tp,
                                      int64_t* fp, int64_t* tn, int64_t* fn, void* stream);
+
+/* tmb_mc_topk_hist_samplewise: top_k > 1 together with multidim_average="samplewise" — the `sum_dim = [1]` form of
+ * the same branch (functional/classification/stat_scores.py:363-393).  preds [n_samples * rows_per_sample,
+ * num_classes] row-major (the extra dimensions of a sample folded into its rows), target one integer per row; the
+ * TMB_MC_STATS histograms of sample n are ADDED into scratch[n * 3 * num_classes ...] (int64 [n_samples, 3 *
+ * num_classes], zero-initialised by the caller); follow with tmb_mc_stats_finalize_samplewise. */
+int tmb_mc_topk_hist_samplewise(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                int64_t n_samples, int64_t rows_per_sample, int64_t num_classes, int64_t top_k,
+                                int has_ignore, int64_t ignore_index, int64_t* scratch, int32_t* err, void* stream);
 
 /* One argmax for a whole MetricCollection (collections.py:200-226 calls every compute group's
  * update, so Accuracy + ConfusionMatrix read the logits twice and run argmax twice): tmb_mc_argmax_hist /

@@ -70,6 +70,28 @@ def main() -> None:
     lt = torch.randint(2, (7, 4, 20), generator=g)
     lt[torch.rand(7, 4, 20, generator=g) < 0.1] = -1
     sw_case("multilabel_logits_ignore", "multilabel", torch.randn(7, 4, 20, generator=g), lt, num_labels=4, ignore_index=-1)
+    # ---- round 2: top_k > 1 beyond 1024 classes, and top_k > 1 together with samplewise ---------------------
+    case("c1500_k5_wide", torch.randn(120, 1500, generator=g), torch.randint(1500, (120,), generator=g), 1500, 5)
+    case("c2049_k3_wide_ignore", torch.randn(64, 2049, generator=g),
+         torch.where(torch.rand(64, generator=g) < 0.2, torch.tensor(-1), torch.randint(2049, (64,), generator=g)),
+         2049, 3, ignore_index=-1)
+
+    def sw_topk_case(name, preds, target, C, k, ignore_index=None):
+        d = {"preds": preds.numpy(), "target": target.numpy(), "num_classes": C, "top_k": k,
+             "ignore_index": -999 if ignore_index is None else ignore_index}
+        kw = dict(num_classes=C, top_k=k, ignore_index=ignore_index, multidim_average="samplewise")
+        for avg in ("micro", "macro", "weighted", "none"):
+            d[f"stat_scores_{avg}"] = rf.multiclass_stat_scores(preds, target, average=avg, **kw).numpy()
+            for fn in ("accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+                d[f"{fn}_{avg}"] = getattr(rf, f"multiclass_{fn}")(preds, target, average=avg, **kw).numpy()
+        np.savez_compressed(OUT / f"f3_swtopk_{name}.npz", **d)
+
+    sw_topk_case("c6_k2", torch.randn(9, 6, 5, 7, generator=g), torch.randint(6, (9, 5, 7), generator=g), 6, 2)
+    st = torch.randint(12, (7, 40), generator=g)
+    st[torch.rand(7, 40, generator=g) < 0.15] = -1
+    sw_topk_case("c12_k4_ignore", torch.randn(7, 12, 40, generator=g), st, 12, 4, ignore_index=-1)
+    sw_topk_case("c5_k3_ignore_inside", torch.randn(6, 5, 30, generator=g), torch.randint(5, (6, 30), generator=g), 5, 3,
+                 ignore_index=2)
     print("wrote", sorted(p.name for p in OUT.glob("f3_*.npz")))
 
 

@@ -360,6 +360,27 @@ def multiclass_stat_scores_topk(preds: Array, target: Array, num_classes: int, t
     return tp, fp, tn, fn
 
 
+def multiclass_stat_scores_samplewise_topk(preds: Array, target: Array, num_classes: int, top_k: int,
+                                           ignore_index: Optional[int] = None) -> Tuple[Array, Array, Array, Array]:
+    """`_multiclass_stat_scores_update` with `top_k > 1` AND `multidim_average="samplewise"` (stat_scores.py:363-393,
+    `sum_dim = [1]`): per sample `[N, C]` counts of the k-hot prediction against the one-hot target over the sample's
+    positions; positions whose target is ignored leave all four counts."""
+    q = np.asarray(preds).astype(np.float32)
+    n = q.shape[0]
+    q = np.moveaxis(q.reshape(n, num_classes, -1), 1, -1)  # [N, S, C]
+    t = np.asarray(target).astype(np.int64).reshape(n, -1)
+    out = [np.zeros((n, num_classes), np.int64) for _ in range(4)]
+    for i in range(n):
+        keep = np.ones(t.shape[1], bool) if ignore_index is None else t[i] != ignore_index
+        member = topk_sets(q[i][keep], top_k)
+        hot = t[i][keep][:, None] == np.arange(num_classes)[None, :]
+        out[0][i] = (hot & member).sum(0)
+        out[3][i] = (hot & ~member).sum(0)
+        out[1][i] = (~hot & member).sum(0)
+        out[2][i] = (~hot & ~member).sum(0)
+    return out[0], out[1], out[2], out[3]
+
+
 # ------------------------------------------------------------------------------------------ K5: multiclass curves (row f2)
 def torch_cpu_softmax(x: Array) -> Array:
     """Row softmax with the bits of torch's CPU kernel (what the golden vectors of the CPU reference contain)."""

@@ -70,7 +70,12 @@ def test_argument_errors_need_no_gpu(lib):
     assert lib.tmb_rows_outside_flag(None, 0, 4, 10, None, 0, 0, 0, None, 1, None) == E_NULL
     assert lib.tmb_mc_curve_update(None, 0, None, 0, 4, 1025, None, 5, 0, 0, 0, None, 0, None, None) == E_LIMIT
     assert lib.tmb_mc_curve_update(None, 0, None, 0, 4, 1, None, 5, 0, 0, 0, None, 0, None, None) == E_SHAPE
-    assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, 1025, 5, 0, 0, None, None, None) == E_LIMIT
+    assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, 1025, 5, 0, 0, None, None, None) == E_NULL  # wide rows are built
+    assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, (1 << 24) + 1, 5, 0, 0, None, None, None) == E_LIMIT
+    assert lib.tmb_mc_topk_hist_samplewise(None, 0, None, 0, 4, 0, 10, 2, 0, 0, None, None, None) == E_SHAPE
+    assert lib.tmb_softmax_normalize(None, 0, 4, 1025, None, 0, 0, 0, None, None, 1, None) == E_LIMIT
+    assert lib.tmb_clf_pack_keys_sharded(None, 1, 0, 0, 4, 3, 0, 0, 1, 0, None, None, 2, 1, 8, 0, None, None) == E_SHAPE
+    assert lib.tmb_clf_sorted_scores(None, None, -1, 3, 1, 0, None, 0, None, None) == E_SHAPE
     assert lib.tmb_mc_topk_hist(None, 0, None, 0, 4, 10, 11, 0, 0, None, None, None) == E_SHAPE  # top_k > classes
     assert lib.tmb_mc_hist_samplewise(None, 9, 0, None, 0, 4, 10, 3, 0, 0, None, None, None) == E_DTYPE
     assert lib.tmb_mc_shared_confmat(None, 10, None, None) == E_NULL

@@ -30,3 +30,12 @@ def test_samplewise_oracle_matches_reference(name):
         tp, fp, tn, fn = O.multiclass_stat_scores_samplewise(c["preds"], c["target"], int(c["num_classes"]), ign)
         assert np.array_equal(np.stack([tp, fp, tn, fn, tp + fn], -1), c["stat_scores_none"])
         assert np.array_equal(np.stack([tp, fp, tn, fn, tp + fn], -1).sum(1), c["stat_scores_micro"])
+
+
+@pytest.mark.parametrize("name", golden_names("f3_swtopk_"))
+def test_samplewise_topk_oracle_matches_reference(name):
+    c = load_golden(name)
+    C, k, ign = int(c["num_classes"]), int(c["top_k"]), ignore_of(c)
+    tp, fp, tn, fn = O.multiclass_stat_scores_samplewise_topk(c["preds"], c["target"], C, k, ign)
+    assert np.array_equal(np.stack([tp, fp, tn, fn, tp + fn], -1), c["stat_scores_none"])
+    assert np.array_equal(np.stack([tp, fp, tn, fn, tp + fn], -1).sum(1), c["stat_scores_micro"])

@@ -84,12 +84,65 @@ def test_topk_argument_handling():
         F.multiclass_accuracy(p, t, 4, top_k=5)
     with pytest.raises(ValueError, match="top_k"):
         F.multiclass_accuracy(t, t, 4, top_k=2)  # label-valued preds cannot be ranked
-    with pytest.raises(NotImplementedError):
-        C.MulticlassStatScores(4, multidim_average="samplewise", top_k=2)  # the combination is not built
+    C.MulticlassStatScores(4, multidim_average="samplewise", top_k=2)  # the combination is built (round 2)
     bad = t.clone()
     bad[0] = 9
     with pytest.raises(RuntimeError, match="target"):
         F.multiclass_accuracy(p, bad, 4, top_k=2)
+
+
+@pytest.mark.parametrize("name", golden_names("f3_swtopk_"))
+def test_samplewise_topk_golden(name):
+    """`top_k > 1` together with `multidim_average="samplewise"` (round 2): per-sample counts bit for bit against the
+    reference's golden vectors and the oracle, derived scores within 1e-6, module API over two updates."""
+    from torchmetrics_forked_b200 import classification as C
+    from torchmetrics_forked_b200 import functional as F
+
+    c = load_golden(name)
+    nC, k, ign = int(c["num_classes"]), int(c["top_k"]), ignore_of(c)
+    preds, target = torch.from_numpy(c["preds"]).cuda(), torch.from_numpy(c["target"]).cuda()
+    kw = dict(top_k=k, ignore_index=ign, multidim_average="samplewise")
+    tp, fp, tn, fn = O.multiclass_stat_scores_samplewise_topk(c["preds"], c["target"], nC, k, ign)
+    want = np.stack([tp, fp, tn, fn, tp + fn], -1)
+    assert np.array_equal(want, c["stat_scores_none"])
+    assert np.array_equal(F.multiclass_stat_scores(preds, target, nC, average="none", **kw).cpu().numpy(), want)
+    for dt in (torch.bfloat16, torch.float16):  # narrow dtypes: compare with the oracle on the rounded scores
+        q = preds.to(dt)
+        o = O.multiclass_stat_scores_samplewise_topk(q.float().cpu().numpy(), c["target"], nC, k, ign)
+        got = F.multiclass_stat_scores(q, target, nC, average="none", **kw).cpu().numpy()
+        # ties at the k-th place (possible after rounding) go to the lower class in both
+        assert np.array_equal(got, np.stack([o[0], o[1], o[2], o[3], o[0] + o[3]], -1)), dt
+    for avg in AVERAGES:
+        for fn_ in ("stat_scores", "accuracy", "precision", "recall", "f1_score", "specificity", "hamming_distance"):
+            got = getattr(F, f"multiclass_{fn_}")(preds, target, nC, average=avg, **kw)
+            np.testing.assert_allclose(got.cpu().numpy(), c[f"{fn_}_{avg}"], rtol=1e-6, atol=1e-7, err_msg=f"{fn_} {avg}")
+    m = C.MulticlassStatScores(nC, average="none", **kw).cuda()
+    h = preds.shape[0] // 2
+    m.update(preds[:h], target[:h])
+    m.update(preds[h:], target[h:])
+    assert isinstance(m.tp, list) and len(m.tp) == 2
+    assert np.array_equal(m.compute().cpu().numpy(), want)
+
+
+def test_topk_wide_rows_follow_torch_topk():
+    """C > 1024 (the row no longer fits the register kernels): ties, NaN and infinities as torch.topk on the device,
+    every dtype; the shared-memory histogram (C = 1500) and the global-atomic one (C = 20000) both."""
+    from torchmetrics_forked_b200 import functional as F
+
+    for C_, k, n in ((1500, 5, 129), (4099, 3, 33), (20_000, 2, 17)):
+        g = torch.Generator().manual_seed(C_)
+        for dtype in (torch.float32, torch.bfloat16, torch.float16):
+            preds = ((torch.randn(n, C_, generator=g) * 2).round() / 2).to(dtype)
+            preds[0, 0] = float("nan")
+            preds[1, C_ - 1] = float("inf")
+            preds[2, :] = float("-inf")
+            target = torch.randint(C_, (n,), generator=g)
+            got = F.multiclass_stat_scores(preds.cuda(), target.cuda(), C_, average="none", top_k=k).cpu().numpy()
+            tp, fp, tn, fn = O.multiclass_stat_scores_topk(preds.float().numpy(), target.numpy(), C_, k)
+            assert np.array_equal(got, np.stack([tp, fp, tn, fn, tp + fn], -1)), (C_, dtype)
+            idx = preds.cuda().topk(k, dim=1).indices.cpu()
+            hits = (idx == target[:, None]).any(1).sum()
+            assert int(got[:, 0].sum()) == int(hits)
 
 
 # ------------------------------------------------------------------------------------------ samplewise

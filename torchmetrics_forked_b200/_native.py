@@ -54,6 +54,11 @@ SIGNATURES = {
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p],
     ),
+    "tmb_mc_topk_hist_samplewise": (
+        c_int,
+        [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int64, c_int64, c_int, c_int64, c_void_p, c_void_p,
+         c_void_p],
+    ),
     "tmb_mc_label_hist": (
         c_int,
         [c_void_p, c_int, c_void_p, c_int, c_int64, c_int64, c_int, c_int64, c_int, c_void_p, c_void_p, c_void_p],

@@ -30,16 +30,116 @@ struct HistArgs {
   int64_t sample_len;  // flattened positions per sample (label-valued preds need it to find their sample)
 };
 
-// per-thread micro counters (mode MICRO) live in registers and are flushed once per CTA
+// per-thread state: the micro counters (mode MICRO), flushed once per CTA, and ONE pending (cell, count) pair of the
+// run-length aggregation below
 struct Micro {
   unsigned int match, n;
+  int pbin;           // pending cell of this thread's register slot (valid while pcnt != 0)
+  unsigned int pcnt;
 };
 
-__device__ __forceinline__ void hist_add(const HistArgs& h, int* sh, int64_t bin) {
-  if (h.sh_bins > 0)
+// Histograms too large for shared memory (C = 1000: 10^6 cells) are updated with RED.64 straight on the int64 state.
+// L2 serialises the atomics of one address: a batch whose rows all fall into ONE cell (a collapsed model, a
+// single-class validation shard, the background of a segmentation map) ran 4.8x slower than the bench data
+// (config 2, 2^20 rows: 1.49 ms against 0.31 ms).  So the atomics are aggregated where the repeats are, in a thread's
+// own sequence of samples: it keeps a pending (cell, count) pair per histogram it feeds and only sends it when the
+// cell changes.  Random cells cost a compare more per sample; a run of equal cells costs one atomic per thread
+// instead of one per sample.
+//   * One pair lives in registers (Micro::pbin / pcnt).  In the warp-per-row kernels lane s owns histogram s of the
+//     mode (count_sample_warp), so all of a row's histograms are handled side by side in registers.
+//   * Kernels where ONE thread classifies a sample keep the pair of the first histogram in registers and those of the
+//     others in thread-private columns of shared memory (all four pairs in registers cost the row kernels 18
+//     registers and a CTA per SM; all four in shared memory put four dependent LDS round trips behind every row:
+//     2.6 % on config 2, 25 % on the four-histogram TMB_MC_BOTH mode).
+constexpr int kPendThreads = 256;
+__shared__ int g_pend_bin[3][kPendThreads];
+__shared__ unsigned int g_pend_cnt[3][kPendThreads];
+
+__device__ __forceinline__ void hist_add_reg(const HistArgs& h, int* sh, Micro& mi, int64_t bin) {
+  if (h.sh_bins > 0) {
     atomicAdd(&sh[bin], 1);
-  else
+    return;
+  }
+  if (bin > 0x7fffffffLL) {  // cells beyond 2^31 (per-sample blocks of many classes): not aggregated
     atomicAdd(&h.out[bin], 1ULL);
+    return;
+  }
+  if (mi.pcnt != 0 && mi.pbin == (int)bin) {
+    mi.pcnt += 1;
+    return;
+  }
+  if (mi.pcnt != 0) atomicAdd(&h.out[mi.pbin], (unsigned long long)mi.pcnt);
+  mi.pbin = (int)bin;
+  mi.pcnt = 1;
+}
+// slot 0 = the register pair, slots 1 .. 3 = shared-memory columns
+__device__ __forceinline__ void hist_add(const HistArgs& h, int* sh, Micro& mi, int slot, int64_t bin) {
+  if (slot == 0) {
+    hist_add_reg(h, sh, mi, bin);
+    return;
+  }
+  if (h.sh_bins > 0) {
+    atomicAdd(&sh[bin], 1);
+    return;
+  }
+  if (bin > 0x7fffffffLL || threadIdx.x >= kPendThreads) {
+    atomicAdd(&h.out[bin], 1ULL);
+    return;
+  }
+  const unsigned cnt = g_pend_cnt[slot - 1][threadIdx.x];
+  const int pending = g_pend_bin[slot - 1][threadIdx.x];
+  if (cnt != 0 && pending == (int)bin) {
+    g_pend_cnt[slot - 1][threadIdx.x] = cnt + 1;
+    return;
+  }
+  if (cnt != 0) atomicAdd(&h.out[pending], (unsigned long long)cnt);
+  g_pend_bin[slot - 1][threadIdx.x] = (int)bin;
+  g_pend_cnt[slot - 1][threadIdx.x] = 1;
+}
+__device__ __forceinline__ void hist_pending_init() {
+  if (threadIdx.x < kPendThreads) {
+#pragma unroll
+    for (int s = 0; s < 3; ++s) g_pend_cnt[s][threadIdx.x] = 0;
+  }
+}
+__device__ __forceinline__ void hist_flush_pending(const HistArgs& h, const Micro& mi) {
+  if (h.sh_bins > 0) return;
+  if (mi.pcnt) atomicAdd(&h.out[mi.pbin], (unsigned long long)mi.pcnt);
+  if (threadIdx.x >= kPendThreads) return;
+#pragma unroll
+  for (int s = 0; s < 3; ++s) {
+    const unsigned cnt = g_pend_cnt[s][threadIdx.x];
+    if (cnt) atomicAdd(&h.out[g_pend_bin[s][threadIdx.x]], (unsigned long long)cnt);
+  }
+}
+
+// A warp that classified ONE sample together (every lane holds t and p): lane s feeds histogram s of the mode from
+// its own register pair, so the histograms of a row are updated side by side.  Must be called by the whole warp.
+__device__ __forceinline__ void count_sample_warp(const HistArgs& h, int* sh, Micro& mi, int64_t t, int64_t p, int lane) {
+  if (h.has_ignore && t == h.ignore) return;
+  if (t < 0 || t >= h.C) {
+    if (lane == 0) atomicOr(h.err, TMB_ERR_TARGET_RANGE);
+    return;
+  }
+  if (h.mode == TMB_MC_MICRO) {
+    if (lane == 0) {
+      mi.n += 1;
+      mi.match += (p == t);
+    }
+    return;
+  }
+  int64_t bin = -1;
+  if (h.mode == TMB_MC_CONFMAT) {
+    if (lane == 0) bin = t * h.C + p;
+  } else {
+    const int64_t base = h.mode == TMB_MC_BOTH ? (int64_t)h.C * h.C : 0;
+    const int s = h.mode == TMB_MC_BOTH ? lane - 1 : lane;  // BOTH: lane 0 takes the confusion matrix
+    if (h.mode == TMB_MC_BOTH && lane == 0) bin = t * h.C + p;
+    if (s == 0) bin = base + t;
+    if (s == 1) bin = base + h.C + p;
+    if (s == 2 && p == t) bin = base + 2 * (int64_t)h.C + t;
+  }
+  if (bin >= 0) hist_add_reg(h, sh, mi, bin);
 }
 
 // one classified sample: t = target, p = predicted class
@@ -55,18 +155,18 @@ __device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& 
     return;
   }
   if (h.mode == TMB_MC_CONFMAT) {
-    hist_add(h, sh, t * h.C + p);
+    hist_add(h, sh, mi, 0, t * h.C + p);
   } else if (h.mode == TMB_MC_BOTH) {  // batch confusion matrix followed by the three stat-score histograms
     const int64_t cc = (int64_t)h.C * h.C;
-    hist_add(h, sh, t * h.C + p);
-    hist_add(h, sh, cc + t);
-    hist_add(h, sh, cc + h.C + p);
-    if (p == t) hist_add(h, sh, cc + 2 * (int64_t)h.C + t);
+    hist_add(h, sh, mi, 0, t * h.C + p);
+    hist_add(h, sh, mi, 1, cc + t);
+    hist_add(h, sh, mi, 2, cc + h.C + p);
+    if (p == t) hist_add(h, sh, mi, 3, cc + 2 * (int64_t)h.C + t);
   } else if (h.mode == TMB_MC_STATS) {
     const int64_t base = sample * h.per_sample;  // 0 unless samplewise (then sh_bins == 0: global atomics)
-    hist_add(h, sh, base + t);
-    hist_add(h, sh, base + h.C + p);
-    if (p == t) hist_add(h, sh, base + 2 * (int64_t)h.C + t);
+    hist_add(h, sh, mi, 0, base + t);
+    hist_add(h, sh, mi, 1, base + h.C + p);
+    if (p == t) hist_add(h, sh, mi, 2, base + 2 * (int64_t)h.C + t);
   } else {
     mi.n += 1;
     mi.match += (p == t);
@@ -74,6 +174,7 @@ __device__ __forceinline__ void count_sample(const HistArgs& h, int* sh, Micro& 
 }
 
 __device__ __forceinline__ void hist_prologue(const HistArgs& h, int* sh) {
+  hist_pending_init();
   if (h.sh_bins > 0) {
     for (int i = threadIdx.x; i < h.sh_bins; i += blockDim.x) sh[i] = 0;
     __syncthreads();
@@ -81,6 +182,7 @@ __device__ __forceinline__ void hist_prologue(const HistArgs& h, int* sh) {
 }
 
 __device__ __forceinline__ void hist_epilogue(const HistArgs& h, int* sh, Micro mi) {
+  hist_flush_pending(h, mi);
   if (h.sh_bins > 0) {
     __syncthreads();
     for (int i = threadIdx.x; i < h.sh_bins; i += blockDim.x) {
@@ -148,7 +250,7 @@ __global__ void __launch_bounds__(256) k1_rows_warp(const char* __restrict__ pre
   constexpr int EPV = VB / ES;
   constexpr int U = 4;
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -175,10 +277,7 @@ __global__ void __launch_bounds__(256) k1_rows_warp(const char* __restrict__ pre
       }
     }
     b = best_warp(b);
-    if (lane == 0) {
-      int64_t t = load_label(target, target_dtype, row);
-      count_sample(h, sh, mi, t, best_index(b), false);
-    }
+    count_sample_warp(h, sh, mi, load_label(target, target_dtype, row), best_index(b), lane);
   }
   hist_epilogue(h, sh, mi);
 }
@@ -275,7 +374,7 @@ __global__ void __launch_bounds__(256) k1_rows_pipe(const char* __restrict__ pre
   constexpr int EPV = VB / ES;
   constexpr int U = 4;
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   const int lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
@@ -314,7 +413,7 @@ __global__ void __launch_bounds__(256) k1_rows_pipe(const char* __restrict__ pre
       }
       p = best_index(best_warp(b));
     }
-    if (lane == 0) count_sample(h, sh, mi, t_cur, p, false);
+    count_sample_warp(h, sh, mi, t_cur, p, lane);
 #pragma unroll
     for (int u = 0; u < U; ++u) cur[u] = nxt[u];
     t_cur = t_nxt;
@@ -346,7 +445,7 @@ __global__ void __launch_bounds__(kTileRows) k1_rows_thread(const char* __restri
   char* tile = (char*)sh_all;
   int* sh = (int*)(tile + tile_cap);
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   const int64_t n_tiles = (n_rows + kTileRows - 1) / kTileRows;
 
   for (int64_t tIdx = blockIdx.x; tIdx < n_tiles; tIdx += gridDim.x) {
@@ -413,14 +512,14 @@ __global__ void __launch_bounds__(kTileRows) k1_rows_thread(const char* __restri
 // One thread owns PPT = VB/ES adjacent pixels of one outer index and walks the C class planes with U
 // loads in flight; a warp therefore reads 32*VB contiguous bytes of every plane.
 template <int DT, int VB>
-__global__ void __launch_bounds__(256) k1_strided(const char* __restrict__ preds, const void* __restrict__ target,
+__global__ void __launch_bounds__(256, 3) k1_strided(const char* __restrict__ preds, const void* __restrict__ target,
                                                   int target_dtype, int64_t n_outer, int64_t S, HistArgs h) {
   extern __shared__ int sh[];
   constexpr int ES = Elem<DT>::kBytes;
   constexpr int PPT = VB / ES;
   constexpr int U = 8;
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   const int64_t groups_per_outer = S / PPT;
   const int64_t n_groups = n_outer * groups_per_outer;
   const int64_t plane_bytes = S * ES;
@@ -496,7 +595,7 @@ __global__ void __launch_bounds__(256) k1_labels(const void* __restrict__ preds,
                                                  HistArgs h) {
   extern __shared__ int sh[];
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     int64_t t = load_label(target, target_dtype, i);
     int64_t p = load_label(preds, preds_dtype, i);
@@ -742,7 +841,7 @@ __global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ pred
   constexpr int EPV = VB / ES;
   constexpr int U = 4;
   hist_prologue(h, sh);
-  Micro mi{0, 0};
+  Micro mi{0, 0, 0, 0};
   const int lane = threadIdx.x & 31;
   constexpr int lanes = LANES, rows_per_warp = 32 / LANES;  // 8 or 16 lanes per row
   const int sub = lane / LANES, j = lane % LANES;
@@ -1337,6 +1436,90 @@ __global__ void __launch_bounds__(256) k1_rows_topk_thread(const void* __restric
   }
 }
 
+// Rows that do not fit the register-resident kernels (C > 1024), and the per-sample histograms of
+// multidim_average="samplewise": a warp walks the row once per selection round (element c in lane c % 32; after the
+// first round the row comes from L1 / L2) and takes the largest (key, lowest class) pair strictly below the pair the
+// previous round took — nothing is marked, so the row needs no storage.  Ties at the k-th score go to the lower class
+// index, NaN ranks highest: the order of the other top-k kernels.  `rows_per_sample` > 0: the three histograms of row
+// r go to the block of sample r / rows_per_sample (global atomics); 0: one [3 C] histogram, privatised in shared
+// memory when `use_shared`.
+template <int DT>
+__global__ void __launch_bounds__(256) k1_rows_topk_wide(const void* __restrict__ preds, const void* __restrict__ target,
+                                                         int tdt, int64_t rows, int C, int top_k, int has_ignore,
+                                                         int64_t ignore, int64_t rows_per_sample, int use_shared,
+                                                         unsigned long long* __restrict__ out, int* err) {
+  extern __shared__ int sh_topk[];  // [3 * C] when use_shared
+  if (use_shared) {
+    for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
+    __syncthreads();
+  }
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < rows; r += nwarps) {  // warp-uniform
+    const int64_t t = load_label(target, tdt, r);
+    if (has_ignore && t == ignore) continue;
+    if (t < 0 || t >= C) {
+      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      continue;
+    }
+    unsigned long long* blk = out + (rows_per_sample > 0 ? (r / rows_per_sample) * 3 * (int64_t)C : 0);
+    auto add = [&](int64_t bin) {
+      if (use_shared)
+        atomicAdd(&sh_topk[bin], 1);
+      else
+        atomicAdd(&blk[bin], 1ULL);
+    };
+    // the pair taken by the previous round; (key, class) pairs are ordered by key descending, then class ascending
+    unsigned long long prev = ~0ULL;  // packed = key << 32 | (0xffffffff - class); a NaN in class 0 packs to ~0 itself,
+                                      // so the first round takes every pair instead of comparing with `prev`
+    bool hit = false;
+    for (int round = 0; round < top_k; ++round) {
+      unsigned long long best = 0ULL;
+      for (int c = lane; c < C; c += 32) {
+        const uint32_t key = topk_key(load_elem<DT>(preds, r * C + c));
+        const unsigned long long packed = ((unsigned long long)key << 32) | (0xffffffffu - (uint32_t)c);
+        if ((round == 0 || packed < prev) && packed > best) best = packed;
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(kFull, best, d);
+        best = o > best ? o : best;
+      }
+      prev = best;
+      const int64_t cls = (int64_t)(0xffffffffu - (uint32_t)(best & 0xffffffffu));
+      if (lane == 0) add(C + cls);
+      hit |= cls == t;
+    }
+    if (lane == 0) {
+      add(t);
+      if (hit) add(2 * (int64_t)C + t);
+    }
+  }
+  if (use_shared) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
+      const int v = sh_topk[i];
+      if (v) atomicAdd(&out[i], (unsigned long long)v);
+    }
+  }
+}
+
+template <int DT>
+static int launch_rows_topk_wide(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
+                                 int has_ignore, int64_t ignore, int64_t rows_per_sample, unsigned long long* out,
+                                 int* err, cudaStream_t st) {
+  auto k = k1_rows_topk_wide<DT>;
+  const int64_t want = (int64_t)3 * C * (int)sizeof(int);
+  const int use_shared = rows_per_sample == 0 && want <= (int64_t)dev_info().max_smem_optin - 1024;
+  const int smem = use_shared ? (int)want : 0;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const int64_t work = (rows * 32 + 255) / 256;
+  k<<<resident_grid(k, 256, smem, work), 256, smem, st>>>(preds, target, tdt, rows, C, top_k, has_ignore, ignore,
+                                                         rows_per_sample, use_shared, out, err);
+  return launch_status();
+}
+
 template <int DT>
 static int launch_rows_topk(const void* preds, const void* target, int tdt, int64_t rows, int C, int top_k,
                             int has_ignore, int64_t ignore, unsigned long long* out, int* err, cudaStream_t st) {
@@ -1501,17 +1684,45 @@ extern "C" int tmb_mc_topk_hist(const void* preds, int preds_dtype, const void* 
                                 int64_t ignore_index, int64_t* scratch, int32_t* err, void* stream) {
   if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
   if (n_rows < 0 || num_classes < 2 || top_k < 1 || top_k > num_classes) return TMB_E_SHAPE;
-  if (num_classes > kSoftmaxMaxClasses) return TMB_E_LIMIT;  // the row lives in 32 registers per lane
+  if (num_classes > (1 << 24)) return TMB_E_LIMIT;
   if (!scratch || !err) return TMB_E_NULL;
   if (n_rows == 0) return 0;
   if (!preds || !target) return TMB_E_NULL;
   cudaStream_t st = (cudaStream_t)stream;
   unsigned long long* out = (unsigned long long*)scratch;
   const int C = (int)num_classes, k = (int)top_k;
+  if (num_classes > kSoftmaxMaxClasses) {  // the row no longer fits 32 registers per lane: one walk per round
+    switch (preds_dtype) {
+      case TMB_F32: return launch_rows_topk_wide<TMB_F32>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, 0, out, err, st);
+      case TMB_F16: return launch_rows_topk_wide<TMB_F16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, 0, out, err, st);
+      default: return launch_rows_topk_wide<TMB_BF16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, 0, out, err, st);
+    }
+  }
   switch (preds_dtype) {
     case TMB_F32: return launch_rows_topk<TMB_F32>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
     case TMB_F16: return launch_rows_topk<TMB_F16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
     default: return launch_rows_topk<TMB_BF16>(preds, target, target_dtype, n_rows, C, k, has_ignore, ignore_index, out, err, st);
+  }
+}
+
+extern "C" int tmb_mc_topk_hist_samplewise(const void* preds, int preds_dtype, const void* target, int target_dtype,
+                                           int64_t n_samples, int64_t rows_per_sample, int64_t num_classes,
+                                           int64_t top_k, int has_ignore, int64_t ignore_index, int64_t* scratch,
+                                           int32_t* err, void* stream) {
+  if (float_bytes(preds_dtype) == 0 || label_bytes(target_dtype) == 0) return TMB_E_DTYPE;
+  if (n_samples < 0 || rows_per_sample < 1 || num_classes < 2 || top_k < 1 || top_k > num_classes) return TMB_E_SHAPE;
+  if (num_classes > (1 << 24)) return TMB_E_LIMIT;
+  if (!scratch || !err) return TMB_E_NULL;
+  if (n_samples == 0) return 0;
+  if (!preds || !target) return TMB_E_NULL;
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned long long* out = (unsigned long long*)scratch;
+  const int C = (int)num_classes, k = (int)top_k;
+  const int64_t rows = n_samples * rows_per_sample;
+  switch (preds_dtype) {
+    case TMB_F32: return launch_rows_topk_wide<TMB_F32>(preds, target, target_dtype, rows, C, k, has_ignore, ignore_index, rows_per_sample, out, err, st);
+    case TMB_F16: return launch_rows_topk_wide<TMB_F16>(preds, target, target_dtype, rows, C, k, has_ignore, ignore_index, rows_per_sample, out, err, st);
+    default: return launch_rows_topk_wide<TMB_BF16>(preds, target, target_dtype, rows, C, k, has_ignore, ignore_index, rows_per_sample, out, err, st);
   }
 }
 

@@ -312,6 +312,26 @@ __device__ __forceinline__ void decode_batch(const TbArgs& a, const Batch& s, un
   const uint32_t ign_lo = (uint32_t)a.ignore, ign_hi = (uint32_t)((uint64_t)a.ignore >> 32);
   d.bad = 0;
   d.outside = 0;
+  if (FULL && !IGN) {
+    // The usual batch: every target is 0 or 1.  One OR over the batch's words settles that (instead of a range test,
+    // a select and an error-word update per sample); then every sample counts and its class is the low bit.
+    unsigned any_hi = 0, any_lo = 0;
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+      any_hi |= s.hi[i];
+      any_lo |= s.lo[i];
+    }
+    if ((any_hi | (any_lo >> 1)) == 0u) {
+#pragma unroll
+      for (int i = 0; i < kPer; ++i) {
+        if (!SIG) d.outside |= (unsigned)!(s.x[i] >= 0.0f && s.x[i] <= 1.0f);
+        d.inc[i] = 1u;
+        d.toff[i] = s.lo[i] << 5;
+        d.x[i] = s.x[i];
+      }
+      return;
+    }
+  }
 #pragma unroll
   for (int i = 0; i < kPer; ++i) {
     const unsigned is_live = FULL ? 1u : ((live >> i) & 1u);

@@ -589,9 +589,9 @@ __global__ void k2_pad_thresholds(const float* __restrict__ thr, int T, float* _
 // One warp per (label, target class).  The per-threshold counts are suffix sums of the bin histogram:
 // above(j) = #{samples with q >= thr[j]} = sum_{k > j} hist[k].  Lanes take 32 bins at a time from the
 // top, a shuffle scan forms the running suffix sum, and the counts are ADDED into the state.
-__global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, int L, int T,
-                                                   const int* __restrict__ perm, int layout, long long* out0,
-                                                   long long* out1, long long* out2, long long* out3) {
+__device__ __forceinline__ void k2_finalize_body(unsigned long long* scratch, int L, int T,
+                                                 const int* __restrict__ perm, int layout, long long* out0,
+                                                 long long* out1, long long* out2, long long* out3) {
   const int variant = scratch[0] != 0ULL ? 1 : 0;
   const int kbins = T + 1;
   const unsigned long long* h = scratch + kHdr + (int64_t)variant * L * 2 * kbins;
@@ -639,10 +639,35 @@ __global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, 
   }
 }
 
+__global__ void __launch_bounds__(256) k2_finalize(unsigned long long* scratch, int L, int T,
+                                                   const int* __restrict__ perm, int layout, long long* out0,
+                                                   long long* out1, long long* out2, long long* out3) {
+  k2_finalize_body(scratch, L, T, perm, layout, out0, out1, out2, out3);
+}
+
 __global__ void __launch_bounds__(256) k2_clear(unsigned long long* scratch, int64_t scratch_elems) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < scratch_elems;
        i += (int64_t)gridDim.x * blockDim.x)
     scratch[i] = 0ULL;
+}
+
+// finalize + clear in one launch: the last CTA of k2_finalize to finish (ticket in scratch[1]) zeroes the scratch —
+// flag, ticket and both histograms — for the next update.  One launch less per update (K2 updates are short enough
+// for a launch to show: config 3 sharded over 8 GPUs is ~0.1 ms of binning).
+__global__ void __launch_bounds__(256) k2_finalize_clear(unsigned long long* scratch, int L, int T,
+                                                         const int* __restrict__ perm, int layout, long long* out0,
+                                                         long long* out1, long long* out2, long long* out3,
+                                                         int64_t scratch_elems) {
+  k2_finalize_body(scratch, L, T, perm, layout, out0, out1, out2, out3);
+  __shared__ int last;
+  __syncthreads();  // every warp of this CTA has read what it needs from the scratch
+  if (threadIdx.x == 0) {
+    __threadfence();
+    last = atomicAdd(&scratch[1], 1ULL) == (unsigned long long)(gridDim.x - 1);
+  }
+  __syncthreads();
+  if (!last) return;
+  for (int64_t i = threadIdx.x; i < scratch_elems; i += blockDim.x) scratch[i] = 0ULL;
 }
 
 // ---- utilities ---------------------------------------------------------------------------------------------
@@ -911,11 +936,17 @@ extern "C" int tmb_thresh_bin_finalize(int64_t* scratch, int64_t scratch_elems, 
   if (scratch_elems < scratch_elems_for(num_labels, num_thresholds)) return TMB_E_SCRATCH;
   cudaStream_t st = (cudaStream_t)stream;
   const int64_t threads = num_labels * 2 * 32;
-  k2_finalize<<<(int)((threads + 255) / 256), 256, 0, st>>>((unsigned long long*)scratch, (int)num_labels,
-                                                            (int)num_thresholds, perm, layout, (long long*)out0,
-                                                            (long long*)out1, (long long*)out2, (long long*)out3);
-  if (int rc = launch_status()) return rc;
   const int64_t used = scratch_elems_for(num_labels, num_thresholds);
+  const int grid = (int)((threads + 255) / 256);
+  if (used <= (int64_t)1 << 16) {  // the last CTA clears (a few hundred stores per thread at most)
+    k2_finalize_clear<<<grid, 256, 0, st>>>((unsigned long long*)scratch, (int)num_labels, (int)num_thresholds, perm,
+                                            layout, (long long*)out0, (long long*)out1, (long long*)out2,
+                                            (long long*)out3, used);
+    return launch_status();
+  }
+  k2_finalize<<<grid, 256, 0, st>>>((unsigned long long*)scratch, (int)num_labels, (int)num_thresholds, perm, layout,
+                                    (long long*)out0, (long long*)out1, (long long*)out2, (long long*)out3);
+  if (int rc = launch_status()) return rc;
   k2_clear<<<wave_grid((used + 255) / 256, 4), 256, 0, st>>>((unsigned long long*)scratch, used);
   return launch_status();
 }

@@ -10,8 +10,8 @@ fused kernel per task that adds into the int64 ``tp/fp/tn/fn`` states in place:
 * binary / multilabel: conditional sigmoid + strict ``> threshold`` + four counters per label (:90-131,
   :647-681).
 
-``top_k > 1`` (:363-393) goes through the top-k selection kernel (row f3); ``multidim_average="samplewise"``
-is not built.
+``top_k > 1`` (:363-393) goes through the top-k selection kernels (row f3), ``multidim_average="samplewise"``
+through per-sample histogram blocks, and their combination through the per-sample top-k kernel.
 """
 from typing import Optional, Tuple
 
@@ -38,11 +38,8 @@ def _check_multidim(multidim_average: str) -> None:
 
 
 def _require_global(multidim_average: str, top_k: int = 1) -> None:
-    """Both halves of row f3 are built, but not their combination."""
-    if multidim_average != "global" and top_k != 1:
-        raise NotImplementedError(
-            "`multidim_average='samplewise'` together with `top_k > 1` is not built on the sm_100a update path"
-        )
+    """Kept for the callers' sake: every combination of ``multidim_average`` and ``top_k`` of the reference's one-hot
+    branch (:363-393) is built (``samplewise`` + ``top_k > 1`` through ``tmb_mc_topk_hist_samplewise``)."""
 
 
 def _samplewise_thresh_stats(
@@ -244,7 +241,7 @@ def _multiclass_stat_scores_functional_state(
     if multidim_average == "samplewise":
         # per-sample, per-class counts [N, C]: the reference's one-hot branch (:363-393) with sum_dim = [1]
         err = torch.zeros(1, dtype=torch.int32, device=dev)
-        out = kernels.mc_stats_samplewise(preds, target, num_classes, ignore_index, err)
+        out = kernels.mc_stats_samplewise(preds, target, num_classes, ignore_index, err, top_k)
         if validate_args:
             kernels.raise_on_error_word(err, where)
         return out

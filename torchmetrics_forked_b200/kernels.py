@@ -76,13 +76,45 @@ def mc_argmax_hist(
 
 
 def mc_stats_samplewise(
-    preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int], err: Tensor
+    preds: Tensor, target: Tensor, num_classes: int, ignore_index: Optional[int], err: Tensor, top_k: int = 1
 ) -> Tuple[Tensor, Tensor, Tensor, Tensor]:
-    """Per-sample ``tp/fp/tn/fn`` (int64 ``[N, C]``) of ``preds [N, C, ...]`` float scores (argmax fused) or
-    ``[N, ...]`` integer labels against ``target [N, ...]``: ``multidim_average="samplewise"``."""
+    """Per-sample ``tp/fp/tn/fn`` (int64 ``[N, C]``) of ``preds [N, C, ...]`` float scores (argmax fused, or the
+    ``top_k`` largest scores of every position) or ``[N, ...]`` integer labels against ``target [N, ...]``:
+    ``multidim_average="samplewise"``."""
     nat.require_cuda(preds, "preds")
     nat.require_cuda(target, "target")
     is_label = not preds.is_floating_point()
+    if top_k > 1:
+        if is_label or preds.ndim < 2 or preds.shape[1] != num_classes:
+            raise ValueError("`top_k > 1` needs float `preds` of shape (N, C, ...) with C equal to `num_classes`")
+        # the positions of a sample become consecutive rows [S, C] (torch transposes; the reference's one-hot does too)
+        n = preds.shape[0]
+        rows = _as_kernel_input(preds.reshape(n, num_classes, -1).movedim(1, -1))
+        per_sample = rows.shape[1]
+        tgt = _as_kernel_input(target.reshape(n, -1))
+        if tgt.shape[1] != per_sample:
+            raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+        dev = preds.device
+        outs = tuple(torch.zeros(n, num_classes, dtype=torch.int64, device=dev) for _ in range(4))
+        if n == 0 or per_sample == 0:
+            return outs
+        step = max(1, (1 << 25) // (3 * num_classes))
+        scratch = torch.zeros(min(n, step) * 3 * num_classes, dtype=torch.int64, device=dev)
+        has_ign, ign = _ignore_args(ignore_index)
+        with nat.on_device(dev):
+            for s0 in range(0, n, step):
+                p, t = rows[s0 : s0 + step], tgt[s0 : s0 + step]
+                rc = nat.lib().tmb_mc_topk_hist_samplewise(
+                    nat.ptr(p), nat.float_code(p), nat.ptr(t), nat.label_code(t), p.shape[0], per_sample,
+                    int(num_classes), int(top_k), has_ign, ign, nat.ptr(scratch), nat.ptr(err), nat.stream_ptr(dev),
+                )  # fmt: skip
+                nat.check(rc, "tmb_mc_topk_hist_samplewise")
+                rc = nat.lib().tmb_mc_stats_finalize_samplewise(
+                    nat.ptr(scratch), p.shape[0], int(num_classes), *(nat.ptr(o[s0 : s0 + step]) for o in outs),
+                    nat.stream_ptr(dev),
+                )
+                nat.check(rc, "tmb_mc_stats_finalize_samplewise")
+        return outs
     if is_label:
         if preds.shape != target.shape:
             raise ValueError("label-valued `preds` must have the shape of `target`")
@@ -147,7 +179,7 @@ def mc_shared_stats(
     nat.check(rc, "tmb_mc_shared_stats")
 
 
-TOPK_MAX_CLASSES = 1024  # row width the top-k kernel keeps in registers
+TOPK_MAX_CLASSES = 1024  # row width the top-k kernels keep in registers; wider rows are walked once per round
 
 
 def mc_topk_hist(
@@ -160,8 +192,6 @@ def mc_topk_hist(
     nat.require_cuda(out, "state")
     if preds.ndim < 2 or preds.shape[1] != num_classes or not preds.is_floating_point():
         raise ValueError("`top_k > 1` needs float `preds` of shape (N, C, ...) with C equal to `num_classes`")
-    if num_classes > TOPK_MAX_CLASSES:
-        raise NotImplementedError(f"`top_k > 1` is built for up to {TOPK_MAX_CLASSES} classes, got {num_classes}")
     if preds.ndim > 2:  # extra dimensions become rows (torch transposes; the reference's one-hot does the same)
         preds = preds.movedim(1, -1).reshape(-1, num_classes)
     preds = _as_kernel_input(preds)
