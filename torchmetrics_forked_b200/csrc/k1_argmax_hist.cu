@@ -907,6 +907,8 @@ static int launch_rows(const void* preds, const void* target, int tdt, int64_t n
   constexpr int ES = Elem<DT>::kBytes;
   const int64_t row_bytes = (int64_t)h.C * ES;
   const int hist_smem = h.sh_bins * (int)sizeof(int);
+  // (rows up to 256 bytes; at 272 - 1100 bytes the same kernel measured 0.99 - 4.3 ms against 0.57 - 1.19 ms for the
+  // lanes-per-row kernel below on 2 GB of scores: the staged tile no longer leaves room for enough CTAs per SM)
   if (row_bytes <= 256) {
     // short rows: thread per row through shared memory
     const int vb = vec_bytes(preds, kTileRows * row_bytes, ES);

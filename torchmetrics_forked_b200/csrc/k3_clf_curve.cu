@@ -177,13 +177,15 @@ __global__ void __launch_bounds__(256) k3_outside_flag_vec(const void* __restric
       }
     }
 #pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int e = 0; e < E; ++e) found |= !(v[u][e] >= 0.0f && v[u][e] <= 1.0f);
+    if (__any_sync(kFull, found)) break;  // before the stores: with logits pass A writes nothing at all
+#pragma unroll
     for (int u = 0; u < U; ++u) {
       const int64_t i = b + lane + (int64_t)u * stride;
       if (i < n_vec) VecIO<DT>::store(out, i, v[u]);
-#pragma unroll
-      for (int e = 0; e < E; ++e) found |= !(v[u][e] >= 0.0f && v[u][e] <= 1.0f);
     }
-    if (__any_sync(kFull, found)) break;
     if ((++trip & 15) == 0 && ld_gen(flag) == gen) break;  // another CTA already settled it (polled now and then)
   }
   publish_found(found, flag, gen);
