@@ -366,6 +366,18 @@ int tmb_compact_not_ignored(const void* preds, int preds_elem_bytes, const void*
  * TMB_ERR_PREDS_RANGE.  Replaces torch.bincount inside _bincount (utilities/data.py:169-199). */
 int tmb_bincount(const void* x, int x_dtype, int64_t n, int64_t length, int64_t* out, int32_t* err,
                  void* stream);
+/* ---- K4: state sync helpers ------------------------------------------------------------------------------------
+ * Metric._sync_dist (metric.py:423-453) calls gather_all_tensors (utilities/distributed.py:97-147) once per state:
+ * a barrier and two all-gathers each, then a stack and a sum.  Here every "sum" state of a metric travels in ONE
+ * all-reduce over a packed buffer (the collective itself is the host's: NCCL through torch.distributed).
+ *   tmb_pack_states    copies the k states into `packed` (one launch, any k);
+ *   tmb_unpack_states  copies `packed` back into the k states (hosts without tensor views; the Python side simply
+ *                      views the reduced buffer).
+ * table: device int64 [2k + 1] = byte offsets of the states inside `packed` (k + 1 entries, the last = total_bytes,
+ * all multiples of 4), then the k device addresses of the states. */
+int tmb_pack_states(const int64_t* table, int64_t num_states, int64_t total_bytes, void* packed, void* stream);
+int tmb_unpack_states(const int64_t* table, int64_t num_states, int64_t total_bytes, const void* packed, void* stream);
+
 /* float32 sum of x[0..n) in index order, one rounding per addition -> *out.  Replaces Python's `sum(tk * pk)` over a
  * device tensor in _matthews_corrcoef_reduce (functional/classification/matthews_corrcoef.py:59-61): the covariances
  * subtract numbers of size N^2, so the order of the additions decides bits that the cancellation magnifies. */

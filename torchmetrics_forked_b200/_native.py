@@ -129,6 +129,8 @@ SIGNATURES = {
     ),
     "tmb_bincount": (c_int, [c_void_p, c_int, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "tmb_label_max": (c_int, [c_void_p, c_int, c_int64, c_void_p, c_void_p]),
+    "tmb_pack_states": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
+    "tmb_unpack_states": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "tmb_sum_sequential_f32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
 }
 

@@ -975,6 +975,45 @@ extern "C" int tmb_label_max(const void* x, int x_dtype, int64_t n, int64_t* out
   return launch_status();
 }
 
+// ---- K4 helpers: pack / unpack the sum-states of a metric for ONE all-reduce -----------------------------------------
+// table (device, int64): [0 .. k] byte offset of state i inside the packed buffer (table[k] = total bytes, all
+// multiples of 4) | [k+1 .. 2k] address of state i.  One launch moves every state, whatever their number.
+__global__ void __launch_bounds__(256) k4_pack_states(const long long* __restrict__ table, int k, uint32_t* packed,
+                                                      int unpack) {
+  const long long total_words = table[k] >> 2;
+  for (long long w = (long long)blockIdx.x * blockDim.x + threadIdx.x; w < total_words;
+       w += (long long)gridDim.x * blockDim.x) {
+    int lo = 0, hi = k - 1;  // last state that starts at or before byte 4 w
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if ((table[mid] >> 2) <= w) lo = mid; else hi = mid - 1;
+    }
+    uint32_t* state = reinterpret_cast<uint32_t*>(table[k + 1 + lo]) + (w - (table[lo] >> 2));
+    if (unpack) *state = packed[w]; else packed[w] = *state;
+  }
+}
+
+static int pack_states_impl(const int64_t* table, int64_t num_states, int64_t total_bytes, void* packed, int unpack,
+                            void* stream) {
+  if (num_states < 1 || num_states > (1 << 20) || total_bytes < 0 || (total_bytes & 3)) return TMB_E_SHAPE;
+  if (!table) return TMB_E_NULL;
+  if (total_bytes == 0) return 0;
+  if (!packed) return TMB_E_NULL;
+  const int64_t words = total_bytes >> 2;
+  k4_pack_states<<<wave_grid((words + 255) / 256, 8), 256, 0, (cudaStream_t)stream>>>(
+      (const long long*)table, (int)num_states, (uint32_t*)packed, unpack);
+  return launch_status();
+}
+
+extern "C" int tmb_pack_states(const int64_t* table, int64_t num_states, int64_t total_bytes, void* packed,
+                               void* stream) {
+  return pack_states_impl(table, num_states, total_bytes, packed, 0, stream);
+}
+extern "C" int tmb_unpack_states(const int64_t* table, int64_t num_states, int64_t total_bytes, const void* packed,
+                                 void* stream) {
+  return pack_states_impl(table, num_states, total_bytes, const_cast<void*>(packed), 1, stream);
+}
+
 extern "C" int tmb_sum_sequential_f32(const float* x, int64_t n, float* out, void* stream) {
   if (n < 0) return TMB_E_SHAPE;
   if (!out || (n > 0 && !x)) return TMB_E_NULL;

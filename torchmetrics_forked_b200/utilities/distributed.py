@@ -58,7 +58,7 @@ def packed_all_reduce_sum(tensors: Sequence[Tensor], group: Optional[Any] = None
     for i, t in enumerate(tensors):
         by_dtype.setdefault((t.dtype, t.device), []).append(i)
     for idxs in by_dtype.values():
-        flat = torch.cat([tensors[i].reshape(-1) for i in idxs])
+        flat = _pack([tensors[i] for i in idxs])
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         offset = 0
         for i in idxs:
@@ -66,6 +66,37 @@ def packed_all_reduce_sum(tensors: Sequence[Tensor], group: Optional[Any] = None
             out[i] = flat[offset : offset + n].view(tensors[i].shape)
             offset += n
     return out  # type: ignore[return-value]
+
+
+_PACK_TABLES: Dict[Any, Tensor] = {}
+
+
+def _pack(states: Sequence[Tensor]) -> Tensor:
+    """The states of one dtype as one flat buffer.  CUDA states of 4- or 8-byte elements go through
+    ``tmb_pack_states`` (one launch for any number of states, the address table cached per set of states); a single
+    state is just cloned; CPU tensors (gloo tests) are concatenated by torch."""
+    if len(states) == 1:
+        return states[0].reshape(-1).clone()
+    first = states[0]
+    if not first.is_cuda or first.element_size() not in (4, 8) or not all(s.is_contiguous() for s in states):
+        return torch.cat([s.reshape(-1) for s in states])
+    from torchmetrics_forked_b200 import _native as nat
+
+    key = (tuple(s.data_ptr() for s in states), tuple(s.numel() for s in states), first.dtype, first.device.index)
+    table = _PACK_TABLES.get(key)
+    offsets = [0]
+    for s in states:
+        offsets.append(offsets[-1] + s.numel() * s.element_size())
+    if table is None:
+        if len(_PACK_TABLES) > 256:
+            _PACK_TABLES.clear()
+        table = torch.tensor(offsets + [s.data_ptr() for s in states], dtype=torch.int64, device=first.device)
+        _PACK_TABLES[key] = table
+    flat = torch.empty(offsets[-1] // first.element_size(), dtype=first.dtype, device=first.device)
+    with nat.on_device(first.device):
+        rc = nat.lib().tmb_pack_states(nat.ptr(table), len(states), offsets[-1], nat.ptr(flat), nat.stream_ptr(first.device))
+    nat.check(rc, "tmb_pack_states")
+    return flat
 
 
 _DTYPES = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int64, torch.int32, torch.int16,
