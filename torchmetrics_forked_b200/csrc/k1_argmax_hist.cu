@@ -867,9 +867,21 @@ __global__ void __launch_bounds__(256) k1_rows_sub(const char* __restrict__ pred
   };
   int64_t row0 = warp * rows_per_warp;  // warp-uniform
   if (row0 < n_rows) issue(row0 + sub, cur, t_cur);
+  const int64_t trip_bytes = (int64_t)rows_per_warp * row_bytes;  // a warp's rows of one trip are contiguous
+  const char* const preds_end = preds + n_rows * row_bytes;
   for (; row0 < n_rows; row0 += nwarps * rows_per_warp) {
     const int64_t next = row0 + nwarps * rows_per_warp;
     if (next < n_rows) issue(next + sub, nxt, t_nxt);
+    // The register loads reach one trip ahead — 1 - 2 KB per warp, too little in flight to cover DRAM latency (fp32
+    // C = 100 ran at 0.45 of the roofline with 60 % of the issue slots idle).  The trips after that are pulled into L2
+    // with one prefetch per 128-byte line; the register loads then only wait for L2.
+    // (fp32 rows: -8 %; the packed 16-bit argmax is issue bound and does not gain: not compiled in there)
+#pragma unroll
+    for (int ahead = 2; ahead <= (ES == 4 ? 3 : 1); ++ahead) {
+      const char* first = preds + (row0 + ahead * nwarps * rows_per_warp) * row_bytes;
+      const char* mine = (const char*)((uintptr_t)first & ~(uintptr_t)127) + lane * 128;
+      if (mine < first + trip_bytes && mine < preds_end) prefetch_l2(mine);
+    }
     int p;
     if constexpr (ES == 2 && VB == 16) {
       p = row_argmax_packed16_group<DT, U, LANES>(cur, nvec, j);
