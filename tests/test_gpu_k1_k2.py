@@ -353,6 +353,27 @@ def test_binary_curve_golden(name, F):
         np.testing.assert_allclose(mm.compute().cpu().numpy(), c[key], rtol=1e-5, atol=1e-6)
 
 
+@pytest.mark.parametrize("name", golden_names("switch16_"))
+def test_16bit_scores_follow_the_reference_loop_or_vectorised_compare(name):
+    """bf16 / fp16 scores near the thresholds: the reference's per-threshold loop compares against thresholds rounded
+    to the score dtype, its vectorised form against float32 ones, and it picks by the number of samples LEFT after the
+    `ignore_index` filter (precision_recall_curve.py:203, 473).  Goldens from the unmodified reference on both sides
+    of the switch, with and without ignored samples (oracle/gen_golden_r2.py)."""
+    from torchmetrics_forked_b200.classification import BinaryPrecisionRecallCurve, MulticlassPrecisionRecallCurve
+
+    c = load_golden(name)
+    dt = getattr(torch, str(c["dtype"]))
+    ign = ignore_of(c)
+    preds = torch.from_numpy(c["preds"]).to(dt).cuda()  # exact: the stored float32 values are dtype values
+    target = torch.from_numpy(c["target"]).cuda()
+    if "binary" in name:
+        m = BinaryPrecisionRecallCurve(thresholds=int(c["thresholds"]), ignore_index=ign).cuda()
+    else:
+        m = MulticlassPrecisionRecallCurve(int(c["num_classes"]), thresholds=int(c["thresholds"]), ignore_index=ign).cuda()
+    m.update(preds, target)
+    assert np.array_equal(m.confmat.cpu().numpy(), c["state"]), (name, int(c["kept"]))
+
+
 @pytest.mark.parametrize("name", golden_names("mlcurve_"))
 def test_multilabel_curve_golden(name, F):
     from torchmetrics_forked_b200.classification import MultilabelAUROC, MultilabelPrecisionRecallCurve

@@ -177,10 +177,11 @@ def test_multiclass_curve_fused_kernel_random(C, dtype):
         sm = lambda a: torch.from_numpy(a).to(dtype).cuda().softmax(1).float().cpu().numpy()  # noqa: E731
         # 16-bit scores: above 1e6 comparisons the reference loops over thresholds and `preds >= thresholds[i]`
         # (0-d threshold) is evaluated in the dtype of preds, i.e. against the ROUNDED threshold (:472, :518)
-        # The reference switches on the number of rows it KEPT; this implementation on the unfiltered row count (the
-        # kept count would cost a host sync per update — DESIGN.md, deviation 7).  C = 16 with 4099 rows sits
-        # between the two (3689 * 256 < 10^6 < 4099 * 256), every other case here is on the same side for both.
-        thr_seen = thr.to(dtype).float() if dtype != torch.float32 and n * C * C > 1_000_000 else thr
+        # The reference switches on the number of rows it KEPT after the ignore filter, and so does this
+        # implementation (round 2).  C = 16 with 4099 rows sits between the kept and the unfiltered count
+        # (3689 * 256 < 10^6 < 4099 * 256).
+        kept = int((target != -1).sum())
+        thr_seen = thr.to(dtype).float() if dtype != torch.float32 and kept * C * C > 1_000_000 else thr
         want = O.multiclass_curve_binned(preds.float().numpy(), target.numpy(), C, thr_seen.numpy(), -1, sm)
         assert np.array_equal(m.confmat.cpu().numpy(), want), (C, dtype, len(thr))
     # probabilities: pass A only; out-of-range target is reported

@@ -64,6 +64,26 @@ def _curve_thresholds_for(preds: Tensor, thr_sorted: Tensor, dimensioned_compare
     return thr_sorted.to(preds.dtype).to(torch.float32)
 
 
+def _dimensioned_compare(
+    preds: Tensor, target: Tensor, ignore_index: Optional[int], per_kept: int, switch: int
+) -> bool:
+    """Does the reference take its vectorised variant (two dimensioned tensors -> float32 compare) or its threshold
+    loop (0-d threshold -> compare in the dtype of ``preds``)?  It decides from the number of samples / rows LEFT
+    after the ``ignore_index`` filter (``precision_recall_curve.py:203, 473``; ``per_kept`` comparisons each).  The
+    answer only matters for 16-bit scores.  Without ``ignore_index``, or when even the unfiltered count is below the
+    switch, it is known on the host; otherwise the kept count is read back — the reference synchronises in the same
+    place (its boolean-mask filter, ``:177-179, 445-447``)."""
+    if preds.dtype == torch.float32:
+        return True  # float32 thresholds either way
+    total = target.numel()
+    if total * per_kept <= switch:
+        return True
+    if ignore_index is None:
+        return False
+    kept = int((target != ignore_index).sum())
+    return kept * per_kept <= switch
+
+
 def _binary_clf_curve(
     preds: Tensor,
     target: Tensor,
@@ -142,7 +162,7 @@ def _binary_precision_recall_curve_update_(
 
     Ignored samples take no part in the sigmoid decision (:176-184, H2).
     """
-    thr = _curve_thresholds_for(preds, thr_sorted, dimensioned_compare=preds.numel() <= _LOOP_SWITCH)
+    thr = _curve_thresholds_for(preds, thr_sorted, _dimensioned_compare(preds, target, ignore_index, 1, _LOOP_SWITCH))
     kernels.thresh_bin_update(preds, target, 1, True, thr, False, ignore_index, False, scratch, err)
     kernels.thresh_bin_finalize(scratch, 1, thr.numel(), perm, kernels.TB_CURVE, (confmat,))
 
@@ -391,8 +411,11 @@ def _multiclass_precision_recall_curve_update_(
     """
     rows, tgt = _multiclass_rows(preds, target, num_classes)
     micro = average == "micro"
-    comparisons = rows.numel() if micro else rows.numel() * num_classes
-    thr = _curve_thresholds_for(rows, thr_sorted, comparisons <= (_LOOP_SWITCH if micro else _MC_VECTOR_SWITCH))
+    per_row = num_classes if micro else num_classes * num_classes  # the reference counts preds.numel() (* C)
+    thr = _curve_thresholds_for(
+        rows, thr_sorted,
+        _dimensioned_compare(rows, tgt, ignore_index, per_row, _LOOP_SWITCH if micro else _MC_VECTOR_SWITCH),
+    )
     labels = 1 if micro else num_classes
     if num_classes <= kernels.MC_CURVE_MAX_CLASSES:
         kernels.mc_curve_update(rows, tgt, thr, ignore_index, micro, scratch, err)
