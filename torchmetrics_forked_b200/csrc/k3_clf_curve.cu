@@ -19,6 +19,8 @@
 //           reference's float32 cumsum yields while counts stay below 2^24 (H6).
 // HBM traffic per label-sample: pack 4+8 read / 4 write, each sort pass 4+4 read / 4 write (+ counters),
 // curve 4+4 read / up to 12 write.
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace tmb {
@@ -470,6 +472,82 @@ __global__ void __launch_bounds__(1024) k3_scan_u32(uint32_t* __restrict__ data,
   if (totals != nullptr && threadIdx.x == 0) totals[blockIdx.x] = (long long)carry;
 }
 
+// One-sweep front end: the digit histograms of ALL four passes of every label from one read of the keys:
+// ghist[(seg * 4 + pass) * 256 + digit].  Per-warp private counters (no inter-warp contention); a round whose 32 keys
+// share the digit — the exponent byte mostly does, quantised scores do in the low bytes — is one add of 32 instead of
+// a 32-way serialised atomic (two REDUX over the keys tell which of the four bytes are uniform).
+constexpr int kHistAllTiles = 4;  // tiles per CTA
+constexpr int kHistAllSmem = 4 * kSortWarps * 256 * 4;
+
+__global__ void __launch_bounds__(kSortThreads) k3_digit_hist_all(const uint32_t* __restrict__ keys, int64_t N,
+                                                                  uint32_t* __restrict__ ghist, int nb) {
+  extern __shared__ uint32_t hh[];  // [4][kSortWarps][256]
+  const int seg = blockIdx.y;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 4 * kSortWarps * 256; i += kSortThreads) hh[i] = 0;
+  __syncthreads();
+  const uint32_t* k = keys + (int64_t)seg * N;
+  for (int tt = 0; tt < kHistAllTiles; ++tt) {
+    const int blk = blockIdx.x * kHistAllTiles + tt;
+    if (blk >= nb) break;
+    const int64_t start = (int64_t)blk * kSortTile + w * kWarpSpan;
+    const int span = (int)min((int64_t)kWarpSpan, N - start);
+    uint32_t key[kSortItems];
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) key[r] = (r * 32 + lane < span) ? ldg_stream4(k + start + r * 32 + lane) : 0u;
+#pragma unroll
+    for (int r = 0; r < kSortItems; ++r) {
+      const bool valid = r * 32 + lane < span;
+      const bool full = (r + 1) * 32 <= span;  // warp-uniform
+      // bytes in which the 32 keys of the round agree: AND and OR over the warp differ in no bit of that byte
+      const uint32_t differ = full ? (__reduce_and_sync(kFull, key[r]) ^ __reduce_or_sync(kFull, key[r])) : ~0u;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const uint32_t d = (key[r] >> (8 * p)) & 255u;
+        uint32_t* row = hh + (p * kSortWarps + w) * 256;
+        if (((differ >> (8 * p)) & 255u) == 0u) {
+          if (lane == 0) atomicAdd(&row[d], 32u);
+        } else if (valid) {
+          atomicAdd(&row[d], 1u);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < 4 * 256; i += kSortThreads) {
+    const int p = i >> 8, d = i & 255;
+    uint32_t sum = 0;
+#pragma unroll
+    for (int ww = 0; ww < kSortWarps; ++ww) sum += hh[(p * kSortWarps + ww) * 256 + d];
+    if (sum) atomicAdd(&ghist[((int64_t)seg * 4 + p) * 256 + d], sum);
+  }
+}
+
+// in place: ghist[(seg, pass)][0 .. 255] -> exclusive prefix over the digits; one warp per (label, pass)
+__global__ void __launch_bounds__(256) k3_digit_base(uint32_t* __restrict__ ghist, int n_rows) {
+  const int row = (int)(((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
+  if (row >= n_rows) return;
+  uint32_t* g = ghist + (int64_t)row * 256 + lane * 8;
+  uint32_t v[8], sum = 0;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    v[e] = g[e];
+    sum += v[e];
+  }
+  uint32_t incl = sum;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t o = __shfl_up_sync(kFull, incl, d);
+    if (lane >= d) incl += o;
+  }
+  uint32_t run = incl - sum;
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    g[e] = run;
+    run += v[e];
+  }
+}
+
 // peers & (lanes whose `bit` of v equals mine): one step of an 8-ballot match over the digit
 __device__ __forceinline__ unsigned match_bit(unsigned peers, uint32_t v, uint32_t bit) {
   asm volatile(
@@ -503,19 +581,65 @@ __device__ __forceinline__ uint32_t get_rank(const uint32_t* rank2, int r) {
 // sector transaction per 4-byte key).
 constexpr int kScatterSmem = (kSortWarps * 256 + 256 + kSortTile) * 4;  // 50 176 B, needs the opt-in
 
+// One-sweep variant (LB = true): the per-label digit histograms of all four passes are taken up front
+// (k3_digit_hist_all) and a tile learns how many keys of each digit the EARLIER tiles of its label hold by decoupled
+// look-back instead of from a per-pass histogram + scan: tiles take their index from a ticket counter (so every tile
+// with a lower index is already running or done: the wait below cannot deadlock), publish their 256 digit counts as
+// "aggregate" words, walk back over their predecessors adding aggregates until they meet an "inclusive prefix", and
+// publish their own prefix.  A status word carries its data (3-bit pass tag | prefix bit | 28-bit count), so plain
+// device-scope relaxed loads and stores are all the protocol needs, and the tag makes one zeroing serve four passes.
+constexpr uint32_t kLbPrefixBit = 1u << 28;
+constexpr uint32_t kLbValueMask = kLbPrefixBit - 1u;
+__device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+struct LookBack {          // only read when LB
+  uint32_t* status;        // [L][nb][256], zero before pass 0
+  const uint32_t* gbase;   // [L][4][256] exclusive digit offsets of every label and pass
+  unsigned int* ticket;    // one counter per pass
+  int pass, L;
+  int group;               // labels whose tiles are interleaved in ticket order
+};
+
+template <bool LB>
 __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_t* __restrict__ in,
                                                                 uint32_t* __restrict__ out, int64_t N, int shift,
-                                                                const uint32_t* __restrict__ scanned, int nb) {
+                                                                const uint32_t* __restrict__ scanned, int nb,
+                                                                LookBack lb) {
   extern __shared__ uint32_t sm[];
   uint32_t(*wh)[256] = reinterpret_cast<uint32_t(*)[256]>(sm);  // [kSortWarps][256]: counts, then warp prefixes
   uint32_t* gdelta = sm + kSortWarps * 256;                      // [256] global position minus local position
   uint32_t* sorted = gdelta + 256;                               // [kSortTile] the tile in digit order
-  const int seg = blockIdx.y, blk = blockIdx.x;
+  __shared__ unsigned int sh_ticket;
+  if (LB && threadIdx.x == 0) sh_ticket = atomicAdd(lb.ticket, 1u);
   const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) sm[i] = 0;
-  // global position of this tile's first key of digit threadIdx.x; fetched now, needed after the ranking
-  const uint32_t digit_base = threadIdx.x < 256 ? scanned[((int64_t)seg * 256 + threadIdx.x) * nb + blk] : 0u;
   __syncthreads();
+  // LB: consecutive tickets go round the labels, so the CTAs that start together work on ~grid / L tiles of each
+  // label and the first look-backs are that short
+  int seg = blockIdx.y, blk = blockIdx.x;
+  if (LB) {  // tickets go round the labels of one group of lb.group labels, group after group
+    const unsigned per_group = (unsigned)lb.group * (unsigned)nb;
+    unsigned g = sh_ticket / per_group;
+    const unsigned n_groups = ((unsigned)lb.L + lb.group - 1) / lb.group;
+    if (g >= n_groups) g = n_groups - 1;
+    const unsigned idx = sh_ticket - g * per_group;
+    const unsigned in_group = min((unsigned)lb.group, (unsigned)lb.L - g * lb.group);
+    seg = (int)(g * lb.group + idx % in_group);
+    blk = (int)(idx / in_group);
+  }
+  // global position of this tile's first key of digit threadIdx.x (LB: of the label's first key of that digit; the
+  // look-back adds the earlier tiles); fetched now, needed after the ranking
+  uint32_t digit_base = 0u;
+  if (threadIdx.x < 256)
+    digit_base = LB ? lb.gbase[((int64_t)seg * 4 + lb.pass) * 256 + threadIdx.x]
+                    : scanned[((int64_t)seg * 256 + threadIdx.x) * nb + blk];
   const uint32_t* k = in + (int64_t)seg * N;
   const int64_t tile0 = (int64_t)blk * kSortTile;
   const int64_t start = tile0 + w * kWarpSpan;
@@ -565,6 +689,15 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
 #pragma unroll
     for (int ww = 0; ww < kSortWarps; ++ww) total += wh[ww][threadIdx.x];
   }
+  uint32_t lb_mine = 0;
+  if (LB && threadIdx.x < 256) {
+    // publish what this tile really holds right away (the padding keys of a ragged last tile were ranked as digit
+    // 255); the walk over the predecessors comes later, behind the shared-memory scatter, when they have had time
+    // to publish too
+    lb_mine = total - (threadIdx.x == 255 ? (uint32_t)(kSortTile - tile_n) : 0u);
+    st_relaxed_u32(lb.status + (((int64_t)seg * nb + blk) * 256 + threadIdx.x),
+                   ((uint32_t)(lb.pass + 1) << 29) | (blk == 0 ? kLbPrefixBit : 0u) | lb_mine);
+  }
   {
     uint32_t incl = total;  // threads >= 256 carry 0 and only take part in the shuffles
 #pragma unroll
@@ -580,7 +713,7 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
 #pragma unroll
       for (int ww = 0; ww < 8; ++ww) before += (ww < w) ? warp_tot[ww] : 0u;
       const uint32_t first = before + incl - total;  // local position of the first key with this digit
-      gdelta[threadIdx.x] = digit_base - first;
+      gdelta[threadIdx.x] = digit_base - first;    // LB: the earlier tiles' keys are added below
       uint32_t run = first;
 #pragma unroll
       for (int ww = 0; ww < kSortWarps; ++ww) {
@@ -593,6 +726,32 @@ __global__ void __launch_bounds__(kSortThreads, 2) k3_sort_scatter(const uint32_
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < kSortItems; ++r) sorted[wh[w][(key[r] >> shift) & 255u] + get_rank(rank2, r)] = key[r];
+  if (LB && threadIdx.x < 256) {
+    const int d = threadIdx.x;
+    uint32_t* st = lb.status + ((int64_t)seg * nb) * 256 + d;
+    const uint32_t tag = (uint32_t)(lb.pass + 1) << 29;
+    uint32_t excl = 0;
+    int b = blk - 1;
+    bool done = b < 0;
+    while (!done) {
+      // four predecessors per round trip (the loads are independent); they are consumed nearest first and the walk
+      // stops at the first inclusive prefix, or retries from the first word that is not published yet (its tile is
+      // running: ticket order)
+      uint32_t v[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) v[q] = b - q >= 0 ? ld_relaxed_u32(st + (int64_t)(b - q) * 256) : 0u;
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        if (done) break;
+        if ((v[q] >> 29) != (uint32_t)(lb.pass + 1)) break;
+        excl += v[q] & kLbValueMask;
+        --b;
+        done = (v[q] & kLbPrefixBit) != 0u || b < 0;
+      }
+    }
+    if (blk > 0) st_relaxed_u32(st + (int64_t)blk * 256, tag | kLbPrefixBit | (excl + lb_mine));
+    gdelta[d] += excl;
+  }
   __syncthreads();
   uint32_t* o = out + (int64_t)seg * N;
   for (int i = threadIdx.x; i < tile_n; i += kSortThreads) {
@@ -1042,7 +1201,7 @@ static int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 struct CurvePlan {
   int64_t N, L;
   int nb, ntile;
-  int64_t off_keys_a, off_keys_b, off_counts, off_pos, off_bnd, off_last, off_nvalid, total;
+  int64_t off_keys_a, off_keys_b, off_counts, off_pos, off_bnd, off_last, off_nvalid, off_ghist, off_ticket, total;
 };
 
 static CurvePlan curve_plan(int64_t N, int64_t L) {
@@ -1059,6 +1218,8 @@ static CurvePlan curve_plan(int64_t N, int64_t L) {
   p.off_bnd = off; off = align_up(off + L * (int64_t)p.ntile * 4, 256);
   p.off_last = off; off = align_up(off + L * (int64_t)p.ntile * 4, 256);
   p.off_nvalid = off; off = align_up(off + L * 8, 256);
+  p.off_ghist = off; off = align_up(off + L * 4 * 256 * 4, 256);
+  p.off_ticket = off; off = align_up(off + 4 * 4, 256);
   p.total = off;
   return p;
 }
@@ -1134,7 +1295,8 @@ extern "C" int64_t tmb_clf_curve_scratch_bytes(int64_t n, int64_t num_labels) {
 namespace tmb {
 
 struct CurveBufs {
-  uint32_t *keys_a, *keys_b, *cnt, *pos_part, *bnd_part, *tile_last;
+  uint32_t *keys_a, *keys_b, *cnt, *pos_part, *bnd_part, *tile_last, *ghist;
+  unsigned int* ticket;
   unsigned long long* n_valid;
 };
 
@@ -1148,6 +1310,8 @@ static CurveBufs curve_bufs(const CurvePlan& p, void* scratch) {
   b.bnd_part = (uint32_t*)(base + p.off_bnd);
   b.tile_last = (uint32_t*)(base + p.off_last);
   b.n_valid = (unsigned long long*)(base + p.off_nvalid);
+  b.ghist = (uint32_t*)(base + p.off_ghist);
+  b.ticket = (unsigned int*)(base + p.off_ticket);
   return b;
 }
 
@@ -1174,19 +1338,54 @@ static int pack_keys(const PackSrc& src, int preds_dtype, int target_dtype, int6
   }
 }
 
-// 4 LSD passes over [L, n] label-major keys; the sorted keys end up back in keys_a
-static int sort_keys(uint32_t* keys_a, uint32_t* keys_b, uint32_t* cnt, int64_t n, int L, int nb, cudaStream_t st) {
-  uint32_t* src_keys = keys_a;
-  uint32_t* dst_keys = keys_b;
-  cudaFuncSetAttribute(k3_sort_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
+// 4 LSD passes over [L, n] label-major keys; the sorted keys end up back in keys_a.
+// One sweep (default, n < 2^28): one histogram kernel for all passes, then per pass ONE scatter launch whose tiles find
+// their offsets by look-back.  Classic (TMB_K3_SORT=classic, or n >= 2^28): per pass tile histogram + scan + scatter.
+static bool use_one_sweep(int64_t n) {
+  static const bool classic = [] {
+    const char* e = getenv("TMB_K3_SORT");
+    return e != nullptr && e[0] == 'c';
+  }();
+  return !classic && n < ((int64_t)1 << 28);
+}
+
+static int sort_keys(const CurveBufs& b, int64_t n, int L, int nb, cudaStream_t st) {
+  uint32_t* src_keys = b.keys_a;
+  uint32_t* dst_keys = b.keys_b;
+  if (use_one_sweep(n)) {
+    auto k = k3_sort_scatter<true>;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
+    cudaFuncSetAttribute(k3_digit_hist_all, cudaFuncAttributeMaxDynamicSharedMemorySize, kHistAllSmem);
+    cudaMemsetAsync(b.cnt, 0, (size_t)L * 256 * nb * 4, st);  // the tile status words (pass tag 0 = nothing published)
+    cudaMemsetAsync(b.ghist, 0, (size_t)L * 4 * 256 * 4, st);
+    cudaMemsetAsync(b.ticket, 0, 4 * 4, st);
+    dim3 hgrid((unsigned)((nb + kHistAllTiles - 1) / kHistAllTiles), (unsigned)L);
+    k3_digit_hist_all<<<hgrid, kSortThreads, kHistAllSmem, st>>>(src_keys, n, b.ghist, nb);
+    if (int rc = launch_status()) return rc;
+    k3_digit_base<<<(L * 4 * 32 + 255) / 256, 256, 0, st>>>(b.ghist, L * 4);
+    if (int rc = launch_status()) return rc;
+    for (int pass = 0; pass < 4; ++pass) {
+      // all labels in one group (group sizes 8 .. 100 measured the same at L = 100; label-major order — one chain of
+      // ~300 co-resident tiles — was 25 % slower)
+      const LookBack lb{b.cnt, b.ghist, b.ticket + pass, pass, L, L};
+      k<<<(unsigned)((int64_t)nb * L), kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, 8 * pass, nullptr, nb, lb);
+      if (int rc = launch_status()) return rc;
+      uint32_t* tmp = src_keys;
+      src_keys = dst_keys;
+      dst_keys = tmp;
+    }
+    return 0;
+  }
+  auto k = k3_sort_scatter<false>;
+  cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, kScatterSmem);
   for (int pass = 0; pass < 4; ++pass) {
     const int shift = 8 * pass;
     dim3 grid((unsigned)nb, (unsigned)L);
-    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src_keys, n, shift, cnt, nb);
+    k3_sort_hist<<<grid, kSortThreads, 0, st>>>(src_keys, n, shift, b.cnt, nb);
     if (int rc = launch_status()) return rc;
-    k3_scan_u32<<<L, 1024, 0, st>>>(cnt, (int64_t)256 * nb, nullptr);
+    k3_scan_u32<<<L, 1024, 0, st>>>(b.cnt, (int64_t)256 * nb, nullptr);
     if (int rc = launch_status()) return rc;
-    k3_sort_scatter<<<grid, kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, shift, cnt, nb);
+    k<<<grid, kSortThreads, kScatterSmem, st>>>(src_keys, dst_keys, n, shift, b.cnt, nb, LookBack{});
     if (int rc = launch_status()) return rc;
     uint32_t* tmp = src_keys;
     src_keys = dst_keys;
@@ -1202,7 +1401,7 @@ static int pack_and_sort(const PackSrc& src, int preds_dtype, int target_dtype, 
   cudaMemsetAsync(b.n_valid, 0, (size_t)L * 8, st);
   const PackDst dst{b.keys_a, b.n_valid, nullptr, nullptr, L, n, 0};
   if (int rc = pack_keys(src, preds_dtype, target_dtype, n, L, has_ignore, ignore, pos_label, dst, err, st)) return rc;
-  return sort_keys(b.keys_a, b.keys_b, b.cnt, n, L, p.nb, st);
+  return sort_keys(b, n, L, p.nb, st);
 }
 
 static int curve_tile_sums(int64_t n, int L, const CurvePlan& p, const CurveBufs& b, long long* counts,
@@ -1367,7 +1566,7 @@ extern "C" int tmb_clf_sorted_scores(uint32_t* keys, uint64_t* n_valid, int64_t 
     k3_fill_u64<<<(L + 255) / 256, 256, 0, st>>>(b.n_valid, (unsigned long long)n, L);
     if (int rc = launch_status()) return rc;
   }
-  if (int rc = sort_keys(b.keys_a, b.keys_b, b.cnt, n, L, p.nb, st)) return rc;
+  if (int rc = sort_keys(b, n, L, p.nb, st)) return rc;
   return scores_from_sorted(n, L, p, b, want_ap, scores, st);
 }
 
