@@ -501,14 +501,22 @@ __global__ void __launch_bounds__(kSortThreads) k3_digit_hist_all(const uint32_t
       const bool full = (r + 1) * 32 <= span;  // warp-uniform
       // bytes in which the 32 keys of the round agree: AND and OR over the warp differ in no bit of that byte
       const uint32_t differ = full ? (__reduce_and_sync(kFull, key[r]) ^ __reduce_or_sync(kFull, key[r])) : ~0u;
+      uint32_t* rows = hh + w * 256;
+      if (full && ((differ - 0x01010101u) & ~differ & 0x80808080u) == 0u) {
+        // the usual round: a full warp and no byte uniform — four plain atomics, no per-byte tests (the tests were
+        // three quarters of this kernel's 75 instructions per round)
 #pragma unroll
-      for (int p = 0; p < 4; ++p) {
-        const uint32_t d = (key[r] >> (8 * p)) & 255u;
-        uint32_t* row = hh + (p * kSortWarps + w) * 256;
-        if (((differ >> (8 * p)) & 255u) == 0u) {
-          if (lane == 0) atomicAdd(&row[d], 32u);
-        } else if (valid) {
-          atomicAdd(&row[d], 1u);
+        for (int p = 0; p < 4; ++p) atomicAdd(&rows[p * kSortWarps * 256 + ((key[r] >> (8 * p)) & 255u)], 1u);
+      } else {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+          const uint32_t d = (key[r] >> (8 * p)) & 255u;
+          uint32_t* row = rows + p * kSortWarps * 256;
+          if (((differ >> (8 * p)) & 255u) == 0u) {
+            if (lane == 0) atomicAdd(&row[d], 32u);
+          } else if (valid) {
+            atomicAdd(&row[d], 1u);
+          }
         }
       }
     }
