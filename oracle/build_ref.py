@@ -11,7 +11,9 @@ packs
 
 into ONE archive that Python imports from directly (zipimport: the archive goes on `sys.path`), and writes
 `oracle/_ref/MANIFEST.json` with a sha256 over the packed reference files, so that a reader can check that nothing
-was edited on the way.  `oracle/_ref/` is git-ignored (no reference source enters the history) but not
+was edited on the way.  A second archive, `oracle/_ref/reference_tests.zip`, holds the reference's own unit tests of
+this path (`tests/unittests/{helpers,classification,bases}`), which `oracle/acceptance.py` runs against the drop-in
+package on the GPU box.  `oracle/_ref/` is git-ignored (no reference source enters the history) but not
 gpurun-ignored: like the built `.so` it ships with the working tree.  `/root/reference` does not exist on the GPU
 box; there `bench.py --impl reference`, the `cpu_baseline` leg and the reference-on-CUDA column import the staged
 copy through `oracle/ref_loader.py`.  Run by `__graft_entry__.build()` whenever `/root/reference` is present.
@@ -28,6 +30,9 @@ SRC = Path("/root/reference/src/torchmetrics")
 SHIM = HERE / "shim" / "lightning_utilities"
 DEST = HERE / "_ref"
 ARCHIVE = DEST / "reference.zip"
+TESTS_SRC = Path("/root/reference/tests/unittests")
+TESTS_ARCHIVE = DEST / "reference_tests.zip"  # the reference's own unit tests of the hot path (oracle/acceptance.py)
+TEST_DIRS = ("", "helpers", "classification", "bases")
 
 
 def tree_digest(root: Path) -> str:
@@ -43,7 +48,7 @@ def build(force: bool = False) -> Path:
         raise RuntimeError(f"{SRC} is not present: oracle/_ref can only be staged where the reference is mounted")
     want = tree_digest(SRC)
     manifest = DEST / "MANIFEST.json"
-    if not force and manifest.exists() and ARCHIVE.exists():
+    if not force and manifest.exists() and ARCHIVE.exists() and TESTS_ARCHIVE.exists():
         try:
             if json.loads(manifest.read_text()).get("sha256_reference_py") == want:
                 return ARCHIVE
@@ -64,8 +69,15 @@ def build(force: bool = False) -> Path:
         for p in sorted(SHIM.rglob("*.py")):
             z.write(p, Path("lightning_utilities") / p.relative_to(SHIM))
     assert h.hexdigest() == want, "packed copy differs from the reference"
+    n_tests = 0
+    with zipfile.ZipFile(TESTS_ARCHIVE, "w", zipfile.ZIP_DEFLATED) as z:
+        for d in TEST_DIRS:
+            for p in sorted((TESTS_SRC / d).glob("*.py")):
+                z.write(p, Path("unittests") / p.relative_to(TESTS_SRC))
+                n_tests += 1
     manifest.write_text(json.dumps({
         "source": str(SRC), "sha256_reference_py": want, "files": files, "archive": ARCHIVE.name,
+        "tests_archive": TESTS_ARCHIVE.name, "test_files": n_tests,
         "shim": "oracle/shim/lightning_utilities (stand-in for lightning-utilities >=0.8.0,<0.10.0)",
     }, indent=1))
     return ARCHIVE

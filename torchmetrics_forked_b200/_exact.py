@@ -5,10 +5,19 @@ from typing import List, Optional, Sequence, Tuple, Union
 import torch
 from torch import Tensor
 
+from torchmetrics_forked_b200 import _f64
 from torchmetrics_forked_b200 import _native as nat
 
 
 def _as_kernel_input(t: Tensor) -> Tensor:
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _as_label_input(t: Tensor) -> Tensor:
+    """Integer, dense targets (float-typed targets holding integer values are truncated like the reference's
+    ``.long()``)."""
+    if t.is_floating_point():
+        t = t.long()
     return t if t.is_contiguous() else t.contiguous()
 
 
@@ -19,6 +28,8 @@ def sigmoid_normalize(preds: Tensor, target: Optional[Tensor], ignore_index: Opt
     exclude ignored positions from the test (pass ``None`` to test every element).
     """
     nat.require_cuda(preds, "preds")
+    if _f64.is_f64(preds):
+        return _f64.sigmoid_where_needed(preds, target, ignore_index)
     preds = _as_kernel_input(preds)
     out = torch.empty_like(preds)
     if preds.numel() == 0:
@@ -28,7 +39,7 @@ def sigmoid_normalize(preds: Tensor, target: Optional[Tensor], ignore_index: Opt
     has_ign = int(target is not None and ignore_index is not None)
     if has_ign:
         nat.require_cuda(target, "target")
-        target = _as_kernel_input(target)
+        target = _as_label_input(target)
     with nat.on_device(dev):
         rc = nat.lib().tmb_sigmoid_normalize(
             nat.ptr(preds), nat.float_code(preds), preds.numel(),
@@ -55,6 +66,8 @@ def softmax_normalize(
     nat.require_cuda(preds, "preds")
     if preds.ndim != 2:
         raise ValueError("`preds` must have shape (M, C)")
+    if _f64.is_f64(preds):
+        return _f64.softmax_where_needed(preds, target, ignore_index)
     preds = _as_kernel_input(preds)
     rows, num_classes = preds.shape
     if preds.numel() == 0:
@@ -64,7 +77,7 @@ def softmax_normalize(
     has_ign = int(target is not None and ignore_index is not None)
     if has_ign:
         nat.require_cuda(target, "target")
-        target = _as_kernel_input(target.reshape(-1))
+        target = _as_label_input(target.reshape(-1))
         if target.numel() != rows:
             raise ValueError("`target` must hold one class index per row of `preds`")
     t_ptr, t_code, ign = (nat.ptr(target), nat.label_code(target), int(ignore_index)) if has_ign else (0, 0, 0)
@@ -95,7 +108,7 @@ def compact_not_ignored(preds: Tensor, target: Tensor, ignore_index: int) -> Tup
     nat.require_cuda(preds, "preds")
     nat.require_cuda(target, "target")
     preds = _as_kernel_input(preds.reshape(-1))
-    target = _as_kernel_input(target.reshape(-1))
+    target = _as_label_input(target.reshape(-1))
     n = preds.numel()
     if target.numel() != n:
         raise ValueError("`preds` and `target` must have the same number of elements")
@@ -154,7 +167,7 @@ def _chunk_lists(preds: Chunks, target: Chunks, class_targets: bool = False) -> 
             raise ValueError("all chunks must agree in the number of labels and in dtype")
         if p.device != ps[0].device or t.device != ps[0].device:
             raise ValueError("all chunks must live on one device")
-    return [_as_kernel_input(p) for p in ps], [_as_kernel_input(t) for t in ts]
+    return [_as_kernel_input(p) for p in ps], [_as_label_input(t) for t in ts]
 
 
 def _chunk_table(ps: List[Tensor], ts: List[Tensor]) -> Tuple[Tensor, int]:
@@ -178,6 +191,10 @@ def _run_curves(
     prefix of each row) and the int32 error word.
     """
     ps, ts = _chunk_lists(preds, target, class_targets)
+    values = None
+    if _f64.is_f64(ps[0]):  # float64 scores go through the sort as their dense ranks (see _f64)
+        ranked, values = _f64.rank_scores(ps)
+        ps = [_as_kernel_input(c) for c in _f64.split_like(ranked, ps)]
     num_labels = ps[0].shape[1]
     n = sum(p.shape[0] for p in ps)
     dev = ps[0].device
@@ -207,7 +224,7 @@ def _run_curves(
                     int(class_targets), *tail
                 )
                 nat.check(rc, "tmb_clf_curves_chunked")
-    return fps, tps, thr, counts, err, ps[0].dtype
+    return fps, tps, thr, counts, err, (ps[0].dtype if values is None else values)
 
 
 def clf_curves(
@@ -228,8 +245,11 @@ def clf_curves(
     num_labels = fps.shape[0]
     f_list = [fps[l, : lengths[l]] for l in range(num_labels)]
     t_list = [tps[l, : lengths[l]] for l in range(num_labels)]
-    h_list = [thr[l, : lengths[l]] if out_dtype == torch.float32 else thr[l, : lengths[l]].to(out_dtype)
-              for l in range(num_labels)]
+    if isinstance(out_dtype, Tensor):  # float64 scores: `thr` holds rank patterns, `out_dtype` the distinct values
+        h_list = [_f64.scores_of_ranks(thr[l, : lengths[l]], out_dtype) for l in range(num_labels)]
+    else:
+        h_list = [thr[l, : lengths[l]] if out_dtype == torch.float32 else thr[l, : lengths[l]].to(out_dtype)
+                  for l in range(num_labels)]
     return f_list, t_list, h_list
 
 
@@ -259,6 +279,8 @@ def clf_curve_scores(
             ps, ts = [], []
         return _sharded.sharded_curve_scores(ps, ts, info, ignore_index, pos_label, want_ap, class_targets)
     ps, ts = _chunk_lists(preds, target, class_targets)
+    if _f64.is_f64(ps[0]):
+        ps = [_as_kernel_input(c) for c in _f64.split_like(_f64.rank_scores(ps)[0], ps)]
     num_labels = ps[0].shape[1]
     dev = ps[0].device
     table, n = _chunk_table(ps, ts)

@@ -38,6 +38,9 @@ from torchmetrics_forked_b200.utilities.data import dim_zero_cat
 from torchmetrics_forked_b200.utilities.enums import ClassificationTask
 
 
+_F64_SCORES = 1 << 40  # travels with the error bits of the label-sharded sync, never stored in them
+
+
 class _CurveStateMixin:
     """Shared state set-up: binned (``confmat``) vs exact (``preds`` / ``target`` lists)."""
 
@@ -98,7 +101,13 @@ class _CurveStateMixin:
         group = process_group or self.process_group
         n_local = sum(int(p.shape[0]) for p in self.preds) if isinstance(self.preds, list) else int(self.preds.shape[0])
         word = int(self._err_word.item()) if self._err_word is not None else 0
+        chunks = self.preds if isinstance(self.preds, list) else [self.preds]
+        if any(c.dtype == torch.float64 for c in chunks):
+            word |= _F64_SCORES  # what a rank stores is data, not configuration: the ranks tell each other
         rows, err_or = _sharded.exchange_rows_and_errors(n_local, word, self.device, group)
+        if err_or & _F64_SCORES:
+            # float64 scores are ranked among ALL rows before the sort (see _f64): gathered like any other state
+            return super()._sync_dist(dist_sync_fn, process_group)
         self.__dict__["_err_merged"] = torch.tensor(err_or)
         labels = getattr(self, "num_labels", None) or getattr(self, "num_classes", None) or 1
         self.__dict__["_shard_info"] = _sharded.ShardInfo(group, rows, int(labels), self.device)

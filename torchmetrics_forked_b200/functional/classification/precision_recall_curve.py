@@ -59,7 +59,7 @@ def _curve_thresholds_for(preds: Tensor, thr_sorted: Tensor, dimensioned_compare
     half / bfloat16 scores the loop variant (:244) rounds each threshold first; the vectorised variants
     compare two dimensioned tensors and promote to float32.
     """
-    if preds.dtype == torch.float32 or dimensioned_compare:
+    if preds.dtype in (torch.float32, torch.float64) or dimensioned_compare:
         return thr_sorted
     return thr_sorted.to(preds.dtype).to(torch.float32)
 
@@ -73,7 +73,7 @@ def _dimensioned_compare(
     answer only matters for 16-bit scores.  Without ``ignore_index``, or when even the unfiltered count is below the
     switch, it is known on the host; otherwise the kept count is read back — the reference synchronises in the same
     place (its boolean-mask filter, ``:177-179, 445-447``)."""
-    if preds.dtype == torch.float32:
+    if preds.dtype in (torch.float32, torch.float64):
         return True  # float32 thresholds either way
     total = target.numel()
     if total * per_kept <= switch:

@@ -4,6 +4,13 @@ from torchmetrics_forked_b200.functional.classification._fixed_point import (  #
     fixed_point_family,
 )
 
+
+
+def _convert_fpr_to_specificity(fpr):
+    """``1 - fpr`` (reference :42-44; its own tests import the helper)."""
+    return 1 - fpr
+
+
 (binary_specificity_at_sensitivity, multiclass_specificity_at_sensitivity, multilabel_specificity_at_sensitivity,
  specificity_at_sensitivity) = fixed_point_family("specificity_at_sensitivity", "min_sensitivity", None)
 for _f in (binary_specificity_at_sensitivity, multiclass_specificity_at_sensitivity, multilabel_specificity_at_sensitivity, specificity_at_sensitivity):

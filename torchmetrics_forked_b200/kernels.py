@@ -9,6 +9,7 @@ from typing import Optional, Tuple
 import torch
 from torch import Tensor
 
+from torchmetrics_forked_b200 import _f64
 from torchmetrics_forked_b200 import _native as nat
 from torchmetrics_forked_b200._exact import (  # noqa: F401
     as_columns,
@@ -28,6 +29,15 @@ def _ignore_args(ignore_index: Optional[int]):
 
 def _as_kernel_input(t: Tensor) -> Tensor:
     """Kernels index dense row-major memory; anything else is made contiguous first (one copy)."""
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _as_label_input(t: Tensor) -> Tensor:
+    """Targets as the kernels read them: an integer dtype, dense.  The reference takes float-typed targets holding
+    integer values too (its updates end in ``.to(torch.long)`` / ``target == 1``; its own tests pass
+    ``torch.zeros(10)`` as a target): they are truncated to int64 here, which is what ``.long()`` does there."""
+    if t.is_floating_point():
+        t = t.long()
     return t if t.is_contiguous() else t.contiguous()
 
 
@@ -55,8 +65,12 @@ def mc_argmax_hist(
     nat.require_cuda(out, "state")
     if preds.ndim < 2 or preds.shape[1] != num_classes:
         raise ValueError("`preds` must have shape (N, C, ...) with C equal to `num_classes`")
+    if _f64.is_f64(preds):  # argmax decided in float64, the label kernel counts
+        if target.numel() != preds.numel() // max(num_classes, 1):
+            raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+        return mc_label_hist(_f64.multiclass_labels(preds), target, num_classes, ignore_index, mode, out, err)
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
+    target = _as_label_input(target)
     n_outer = preds.shape[0]
     n_inner = 1
     for d in preds.shape[2:]:
@@ -83,6 +97,8 @@ def mc_stats_samplewise(
     ``multidim_average="samplewise"``."""
     nat.require_cuda(preds, "preds")
     nat.require_cuda(target, "target")
+    if _f64.is_f64(preds) and preds.ndim >= 2 and preds.shape[1] == num_classes:
+        preds = _f64.topk_marks(preds, top_k) if top_k > 1 else _f64.multiclass_labels(preds)
     is_label = not preds.is_floating_point()
     if top_k > 1:
         if is_label or preds.ndim < 2 or preds.shape[1] != num_classes:
@@ -91,7 +107,7 @@ def mc_stats_samplewise(
         n = preds.shape[0]
         rows = _as_kernel_input(preds.reshape(n, num_classes, -1).movedim(1, -1))
         per_sample = rows.shape[1]
-        tgt = _as_kernel_input(target.reshape(n, -1))
+        tgt = _as_label_input(target.reshape(n, -1))
         if tgt.shape[1] != per_sample:
             raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
         dev = preds.device
@@ -121,7 +137,7 @@ def mc_stats_samplewise(
     elif preds.ndim < 2 or preds.shape[1] != num_classes or preds.ndim != target.ndim + 1:
         raise ValueError("`preds` must have shape (N, C, ...) with C equal to `num_classes`")
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
+    target = _as_label_input(target)
     n = preds.shape[0]
     inner = target.numel() // n if n else 1
     dev = preds.device
@@ -192,10 +208,12 @@ def mc_topk_hist(
     nat.require_cuda(out, "state")
     if preds.ndim < 2 or preds.shape[1] != num_classes or not preds.is_floating_point():
         raise ValueError("`top_k > 1` needs float `preds` of shape (N, C, ...) with C equal to `num_classes`")
+    if _f64.is_f64(preds):
+        preds = _f64.topk_marks(preds, top_k)
     if preds.ndim > 2:  # extra dimensions become rows (torch transposes; the reference's one-hot does the same)
         preds = preds.movedim(1, -1).reshape(-1, num_classes)
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target.reshape(-1))
+    target = _as_label_input(target.reshape(-1))
     if target.numel() != preds.shape[0]:
         raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
     if preds.shape[0] == 0:
@@ -223,7 +241,7 @@ def mc_label_hist(
     nat.require_cuda(target, "target")
     nat.require_cuda(out, "state")
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
+    target = _as_label_input(target)
     if preds.numel() != target.numel():
         raise ValueError("`preds` and `target` must have the same number of elements")
     has_ign, ign = _ignore_args(ignore_index)
@@ -317,8 +335,12 @@ def thresh_bin_update(
         )
     if thresholds.dtype != torch.float32 or not thresholds.is_contiguous():
         raise ValueError("`thresholds` must be a contiguous float32 tensor")
+    if _f64.is_f64(preds) and preds.numel():
+        # normalised in float64, then rounded toward the side that keeps every comparison with a float32 threshold
+        normal = _f64.sigmoid_where_needed(preds, None if flag_counts_ignored else target, ignore_index)
+        preds = _f64.scores_for_binning(normal, strict=bool(cmp_gt))
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
+    target = _as_label_input(target)
     n_outer, n_labels, n_inner = _label_layout(preds, num_labels, binary)
     if preds.numel() == 0:
         return
@@ -357,8 +379,10 @@ def mc_curve_update(
         raise ValueError("`preds` must have shape (M, C) and `target` shape (M,)")
     if thresholds.dtype != torch.float32 or not thresholds.is_contiguous():
         raise ValueError("`thresholds` must be a contiguous float32 tensor")
+    if _f64.is_f64(preds) and preds.numel():
+        preds = _f64.scores_for_binning(_f64.softmax_where_needed(preds, target, ignore_index), strict=False)
     preds = _as_kernel_input(preds)
-    target = _as_kernel_input(target)
+    target = _as_label_input(target)
     if preds.numel() == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
@@ -422,6 +446,13 @@ def thresh_count(
     """
     if binary is None:
         binary = num_labels == 1
+    if _f64.is_f64(preds):  # the threshold is a Python float: compared in float64, the kernel counts 0/1 labels
+        nat.require_cuda(preds, "preds")
+        if preds.shape != target.shape:
+            raise RuntimeError(
+                f"Predictions and targets are expected to have the same shape, but got {preds.shape} and {target.shape}."
+            )
+        preds = _f64.binary_labels(preds, target, threshold, ignore_index, bool(flag_counts_ignored))
     thr = _scalar_threshold(threshold, preds)
     thresh_bin_update(preds, target, num_labels, binary, thr, True, ignore_index, flag_counts_ignored, scratch, err)
     thresh_bin_finalize(scratch, 1 if binary else num_labels, 1, None, layout, out)
