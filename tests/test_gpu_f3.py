@@ -75,6 +75,32 @@ def test_topk_ties_and_special_values_follow_torch_topk(C, k, dtype):
     assert np.array_equal(got, np.stack([tp, fp, tn, fn, tp + fn], -1))
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("C,k", [(136, 3), (264, 5), (520, 9), (1000, 5), (1000, 1), (1024, 20), (1000, 32), (1000, 40)])
+def test_topk_natural_scores_follow_torch_topk(C, k, dtype):
+    """Unquantised scores: the rows where the k largest sit in k lanes, the rows where two of them share a lane, and
+    (16-bit dtypes) the occasional tie across the k-th place all take the lane-maxima route of the top-k kernels; k = 32
+    is its limit, k = 40 the full ranking.  A few rows are made adversarial: the k largest in consecutive classes (one
+    lane), a plateau of equal scores around the k-th place."""
+    from torchmetrics_forked_b200 import functional as F
+
+    g = torch.Generator().manual_seed(C * 7 + k)
+    n = 4099
+    preds = torch.randn(n, C, generator=g).to(dtype)
+    preds[0, 8:8 + min(k + 2, C - 8)] = 9.0 + torch.arange(min(k + 2, C - 8)).to(dtype) * 0.25  # one lane holds them all
+    preds[1, ::3] = 7.0  # a plateau far wider than k
+    preds[2, 5:5 + k + 1] = 6.5  # a plateau of k + 1: one of them stays out
+    preds[3, C - k:] = 8.0  # exactly k equal winners at the end of the row
+    target = torch.randint(C, (n,), generator=g)
+    dp, dt = preds.cuda(), target.cuda()
+    got = F.multiclass_stat_scores(dp, dt, C, average="none", top_k=k).cpu().numpy()
+    member = torch.zeros(n, C, dtype=torch.bool, device="cuda").scatter_(1, dp.topk(k, dim=1).indices, True)
+    hot = torch.nn.functional.one_hot(dt, C).bool()
+    want = torch.stack([(hot & member).sum(0), (~hot & member).sum(0), (~hot & ~member).sum(0), (hot & ~member).sum(0),
+                        hot.sum(0)], -1).cpu().numpy()
+    assert np.array_equal(got, want), (C, k, dtype)
+
+
 def test_topk_argument_handling():
     from torchmetrics_forked_b200 import classification as C
     from torchmetrics_forked_b200 import functional as F

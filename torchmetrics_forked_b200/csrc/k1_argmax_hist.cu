@@ -1126,29 +1126,184 @@ __device__ __forceinline__ uint32_t topk_key16(uint32_t b) {  // b: the raw 16-b
   return (b & 0x8000u) ? (~b & 0xffffu) : (b | 0x8000u);  // torch's TopKTypeConfig<half / bfloat16>::convert
 }
 
+// ---- top-k through the lane maxima ------------------------------------------------------------------------------
+// Ranking every score costs ~8 instructions each (key, class, per-vector maximum) plus ~60 per selection round: ~600
+// instructions for a row of 1000.  Most of that is spent on scores that are nowhere near the top.  Instead:
+//   1. a lane reduces its 32 scores to their maximum with packed max instructions on the raw 16-bit patterns
+//      (two scores per operand, three operands per instruction);
+//   2. k REDUX rounds over the 32 lane maxima give tau, the k-th largest of them.  The k largest scores of the row
+//      are all >= tau (the k lane maxima found so far are k different scores >= tau), so
+//   3. ONE packed compare pass marks, per lane, the scores >= tau: the candidates, m >= k of them;
+//   4. m == k (the k largest sit in k different lanes and nothing ties with tau): the candidates are the answer;
+//      otherwise the m candidates get their full keys (value key << 16 | 0xffff - class, as below), one per lane, and
+//      k REDUX rounds pick the k largest — the same order as the full ranking, ties included.
+// ~170 instructions for a row that ends in step 4's first case, ~280 otherwise.  The full ranking below remains for
+// rows that hold a NaN (packed compares do not order them) and for m > 32 (rows of mostly equal scores).
+template <int DT>
+struct Pair16 {  // operations on two raw 16-bit scores in one register
+  static constexpr uint32_t kNegInf2 = DT == TMB_BF16 ? 0xff80ff80u : 0xfc00fc00u;
+  static __device__ __forceinline__ uint32_t max_nan(uint32_t a, uint32_t b) {  // NaN if either is NaN
+    uint32_t d;
+    if constexpr (DT == TMB_BF16) {
+      asm("max.NaN.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    } else {
+      asm("max.NaN.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+    }
+    return d;
+  }
+  static __device__ __forceinline__ uint32_t ge_mask(uint32_t a, uint32_t b) {  // 0xffff in each half where a >= b
+    if constexpr (DT == TMB_BF16) {
+      return __hge2_mask(*reinterpret_cast<const __nv_bfloat162*>(&a), *reinterpret_cast<const __nv_bfloat162*>(&b));
+    } else {
+      return __hge2_mask(*reinterpret_cast<const __half2*>(&a), *reinterpret_cast<const __half2*>(&b));
+    }
+  }
+  static __device__ __forceinline__ bool is_nan(uint32_t bits16) {
+    constexpr uint32_t kExpAll = DT == TMB_BF16 ? 0x7f80u : 0x7c00u;
+    return (bits16 & 0x7fffu) > kExpAll;
+  }
+  static __device__ __forceinline__ uint32_t key_of(uint32_t bits16) {  // topk_key16 for a score that is no NaN
+    return (bits16 & 0x8000u) ? (~bits16 & 0xffffu) : (bits16 | 0x8000u);
+  }
+  static __device__ __forceinline__ uint32_t bits_of(uint32_t key) {  // its inverse
+    return (key & 0x8000u) ? (key & 0x7fffu) : (~key & 0xffffu);
+  }
+};
+
+// One row held in the lanes' `raw` vectors (vector q of this lane is vector lane + 32 q of the row, 8 scores each).
+// Returns false when the row needs the full ranking; otherwise the row's k classes have been added to the
+// "predicted" histogram `pred_hist` and `hit` says whether `t` is among them.  `list` is this warp's 32-word buffer.
 template <int DT, int VECS>
-__global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ preds, const void* __restrict__ target,
+__device__ __forceinline__ bool topk16_by_lane_maxima(const uint4 (&raw)[VECS], const void* __restrict__ preds,
+                                                      int64_t row_base, int lane, int n_vec, int top_k, int64_t t,
+                                                      int* pred_hist, uint32_t* list, bool& hit) {
+  using P = Pair16<DT>;
+  uint32_t m2 = P::kNegInf2;
+#pragma unroll
+  for (int q = 0; q < VECS; ++q) {
+    const uint32_t v2 = P::max_nan(P::max_nan(raw[q].x, raw[q].y), P::max_nan(raw[q].z, raw[q].w));
+    m2 = P::max_nan(m2, lane + 32 * q < n_vec ? v2 : P::kNegInf2);
+  }
+  const uint32_t lo = m2 & 0xffffu, hi = m2 >> 16;
+  const bool nan = P::is_nan(lo) | P::is_nan(hi);
+  const uint32_t kb = max(P::key_of(lo), P::key_of(hi));  // this lane's best score as a key
+  if (__any_sync(kFull, nan)) return false;
+  // tau: the lane number makes the words unique; which lane of a tie goes first does not matter for tau
+  uint32_t mine = (kb << 16) | (uint32_t)lane;
+  uint32_t kth = 0;
+  for (int round = 0; round < top_k; ++round) {
+    const uint32_t top = __reduce_max_sync(kFull, mine);
+    kth = top >> 16;
+    if (top == mine) mine = 0u;
+  }
+  // the compare pass.  Word i of the lane (i = 4 q + h) reports its low score in bit i and its high score in bit
+  // 16 + i: one AND-OR per word with an immediate.
+  const uint32_t tau = P::bits_of(kth);
+  const uint32_t tau2 = tau | (tau << 16);
+  uint32_t marks = 0;
+#pragma unroll
+  for (int q = 0; q < VECS; ++q) {
+    const uint32_t w[4] = {raw[q].x, raw[q].y, raw[q].z, raw[q].w};
+    if (lane + 32 * q < n_vec) {
+#pragma unroll
+      for (int h = 0; h < 4; ++h) marks |= P::ge_mask(w[h], tau2) & (0x00010001u << (q * 4 + h));
+    }
+  }
+  const int count = __popc(marks);
+  const int m = __reduce_add_sync(kFull, count);
+  if (m > 32) return false;
+  auto class_of = [&](int bit) {  // bit i or 16 + i of `marks` -> class
+    const int word = bit & 15;
+    return (lane + 32 * (word >> 2)) * 8 + 2 * (word & 3) + (bit >> 4);
+  };
+  hit = false;
+  if (m == top_k) {
+    bool mine_hit = false;
+    for (uint32_t left = marks; left; left &= left - 1u) {
+      const int cls = class_of(__ffs(left) - 1);
+      atomicAdd(&pred_hist[cls], 1);
+      mine_hit |= (int64_t)cls == t;
+    }
+    hit = __any_sync(kFull, mine_hit);
+    return true;
+  }
+  // m > k: every candidate gets its full key and a lane of its own
+  int at = count;  // exclusive prefix sum of the counts over the lanes
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int up = __shfl_up_sync(kFull, at, d);
+    if (lane >= d) at += up;
+  }
+  at -= count;
+  for (uint32_t left = marks; left; left &= left - 1u) {
+    const int cls = class_of(__ffs(left) - 1);
+    // a lane's only candidate is its maximum; a lane with several reads each score again (the row is in L2)
+    const uint32_t key = count == 1 ? kb : P::key_of((uint32_t)__ldg((const unsigned short*)preds + row_base + cls));
+    list[at++] = (key << 16) | (0xffffu - (uint32_t)cls);
+  }
+  __syncwarp();
+  uint32_t cand = lane < m ? list[lane] : 0u;
+  __syncwarp();
+  for (int round = 0; round < top_k; ++round) {
+    const uint32_t top = __reduce_max_sync(kFull, cand);
+    const int cls = (int)(0xffffu - (top & 0xffffu));
+    if (cand == top) {
+      atomicAdd(&pred_hist[cls], 1);
+      cand = 0u;
+    }
+    hit |= (int64_t)cls == t;
+  }
+  return true;
+}
+
+template <int DT, int VECS>
+__global__ void __launch_bounds__(256, 4) k1_rows_topk16(const void* __restrict__ preds, const void* __restrict__ target,
                                                       int tdt, int64_t rows, int C, int top_k, int has_ignore,
                                                       int64_t ignore, unsigned long long* __restrict__ out, int* err) {
   extern __shared__ int sh_topk[];  // [3 * C]: T | P | M
+  __shared__ uint32_t cand_list[8][32];  // per warp: the candidates of topk16_by_lane_maxima
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int n_vec = C >> 3;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  // vector q of a lane sits 512 q bytes behind its first one, and rows follow each other at a fixed distance: one
+  // pointer, advanced by a constant, and immediate offsets.  Vectors past the row end are never loaded and stay zero.
   uint4 raw[VECS];
-  auto fetch = [&](int64_t r) {
 #pragma unroll
-    for (int q = 0; q < VECS; ++q) {
-      const int v = lane + 32 * q;
-      raw[q] = v < n_vec ? ldg_stream16((const char*)preds + (r * C + (int64_t)v * 8) * 2) : make_uint4(0, 0, 0, 0);
-    }
+  for (int q = 0; q < VECS; ++q) raw[q] = make_uint4(0, 0, 0, 0);
+  int64_t t_ahead = 0;  // the row's label travels with the row: asked for a trip ahead, not when it is needed
+  const char* ahead = (const char*)preds + (warp * C + (int64_t)lane * 8) * 2;  // the row `fetch` loads next
+  const int64_t row_step = nwarps * C * 2;
+  auto fetch = [&](int64_t r) {
+    t_ahead = load_label(target, tdt, r);
+#pragma unroll
+    for (int q = 0; q < VECS; ++q)
+      if (lane + 32 * q < n_vec) raw[q] = ldg_stream16(ahead + q * 512);
+    ahead += row_step;
   };
   int64_t r = warp;
   if (r < rows) fetch(r);
   for (; r < rows; r += nwarps) {  // warp-uniform
-    const int64_t t = load_label(target, tdt, r);
+    const int64_t t = t_ahead;
+    if ((has_ignore && t == ignore) || t < 0 || t >= C) {  // nothing of this row is counted
+      if (!(has_ignore && t == ignore) && lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      if (r + nwarps < rows) fetch(r + nwarps);
+      continue;
+    }
+    if (top_k <= 32) {
+      bool hit;
+      if (topk16_by_lane_maxima<DT, VECS>(raw, preds, r * C, lane, n_vec, top_k, t, sh_topk + C,
+                                          cand_list[threadIdx.x >> 5], hit)) {
+        if (r + nwarps < rows) fetch(r + nwarps);
+        if (lane == 0) {
+          atomicAdd(&sh_topk[(int)t], 1);
+          if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+        }
+        continue;
+      }
+    }
     // Keys, four instructions each: the score moves to the high half (it is there already for the odd elements),
     // torch's order-preserving map is "flip everything if negative, else the sign" on the whole word, and one LOP3
     // puts 0xffff - class into the low half.  NaN (-> 0xffff) needs a compare per element; instead one test per
@@ -1180,12 +1335,6 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
           key[q * 8 + e] = (topk_key16<DT>(bits) << 16) | (key[q * 8 + e] & 0xffffu);
         }
       }
-    }
-    if (r + nwarps < rows) fetch(r + nwarps);  // the next row travels while this one is ranked
-    if (has_ignore && t == ignore) continue;
-    if (t < 0 || t >= C) {
-      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
-      continue;
     }
     // A lane keeps the maximum of each of its vectors (8 keys) and the maximum of those.  Keys are unique, so a round
     // is one REDUX.MAX, and only the lane that owned the winner has anything to update: it clears the key in the one
@@ -1226,6 +1375,9 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
       atomicAdd(&sh_topk[(int)t], 1);
       if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
     }
+    // the full ranking is the rare route (see topk16_by_lane_maxima): its keys and the next row's vectors do not have
+    // to be live together, which keeps the kernel at four CTAs per SM
+    if (r + nwarps < rows) fetch(r + nwarps);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
@@ -1237,29 +1389,145 @@ __global__ void __launch_bounds__(256) k1_rows_topk16(const void* __restrict__ p
 // fp32 scores: no spare key bits, so the (value key, class) pair stays split as in k1_rows_topk, but the row arrives
 // as 16-byte vectors (vector v of the row in lane v % 32, 4 scores each) with the next row already in flight.
 // Needs C % 4 == 0 (16-byte aligned rows) and C <= 1024.
+// topk16_by_lane_maxima for fp32 scores: the lane maximum is a chain of three-operand float max instructions
+// (NaN-propagating), the 32-bit value key has no room for the class, so equal keys are told apart by a second REDUX
+// (lowest class first), and a candidate travels as two words.
+__device__ __forceinline__ float fmax3_nan(float a, float b, float c) {
+  float d;
+  asm("max.NaN.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+__device__ __forceinline__ uint32_t key32_of(float v) {  // topk_key for a score that is no NaN
+  const uint32_t b = __float_as_uint(v);
+  return b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
+}
+
 template <int VECS>
-__global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ preds, const void* __restrict__ target,
+__device__ __forceinline__ bool topk32_by_lane_maxima(const uint4 (&raw)[VECS], const void* __restrict__ preds,
+                                                      int64_t row_base, int lane, int n_vec, int top_k, int64_t t,
+                                                      int* pred_hist, uint32_t* list_key, uint32_t* list_cls,
+                                                      bool& hit) {
+  float best = -INFINITY;
+#pragma unroll
+  for (int q = 0; q < VECS; ++q) {
+    const float x = __uint_as_float(raw[q].x), y = __uint_as_float(raw[q].y);
+    const float z = __uint_as_float(raw[q].z), w = __uint_as_float(raw[q].w);
+    const float v = fmax3_nan(fmax3_nan(x, y, z), w, -INFINITY);
+    best = fmax3_nan(best, lane + 32 * q < n_vec ? v : -INFINITY, -INFINITY);
+  }
+  if (__any_sync(kFull, best != best)) return false;
+  const uint32_t kb = key32_of(best);
+  // tau = the k-th largest lane maximum; equal maxima leave one lane per round (the lowest)
+  uint32_t mine = kb, kth = 0;
+  for (int round = 0; round < top_k; ++round) {
+    kth = __reduce_max_sync(kFull, mine);
+    const unsigned holders = __ballot_sync(kFull, mine == kth);
+    if (lane == __ffs(holders) - 1) mine = 0u;  // 0 is below the key of every score, -inf included
+  }
+  const uint32_t tb = (kth & 0x80000000u) ? (kth & 0x7fffffffu) : ~kth;
+  const float tau = __uint_as_float(tb);
+  uint32_t marks = 0;
+#pragma unroll
+  for (int q = 0; q < VECS; ++q) {
+    const float x[4] = {__uint_as_float(raw[q].x), __uint_as_float(raw[q].y), __uint_as_float(raw[q].z),
+                        __uint_as_float(raw[q].w)};
+    if (lane + 32 * q < n_vec) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) marks |= (x[e] >= tau ? 1u : 0u) << (q * 4 + e);
+    }
+  }
+  const int count = __popc(marks);
+  const int m = __reduce_add_sync(kFull, count);
+  if (m > 32) return false;
+  auto class_of = [&](int bit) { return (lane + 32 * (bit >> 2)) * 4 + (bit & 3); };
+  hit = false;
+  if (m == top_k) {
+    bool mine_hit = false;
+    for (uint32_t left = marks; left; left &= left - 1u) {
+      const int cls = class_of(__ffs(left) - 1);
+      atomicAdd(&pred_hist[cls], 1);
+      mine_hit |= (int64_t)cls == t;
+    }
+    hit = __any_sync(kFull, mine_hit);
+    return true;
+  }
+  int at = count;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int up = __shfl_up_sync(kFull, at, d);
+    if (lane >= d) at += up;
+  }
+  at -= count;
+  for (uint32_t left = marks; left; left &= left - 1u) {
+    const int cls = class_of(__ffs(left) - 1);
+    list_key[at] = count == 1 ? kb : key32_of(__ldg((const float*)preds + row_base + cls));
+    list_cls[at] = (uint32_t)cls;
+    ++at;
+  }
+  __syncwarp();
+  uint32_t ck = lane < m ? list_key[lane] : 0u;
+  const uint32_t cc = lane < m ? list_cls[lane] : 0xffffffffu;
+  __syncwarp();
+  for (int round = 0; round < top_k; ++round) {
+    const uint32_t top = __reduce_max_sync(kFull, ck);
+    const uint32_t cls = __reduce_min_sync(kFull, ck == top ? cc : 0xffffffffu);
+    if (ck == top && cc == cls) {
+      atomicAdd(&pred_hist[cls], 1);
+      ck = 0u;
+    }
+    hit |= (int64_t)cls == t;
+  }
+  return true;
+}
+
+template <int VECS>
+__global__ void __launch_bounds__(256, 3) k1_rows_topk32(const void* __restrict__ preds, const void* __restrict__ target,
                                                       int tdt, int64_t rows, int C, int top_k, int has_ignore,
                                                       int64_t ignore, unsigned long long* __restrict__ out, int* err) {
   extern __shared__ int sh_topk[];  // [3 * C]: T | P | M
+  __shared__ uint32_t cand_key[8][32], cand_cls[8][32];  // per warp: the candidates of topk32_by_lane_maxima
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) sh_topk[i] = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int n_vec = C >> 2;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  // vector q of a lane sits 512 q bytes behind its first one, and rows follow each other at a fixed distance: one
+  // pointer, advanced by a constant, and immediate offsets.  Vectors past the row end are never loaded and stay zero.
   uint4 raw[VECS];
-  auto fetch = [&](int64_t r) {
 #pragma unroll
-    for (int q = 0; q < VECS; ++q) {
-      const int v = lane + 32 * q;
-      raw[q] = v < n_vec ? ldg_stream16((const char*)preds + (r * C + (int64_t)v * 4) * 4) : make_uint4(0, 0, 0, 0);
-    }
+  for (int q = 0; q < VECS; ++q) raw[q] = make_uint4(0, 0, 0, 0);
+  int64_t t_ahead = 0;  // the row's label travels with the row: asked for a trip ahead, not when it is needed
+  const char* ahead = (const char*)preds + (warp * C + (int64_t)lane * 4) * 4;  // the row `fetch` loads next
+  const int64_t row_step = nwarps * C * 4;
+  auto fetch = [&](int64_t r) {
+    t_ahead = load_label(target, tdt, r);
+#pragma unroll
+    for (int q = 0; q < VECS; ++q)
+      if (lane + 32 * q < n_vec) raw[q] = ldg_stream16(ahead + q * 512);
+    ahead += row_step;
   };
   int64_t r = warp;
   if (r < rows) fetch(r);
   for (; r < rows; r += nwarps) {  // warp-uniform
-    const int64_t t = load_label(target, tdt, r);
+    const int64_t t = t_ahead;
+    if ((has_ignore && t == ignore) || t < 0 || t >= C) {  // nothing of this row is counted
+      if (!(has_ignore && t == ignore) && lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
+      if (r + nwarps < rows) fetch(r + nwarps);
+      continue;
+    }
+    if (top_k <= 32) {
+      bool hit;
+      if (topk32_by_lane_maxima<VECS>(raw, preds, r * C, lane, n_vec, top_k, t, sh_topk + C,
+                                      cand_key[threadIdx.x >> 5], cand_cls[threadIdx.x >> 5], hit)) {
+        if (r + nwarps < rows) fetch(r + nwarps);
+        if (lane == 0) {
+          atomicAdd(&sh_topk[(int)t], 1);
+          if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
+        }
+        continue;
+      }
+    }
     // keys: "flip everything if negative, else the sign" is two instructions; NaN (-> all ones) is looked for once per
     // lane (an all-ones exponent, i.e. inf or NaN, in any of its scores) and fixed up in the rare lane that has one
     uint32_t key[VECS * 4], group[VECS];
@@ -1280,12 +1548,6 @@ __global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ p
 #pragma unroll
         for (int e = 0; e < 4; ++e) key[q * 4 + e] = topk_key(__uint_as_float(w[e]));
       }
-    }
-    if (r + nwarps < rows) fetch(r + nwarps);
-    if (has_ignore && t == ignore) continue;
-    if (t < 0 || t >= C) {
-      if (lane == 0) atomicOr(err, TMB_ERR_TARGET_RANGE);
-      continue;
     }
     // Per-vector maxima as in k1_rows_topk16.  Equal scores are possible here: the lanes holding the warp maximum
     // name the lowest class they hold it for (vectors and elements ascend with the class inside a lane), REDUX.MIN
@@ -1330,6 +1592,9 @@ __global__ void __launch_bounds__(256) k1_rows_topk32(const void* __restrict__ p
       atomicAdd(&sh_topk[(int)t], 1);
       if (hit) atomicAdd(&sh_topk[2 * C + (int)t], 1);
     }
+    // the full ranking is the rare route (see topk16_by_lane_maxima): its keys and the next row's vectors do not have
+    // to be live together, which keeps the kernel at four CTAs per SM
+    if (r + nwarps < rows) fetch(r + nwarps);
   }
   __syncthreads();
   for (int i = threadIdx.x; i < 3 * C; i += blockDim.x) {
