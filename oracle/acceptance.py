@@ -71,15 +71,31 @@ class _Alias(importlib.abc.MetaPathFinder, importlib.abc.Loader):
 
 if not _CONTROL:
     sys.meta_path.insert(0, _Alias())
+    # bases/test_metric.py imports one metric of another domain at module level, for ONE test
+    # (test_specific_error_on_wrong_device); a placeholder lets the other 29 be collected, that test is deselected
+    import types as _types
+    _reg = _types.ModuleType("torchmetrics.regression")
+    _reg.PearsonCorrCoef = None
+    sys.modules["torchmetrics.regression"] = _reg
 
 import contextlib, warnings, pytest
 _pytest_warns = pytest.warns
+
+class _Recorded(list):
+    """What `pytest.warns(None)` used to yield: the recorded warnings, also reachable as `.list`."""
+    @property
+    def list(self):
+        return self
 
 @contextlib.contextmanager
 def _record_all():
     with warnings.catch_warnings(record=True) as record:
         warnings.simplefilter("always")
-        yield record
+        seen = _Recorded()
+        try:
+            yield seen
+        finally:
+            seen.extend(record)
 
 def _warns(expected=Warning, *args, **kwargs):
     """`pytest.warns(None)` (record everything, expect nothing) left pytest in 8.0; the reference's tests still use it."""

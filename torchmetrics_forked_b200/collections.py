@@ -411,15 +411,15 @@ class MetricCollection(ModuleDict):
 
     def keys(self, keep_base: bool = False) -> Iterable[Hashable]:
         """Metric names, with prefix/postfix unless ``keep_base``."""
-        if keep_base:
-            return self._modules.keys()
+        if keep_base:  # one view type either way (`Module._modules` is a plain dict in current torch, an OrderedDict before)
+            return OrderedDict(self._modules).keys()
         return self._to_renamed_ordered_dict().keys()
 
     def items(self, keep_base: bool = False, copy_state: bool = True) -> Iterable[Tuple[str, Metric]]:
         """(name, metric) pairs; ``copy_state=True`` un-links compute-group members first."""
         self._compute_groups_create_state_ref(copy_state)
         if keep_base:
-            return self._modules.items()
+            return OrderedDict(self._modules).items()
         return self._to_renamed_ordered_dict().items()
 
     def values(self, copy_state: bool = True) -> Iterable[Metric]:
