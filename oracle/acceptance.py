@@ -210,6 +210,8 @@ def main() -> int:
                     help="run with torch.set_default_device('cuda'): for the tests that create their inputs inline")
     ap.add_argument("--adapt-cpu", action="store_true",
                     help="move CPU tensors to cuda:0 at the package boundary and results back (inline-input tests)")
+    ap.add_argument("--ddp", action="store_true",
+                    help="keep the reference's pool of two gloo workers and run the ddp=True cases (use with --adapt-cpu -k True)")
     ap.add_argument("--against-reference", action="store_true",
                     help="control run: the same tests against the staged unmodified reference")
     ap.add_argument("--tb", default="line")
@@ -225,11 +227,21 @@ def main() -> int:
         z.extractall(root)
     conf = root / "unittests" / "conftest.py"
     text = conf.read_text()
-    text = re.sub(r"def pytest_sessionstart\(\):.*?(?=\ndef |\Z)", "def pytest_sessionstart():\n    pass\n\n", text, flags=re.S)
-    text = re.sub(r"def pytest_sessionfinish\(\):.*?(?=\ndef |\Z)", "def pytest_sessionfinish():\n    pass\n\n", text, flags=re.S)
-    conf.write_text(text)
-    (root / "conftest.py").write_text(ALIAS.format(repo=str(HERE.parent), shim=str(HERE / "shim"),
-                                                  refzip=str(HERE / "_ref" / "reference.zip")))
+    alias = ALIAS.format(repo=str(HERE.parent), shim=str(HERE / "shim"), refzip=str(HERE / "_ref" / "reference.zip"))
+    if args.ddp:
+        # the `ddp=True` parametrisations: the reference's pool of two workers (spawned, gloo) is kept.  The workers
+        # import unittests/conftest.py when they unpickle their first task, so the alias goes THERE; both ranks use
+        # cuda:0 through the --adapt-cpu carrier and gloo moves the CUDA states
+        text = text.replace('"localhost"', '"127.0.0.1"')
+        future = [ln for ln in text.splitlines() if ln.startswith("from __future__")]
+        text = "\n".join(future) + "\n" + alias + "\n" + "\n".join(ln for ln in text.splitlines() if ln not in future) + "\n"
+        conf.write_text(text)
+        (root / "conftest.py").write_text("")
+    else:
+        text = re.sub(r"def pytest_sessionstart\(\):.*?(?=\ndef |\Z)", "def pytest_sessionstart():\n    pass\n\n", text, flags=re.S)
+        text = re.sub(r"def pytest_sessionfinish\(\):.*?(?=\ndef |\Z)", "def pytest_sessionfinish():\n    pass\n\n", text, flags=re.S)
+        conf.write_text(text)
+        (root / "conftest.py").write_text(alias)
     files = [f"unittests/{f}" for f in (args.files or DEFAULT_FILES)]
     cmd = [sys.executable, "-m", "pytest", *files, "-q", "-c", "/dev/null", f"--rootdir={root}", "-p", "no:cacheprovider",
            "-k", args.select, f"--tb={args.tb}", "-W", "ignore", "-rf"] + (["--collect-only"] if args.collect_only else []) + (
