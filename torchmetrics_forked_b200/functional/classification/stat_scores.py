@@ -363,7 +363,8 @@ def _binary_stat_scores_functional_state(
     dev = preds.device
     err = torch.zeros(1, dtype=torch.int32, device=dev)
     if multidim_average == "samplewise":
-        out = _samplewise_thresh_stats(preds, target, preds.shape[0], threshold, ignore_index, err)
+        # `.squeeze()` like the reference (:127-130): a batch of one sample gives 0-d counts, and a 0-d result
+        out = tuple(x.squeeze() for x in _samplewise_thresh_stats(preds, target, preds.shape[0], threshold, ignore_index, err))
     else:
         tp, fp, tn, fn = (torch.zeros(1, dtype=torch.long, device=dev) for _ in range(4))
         scratch = torch.zeros(kernels.thresh_count_scratch_numel(1), dtype=torch.long, device=dev)
