@@ -11,6 +11,7 @@ thresholds), `MulticlassPrecisionRecallCurve(average="micro")` as a class (the r
 labels outside the class range (validation differs by design), and a `multidim_average="samplewise"` multilabel batch
 of one sample (the reference's `.squeeze()` drops the sample dimension there: deviation 12, found by this test).
 """
+import os
 import random
 
 import pytest
@@ -24,7 +25,8 @@ if not ref_loader.staged_available() and not ref_loader.reference_available():
     pytest.skip("oracle/_ref is not staged (run __graft_entry__.build() where /root/reference exists)",
                 allow_module_level=True)
 
-N_CASES = 600
+SCALE = int(os.environ.get("TMB_FUZZ_SCALE", "1"))  # more seeds for a longer hunt: TMB_FUZZ_SCALE=5 pytest ...
+N_CASES = 600 * SCALE
 OUTCOME = {"compared": 0, "rejected_by_both": 0, "skipped": 0}
 STAT_FAMILY = ["StatScores", "Accuracy", "Precision", "Recall", "F1Score", "Specificity", "HammingDistance",
                "JaccardIndex", "ConfusionMatrix", "CohenKappa", "MatthewsCorrCoef"]
@@ -208,7 +210,7 @@ FIXED_POINT = [("PrecisionAtFixedRecall", "min_recall"), ("RecallAtFixedPrecisio
                ("SpecificityAtSensitivity", "min_sensitivity")]
 
 
-@pytest.mark.parametrize("seed", range(120))
+@pytest.mark.parametrize("seed", range(120 * SCALE))
 def test_random_fixed_point_metric(R, M, seed):
     """The *AtFixed* family (row f1): exact and binned curves behind a constrained arg-max."""
     rnd = random.Random(10_000 + seed)
@@ -251,7 +253,7 @@ def test_random_fixed_point_metric(R, M, seed):
     _close(ours.compute(), want, f"{task + base}({kw})")
 
 
-@pytest.mark.parametrize("seed", range(80))
+@pytest.mark.parametrize("seed", range(80 * SCALE))
 def test_random_collection_forward_update_reset(R, M, seed):
     """MetricCollection with compute groups (rows b, f4): forward() batch values, accumulation across forward and
     update, reset, forward again — the sequence in which the in-place forward and the shared group states interact."""
@@ -315,7 +317,7 @@ _SNAKE = {"StatScores": "stat_scores", "Accuracy": "accuracy", "Precision": "pre
           "AUROC": "auroc", "AveragePrecision": "average_precision"}
 
 
-@pytest.mark.parametrize("seed", range(300))
+@pytest.mark.parametrize("seed", range(300 * SCALE))
 def test_random_functional_call(R, M, seed):
     """The functional face (`torchmetrics.functional.classification.*`) and the task wrappers (`Accuracy(task=...)`):
     the same generator, one batch, `validate_args` on or off."""
@@ -352,3 +354,98 @@ def test_random_functional_call(R, M, seed):
                 ours(preds, target)
             return
         _close(ours(preds, target), want, f"{base}(task={task.lower()!r}, {wkw})")
+
+
+def _misaligned(x, off):
+    """The same values in storage that starts `off` elements past a 256-byte boundary (kernel dispatch looks at the
+    alignment of the pointer and of the rows)."""
+    if off == 0:
+        return x
+    flat = torch.empty(x.numel() + off, dtype=x.dtype, device=x.device)
+    flat[off:] = x.reshape(-1)
+    return flat[off:].view(x.shape)
+
+
+@pytest.mark.parametrize("seed", range(160 * SCALE))
+def test_random_shapes_through_the_kernel_dispatch(R, M, seed):
+    """Mid-size inputs (1e5 - 4e6 scores) of random width, dtype, pointer alignment and target dtype: the shapes at
+    which the launchers switch between their kernels (thread per row, lanes per row, warp per row, pipelined rows,
+    strided planes, top-k by lane maxima, binary lanes, multilabel tiles, fused softmax rows ...)."""
+    rnd = random.Random(70_000 + seed)
+    kind = rnd.choice(["confmat", "stats", "topk", "strided", "binary_curve", "multilabel_curve", "multilabel_stats",
+                       "multiclass_curve", "exact_auroc"])
+    dtype = rnd.choice([torch.float32, torch.bfloat16, torch.float16])
+    tdt = rnd.choice([torch.int64, torch.int64, torch.int32, torch.uint8])
+    off = rnd.choice([0, 0, 1, 3, 4, 8])
+    ignore = rnd.choice([None, None, 0, -1])
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    total = rnd.choice([100_000, 700_000, 4_000_000])
+
+    def labels(shape, hi):
+        t = torch.randint(hi, shape, generator=gen, device="cuda")
+        if ignore is not None:
+            t = torch.where(torch.rand(shape, generator=gen, device="cuda") < 0.1, torch.full_like(t, ignore), t)
+        ok = tdt != torch.uint8 or (hi <= 256 and ignore != -1)
+        return t.to(tdt) if ok else t
+
+    if kind in ("confmat", "stats", "topk", "multiclass_curve", "exact_auroc"):
+        C = rnd.choice([2, 3, 7, 8, 10, 16, 31, 32, 33, 64, 100, 128, 136, 200, 256, 264, 500, 512, 1000, 1024, 1100])
+        if kind in ("multiclass_curve", "exact_auroc"):
+            C = min(C, rnd.choice([10, 100, 1100]))
+        if kind == "exact_auroc":
+            total = min(total, 700_000)
+            C = min(C, 100)
+        n = max(total // C, 3)
+        p = _misaligned((torch.randn(n, C, generator=gen, device="cuda") * 3).to(dtype), off)
+        if rnd.random() < 0.3:
+            p = _misaligned(((p.float() * 2).round() / 2).to(dtype), off)  # ties
+        t = labels((n,), C)
+        ign = ignore if ignore is None or ignore < C else None
+        if kind == "confmat":
+            name, kw = "MulticlassConfusionMatrix", {"num_classes": C, "ignore_index": ign}
+        elif kind == "stats":
+            name, kw = "MulticlassStatScores", {"num_classes": C, "ignore_index": ign, "average": rnd.choice(["micro", "none"])}
+        elif kind == "topk":
+            name, kw = "MulticlassStatScores", {"num_classes": C, "ignore_index": ign, "average": "none",
+                                                "top_k": rnd.randint(2, min(C, 7)) if C > 2 else 1}
+        elif kind == "multiclass_curve":
+            name, kw = "MulticlassPrecisionRecallCurve", {"num_classes": C, "ignore_index": ign,
+                                                          "thresholds": rnd.choice([1, 7, 200, 300])}
+        else:
+            name, kw = "MulticlassAUROC", {"num_classes": C, "ignore_index": ign, "thresholds": None, "average": "macro"}
+    elif kind == "strided":
+        C, hw = rnd.choice([2, 5, 21, 150]), rnd.choice([(7, 9), (64, 64), (31, 128)])
+        n = max(total // (C * hw[0] * hw[1]), 1)
+        p = _misaligned(torch.randn(n, C, *hw, generator=gen, device="cuda").to(dtype), off)
+        t = labels((n, *hw), C)
+        name, kw = "MulticlassJaccardIndex", {"num_classes": C, "ignore_index": ignore if ignore in (None, 0) else None}
+    elif kind == "binary_curve":
+        p = _misaligned((torch.randn(total, generator=gen, device="cuda") * 3).to(dtype), off)
+        if rnd.random() < 0.5:
+            p = _misaligned(p.float().sigmoid().to(dtype), off)
+        t = labels((total,), 2)
+        name, kw = "BinaryPrecisionRecallCurve", {"ignore_index": ignore, "thresholds": rnd.choice([1, 2, 50, 200, 257, 1000])}
+    else:
+        L = rnd.choice([1, 2, 3, 4, 5, 16, 100, 300])
+        n = max(total // L, 3)
+        p = _misaligned((torch.randn(n, L, generator=gen, device="cuda") * 3).to(dtype), off)
+        t = labels((n, L), 2)
+        if kind == "multilabel_curve":
+            name, kw = "MultilabelPrecisionRecallCurve", {"num_labels": L, "ignore_index": ignore,
+                                                          "thresholds": rnd.choice([1, 50, 200, 600])}
+        else:
+            name, kw = "MultilabelStatScores", {"num_labels": max(L, 2), "ignore_index": ignore, "average": "none"}
+            if L == 1:
+                p, t = p.expand(n, 2).contiguous(), t.expand(n, 2).contiguous()
+    theirs = getattr(R.classification, name)(**kw, validate_args=False).cuda()
+    ours = getattr(M.classification, name)(**kw, validate_args=False).cuda()
+    try:
+        theirs.update(p, t)
+    except Exception as ref_err:  # noqa: BLE001
+        pytest.skip(f"the reference's update raises here: {type(ref_err).__name__}: {str(ref_err)[:80]}")
+    ours.update(p, t)
+    mine, ref = _states(ours), _states(theirs)
+    for k, want in ref.items():
+        assert mine[k].shape == want.shape and torch.equal(mine[k].to(want.dtype), want), (name, kw, p.shape, p.dtype, k)
+    if kind == "exact_auroc":
+        _close(ours.compute(), theirs.compute(), f"{name}({kw})")
