@@ -102,6 +102,7 @@ def _pack(states: Sequence[Tensor]) -> Tensor:
 _DTYPES = [torch.float32, torch.float16, torch.bfloat16, torch.float64, torch.int64, torch.int32, torch.int16,
            torch.int8, torch.uint8, torch.bool]
 _MAX_TRAIL = 6
+_WIRE = {torch.bool: torch.uint8, torch.int16: torch.float16}  # dtype of a list state -> dtype on the wire
 
 
 def all_gather_cat(
@@ -164,11 +165,13 @@ def _all_gather_cat(local: Optional[Tensor], device: torch.device, group: Option
         send[: local.shape[0]] = local
     else:
         send = local
-    wire = send.view(torch.uint8) if dtype == torch.bool else send
+    # NCCL moves a fixed list of dtypes; an all-gather only copies bits, so the others travel as a same-sized one
+    wire_dtype = _WIRE.get(dtype)
+    wire = send.view(wire_dtype) if wire_dtype is not None else send
     recv = torch.empty((world * most, *trail), dtype=wire.dtype, device=device)
     dist.all_gather_into_tensor(recv, wire, group=group)
-    if dtype == torch.bool:
-        recv = recv.view(torch.bool)
+    if wire_dtype is not None:
+        recv = recv.view(dtype)
     if all(r == most for r in rows):
         return recv, word_or
     recv = recv.view(world, most, *trail)
