@@ -449,3 +449,71 @@ def test_random_shapes_through_the_kernel_dispatch(R, M, seed):
         assert mine[k].shape == want.shape and torch.equal(mine[k].to(want.dtype), want), (name, kw, p.shape, p.dtype, k)
     if kind == "exact_auroc":
         _close(ours.compute(), theirs.compute(), f"{name}({kw})")
+
+
+@pytest.mark.parametrize("seed", range(150 * SCALE))
+def test_random_lifecycle(R, M, seed):
+    """One metric through a random life: update / forward / compute / reset mixed with clone, pickle, deepcopy,
+    `state_dict` round trips (with `persistent(True)`), `.half()` / `.float()` / `.double()` and a move to the CPU and
+    back — the same steps on the reference's object, every returned value compared."""
+    import copy
+    import pickle
+
+    name, kw, batch = _draw(30_000 + seed)
+    rnd = random.Random(31_000 + seed)
+    try:
+        theirs = getattr(R.classification, name)(**kw).cuda()
+    except Exception:  # noqa: BLE001
+        return
+    ours = getattr(M.classification, name)(**kw).cuda()
+    gen = torch.Generator(device="cuda").manual_seed(seed)
+    steps = [rnd.choice(["update", "update", "forward", "compute", "reset", "clone", "pickle", "deepcopy", "state_dict",
+                         "float", "cpu_and_back"]) for _ in range(8)] + ["update", "compute"]
+    for i, step in enumerate(steps):
+        where = f"{name}({kw}) step {i} {step} of {steps}"
+        if step in ("update", "forward"):
+            preds, target = batch(gen)
+            try:
+                want = getattr(theirs, step)(preds, target)
+            except Exception as ref_err:  # noqa: BLE001
+                pytest.skip(f"the reference raises here: {type(ref_err).__name__}: {str(ref_err)[:80]}")
+            got = getattr(ours, step)(preds, target)
+            if step == "forward":
+                _close(got, want, where)
+        elif step == "compute":
+            try:
+                want = theirs.compute()
+            except Exception as ref_err:  # noqa: BLE001
+                pytest.skip(f"the reference's compute() raises here: {type(ref_err).__name__}: {str(ref_err)[:80]}")
+            _close(ours.compute(), want, where)
+        elif step == "reset":
+            ours.reset()
+            theirs.reset()
+        elif step == "clone":
+            ours, theirs = ours.clone(), theirs.clone()
+        elif step == "pickle":
+            ours, theirs = pickle.loads(pickle.dumps(ours)), pickle.loads(pickle.dumps(theirs))
+        elif step == "deepcopy":
+            ours, theirs = copy.deepcopy(ours), copy.deepcopy(theirs)
+        elif step == "state_dict":
+            ours.persistent(True)
+            theirs.persistent(True)
+            a, b = ours.state_dict(), theirs.state_dict()
+            assert a.keys() == b.keys(), where
+            fresh_o, fresh_t = getattr(M.classification, name)(**kw).cuda(), getattr(R.classification, name)(**kw).cuda()
+            fresh_o.persistent(True)
+            fresh_t.persistent(True)
+            try:
+                fresh_t.load_state_dict(b)
+            except Exception as ref_err:  # noqa: BLE001 - list states of the reference do not always load back
+                with pytest.raises(type(ref_err)):
+                    fresh_o.load_state_dict(a)
+                continue
+            fresh_o.load_state_dict(a)
+            fresh_o._update_count, fresh_t._update_count = ours._update_count, theirs._update_count
+            ours, theirs = fresh_o, fresh_t
+        elif step == "float":
+            how = rnd.choice(["half", "float", "double"])
+            ours, theirs = getattr(ours, how)(), getattr(theirs, how)()
+        else:
+            ours, theirs = ours.cpu().cuda(), theirs.cpu().cuda()
