@@ -517,3 +517,58 @@ def test_random_lifecycle(R, M, seed):
             ours, theirs = getattr(ours, how)(), getattr(theirs, how)()
         else:
             ours, theirs = ours.cpu().cuda(), theirs.cpu().cuda()
+
+
+_BAD_ARGS = [("average", "mean"), ("average", 3), ("threshold", 1.5), ("threshold", "high"), ("thresholds", -4),
+             ("thresholds", [0.2, 1.3]), ("thresholds", 0.5), ("num_classes", 1), ("num_classes", 2.5), ("num_labels", 0),
+             ("top_k", 0), ("top_k", 10_000), ("ignore_index", "last"), ("ignore_index", 1.5), ("multidim_average", "rows"),
+             ("normalize", "both"), ("weights", "cubic"), ("max_fpr", 1.5), ("max_fpr", 0)]
+
+
+@pytest.mark.parametrize("seed", range(200 * SCALE))
+def test_random_invalid_use_is_rejected_like_the_reference(R, M, seed):
+    """Arguments and inputs the reference rejects (`validate_args=True`): the same exception type here, from the
+    constructor, `update` or `compute` — bad argument values, shapes that do not match, integer scores for a curve,
+    float targets, labels outside the task's range.  (Where the reference lets a bad input pass, nothing is asked.)"""
+    name, kw, batch = _draw(40_000 + seed)
+    rnd = random.Random(41_000 + seed)
+    mode = rnd.choice(["argument", "argument", "shape", "rank", "dtype", "label"])
+    kw = dict(kw)
+    if mode == "argument":
+        key, value = rnd.choice(_BAD_ARGS)
+        kw[key] = value
+
+    def attempt(pkg, device="cuda"):
+        metric = getattr(pkg.classification, name)(**kw).to(device)
+        preds, target = (x.to(device) for x in batch(torch.Generator(device="cuda").manual_seed(seed)))
+        if mode == "shape" and preds.shape[0] > 1:
+            preds = preds[:-1]
+        elif mode == "rank":
+            preds = preds.unsqueeze(-1).expand(*preds.shape, 2)
+        elif mode == "dtype":
+            if rnd_mode == 0:
+                preds = (preds * 3).long() if preds.is_floating_point() else preds.double() / 3 + 0.1
+            else:
+                target = target.float() + 0.5
+        elif mode == "label" and target.numel():
+            target = target.long().clone()
+            target.view(-1)[0] = 7_000 if rnd_mode == 0 else -9
+        metric.update(preds, target)
+        return metric.compute()
+
+    rnd_mode = rnd.randint(0, 1)
+    try:
+        # a bad label (or an integer "score") that gets past the reference's checks ends in an index assert of a torch
+        # kernel; on the GPU that is a device-side assert, which poisons the CUDA context of the whole process: the
+        # reference meets these inputs on the CPU
+        attempt(R, "cpu")
+    except Exception as ref_err:  # noqa: BLE001
+        kind = type(ref_err)
+        diagnosis = kind is ValueError or (kind is RuntimeError and any(
+            phrase in str(ref_err) for phrase in ("Detected", "expected to have the same shape", "Expected", "must match")))
+        if not diagnosis:  # an IndexError, a torch kernel's complaint about its operands, ...: the reference crashed
+            pytest.skip(f"the reference fails without a diagnosis here: {kind.__name__}: {str(ref_err)[:80]}")
+        with pytest.raises(kind):
+            attempt(M)
+        return
+    pytest.skip("the reference accepts this")

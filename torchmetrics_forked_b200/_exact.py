@@ -13,11 +13,15 @@ def _as_kernel_input(t: Tensor) -> Tensor:
     return t if t.is_contiguous() else t.contiguous()
 
 
+_NOT_A_LABEL = -(2.0**62)  # exactly representable in every float dtype that can hold it; float16 targets saturate to -inf -> int64 min
+
+
 def _as_label_input(t: Tensor) -> Tensor:
     """Integer, dense targets (float-typed targets holding integer values are truncated like the reference's
     ``.long()``)."""
     if t.is_floating_point():
-        t = t.long()
+        # a value with a fraction (or NaN) is no label: it becomes one that every task's range check rejects
+        t = torch.where(t == t.trunc(), t, torch.full_like(t, _NOT_A_LABEL)).long()
     return t if t.is_contiguous() else t.contiguous()
 
 

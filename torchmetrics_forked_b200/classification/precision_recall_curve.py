@@ -19,6 +19,7 @@ from torchmetrics_forked_b200.functional.classification.precision_recall_curve i
     _binary_precision_recall_curve_arg_validation,
     _binary_precision_recall_curve_compute,
     _binary_precision_recall_curve_format_exact,
+    _flag_non_binary_targets,
     _binary_precision_recall_curve_tensor_validation,
     _binary_precision_recall_curve_update_,
     _multiclass_precision_recall_curve_arg_validation,
@@ -167,6 +168,8 @@ class BinaryPrecisionRecallCurve(_CurveStateMixin, Metric):
         dev = preds.device
         err = self._error_word(dev)
         if self.thresholds is None:
+            if self.validate_args:
+                _flag_non_binary_targets(target, self.ignore_index, err)
             p, t = _binary_precision_recall_curve_format_exact(preds, target, self.ignore_index, err)
             self.preds.append(p)
             self.target.append(t)
@@ -276,6 +279,8 @@ class MultilabelPrecisionRecallCurve(_CurveStateMixin, Metric):
         dev = preds.device
         err = self._error_word(dev)
         if self.thresholds is None:
+            if self.validate_args:
+                _flag_non_binary_targets(target, self.ignore_index, err)
             p, t = _multilabel_precision_recall_curve_format_exact(preds, target, self.num_labels, err)
             self.preds.append(p)
             self.target.append(t)

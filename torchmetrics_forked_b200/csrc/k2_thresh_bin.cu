@@ -529,8 +529,10 @@ __global__ void __launch_bounds__(1024) k2_generic(TbArgs a, int sh_bins, int sh
     int k = -1;
     if (LABELS) {
       int64_t p = load_label(a.preds, a.pdt, i);
+      // the reference's check of label-valued preds looks at every element, ignored positions included
+      // (stat_scores.py:80-88, confusion_matrix.py:95-103)
+      if (p != 0 && p != 1) atomicOr(a.err, TMB_ERR_PREDS_RANGE);
       if (!ignored) {
-        if (p != 0 && p != 1) atomicOr(a.err, TMB_ERR_PREDS_RANGE);
         k = (p == 1) ? 1 : 0;
         // reference semantics for stray labels (stat_scores.py:127-130): only p == target counts as a match
         if (p != 0 && p != 1) k = (t == 1) ? 0 : 1;

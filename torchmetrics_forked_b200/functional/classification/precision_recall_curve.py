@@ -18,6 +18,7 @@ import torch
 from torch import Tensor
 from typing_extensions import Literal
 
+from torchmetrics_forked_b200 import _native as nat
 from torchmetrics_forked_b200 import kernels
 from torchmetrics_forked_b200.utilities.checks import _check_same_shape
 from torchmetrics_forked_b200.utilities.compute import _safe_divide, interp
@@ -167,6 +168,16 @@ def _binary_precision_recall_curve_update_(
     kernels.thresh_bin_finalize(scratch, 1, thr.numel(), perm, kernels.TB_CURVE, (confmat,))
 
 
+def _flag_non_binary_targets(target: Tensor, ignore_index: Optional[int], err: Tensor) -> None:
+    """Exact mode stores the targets as they come, no kernel looks at them during `update`.  With ``validate_args``
+    the reference's {0, 1} check (:149-159, a ``torch.unique``) becomes one elementwise expression whose verdict is
+    ORed into the device error word — read where the other data errors are read, no synchronisation here."""
+    bad = (target != 0) & (target != 1)
+    if ignore_index is not None:
+        bad &= target != ignore_index
+    err.bitwise_or_(bad.any().to(torch.int32) * nat.ERR_TARGET_BINARY)
+
+
 def _binary_precision_recall_curve_format_exact(
     preds: Tensor, target: Tensor, ignore_index: Optional[int], err: Tensor
 ) -> Tuple[Tensor, Tensor]:
@@ -204,6 +215,8 @@ def _binary_state_functional(
     dev = preds.device
     err = torch.zeros(1, dtype=torch.int32, device=dev)
     if thresholds is None:
+        if validate_args:
+            _flag_non_binary_targets(target, ignore_index, err)
         state = _binary_precision_recall_curve_format_exact(preds, target, ignore_index, err)
     else:
         thr_sorted, perm = _threshold_plan(thresholds, dev)
@@ -316,6 +329,8 @@ def _multilabel_state_functional(
     dev = preds.device
     err = torch.zeros(1, dtype=torch.int32, device=dev)
     if thresholds is None:
+        if validate_args:
+            _flag_non_binary_targets(target, ignore_index, err)
         state = _multilabel_precision_recall_curve_format_exact(preds, target, num_labels, err)
     else:
         thr_sorted, perm = _threshold_plan(thresholds, dev)

@@ -32,12 +32,16 @@ def _as_kernel_input(t: Tensor) -> Tensor:
     return t if t.is_contiguous() else t.contiguous()
 
 
+_NOT_A_LABEL = -(2.0**62)  # exactly representable in every float dtype that can hold it; float16 targets saturate to -inf -> int64 min
+
+
 def _as_label_input(t: Tensor) -> Tensor:
     """Targets as the kernels read them: an integer dtype, dense.  The reference takes float-typed targets holding
     integer values too (its updates end in ``.to(torch.long)`` / ``target == 1``; its own tests pass
     ``torch.zeros(10)`` as a target): they are truncated to int64 here, which is what ``.long()`` does there."""
     if t.is_floating_point():
-        t = t.long()
+        # a value with a fraction (or NaN) is no label: it becomes one that every task's range check rejects
+        t = torch.where(t == t.trunc(), t, torch.full_like(t, _NOT_A_LABEL)).long()
     return t if t.is_contiguous() else t.contiguous()
 
 
@@ -67,7 +71,7 @@ def mc_argmax_hist(
         raise ValueError("`preds` must have shape (N, C, ...) with C equal to `num_classes`")
     if _f64.is_f64(preds):  # argmax decided in float64, the label kernel counts
         if target.numel() != preds.numel() // max(num_classes, 1):
-            raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+            raise RuntimeError("`target` must have one entry per (N, ...) position of `preds`")
         return mc_label_hist(_f64.multiclass_labels(preds), target, num_classes, ignore_index, mode, out, err)
     preds = _as_kernel_input(preds)
     target = _as_label_input(target)
@@ -76,7 +80,7 @@ def mc_argmax_hist(
     for d in preds.shape[2:]:
         n_inner *= d
     if target.numel() != n_outer * n_inner:
-        raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+        raise RuntimeError("`target` must have one entry per (N, ...) position of `preds`")
     if n_inner == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
@@ -109,7 +113,7 @@ def mc_stats_samplewise(
         per_sample = rows.shape[1]
         tgt = _as_label_input(target.reshape(n, -1))
         if tgt.shape[1] != per_sample:
-            raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+            raise RuntimeError("`target` must have one entry per (N, ...) position of `preds`")
         dev = preds.device
         outs = tuple(torch.zeros(n, num_classes, dtype=torch.int64, device=dev) for _ in range(4))
         if n == 0 or per_sample == 0:
@@ -136,6 +140,8 @@ def mc_stats_samplewise(
             raise ValueError("label-valued `preds` must have the shape of `target`")
     elif preds.ndim < 2 or preds.shape[1] != num_classes or preds.ndim != target.ndim + 1:
         raise ValueError("`preds` must have shape (N, C, ...) with C equal to `num_classes`")
+    elif preds.shape[0] != target.shape[0] or preds.shape[2:] != target.shape[1:]:
+        raise RuntimeError("`target` must have one entry per (N, ...) position of `preds`")
     preds = _as_kernel_input(preds)
     target = _as_label_input(target)
     n = preds.shape[0]
@@ -215,7 +221,7 @@ def mc_topk_hist(
     preds = _as_kernel_input(preds)
     target = _as_label_input(target.reshape(-1))
     if target.numel() != preds.shape[0]:
-        raise ValueError("`target` must have one entry per (N, ...) position of `preds`")
+        raise RuntimeError("`target` must have one entry per (N, ...) position of `preds`")
     if preds.shape[0] == 0:
         return
     has_ign, ign = _ignore_args(ignore_index)
